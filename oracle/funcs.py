@@ -1,0 +1,113 @@
+"""Oracle: the per-evaluation math of the two ODE functions (TEST INFRASTRUCTURE ONLY).
+
+Plain torch on the CPU, differentiable (autograd supplies the gradient oracle), dtype chosen by the
+caller: float64 is the truth the tolerances are judged against, float32 reproduces the reference's
+own rounding.  Un-batched tensors: x [N,d], edge_index [2,E] (row = edge_index[0] = the node the
+message is summed INTO, col = edge_index[1] = the node whose features are gathered; this is the
+orientation of `sparse_coo_tensor(indices=[row, col]) @ x` in
+`src/function_laplacian_diffusion.py:41-57` and of upstream's `torch_sparse.spmm`).
+
+Follows:
+  segment_softmax        src/utils.py:116-127
+  attention_layer        src/function_transformer_attention.py:159-267 (line 249 replaced by the
+                         per-edge dot product unless fork_literal=True)
+  laplacian_f            src/function_laplacian_diffusion.py:39-77
+  transformer_f          src/function_transformer_attention.py:20-59 (mix_features=False branch)
+"""
+import math
+import torch
+
+
+def segment_softmax(src, index, num_nodes):
+    """src [E,H], index int64 [E] -> [E,H]; out = exp(s - max_g) / (sum_g exp(s - max_g) + 1e-16)."""
+    e, h = src.shape
+    idx = index[:, None].expand(e, h)
+    mx = torch.zeros(num_nodes, h, dtype=src.dtype).scatter_reduce(0, idx, src, reduce='amax', include_self=False)
+    out = (src - mx[index]).exp()
+    den = torch.zeros(num_nodes, h, dtype=src.dtype).index_add_(0, index, out)
+    return out / (den[index] + 1e-16)
+
+
+def squareplus(src, index, num_nodes):
+    """Intended behaviour of `src/utils.py:129-140` (the fork's call site passes 2 args to a 3-arg
+    function and its amax is over the whole tensor; this keeps the fork's global-max form)."""
+    out = src - src.amax()
+    out = (out + torch.sqrt(out ** 2 + 4)) / 2
+    den = torch.zeros(num_nodes, src.shape[1], dtype=src.dtype).index_add_(0, index, out)
+    return out / (den[index] + 1e-16)
+
+
+def edge_scores(q, k, edge_index, heads, attention_type='scaled_dot', fork_literal=False,
+                output_var=None, lengthscale=None):
+    """q,k [N,A] -> prods [E,H].  Head h owns the contiguous slice [h*dk,(h+1)*dk) of the A axis
+    (`.view(N, h, d_k)` at function_transformer_attention.py:230-232)."""
+    n, a = q.shape
+    dk = a // heads
+    row, col = edge_index[0], edge_index[1]
+    src = q.view(n, heads, dk)[row]        # [E,H,dk]
+    dst = k.view(n, heads, dk)[col]
+    if attention_type == 'scaled_dot':
+        if fork_literal:
+            # line 249: matmul([H,E,dk],[H,dk,E]/sqrt(dk)).sum(dim=3): every edge sees the SUM of all dst rows
+            return torch.matmul(src.permute(1, 0, 2), dst.permute(1, 2, 0) / math.sqrt(dk)).sum(dim=2).permute(1, 0)
+        return (src * dst).sum(dim=2) / math.sqrt(dk)
+    if attention_type == 'cosine_sim':
+        return torch.nn.functional.cosine_similarity(src, dst, dim=2, eps=1e-5)
+    if attention_type == 'pearson':
+        src = src - src.mean(dim=2, keepdim=True)
+        dst = dst - dst.mean(dim=2, keepdim=True)
+        return torch.nn.functional.cosine_similarity(src, dst, dim=2, eps=1e-5)
+    if attention_type == 'exp_kernel':
+        return output_var ** 2 * torch.exp(-((src - dst) ** 2).sum(dim=2) / (2 * lengthscale ** 2))
+    raise NotImplementedError(attention_type)
+
+
+def attention_layer(x, edge_index, wq, bq, wk, bk, heads, attention_type='scaled_dot',
+                    attention_norm_idx=0, edge_weight=None, reweight_attention=False,
+                    square_plus=False, fork_literal=False, output_var=None, lengthscale=None):
+    """SpGraphTransAttentionLayer.forward (non-beltrami-exp_kernel branch).  Returns
+    (attention [E,H], prods [E,H]).  V is computed by the reference and never used when
+    mix_features=False, so it is omitted (its gradient is None in the reference too)."""
+    n = x.shape[0]
+    q = x @ wq.t() + bq
+    k = x @ wk.t() + bk
+    prods = edge_scores(q, k, edge_index, heads, attention_type, fork_literal, output_var, lengthscale)
+    if reweight_attention and edge_weight is not None:
+        prods = prods * edge_weight[:, None]
+    grp = edge_index[attention_norm_idx]
+    if square_plus:
+        return squareplus(prods, grp, n), prods
+    return segment_softmax(prods, grp, n), prods
+
+
+def spmm(edge_index, values, x):
+    """ax[i] = sum_{e: row_e = i} values_e * x[col_e]; duplicates add."""
+    row, col = edge_index[0], edge_index[1]
+    return torch.zeros_like(x).index_add_(0, row, values[:, None] * x[col])
+
+
+def _alpha(alpha_train, no_alpha_sigmoid):
+    return alpha_train if no_alpha_sigmoid else torch.sigmoid(alpha_train)
+
+
+def laplacian_f(x, edge_index, values, alpha_train, beta_train, x0, add_source=True,
+                no_alpha_sigmoid=False):
+    """LaplacianODEFunc.forward. `values` [E] is edge_weight (constant block) or the head-mean of
+    attention_weights (attention block, function_laplacian_diffusion.py:45-49)."""
+    ax = spmm(edge_index, values, x)
+    f = _alpha(alpha_train, no_alpha_sigmoid) * (ax - x)
+    if add_source:
+        f = f + beta_train * x0
+    return f
+
+
+def transformer_f(x, edge_index, wq, bq, wk, bk, heads, alpha_train, beta_train, x0,
+                  add_source=True, no_alpha_sigmoid=False, **att_kwargs):
+    """ODEFuncTransformerAtt.forward: attention recomputed from the current x, head-mean, A @ x
+    (applied to x, not v), same alpha/beta epilogue."""
+    att, _ = attention_layer(x, edge_index, wq, bq, wk, bk, heads, **att_kwargs)
+    ax = spmm(edge_index, att.mean(dim=1), x)
+    f = _alpha(alpha_train, no_alpha_sigmoid) * (ax - x)
+    if add_source:
+        f = f + beta_train * x0
+    return f
