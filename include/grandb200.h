@@ -1,0 +1,207 @@
+/* grandb200.h - C ABI of libgrandb200.so: the B200 (sm_100a) graph-diffusion operator.
+ *
+ * This is the drop-in boundary for ONE hot path of alimt1992/graph-neural-pde: one evaluation of
+ *     f(t, x) = alpha * (A(x) x - x) + beta * x0
+ * (forward and vector-Jacobian product) as computed by the reference's
+ *     LaplacianODEFunc.forward          src/function_laplacian_diffusion.py:39-77
+ *     ODEFuncTransformerAtt.forward     src/function_transformer_attention.py:20-59
+ *     SpGraphTransAttentionLayer.forward src/function_transformer_attention.py:159-267
+ *     utils.softmax                     src/utils.py:116-127
+ *     utils.get_rw_adj / gcn_norm_fill_val   src/utils.py:177-233
+ * and their autograd backward (the reference has no hand-written backward; torchdiffeq's
+ * odeint_adjoint calls autograd.grad on the same forward, src/base_classes.py:45-48).
+ *
+ * Conventions
+ *  - Plain C: pointers + sizes, no torch types.  Every pointer is a DEVICE pointer unless its name
+ *    ends in _host.  The library owns no memory between calls: the caller (torch's caching
+ *    allocator in the Python host, any allocator elsewhere) provides outputs and workspaces.
+ *  - `stream` is a cudaStream_t passed as void*.  All work is enqueued on it; no call synchronises
+ *    the device except gb_plan_finalize_host (plan build, once per graph) and gb_prof_collect.
+ *  - Return value: 0 = GB_OK, otherwise a gb_status; gb_last_error() gives the text
+ *    (thread-local).  Nothing ever falls back to a CPU path.
+ *  - Feature matrices are row-major fp32 with an explicit leading dimension (in floats).
+ *  - Edge orientation: row = edge_index[0] = node summed INTO, col = edge_index[1] = node whose
+ *    features are gathered (the orientation of sparse_coo_tensor([row, col]) @ x at
+ *    function_laplacian_diffusion.py:41-57).
+ *  - "CSR slot" s in [0,E): position after the stable sort of the edges by (row, col).
+ *    "CSC slot" p in [0,E): position after the stable sort of the CSR slots by (col, row).
+ *    Per-edge arrays handed to kernels are in CSR-slot order unless stated otherwise.
+ */
+#ifndef GRANDB200_H
+#define GRANDB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GB_ABI_VERSION 1
+
+typedef enum {
+  GB_OK = 0,
+  GB_ERR_INVALID = 1,      /* bad argument (null pointer, size, alignment) */
+  GB_ERR_CUDA = 2,         /* a CUDA runtime call or launch failed */
+  GB_ERR_UNSUPPORTED = 3,  /* valid request the library does not implement */
+  GB_ERR_WORKSPACE = 4     /* workspace too small */
+} gb_status;
+
+/* attention_type of SpGraphTransAttentionLayer (function_transformer_attention.py:246-259) */
+typedef enum {
+  GB_ATT_SCALED_DOT = 0,   /* per-edge q.k/sqrt(dk) (upstream semantics) */
+  GB_ATT_COSINE = 1,       /* cosine similarity, eps 1e-5 */
+  GB_ATT_PEARSON = 2,      /* mean-centred cosine similarity */
+  GB_ATT_EXP_KERNEL = 3    /* output_var^2 * exp(-|q-k|^2 / (2 lengthscale^2)) */
+} gb_att_type;
+
+/* Immutable device-side description of one graph ("plan").  Built once per
+ * ODEblock.reset_graph_data (src/base_classes.py:70-90) and reused by every evaluation. */
+typedef struct {
+  int32_t n;               /* nodes */
+  int32_t e;               /* edges (duplicates kept as separate entries) */
+  const int32_t* rowptr;   /* [n+1] CSR */
+  const int32_t* colidx;   /* [e]   column of CSR slot s */
+  const int32_t* eperm;    /* [e]   CSR slot -> caller's edge id (COO position) */
+  const int32_t* colptr;   /* [n+1] CSC */
+  const int32_t* rowidx;   /* [e]   row of CSC slot p */
+  const int32_t* tperm;    /* [e]   CSC slot -> CSR slot */
+  const int32_t* long_rows;/* [n_long_rows] rows with more than long_threshold edges (may be NULL) */
+  const int32_t* long_cols;/* [n_long_cols] columns with more than long_threshold edges */
+  int32_t n_long_rows;
+  int32_t n_long_cols;
+  int32_t long_threshold;
+  int32_t reserved;
+} gb_graph;
+
+/* Optional Runge-Kutta stage fusion for gb_spmm_fwd: besides f the kernel also writes
+ *   ynext = y + sum_{j<n_prev} c[j]*k[j] + c[n_prev]*f
+ * (the stage combination torchdiffeq does with separate axpy kernels). */
+typedef struct {
+  const float* y;          /* [n, ld] state at the start of the step */
+  const float* k[6];       /* previous stage derivatives */
+  float c[7];              /* coefficients already multiplied by dt */
+  int32_t n_prev;
+  int32_t write_f;         /* 0: f itself is not needed (last stage), skip its store */
+  float* ynext;            /* [n, ld] */
+  int32_t ld;              /* leading dimension of y, k[*], ynext */
+  int32_t reserved;
+} gb_stage;
+
+/* ---- library ------------------------------------------------------------------------------ */
+int gb_abi_version(void);
+const char* gb_last_error(void);
+/* sm count / compute capability of the current device */
+int gb_device_info(int32_t* sm_count_host, int32_t* cc_major_host, int32_t* cc_minor_host);
+/* number of kernels this library launched since load (monotone; used for bench "gpu_launches") */
+int64_t gb_launch_count(void);
+
+/* per-kernel CUDA-event timing (off by default). ids are gb_kernel_id values. */
+int gb_prof_enable(int on);
+int gb_prof_reset(void);
+int gb_prof_collect(void);                      /* synchronises the recorded events */
+int gb_prof_get(int kernel_id, double* total_ms_host, int64_t* launches_host);
+int gb_prof_num_kernels(void);
+const char* gb_prof_name(int kernel_id);
+
+/* ---- graph plan (replaces utils.get_rw_adj / gcn_norm_fill_val scatter_add + the COO->dense
+ *      conversion of sparse_multiply; src/utils.py:177-233, function_laplacian_diffusion.py:39-58) */
+size_t gb_plan_workspace_bytes(int32_t n, int64_t e);
+/* COO (int64, caller order) -> CSR + CSC arrays.  Bit-exact contract: oracle/graph.py coo_to_csr /
+ * csr_to_csc.  All outputs are caller-allocated int32 device arrays. */
+int gb_plan_build(const int64_t* row, const int64_t* col, int64_t e, int32_t n,
+                  int32_t* rowptr, int32_t* colidx, int32_t* eperm,
+                  int32_t* colptr, int32_t* rowidx, int32_t* tperm,
+                  void* workspace, size_t workspace_bytes, void* stream);
+/* Lists the segments longer than `threshold`. ptr = rowptr or colptr. Writes ids to `out` (capacity
+ * `cap`) in increasing order and the count to *count_host (synchronises the stream). */
+int gb_plan_long_segments(const int32_t* ptr, int32_t n, int32_t threshold, int32_t* out, int32_t cap,
+                          int32_t* count_host, void* workspace, size_t workspace_bytes, void* stream);
+
+/* deg[i] = sum of w over edges with idx == i, summed SEQUENTIALLY IN EDGE ORDER (the order of
+ * torch's CPU scatter_add, so the fp32 bits match the oracle); utils.py:191,230 */
+size_t gb_degree_workspace_bytes(int32_t n, int64_t e);
+int gb_degree(const int64_t* idx, const float* w, int64_t e, int32_t n, float* deg,
+              void* workspace, size_t workspace_bytes, void* stream);
+/* utils.get_rw_adj: w_out = w * (1/deg)[idx]   (reciprocal, then multiply; utils.py:231-232) */
+int gb_rw_normalize(const int64_t* idx, const float* w, const float* deg, int64_t e, float* w_out, void* stream);
+/* utils.gcn_norm_fill_val: dis = deg^-1/2 (inf -> 0); w_out = (dis[row]*w)*dis[col]; utils.py:192-194 */
+int gb_gcn_normalize(const int64_t* row, const int64_t* col, const float* w, const float* deg, int64_t e,
+                     float* w_out, void* stream);
+
+/* per-edge plumbing between the caller's COO order and CSR-slot order */
+int gb_gather_f32(const float* src, const int32_t* perm, int64_t e, float* dst, void* stream);          /* dst[s] = src[perm[s]] */
+int gb_head_mean_gather(const float* att_coo, int32_t heads, const int32_t* eperm, int64_t e,
+                        float* abar_csr, void* stream);   /* mean over heads (function_laplacian_diffusion.py:46) */
+int gb_scatter_rows_f32(const float* src_csr, int32_t width, const int32_t* eperm, int64_t e,
+                        float* dst_coo, void* stream);    /* dst[eperm[s], :] = src[s, :] */
+
+/* ---- K1: CSR SpMM + fused epilogue (LaplacianODEFunc.forward, function_laplacian_diffusion.py:60-77)
+ *   out[i,:] = alpha * (sum_{s in row i} vals[s] * x[colidx[s],:] - x[i,:]) + beta * x0[i,:]
+ *   alpha = sigmoid(*alpha_train) if alpha_sigmoid else *alpha_train ; beta = *beta_train.
+ *   x0 == NULL or beta_train == NULL  -> no source term (opt['add_source'] False).
+ *   stage == NULL -> plain evaluation. */
+int gb_spmm_fwd(const gb_graph* g, const float* vals, const float* x, int32_t ldx,
+                const float* x0, int32_t ldx0, const float* alpha_train, int32_t alpha_sigmoid,
+                const float* beta_train, int32_t d, float* out, int32_t ldo,
+                const gb_stage* stage, void* stream);
+
+/* ---- K5a: transpose (CSC) SpMM + parameter-gradient reductions (VJP of K1 w.r.t. x, alpha_train,
+ *      beta_train).  gout = dL/df.
+ *   t[j,:]  = sum_{p in col j} vals[tperm[p]] * gout[rowidx[p],:] - gout[j,:]
+ *   dx[j,:] = alpha * t[j,:]                      (accumulate != 0: dx += ...)
+ *   dparams[0] = dalpha_train = (alpha_sigmoid ? alpha(1-alpha) : 1) * sum_j <x[j,:], t[j,:]>
+ *   dparams[1] = dbeta_train  = sum_j <gout[j,:], x0[j,:]>          (0 if x0 == NULL)
+ *   Reductions are two-pass and order-fixed (no float atomics). `partials` needs
+ *   gb_spmm_bwd_partials(g, d) floats. */
+size_t gb_spmm_bwd_partials(const gb_graph* g, int32_t d);   /* in floats */
+int gb_spmm_bwd(const gb_graph* g, const float* vals, const float* gout, int32_t ldg,
+                const float* x, int32_t ldx, const float* x0, int32_t ldx0,
+                const float* alpha_train, int32_t alpha_sigmoid, int32_t d,
+                float* dx, int32_t lddx, int32_t accumulate,
+                float* partials, float* dparams, void* stream);
+
+/* ---- K3: Q/K projection (nn.Linear x2, function_transformer_attention.py:224-225)
+ *   out[i, j] = sum_c x[i,c] * w[j,c] + b[j],  j < nout   (w is torch's Linear.weight layout [nout, d];
+ *   pass Q and K weights concatenated along dim 0 to get [q | k] rows in one pass) */
+int gb_linear_fwd(const float* x, int32_t ldx, int32_t n, int32_t d, const float* w, const float* b,
+                  int32_t nout, float* out, int32_t ldo, void* stream);
+/* dx[i,c] (+)= sum_j dy[i,j] * w[j,c] */
+int gb_linear_bwd_x(const float* dy, int32_t lddy, int32_t n, int32_t nout, const float* w, int32_t d,
+                    float* dx, int32_t lddx, int32_t accumulate, void* stream);
+/* dw[j,c] = sum_i dy[i,j]*x[i,c] ; db[j] = sum_i dy[i,j]   (split over i, fixed-order second pass) */
+size_t gb_linear_bwd_w_workspace_bytes(int32_t n, int32_t d, int32_t nout);
+int gb_linear_bwd_w(const float* dy, int32_t lddy, const float* x, int32_t ldx, int32_t n, int32_t d,
+                    int32_t nout, float* dw, float* db, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- K2+K4: fused per-edge score + segment softmax + head mean
+ *      (function_transformer_attention.py:240-266 + utils.py:116-127)
+ *   s[e,h]   = score(q[row_e, h, :], k[col_e, h, :])      (x edge_w[e] if edge_w != NULL)
+ *   att[e,h] = exp(s - max_g) / (sum_g exp(s - max_g) + 1e-16), groups g = rows (norm_idx 0) or
+ *              columns (norm_idx 1)
+ *   abar[e]  = mean_h att[e,h]
+ *   att / abar / prods are in CSR-slot order; prods (raw scores) may be NULL.
+ *   kparams: [output_var, lengthscale] device floats for GB_ATT_EXP_KERNEL, else NULL. */
+int gb_edge_softmax_fwd(const gb_graph* g, int32_t norm_idx, const float* q, int32_t ldq,
+                        const float* k, int32_t ldk, int32_t heads, int32_t dk, int32_t att_type,
+                        const float* edge_w, const float* kparams,
+                        float* att, float* abar, float* prods, void* stream);
+
+/* ---- K5b: attention VJP.
+ *  (1) SDDMM:        dabar[s] = alpha * <gout[row_s,:], x[col_s,:]>                        (CSR pass)
+ *  (2) softmax bwd:  ds[s,h]  = att[s,h] * (dabar[s]/H - sum_{g} att[.,h]*dabar[.]/H)      (segment pass)
+ *  (3) dq[i,h,:] = sum_{s in row i} ds[s,h] * dscore/dq ;  dk[j,h,:] = sum_{p in col j} ds[.,h] * dscore/dk
+ *  All reductions are segment reductions over the pre-sorted CSR/CSC orders: deterministic. */
+int gb_sddmm(const gb_graph* g, const float* gout, int32_t ldg, const float* x, int32_t ldx, int32_t d,
+             const float* alpha_train, int32_t alpha_sigmoid, float* dabar, void* stream);
+int gb_edge_softmax_bwd(const gb_graph* g, int32_t norm_idx, const float* att, const float* dabar,
+                        int32_t heads, const float* edge_w, float* ds, void* stream);
+int gb_edge_score_bwd(const gb_graph* g, const float* ds, const float* q, int32_t ldq, const float* k,
+                      int32_t ldk, int32_t heads, int32_t dk, int32_t att_type, const float* kparams,
+                      const float* prods, float* dq, int32_t lddq, float* dk_out, int32_t lddk,
+                      float* dkparams_partials, float* dkparams, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GRANDB200_H */
