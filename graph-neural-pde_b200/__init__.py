@@ -1,0 +1,26 @@
+"""grand_b200 - B200-native drop-in for the per-step graph-diffusion operator of
+alimt1992/graph-neural-pde (GRAND / BLEND).  Import as `import grand_b200` (repo-root shim) - the
+directory name `graph-neural-pde_b200` is not a Python identifier.
+
+Module names mirror the reference's `src/` files so a maintainer can swap imports one for one:
+  base_classes, function_laplacian_diffusion, function_transformer_attention, block_constant,
+  block_transformer_attention, model_configurations, utils  (+ integrators: torchdiffeq-compatible
+  odeint / odeint_adjoint used when torchdiffeq is not installed).
+All device work goes through libgrandb200.so (csrc/, C ABI in include/grandb200.h).
+"""
+from . import _lib
+from .plan import GraphPlan, get_plan
+from .utils import MaxNFEException, get_rw_adj, gcn_norm_fill_val, add_remaining_self_loops, Meter
+from .base_classes import ODEFunc, ODEblock, GraphData
+from .function_laplacian_diffusion import LaplacianODEFunc
+from .function_transformer_attention import ODEFuncTransformerAtt, SpGraphTransAttentionLayer
+from .block_constant import ConstantODEblock
+from .block_transformer_attention import AttODEblock
+from .model_configurations import set_block, set_function
+from . import integrators
+from .integrators import odeint, odeint_adjoint
+
+__all__ = ['GraphPlan', 'get_plan', 'MaxNFEException', 'get_rw_adj', 'gcn_norm_fill_val',
+           'add_remaining_self_loops', 'Meter', 'ODEFunc', 'ODEblock', 'GraphData', 'LaplacianODEFunc',
+           'ODEFuncTransformerAtt', 'SpGraphTransAttentionLayer', 'ConstantODEblock', 'AttODEblock',
+           'set_block', 'set_function', 'odeint', 'odeint_adjoint', 'integrators']

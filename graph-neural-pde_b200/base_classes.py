@@ -1,0 +1,203 @@
+"""Mirror of the reference's `src/base_classes.py` for the hot path: `ODEFunc` (plugin state
+container, base_classes.py:116-134), `ODEblock` (base_classes.py:33-98) and `GraphData`
+(base_classes.py:100-113).  Same constructor signatures, attribute names and parameter names
+(`alpha_train`, `beta_train`, `alpha_sc`, `beta_sc`) so reference checkpoints load with
+strict=True and the reference's blocks / solvers can drive these classes unchanged.
+
+Differences, all deliberate:
+  * `ODEFunc` derives from nn.Module (the reference derives from PyG MessagePassing only for
+    nn.Module-ness; no propagate() call exists).
+  * graph normalisation goes through the un-broken helpers in utils.py and the result is cached
+    while `data.edge_index` is the same tensor (the reference redoes it every block forward).
+  * integration uses torchdiffeq when it is importable, else the restated solvers in
+    integrators.py (same call signature).
+"""
+import torch
+from torch import nn
+
+from . import plan as _plan
+from .utils import get_rw_adj, gcn_norm_fill_val, add_remaining_self_loops, Meter
+
+
+def _integrators(adjoint):
+    try:
+        if adjoint:
+            from torchdiffeq import odeint_adjoint as odeint
+        else:
+            from torchdiffeq import odeint
+        return odeint
+    except ImportError:
+        from . import integrators
+        return integrators.odeint_adjoint if adjoint else integrators.odeint
+
+
+REG_KEYS = ('kinetic_energy', 'jacobian_norm2', 'total_deriv', 'directional_penalty')
+
+
+def create_regularization_fns(args):
+    """base_classes.py:19-30.  The RNODE regularisers need double backward through the ODE
+    function (regularized_ODE_function.py:39-75), which the CUDA operators do not provide."""
+    active = [k for k in REG_KEYS if args.get(k) is not None]
+    if active:
+        raise NotImplementedError(f'regularisation terms {active} need create_graph=True through the ODE '
+                                  'function; the B200 operators implement first-order VJPs only')
+    return [], []
+
+
+class ODEFunc(nn.Module):
+    """base_classes.py:116-134"""
+
+    def __init__(self, opt, device):
+        super(ODEFunc, self).__init__()
+        self.opt = opt
+        self.device = device
+        self.edge_index = None
+        self.edge_weight = None
+        self.attention_weights = None
+        self.alpha_train = nn.Parameter(torch.tensor(0.0))
+        self.beta_train = nn.Parameter(torch.tensor(0.0))
+        self.x0 = None
+        self.nfe = 0
+        self.alpha_sc = nn.Parameter(torch.ones(1))
+        self.beta_sc = nn.Parameter(torch.ones(1))
+
+    # ---- helpers shared by the two ODE functions ------------------------------------------------
+    @staticmethod
+    def _as_2d(x):
+        if x.dim() == 3:
+            if x.shape[0] != 1:
+                raise NotImplementedError('batched states (B > 1) are evaluated one graph at a time; pass B == 1')
+            return x[0]
+        if x.dim() != 2:
+            raise ValueError(f'state must be [N,d] or [1,N,d], got {tuple(x.shape)}')
+        return x
+
+    def _plan(self, num_nodes):
+        if self.edge_index is None:
+            raise RuntimeError('edge_index has not been set on the ODE function (ODEblock.reset_graph_data)')
+        return _plan.get_plan(self.edge_index, num_nodes)
+
+    def _check_nfe(self):
+        from .utils import MaxNFEException
+        if self.nfe > self.opt['max_nfe']:          # function_laplacian_diffusion.py:65-67
+            raise MaxNFEException
+        self.nfe += 1
+
+    def __repr__(self):
+        return self.__class__.__name__
+
+
+class ODEblock(nn.Module):
+    """base_classes.py:33-98"""
+
+    def __init__(self, odefunc, regularization_fns, opt, device, t):
+        super(ODEblock, self).__init__()
+        self.opt = opt
+        self.t = t
+        self.device = device
+        self.aug_dim = 2 if opt['augment'] else 1
+        self.odefunc = odefunc(self.aug_dim * opt['hidden_dim'], self.aug_dim * opt['hidden_dim'], opt, device)
+        self.nreg = len(regularization_fns)
+        self.reg_odefunc = _RegShim(self.odefunc)
+        self.train_integrator = _integrators(opt['adjoint'])
+        self.test_integrator = None
+        self.set_tol()
+        self._graph_cache = None
+
+    def set_x0(self, x0):
+        self.odefunc.x0 = x0.clone().detach()
+
+    def set_tol(self):
+        self.atol = self.opt['tol_scale'] * 1e-7
+        self.rtol = self.opt['tol_scale'] * 1e-9
+        if self.opt['adjoint']:
+            self.atol_adjoint = self.opt['tol_scale_adjoint'] * 1e-7
+            self.rtol_adjoint = self.opt['tol_scale_adjoint'] * 1e-9
+
+    def reset_tol(self):
+        self.atol = 1e-7
+        self.rtol = 1e-9
+        self.atol_adjoint = 1e-7
+        self.rtol_adjoint = 1e-9
+
+    def reset_graph_data(self, data, dtype, y=None):
+        """base_classes.py:70-90; the normalised graph is reused while data.edge_index /
+        data.edge_attr are the same tensors (identity + version)."""
+        if data is not None:
+            ei, ea = data.edge_index, data.edge_attr
+            key = (id(ei), ei._version, id(ea), None if ea is None else ea._version, data.num_nodes,
+                   self.opt['data_norm'], self.opt['self_loop_weight'])
+            if self._graph_cache is None or self._graph_cache[0] != key or self._graph_cache[1] is not ei:
+                self.num_nodes = data.num_nodes
+                ei_d = ei.to(self.device)
+                ea_d = None if ea is None else ea.to(self.device)
+                if self.opt['data_norm'] == 'rw':
+                    edge_index, edge_weight = get_rw_adj(ei_d, edge_weight=ea_d, norm_dim=1,
+                                                         fill_value=self.opt['self_loop_weight'],
+                                                         num_nodes=data.num_nodes, dtype=dtype)
+                else:
+                    edge_index, edge_weight = gcn_norm_fill_val(ei_d, edge_weight=ea_d,
+                                                                fill_value=self.opt['self_loop_weight'],
+                                                                num_nodes=data.num_nodes, dtype=dtype)
+                if self.opt['self_loop_weight'] > 0:
+                    edge_index, edge_weight = add_remaining_self_loops(
+                        edge_index, edge_weight, fill_value=self.opt['self_loop_weight'], num_nodes=data.num_nodes)
+                self._graph_cache = (key, ei, edge_index, edge_weight)
+            _, _, edge_index, edge_weight = self._graph_cache
+            self.data_edge_index = edge_index
+            self.odefunc.edge_index = edge_index
+            self.odefunc.edge_weight = edge_weight
+        self.odefunc.y = y
+
+    def set_time(self, time):
+        self.t = torch.tensor([0, time]).to(self.device)
+
+    def _integrate(self, x):
+        """the integrator call shared by ConstantODEblock / AttODEblock (block_constant.py:34-58)"""
+        t = self.t.type_as(x)
+        integrator = self.train_integrator if self.training else self.test_integrator
+        func = self.odefunc
+        opt = self.opt
+        if opt['adjoint'] and self.training:
+            state_dt = integrator(
+                func, x, t, method=opt['method'],
+                options=dict(step_size=opt['step_size'], max_iters=opt['max_iters']),
+                adjoint_method=opt['adjoint_method'],
+                adjoint_options=dict(step_size=opt['adjoint_step_size'], max_iters=opt['max_iters']),
+                atol=self.atol, rtol=self.rtol, adjoint_atol=self.atol_adjoint, adjoint_rtol=self.rtol_adjoint)
+        else:
+            state_dt = integrator(
+                func, x, t, method=opt['method'],
+                options=dict(step_size=opt['step_size'], max_iters=opt['max_iters']),
+                atol=self.atol, rtol=self.rtol)
+        return state_dt[1]
+
+    def __repr__(self):
+        return self.__class__.__name__ + '( Time Interval ' + str(self.t[0].item()) + ' -> ' + str(self.t[1].item()) \
+            + ")"
+
+
+class _RegShim(object):
+    """stands where the reference keeps `reg_odefunc` (base_classes.py:43): callers read
+    `block.reg_odefunc.odefunc.nfe` (base_classes.py:174-179)."""
+
+    def __init__(self, odefunc):
+        self.odefunc = odefunc
+
+
+class GraphData(object):
+    """base_classes.py:100-113"""
+
+    def __init__(self):
+        super(GraphData, self).__init__()
+        self.edge_index = None
+        self.edge_attr = None
+        self.num_nodes = None
+
+    def new_graph(self, edge_index, num_nodes, edge_attr=None):
+        self.edge_index = edge_index
+        self.edge_attr = edge_attr
+        self.num_nodes = num_nodes
+
+    def __repr__(self):
+        return self.__class__.__name__

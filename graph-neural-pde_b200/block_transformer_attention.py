@@ -1,0 +1,28 @@
+"""`AttODEblock` - mirror of the reference's src/block_transformer_attention.py:6-69: owns a second
+SpGraphTransAttentionLayer, computes attention ONCE at t = 0 from the block input and parks it on
+`odefunc.attention_weights` (read by LaplacianODEFunc when opt['block'] == 'attention'), then
+integrates.  With opt['function'] == 'transformer' that block-level attention is computed but never
+read, exactly as in the reference."""
+import torch
+
+from .base_classes import ODEblock, _integrators
+from .function_transformer_attention import SpGraphTransAttentionLayer
+
+
+class AttODEblock(ODEblock):
+    def __init__(self, odefunc, regularization_fns, opt, device, t=torch.tensor([0, 1]), gamma=0.5):
+        super(AttODEblock, self).__init__(odefunc, regularization_fns, opt, device, t)
+        self.train_integrator = _integrators(opt['adjoint'])
+        self.test_integrator = _integrators(opt['adjoint'])
+        self.set_tol()
+        self.multihead_att_layer = SpGraphTransAttentionLayer(opt['hidden_dim'], opt['hidden_dim'], opt, device,
+                                                              edge_weights=self.odefunc.edge_weight).to(device)
+
+    def get_attention_weights(self, x):
+        attention, values = self.multihead_att_layer(x, self.odefunc.edge_index)
+        return attention
+
+    def forward(self, x, graph_data, y=None):
+        self.reset_graph_data(graph_data, x.dtype, y)
+        self.odefunc.attention_weights = self.get_attention_weights(x)
+        return self._integrate(x)

@@ -274,12 +274,20 @@ struct SmBwdArgs {
   const int32_t* ptr;
   const int32_t* perm;     // nullptr or tperm
   const float* att;        // [E,H]
-  const float* dabar;      // [E]   dL/d(mean_h att)
+  const float* dabar;      // optional [E]   dL/d(mean_h att)
+  const float* datt;       // optional [E,H] dL/d att (CSR order), added to dabar/H
   const float* edge_w;     // optional
   float* ds;               // [E,H] dL/d(raw score)
   int32_t n, heads, long_threshold;
   const int32_t* long_list;
 };
+
+__device__ __forceinline__ float sm_da(const SmBwdArgs& a, int slot, int h, float inv_h) {
+  float v = 0.f;
+  if (a.dabar) v = __ldg(a.dabar + slot) * inv_h;
+  if (a.datt) v += __ldg(a.datt + (size_t)slot * a.heads + h);
+  return v;
+}
 
 // one thread per (segment, head); two sequential passes over the segment (fixed order)
 __global__ void __launch_bounds__(256) softmax_bwd_kernel(const SmBwdArgs a) {
@@ -292,11 +300,11 @@ __global__ void __launch_bounds__(256) softmax_bwd_kernel(const SmBwdArgs a) {
   float dot = 0.f;
   for (int p = start; p < end; ++p) {
     const int slot = a.perm ? __ldg(a.perm + p) : p;
-    dot = fmaf(__ldg(a.att + (size_t)slot * a.heads + h), __ldg(a.dabar + slot) * inv_h, dot);
+    dot = fmaf(__ldg(a.att + (size_t)slot * a.heads + h), sm_da(a, slot, h, inv_h), dot);
   }
   for (int p = start; p < end; ++p) {
     const int slot = a.perm ? __ldg(a.perm + p) : p;
-    float v = __ldg(a.att + (size_t)slot * a.heads + h) * (__ldg(a.dabar + slot) * inv_h - dot);
+    float v = __ldg(a.att + (size_t)slot * a.heads + h) * (sm_da(a, slot, h, inv_h) - dot);
     if (a.edge_w) v *= __ldg(a.edge_w + slot);
     a.ds[(size_t)slot * a.heads + h] = v;
   }
@@ -316,7 +324,7 @@ __global__ void __launch_bounds__(256) softmax_bwd_long_kernel(const SmBwdArgs a
   if (on)
     for (int p = start + lane; p < end; p += per) {
       const int slot = a.perm ? __ldg(a.perm + p) : p;
-      part = fmaf(__ldg(a.att + (size_t)slot * a.heads + h), __ldg(a.dabar + slot) * inv_h, part);
+      part = fmaf(__ldg(a.att + (size_t)slot * a.heads + h), sm_da(a, slot, h, inv_h), part);
     }
   sh[threadIdx.x] = on ? part : 0.f;
   __syncthreads();
@@ -330,7 +338,7 @@ __global__ void __launch_bounds__(256) softmax_bwd_long_kernel(const SmBwdArgs a
   if (on)
     for (int p = start + lane; p < end; p += per) {
       const int slot = a.perm ? __ldg(a.perm + p) : p;
-      float v = __ldg(a.att + (size_t)slot * a.heads + h) * (__ldg(a.dabar + slot) * inv_h - dot);
+      float v = __ldg(a.att + (size_t)slot * a.heads + h) * (sm_da(a, slot, h, inv_h) - dot);
       if (a.edge_w) v *= __ldg(a.edge_w + slot);
       a.ds[(size_t)slot * a.heads + h] = v;
     }
@@ -577,15 +585,15 @@ int gb_sddmm(const gb_graph* g, const float* gout, int32_t ldg, const float* x, 
   return GB_OK;
 }
 
-int gb_edge_softmax_bwd(const gb_graph* g, int32_t norm_idx, const float* att, const float* dabar, int32_t heads,
-                        const float* edge_w, float* ds, void* stream_) {
+int gb_edge_softmax_bwd(const gb_graph* g, int32_t norm_idx, const float* att, const float* dabar, const float* datt,
+                        int32_t heads, const float* edge_w, float* ds, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   if (int rc = check_graph_att(g, "gb_edge_softmax_bwd")) return rc;
-  GB_REQUIRE(att && dabar && ds && heads > 0 && heads <= 64, "gb_edge_softmax_bwd: bad arguments (heads <= 64)");
+  GB_REQUIRE(att && (dabar || datt) && ds && heads > 0 && heads <= 64, "gb_edge_softmax_bwd: bad arguments (heads <= 64)");
   GB_REQUIRE(norm_idx == 0 || norm_idx == 1, "gb_edge_softmax_bwd: attention_norm_idx must be 0 or 1");
   if (g->e == 0) return GB_OK;
   SmBwdArgs a{};
-  a.att = att; a.dabar = dabar; a.edge_w = edge_w; a.ds = ds; a.n = g->n; a.heads = heads;
+  a.att = att; a.dabar = dabar; a.datt = datt; a.edge_w = edge_w; a.ds = ds; a.n = g->n; a.heads = heads;
   a.long_threshold = eff_threshold(g);
   int n_long;
   if (norm_idx == 0) { a.ptr = g->rowptr; a.perm = nullptr; a.long_list = g->long_rows; n_long = g->n_long_rows; }

@@ -1,0 +1,63 @@
+"""`LaplacianODEFunc` - drop-in for the reference's src/function_laplacian_diffusion.py:15-77.
+
+    f(t, x) = alpha * (A x - x) + beta * x0
+    A's values: edge_weight (constant block) | mean_h attention_weights (attention block)
+                | attention_weights (mixed / hard_attention blocks)        (reference :45-57)
+
+The reference densifies A to [N,N] and calls a dense matmul per evaluation; here the evaluation is
+one fused CSR SpMM kernel (csrc/spmm.cu) and its VJP one transpose-SpMM kernel plus a fixed-order
+reduction.  Constructor, parameters (`w`, `d`, `alpha_sc`, `beta_sc` are kept although forward never
+reads them, as in the reference) and the forward(t, x) contract are unchanged.
+"""
+import torch
+from torch import nn
+
+from .base_classes import ODEFunc
+from . import plan as _plan
+from .ops import DiffusionFn, HeadMeanToCsrFn
+
+
+class LaplacianODEFunc(ODEFunc):
+
+    def __init__(self, in_features, out_features, opt, device):
+        super(LaplacianODEFunc, self).__init__(opt, device)
+        self.device = device
+        self.in_features = in_features
+        self.out_features = out_features
+        self.w = nn.Parameter(torch.eye(opt['hidden_dim']))
+        self.d = nn.Parameter(torch.zeros(opt['hidden_dim']) + 1)
+        self.alpha_sc = nn.Parameter(torch.ones(1))
+        self.beta_sc = nn.Parameter(torch.ones(1))
+        if self.opt.get('multi_modal', False):
+            raise NotImplementedError("opt['multi_modal']: the cross-modal pre-step of the fork "
+                                      '(function_laplacian_diffusion.py:61-63) is out of scope and broken upstream')
+
+    def _edge_values(self, plan):
+        """values of A in CSR-slot order (reference: sparse_multiply, :39-58)"""
+        block = self.opt['block']
+        if block == 'attention':
+            att = self.attention_weights
+            if att is None:
+                raise RuntimeError("block == 'attention' but attention_weights has not been set on the function")
+            att2 = att.reshape(plan.e, -1)
+            if att.requires_grad and torch.is_grad_enabled():
+                return HeadMeanToCsrFn.apply(att2, plan)
+            return _plan.cached_per_edge(plan, att, 'att_mean', lambda t: plan.head_mean_to_csr(t.detach()))
+        src = self.attention_weights if block in ('mixed', 'hard_attention') else self.edge_weight
+        if src is None:
+            raise RuntimeError('edge_weight / attention_weights has not been set on the function')
+        if src.requires_grad and torch.is_grad_enabled():
+            flat = src.reshape(-1)
+            return flat if plan.identity_order else flat[plan.eperm.long()]
+        return _plan.cached_per_edge(plan, src, 'w', lambda t: plan.to_csr_order(t.detach()))
+
+    def forward(self, t, x):  # the t param is needed by the ODE solver.
+        self._check_nfe()
+        x2 = self._as_2d(x)
+        plan = self._plan(x2.shape[0])
+        vals = self._edge_values(plan)
+        source = bool(self.opt['add_source'])
+        x0 = self._as_2d(self.x0) if (source and self.x0 is not None) else None
+        f = DiffusionFn.apply(x2, vals, self.alpha_train, self.beta_train if x0 is not None else None, x0, plan,
+                              not self.opt['no_alpha_sigmoid'], None)
+        return f.view_as(x)

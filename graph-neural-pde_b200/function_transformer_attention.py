@@ -1,0 +1,144 @@
+"""`ODEFuncTransformerAtt` and `SpGraphTransAttentionLayer` - drop-ins for the reference's
+src/function_transformer_attention.py:9-270.
+
+    attention, (v, prods) = multihead_att_layer(x, edge_index)       # recomputed every evaluation
+    f(t, x) = alpha * (mean_h(attention) applied as A to x  -  x) + beta * x0
+
+One evaluation = three kernels: Q|K projection GEMM, fused per-edge score + segment softmax + head
+mean (csrc/attention.cu), fused SpMM + epilogue (csrc/spmm.cu).  `scaled_dot` scores are per-edge
+q[row].k[col]/sqrt(dk) (upstream / BASELINE north_star semantics; the fork's line 249 sums k over
+ALL edges, SURVEY.md F4 - reproduced only by the oracle's fork_literal switch).
+
+Parameter names/shapes match the reference (`Q`, `K`, `V`, `Wout` Linear layers initialised to the
+constant 1e-5, default biases; `output_var`, `lengthscale` for exp_kernel).  `V` and `Wout` are
+only read by the `mix_features` branch, which is broken in the fork (tuple passed where a tensor is
+expected) and raises NotImplementedError here; their gradients are None, as in the reference.
+"""
+import torch
+from torch import nn
+
+from .base_classes import ODEFunc
+from . import _lib
+from . import plan as _plan
+from .ops import QKProjFn, EdgeSoftmaxFn, DiffusionFn, ToCooOrderFn
+
+
+class SpGraphTransAttentionLayer(nn.Module):
+    """function_transformer_attention.py:65-270"""
+
+    def __init__(self, in_features, out_features, opt, device, concat=True, edge_weights=None):
+        super(SpGraphTransAttentionLayer, self).__init__()
+        self.in_features = in_features
+        self.out_features = out_features
+        self.alpha = opt['leaky_relu_slope']
+        self.concat = concat
+        self.device = device
+        self.opt = opt
+        self.h = int(opt['heads'])
+        self.edge_weights = edge_weights
+        try:
+            self.attention_dim = opt['attention_dim']
+        except KeyError:
+            self.attention_dim = out_features
+        assert self.attention_dim % self.h == 0, "Number of heads ({}) must be a factor of the dimension size ({})".format(
+            self.h, self.attention_dim)
+        self.d_k = self.attention_dim // self.h
+        self.beltrami_kernel = bool(opt.get('beltrami', False)) and opt.get('attention_type') == 'exp_kernel'
+        if self.beltrami_kernel:
+            fd = opt['hidden_dim'] - opt['pos_enc_hidden_dim']
+            for name in ('output_var_x', 'lengthscale_x', 'output_var_p', 'lengthscale_p'):
+                setattr(self, name, nn.Parameter(torch.ones(1)))
+            for name, width in (('Qx', fd), ('Vx', fd), ('Kx', fd), ('Qp', opt['pos_enc_hidden_dim']),
+                                ('Vp', opt['pos_enc_hidden_dim']), ('Kp', opt['pos_enc_hidden_dim'])):
+                lin = nn.Linear(width, self.attention_dim)
+                self.init_weights(lin)
+                setattr(self, name, lin)
+        else:
+            if opt.get('attention_type') == 'exp_kernel':
+                self.output_var = nn.Parameter(torch.ones(1))
+                self.lengthscale = nn.Parameter(torch.ones(1))
+            self.Q = nn.Linear(in_features, self.attention_dim)
+            self.init_weights(self.Q)
+            self.V = nn.Linear(in_features, self.attention_dim)
+            self.init_weights(self.V)
+            self.K = nn.Linear(in_features, self.attention_dim)
+            self.init_weights(self.K)
+        if opt.get('multi_modal', False):
+            raise NotImplementedError("opt['multi_modal'] is out of scope (SURVEY.md 2.1)")
+        self.activation = nn.Sigmoid()
+        self.Wout = nn.Linear(self.d_k, in_features)
+        self.init_weights(self.Wout)
+
+    def init_weights(self, m):
+        if type(m) == nn.Linear:
+            nn.init.constant_(m.weight, 1e-5)      # function_transformer_attention.py:153-157
+
+    def _check_supported(self):
+        att_type = self.opt.get('attention_type', 'scaled_dot')
+        if att_type not in _lib.GB_ATT:
+            raise NotImplementedError(f"attention_type '{att_type}'")
+        if self.beltrami_kernel:
+            raise NotImplementedError("beltrami + exp_kernel (split feature/positional kernels, "
+                                      'function_transformer_attention.py:164-216) is not implemented yet')
+        if self.opt.get('square_plus', False):
+            raise NotImplementedError("opt['square_plus']: the fork's call site is broken (2 args to a 3-arg "
+                                      'function, function_transformer_attention.py:264); softmax only')
+        return _lib.GB_ATT[att_type]
+
+    def attention_csr(self, x2, plan):
+        """(att [E,H], abar [E], prods [E,H]) in CSR-slot order for an un-batched state x2 [N,d]"""
+        att_type = self._check_supported()
+        qk = QKProjFn.apply(x2, self.Q.weight, self.Q.bias, self.K.weight, self.K.bias)
+        edge_w = None
+        if self.opt.get('reweight_attention', False) and self.edge_weights is not None:
+            edge_w = _plan.cached_per_edge(plan, self.edge_weights, 'rw', lambda t: plan.to_csr_order(t.detach()))
+        kparams = None
+        if att_type == _lib.GB_ATT['exp_kernel']:
+            kparams = torch.cat([self.output_var.detach(), self.lengthscale.detach()]).to(torch.float32).contiguous()
+        return EdgeSoftmaxFn.apply(qk, plan, self.h, att_type, int(self.opt['attention_norm_idx']), edge_w, kparams)
+
+    def forward(self, x, edge, y=None):
+        """returns (attention [B,E,H] in the caller's edge order, (v, prods)); v is None because the
+        value projection is dead code unless mix_features (see module docstring)."""
+        batched = x.dim() == 3
+        x2 = ODEFunc._as_2d(x)
+        plan = _plan.get_plan(edge, x2.shape[0])
+        att, _abar, prods = self.attention_csr(x2, plan)
+        att = ToCooOrderFn.apply(att, plan)
+        prods = plan.to_coo_order(prods)
+        if batched:
+            att, prods = att[None], prods[None]
+        return att, (None, prods)
+
+    def __repr__(self):
+        return self.__class__.__name__ + ' (' + str(self.in_features) + ' -> ' + str(self.out_features) + ')'
+
+
+class ODEFuncTransformerAtt(ODEFunc):
+    """function_transformer_attention.py:9-62"""
+
+    def __init__(self, in_features, out_features, opt, device):
+        super(ODEFuncTransformerAtt, self).__init__(opt, device)
+        self.device = device
+        self.in_features = in_features
+        self.out_features = out_features
+        self.multihead_att_layer = SpGraphTransAttentionLayer(in_features, out_features, opt, device,
+                                                              edge_weights=self.edge_weight).to(device)
+        self.y = None
+
+    def forward(self, t, x):  # t is needed when called by the integrator
+        self._check_nfe()
+        if self.opt.get('mix_features', False):
+            raise NotImplementedError("opt['mix_features'] is broken in the reference "
+                                      '(function_transformer_attention.py:23-32,49-50) and not implemented')
+        x2 = self._as_2d(x)
+        plan = self._plan(x2.shape[0])
+        _att, abar, _prods = self.multihead_att_layer.attention_csr(x2, plan)
+        source = bool(self.opt['add_source'])
+        x0 = self._as_2d(self.x0) if (source and self.x0 is not None) else None
+        f = DiffusionFn.apply(x2, abar, self.alpha_train, self.beta_train if x0 is not None else None, x0, plan,
+                              not self.opt['no_alpha_sigmoid'], None)
+        return f.view_as(x)
+
+    def __repr__(self):
+        return self.__class__.__name__ + ' (' + str(self.in_features) + ' -> ' + str(self.out_features) + ')'

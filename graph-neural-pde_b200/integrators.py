@@ -1,0 +1,290 @@
+"""torchdiffeq-compatible `odeint` / `odeint_adjoint` (the subset the reference calls).
+
+The reference integrates with torchdiffeq (src/base_classes.py:45-48, src/block_constant.py:34-51,
+README pin 0.2.1), which is not installable in this image; ODEblock uses the real package when it
+imports and these solvers otherwise.  Same call signature:
+
+    odeint(func, y0, t, rtol=, atol=, method=, options=dict(step_size=...))
+    odeint_adjoint(func, y0, t, ..., adjoint_method=, adjoint_options=, adjoint_rtol=, adjoint_atol=,
+                   adjoint_params=)
+
+Methods: euler, midpoint, rk4 (3/8 rule = torchdiffeq's rk4_alt_step_func), dopri5, adaptive_heun.
+Fixed grid: t0 + k*step_size, ceil((t1-t0)/step_size + 1) points, last clamped to t1.  Adaptive:
+Hairer initial step, rms norm (max over tuple components), safety 0.9 / ifactor 10 / dfactor 0.2,
+dense output to land on requested times.  Adjoint: reverse-time solve of (vjp_t, y, a_y, a_params)
+with f evaluated under enable_grad and autograd.grad(f, (t, y, *params), -a_y, allow_unused=True);
+decreasing time is handled by negating t and f, as torchdiffeq does.  NFE is whatever `func`
+counts: one per call.
+
+Stage combinations y + dt*sum(b_j k_j) use one fused multi-tensor pass per component
+(`torch._foreach`-free: a single `torch.add(..., alpha=)` chain) - the SpMM-epilogue fusion of
+those passes lives in fused_rk.py and is used when the function advertises `fused_stage`.
+"""
+import math
+
+import torch
+
+_FIXED = ('euler', 'midpoint', 'rk4')
+_ADAPTIVE = ('dopri5', 'adaptive_heun')
+
+# Dormand-Prince 5(4), Shampine coefficients
+_DP = dict(
+    alpha=[1 / 5, 3 / 10, 4 / 5, 8 / 9, 1., 1.],
+    beta=[[1 / 5], [3 / 40, 9 / 40], [44 / 45, -56 / 15, 32 / 9],
+          [19372 / 6561, -25360 / 2187, 64448 / 6561, -212 / 729],
+          [9017 / 3168, -355 / 33, 46732 / 5247, 49 / 176, -5103 / 18656],
+          [35 / 384, 0, 500 / 1113, 125 / 192, -2187 / 6784, 11 / 84]],
+    c_sol=[35 / 384, 0, 500 / 1113, 125 / 192, -2187 / 6784, 11 / 84, 0],
+    c_err=[35 / 384 - 1951 / 21600, 0, 500 / 1113 - 22642 / 50085, 125 / 192 - 451 / 720,
+           -2187 / 6784 - -12231 / 42400, 11 / 84 - 649 / 6300, -1. / 60.],
+    c_mid=[6025192743 / 30085553152 / 2, 0, 51252292925 / 65400821598 / 2, -2691868925 / 45128329728 / 2,
+           187940372067 / 1594534317056 / 2, -1776094331 / 19743644256 / 2, 11237099 / 235043384 / 2],
+    order=5, fsal=True)
+_AH = dict(alpha=[1.], beta=[[1.]], c_sol=[0.5, 0.5], c_err=[0.5, -0.5], c_mid=None, order=2, fsal=False)
+
+
+def _combine(y, dt, ks, coeffs):
+    """y + dt * sum_j coeffs[j] * ks[j], per tuple component"""
+    out = []
+    for i, yi in enumerate(y):
+        acc = None
+        for k, c in zip(ks, coeffs):
+            if c == 0:
+                continue
+            acc = torch.add(yi if acc is None else acc, k[i], alpha=dt * c)
+        out.append(yi if acc is None else acc)
+    return tuple(out)
+
+
+def _rms(x):
+    return x.pow(2).mean().sqrt()
+
+
+def _mixed_norm(state):
+    return max(float(_rms(s)) for s in state if s.numel() > 0)
+
+
+class _Problem:
+    """normalises (func, y0, t) to tuple states and forward time"""
+
+    def __init__(self, func, y0, t):
+        self.is_tuple = isinstance(y0, (tuple, list))
+        self.y0 = tuple(y0) if self.is_tuple else (y0,)
+        ref = self.y0[0]
+        self.times = [float(v) for v in (t.tolist() if torch.is_tensor(t) else t)]
+        if len(self.times) < 2:
+            raise ValueError('t must hold at least two time points')
+        diffs = [b - a for a, b in zip(self.times[:-1], self.times[1:])]
+        if not (all(d > 0 for d in diffs) or all(d < 0 for d in diffs)):
+            raise ValueError('t must be strictly increasing or decreasing')
+        self.sign = 1.0 if diffs[0] > 0 else -1.0
+        self.times = [self.sign * v for v in self.times]
+        self.dtype, self.device = ref.dtype, ref.device
+        self._func = func
+
+    def tensor_time(self, s):
+        return torch.full((), self.sign * s, dtype=self.dtype, device=self.device)
+
+    def f(self, s, state):
+        """derivative in the internal (forward) time s"""
+        t = self.tensor_time(s)
+        out = self._func(t, state) if self.is_tuple else (self._func(t, state[0]),)
+        out = tuple(out)
+        if self.sign < 0:
+            out = tuple(-o for o in out)
+        return out
+
+
+def _fixed_grid(t0, t1, step_size):
+    n = int(math.ceil((t1 - t0) / step_size + 1))
+    grid = [t0 + k * step_size for k in range(n)]
+    grid[-1] = t1
+    return grid
+
+
+def _fixed_step(prob, method, t0, dt, t1, y):
+    f = prob.f
+    if method == 'euler':
+        return _combine(y, dt, [f(t0, y)], [1.0])
+    if method == 'midpoint':
+        k1 = f(t0, y)
+        k2 = f(t0 + 0.5 * dt, _combine(y, dt, [k1], [0.5]))
+        return _combine(y, dt, [k2], [1.0])
+    k1 = f(t0, y)
+    k2 = f(t0 + dt / 3, _combine(y, dt, [k1], [1 / 3]))
+    k3 = f(t0 + dt * 2 / 3, _combine(y, dt, [k1, k2], [-1 / 3, 1.0]))
+    k4 = f(t1, _combine(y, dt, [k1, k2, k3], [1.0, -1.0, 1.0]))
+    return _combine(y, dt, [k1, k2, k3, k4], [0.125, 0.375, 0.375, 0.125])
+
+
+def _solve_fixed(prob, method, step_size):
+    times = prob.times
+    if step_size is None:
+        grid = list(times)
+    else:
+        grid = _fixed_grid(times[0], times[-1], float(step_size))
+    sols = [prob.y0]
+    y = prob.y0
+    j = 1
+    for g0, g1 in zip(grid[:-1], grid[1:]):
+        y1 = _fixed_step(prob, method, g0, g1 - g0, g1, y)
+        while j < len(times) and g1 >= times[j]:
+            if times[j] == g1:
+                sols.append(y1)
+            else:                                   # linear interpolation onto a requested time
+                w = (times[j] - g0) / (g1 - g0)
+                sols.append(tuple(a + w * (b - a) for a, b in zip(y, y1)))
+            j += 1
+        y = y1
+    return sols
+
+
+def _initial_step(prob, t0, y0, order, rtol, atol, f0):
+    scale = tuple(atol + y.abs() * rtol for y in y0)
+    d0 = _mixed_norm(tuple(y / s for y, s in zip(y0, scale)))
+    d1 = _mixed_norm(tuple(f / s for f, s in zip(f0, scale)))
+    h0 = 1e-6 if (d0 < 1e-5 or d1 < 1e-5) else 0.01 * d0 / d1
+    y1 = _combine(y0, h0, [f0], [1.0])
+    f1 = prob.f(t0 + h0, y1)
+    d2 = _mixed_norm(tuple((a - b) / s for a, b, s in zip(f1, f0, scale))) / h0
+    if d1 <= 1e-15 and d2 <= 1e-15:
+        h1 = max(1e-6, h0 * 1e-3)
+    else:
+        h1 = (0.01 / max(d1, d2)) ** (1.0 / float(order + 1))
+    return min(100 * h0, h1)
+
+
+def _interp4(y0, y1, y_mid, f0, f1, dt, x):
+    out = []
+    for a0, a1, am, g0, g1 in zip(y0, y1, y_mid, f0, f1):
+        a = 2 * dt * (g1 - g0) - 8 * (a1 + a0) + 16 * am
+        b = dt * (5 * g0 - 3 * g1) + 18 * a0 + 14 * a1 - 32 * am
+        c = dt * (g1 - 4 * g0) - 11 * a0 - 5 * a1 + 16 * am
+        d = dt * g0
+        out.append(a0 + x * (d + x * (c + x * (b + x * a))))
+    return tuple(out)
+
+
+def _solve_adaptive(prob, method, rtol, atol, max_num_steps=2 ** 31 - 1):
+    tab = _DP if method == 'dopri5' else _AH
+    times = prob.times
+    t, y = times[0], prob.y0
+    f0 = prob.f(t, y)
+    dt = _initial_step(prob, t, y, tab['order'] - 1, rtol, atol, f0)
+    sols = [y]
+    # interpolation window of the last accepted step
+    win = None
+    steps = 0
+    for target in times[1:]:
+        while t < target:
+            if steps >= max_num_steps:
+                raise RuntimeError('max_num_steps exceeded')
+            steps += 1
+            ks = [f0]
+            for a_i, b_i in zip(tab['alpha'], tab['beta']):
+                ks.append(prob.f(t + a_i * dt, _combine(y, dt, ks, b_i)))
+            y1 = _combine(y, dt, ks, tab['c_sol'])
+            err = _combine(tuple(torch.zeros_like(v) for v in y), dt, ks, tab['c_err'])
+            tol = tuple(atol + rtol * torch.max(a.abs(), b.abs()) for a, b in zip(y, y1))
+            ratio = _mixed_norm(tuple(e / s for e, s in zip(err, tol)))
+            if ratio <= 1:
+                f1 = ks[-1] if tab['fsal'] else prob.f(t + dt, y1)
+                y_mid = _combine(y, dt, ks, tab['c_mid']) if tab['c_mid'] else None
+                win = (t, t + dt, y, y1, y_mid, f0, f1)
+                t, y, f0 = t + dt, y1, f1
+            if ratio == 0:
+                factor = 10.0
+            else:
+                dfactor = 1.0 if ratio < 1 else 0.2
+                factor = min(10.0, max(0.9 / ratio ** (1.0 / tab['order']), dfactor))
+            dt = dt * factor
+        # t >= target: evaluate the dense output of the last accepted step at `target`
+        w0, w1, ya, yb, ym, fa, fb = win
+        if target == w1:
+            sols.append(yb)
+        elif ym is not None:
+            sols.append(_interp4(ya, yb, ym, fa, fb, w1 - w0, (target - w0) / (w1 - w0)))
+        else:
+            x = (target - w0) / (w1 - w0)
+            sols.append(tuple(a + x * (b - a) for a, b in zip(ya, yb)))
+    return sols
+
+
+def odeint(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, event_fn=None):
+    if event_fn is not None:
+        raise NotImplementedError('event handling is not part of the reference call sites')
+    method = method or 'dopri5'
+    options = dict(options or {})
+    prob = _Problem(func, y0, t)
+    fused = getattr(func, 'fused_odeint', None)
+    if fused is not None and not prob.is_tuple and method in _FIXED:
+        res = fused(prob, method, options.get('step_size'))
+        if res is not None:
+            return res
+    if method in _FIXED:
+        sols = _solve_fixed(prob, method, options.get('step_size'))
+    elif method in _ADAPTIVE:
+        sols = _solve_adaptive(prob, method, float(rtol), float(atol))
+    else:
+        raise NotImplementedError(f"method '{method}' (supported: {_FIXED + _ADAPTIVE})")
+    out = tuple(torch.stack([s[i] for s in sols]) for i in range(len(prob.y0)))
+    return out if prob.is_tuple else out[0]
+
+
+class _OdeintAdjoint(torch.autograd.Function):
+
+    @staticmethod
+    def forward(ctx, func, t, cfg, n_params, y0, *params):
+        with torch.no_grad():
+            ys = odeint(func, y0, t, rtol=cfg['rtol'], atol=cfg['atol'], method=cfg['method'], options=cfg['options'])
+        ctx.func, ctx.cfg, ctx.params = func, cfg, params
+        ctx.times = [float(v) for v in (t.tolist() if torch.is_tensor(t) else t)]
+        ctx.save_for_backward(ys)
+        return ys
+
+    @staticmethod
+    def backward(ctx, grad_ys):
+        func, cfg, params = ctx.func, ctx.cfg, ctx.params
+        times = ctx.times
+        ys, = ctx.saved_tensors
+
+        def aug_dynamics(tt, state):
+            y, a_y = state[1], state[2]
+            with torch.enable_grad():
+                tt_ = tt.detach().requires_grad_(True)
+                y_ = y.detach().requires_grad_(True)
+                f = func(tt_, y_)
+                grads = torch.autograd.grad(f, (tt_, y_) + tuple(params), -a_y, allow_unused=True)
+            vt = grads[0] if grads[0] is not None else torch.zeros_like(tt)
+            vy = grads[1] if grads[1] is not None else torch.zeros_like(y)
+            vp = [g if g is not None else torch.zeros_like(p) for g, p in zip(grads[2:], params)]
+            return (vt, f.detach(), vy, *vp)
+
+        with torch.no_grad():
+            state = [torch.zeros((), dtype=ys.dtype, device=ys.device), ys[-1], grad_ys[-1]] + \
+                    [torch.zeros_like(p) for p in params]
+            for i in range(len(times) - 1, 0, -1):
+                sol = odeint(aug_dynamics, tuple(state), [times[i], times[i - 1]], rtol=cfg['adjoint_rtol'],
+                             atol=cfg['adjoint_atol'], method=cfg['adjoint_method'], options=cfg['adjoint_options'])
+                state = [s[1] for s in sol]
+                state[1] = ys[i - 1]
+                state[2] = state[2] + grad_ys[i - 1]
+        return (None, None, None, None, state[2]) + tuple(state[3:])
+
+
+def odeint_adjoint(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, event_fn=None,
+                   adjoint_rtol=None, adjoint_atol=None, adjoint_method=None, adjoint_options=None,
+                   adjoint_params=None):
+    if event_fn is not None:
+        raise NotImplementedError('event handling is not part of the reference call sites')
+    if isinstance(y0, (tuple, list)):
+        raise NotImplementedError('odeint_adjoint: tuple states (regularised ODE functions) are not supported')
+    if adjoint_params is None:
+        adjoint_params = tuple(func.parameters()) if isinstance(func, torch.nn.Module) else ()
+    params = tuple(p for p in adjoint_params if p.requires_grad)
+    cfg = dict(rtol=rtol, atol=atol, method=method or 'dopri5', options=dict(options or {}),
+               adjoint_rtol=rtol if adjoint_rtol is None else adjoint_rtol,
+               adjoint_atol=atol if adjoint_atol is None else adjoint_atol,
+               adjoint_method=adjoint_method or method or 'dopri5',
+               adjoint_options=dict(adjoint_options if adjoint_options is not None else (options or {})))
+    return _OdeintAdjoint.apply(func, t, cfg, len(params), y0, *params)

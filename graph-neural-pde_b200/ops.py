@@ -1,0 +1,199 @@
+"""autograd.Functions over the C ABI: the three composable pieces of one ODE-function evaluation.
+
+  QKProjFn        q|k = x [Wq;Wk]^T + [bq;bk]                (function_transformer_attention.py:224-225)
+  EdgeSoftmaxFn   att[E,H], abar[E] from q,k over the plan    (…:240-266 + utils.py:116-127)
+  DiffusionFn     f = alpha (A x - x) + beta x0                (function_laplacian_diffusion.py:60-77)
+
+Each `backward` is a hand-written VJP (the reference has none: it relies on torch autograd through
+its dense restatement, and `odeint_adjoint` calls autograd.grad on the same forward).  Double
+backward (`create_graph=True`, used only by regularized_ODE_function.py:39-75) is not supported and
+raises.  Every tensor must live on a CUDA device: there is no CPU path.
+"""
+import torch
+from torch.autograd.function import once_differentiable
+
+from . import _lib
+
+
+def _f32c(t):
+    if t.dtype != torch.float32:
+        raise TypeError(f'grand_b200 computes in float32 (reference dtype); got {t.dtype}')
+    return t if t.is_contiguous() else t.contiguous()
+
+
+class QKProjFn(torch.autograd.Function):
+    """x [N,d]; wq,wk [A,d]; bq,bk [A]  ->  qk [N,2A] (q = qk[:, :A], k = qk[:, A:])"""
+
+    @staticmethod
+    def forward(ctx, x, wq, bq, wk, bk):
+        lib = _lib.load()
+        _lib.require_cuda(x, wq, bq, wk, bk)
+        x = _f32c(x)
+        n, d = x.shape
+        a = wq.shape[0]
+        w = torch.cat([wq, wk], dim=0).contiguous()
+        b = torch.cat([bq, bk], dim=0).contiguous()
+        out = torch.empty(n, 2 * a, dtype=torch.float32, device=x.device)
+        _lib.check(lib.gb_linear_fwd(x.data_ptr(), d, n, d, w.data_ptr(), b.data_ptr(), 2 * a, out.data_ptr(),
+                                     2 * a, _lib.stream()), 'gb_linear_fwd')
+        ctx.save_for_backward(x, w)
+        ctx.a = a
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dqk):
+        lib = _lib.load()
+        x, w = ctx.saved_tensors
+        n, d = x.shape
+        a = ctx.a
+        dqk = _f32c(dqk)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x)
+            _lib.check(lib.gb_linear_bwd_x(dqk.data_ptr(), 2 * a, n, 2 * a, w.data_ptr(), d, dx.data_ptr(), d, 0,
+                                           _lib.stream()), 'gb_linear_bwd_x')
+        if any(ctx.needs_input_grad[1:]):
+            dw = torch.empty(2 * a, d, dtype=torch.float32, device=x.device)
+            db = torch.empty(2 * a, dtype=torch.float32, device=x.device)
+            ws = torch.empty(int(lib.gb_linear_bwd_w_workspace_bytes(n, d, 2 * a)), dtype=torch.uint8, device=x.device)
+            _lib.check(lib.gb_linear_bwd_w(dqk.data_ptr(), 2 * a, x.data_ptr(), d, n, d, 2 * a, dw.data_ptr(),
+                                           db.data_ptr(), ws.data_ptr(), ws.numel(), _lib.stream()), 'gb_linear_bwd_w')
+            return dx, dw[:a], db[:a], dw[a:], db[a:]
+        return dx, None, None, None, None
+
+
+class EdgeSoftmaxFn(torch.autograd.Function):
+    """qk [N,2A] -> (att [E,H], abar [E], prods [E,H]) in CSR-slot order."""
+
+    @staticmethod
+    def forward(ctx, qk, plan, heads, att_type, norm_idx, edge_w, kparams):
+        lib = _lib.load()
+        _lib.require_cuda(qk)
+        qk = _f32c(qk)
+        n, a2 = qk.shape
+        a = a2 // 2
+        dk = a // heads
+        att = torch.empty(plan.e, heads, dtype=torch.float32, device=qk.device)
+        abar = torch.empty(plan.e, dtype=torch.float32, device=qk.device)
+        prods = torch.empty(plan.e, heads, dtype=torch.float32, device=qk.device)
+        _lib.check(lib.gb_edge_softmax_fwd(plan.c, norm_idx, qk.data_ptr(), a2, qk.data_ptr() + 4 * a, a2, heads, dk,
+                                           att_type, _lib.ptr(edge_w), _lib.ptr(kparams), att.data_ptr(),
+                                           abar.data_ptr(), prods.data_ptr(), _lib.stream()), 'gb_edge_softmax_fwd')
+        ctx.save_for_backward(qk, att)
+        ctx.plan, ctx.heads, ctx.dk, ctx.att_type, ctx.norm_idx, ctx.edge_w, ctx.kparams = \
+            plan, heads, dk, att_type, norm_idx, edge_w, kparams
+        ctx.set_materialize_grads(False)
+        ctx.mark_non_differentiable(prods)
+        return att, abar, prods
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, datt, dabar, _dprods):
+        lib = _lib.load()
+        qk, att = ctx.saved_tensors
+        plan, heads, dk = ctx.plan, ctx.heads, ctx.dk
+        n, a2 = qk.shape
+        a = a2 // 2
+        if datt is None and dabar is None:
+            return (None,) * 7
+        datt = None if datt is None else _f32c(datt)
+        dabar = None if dabar is None else _f32c(dabar)
+        ds = torch.empty(plan.e, heads, dtype=torch.float32, device=qk.device)
+        _lib.check(lib.gb_edge_softmax_bwd(plan.c, ctx.norm_idx, att.data_ptr(), _lib.ptr(dabar), _lib.ptr(datt), heads,
+                                           _lib.ptr(ctx.edge_w), ds.data_ptr(), _lib.stream()), 'gb_edge_softmax_bwd')
+        dqk = torch.empty_like(qk)
+        _lib.check(lib.gb_edge_score_bwd(plan.c, ds.data_ptr(), qk.data_ptr(), a2, qk.data_ptr() + 4 * a, a2, heads, dk,
+                                         ctx.att_type, _lib.ptr(ctx.kparams), None, dqk.data_ptr(), a2,
+                                         dqk.data_ptr() + 4 * a, a2, None, None, _lib.stream()), 'gb_edge_score_bwd')
+        return dqk, None, None, None, None, None, None
+
+
+class DiffusionFn(torch.autograd.Function):
+    """f = alpha (A x - x) + beta x0 with A given by `vals` [E] in CSR-slot order.
+
+    alpha = sigmoid(alpha_train) unless no_alpha_sigmoid; beta_train/x0 None -> no source term.
+    Gradients: x, vals (SDDMM, only when requested), alpha_train, beta_train.  x0 is detached by the
+    caller (base_classes.py:53-55) and gets none."""
+
+    @staticmethod
+    def forward(ctx, x, vals, alpha_train, beta_train, x0, plan, alpha_sigmoid, stage):
+        lib = _lib.load()
+        _lib.require_cuda(x, vals, alpha_train, beta_train, x0)
+        x = _f32c(x)
+        vals = _f32c(vals)
+        n, d = x.shape
+        if n != plan.n:
+            raise ValueError(f'x has {n} rows but the graph has {plan.n} nodes')
+        source = beta_train is not None and x0 is not None
+        if source:
+            x0 = _f32c(x0)
+        out = torch.empty_like(x)
+        _lib.check(lib.gb_spmm_fwd(plan.c, vals.data_ptr(), x.data_ptr(), d, _lib.ptr(x0) if source else None, d,
+                                   alpha_train.data_ptr(), int(alpha_sigmoid),
+                                   beta_train.data_ptr() if source else None, d, out.data_ptr(), d, stage,
+                                   _lib.stream()), 'gb_spmm_fwd')
+        ctx.save_for_backward(x, vals, alpha_train, x0 if source else None)
+        ctx.plan, ctx.alpha_sigmoid, ctx.source = plan, int(alpha_sigmoid), source
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gout):
+        lib = _lib.load()
+        x, vals, alpha_train, x0 = ctx.saved_tensors
+        plan = ctx.plan
+        n, d = x.shape
+        gout = _f32c(gout)
+        dx = torch.empty_like(x)
+        want_params = ctx.needs_input_grad[2] or ctx.needs_input_grad[3]
+        partials = torch.empty(int(lib.gb_spmm_bwd_partials(plan.c, d)), dtype=torch.float32, device=x.device)
+        dparams = torch.empty(2, dtype=torch.float32, device=x.device) if want_params else None
+        _lib.check(lib.gb_spmm_bwd(plan.c, vals.data_ptr(), gout.data_ptr(), d, x.data_ptr(), d, _lib.ptr(x0), d,
+                                   alpha_train.data_ptr(), ctx.alpha_sigmoid, d, dx.data_ptr(), d, 0,
+                                   partials.data_ptr(), _lib.ptr(dparams), _lib.stream()), 'gb_spmm_bwd')
+        dvals = None
+        if ctx.needs_input_grad[1]:
+            dvals = torch.empty_like(vals)
+            _lib.check(lib.gb_sddmm(plan.c, gout.data_ptr(), d, x.data_ptr(), d, d, alpha_train.data_ptr(),
+                                    ctx.alpha_sigmoid, dvals.data_ptr(), _lib.stream()), 'gb_sddmm')
+        dalpha = dparams[0].reshape(alpha_train.shape) if ctx.needs_input_grad[2] else None
+        dbeta = None
+        if ctx.needs_input_grad[3] and ctx.source:
+            dbeta = dparams[1].reshape(())
+        return (dx if ctx.needs_input_grad[0] else None), dvals, dalpha, dbeta, None, None, None, None
+
+
+class HeadMeanToCsrFn(torch.autograd.Function):
+    """attention_weights [E,H] in the caller's COO order -> mean over heads in CSR-slot order"""
+
+    @staticmethod
+    def forward(ctx, att_coo, plan):
+        ctx.plan, ctx.heads = plan, att_coo.reshape(plan.e, -1).shape[1]
+        return plan.head_mean_to_csr(att_coo)
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dabar):
+        plan = ctx.plan
+        g = (dabar / ctx.heads)[:, None].expand(plan.e, ctx.heads)
+        out = torch.empty(plan.e, ctx.heads, dtype=dabar.dtype, device=dabar.device)
+        out[plan.eperm.long()] = g
+        return out, None
+
+
+class ToCooOrderFn(torch.autograd.Function):
+    """[E,W] CSR-slot order -> caller's COO order (what SpGraphTransAttentionLayer returns)"""
+
+    @staticmethod
+    def forward(ctx, rows_csr, plan):
+        ctx.plan = plan
+        return plan.to_coo_order(rows_csr)
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g):
+        plan = ctx.plan
+        if plan.identity_order:
+            return g, None
+        return g[plan.eperm.long()], None

@@ -189,13 +189,14 @@ int gb_edge_softmax_fwd(const gb_graph* g, int32_t norm_idx, const float* q, int
 
 /* ---- K5b: attention VJP.
  *  (1) SDDMM:        dabar[s] = alpha * <gout[row_s,:], x[col_s,:]>                        (CSR pass)
- *  (2) softmax bwd:  ds[s,h]  = att[s,h] * (dabar[s]/H - sum_{g} att[.,h]*dabar[.]/H)      (segment pass)
+ *  (2) softmax bwd:  da[s,h] = dabar[s]/H (+ datt[s,h]);  ds[s,h] = att[s,h] * (da[s,h] - sum_{g} att[.,h]*da[.,h])
+ *      (dabar = dL/d mean_h att [E], datt = dL/d att [E,H]; either may be NULL)                (segment pass)
  *  (3) dq[i,h,:] = sum_{s in row i} ds[s,h] * dscore/dq ;  dk[j,h,:] = sum_{p in col j} ds[.,h] * dscore/dk
  *  All reductions are segment reductions over the pre-sorted CSR/CSC orders: deterministic. */
 int gb_sddmm(const gb_graph* g, const float* gout, int32_t ldg, const float* x, int32_t ldx, int32_t d,
              const float* alpha_train, int32_t alpha_sigmoid, float* dabar, void* stream);
 int gb_edge_softmax_bwd(const gb_graph* g, int32_t norm_idx, const float* att, const float* dabar,
-                        int32_t heads, const float* edge_w, float* ds, void* stream);
+                        const float* datt, int32_t heads, const float* edge_w, float* ds, void* stream);
 int gb_edge_score_bwd(const gb_graph* g, const float* ds, const float* q, int32_t ldq, const float* k,
                       int32_t ldk, int32_t heads, int32_t dk, int32_t att_type, const float* kparams,
                       const float* prods, float* dq, int32_t lddq, float* dk_out, int32_t lddk,
