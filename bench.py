@@ -1,0 +1,353 @@
+#!/usr/bin/env python
+"""bench.py - headline benchmark of the B200 graph-diffusion operator (see DESIGN.md "Measurement").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c1..c5] [--impl ours|reference]
+
+Metric (BASELINE.json): ODE-function evaluations per second, forward + adjoint backward.
+A "step" is one training pass of the reference's call pattern over one synthetic graph:
+`AttODEblock(ODEFuncTransformerAtt)` (GRAND-nl, 4 heads) integrated with rk4 over [0, T] under
+`odeint_adjoint` (adjoint_method rk4), forward then backward of sum(z * g).  Evaluations are counted
+exactly as the reference counts them (`odefunc.nfe`, +1 per forward call; one adjoint-dynamics call
+= 1 evaluation + 1 VJP).  value = evals / device time with the state already in HBM; e2e = the same
+pass with the state copied from pinned host memory and the result read back, inside the timed region.
+One JSON line on stdout (rank 0).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+T_END = 2.0            # integration time -> 2 rk4 steps forward, 2 backward
+STEP_SIZE = 1.0
+
+
+def read_peaks():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(path):
+        with open(path) as fh:
+            p = json.load(fh)
+        return float(p['hbm_gbs']), 'measured (MEASURED_PEAKS.json)'
+    return 6650.0, 'fallback (B200_PROFILING.md)'
+
+
+def make_opt(cfg, adjoint=True):
+    return {'hidden_dim': cfg['d'], 'block': 'attention', 'function': 'transformer', 'max_nfe': 10 ** 9,
+            'no_alpha_sigmoid': False, 'add_source': True, 'augment': False, 'adjoint': adjoint, 'tol_scale': 1.0,
+            'tol_scale_adjoint': 1.0, 'data_norm': 'rw', 'self_loop_weight': 1.0, 'method': 'rk4',
+            'step_size': STEP_SIZE, 'max_iters': 100, 'adjoint_method': 'rk4', 'adjoint_step_size': STEP_SIZE,
+            'leaky_relu_slope': 0.2, 'heads': cfg['heads'], 'attention_dim': cfg['adim'], 'attention_norm_idx': 0,
+            'reweight_attention': False, 'beltrami': False, 'attention_type': 'scaled_dot', 'square_plus': False,
+            'mix_features': False, 'multi_modal': False, 'kinetic_energy': None, 'jacobian_norm2': None,
+            'total_deriv': None, 'directional_penalty': None}
+
+
+# ---- algorithmic bytes per launch of each kernel (fp32 = 4 B, int32 index = 4 B; every matrix read
+# ---- once per kernel that needs it, perfect reuse of gathered rows) - DESIGN.md "Kernels" ---------
+def algorithmic_bytes(n, e, d, a, h):
+    return {
+        'spmm_fwd': 8 * e + 12 * n * d + 4 * n,
+        'spmm_bwd': 12 * e + 16 * n * d + 4 * n,
+        'edge_softmax_fwd': 8 * n * a + 4 * n + 8 * e + 8 * e * h,
+        'sddmm': 8 * n * d + 8 * e + 4 * n,
+        'edge_softmax_bwd': 8 * e * h + 4 * e + 4 * n,
+        'edge_score_bwd_q': 4 * e * h + 4 * e + 8 * n * a + 4 * n,
+        'edge_score_bwd_k': 4 * e * h + 8 * e + 8 * n * a + 4 * n,
+        'linear_fwd': 4 * n * d + 8 * n * a,
+        'linear_bwd_x': 4 * n * d + 8 * n * a,
+        'linear_bwd_w': 4 * n * d + 8 * n * a,
+    }
+
+
+class ClockSampler:
+    """samples nvidia-smi during the timed region (B200_PROFILING.md clocks line)"""
+    Q = 'clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,' \
+        'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap'
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), f'--query-gpu={self.Q}',
+                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(',')])
+
+    def __exit__(self, *exc):
+        if self.proc is not None:
+            time.sleep(0.15)
+            self.proc.terminate()
+            self.thread.join(timeout=2)
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for nm, v in zip(names, r[2:6]):
+                if v.lower().startswith('active'):
+                    reasons.add(nm)
+        if not sm:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        sm.sort()
+        return {'sm_mhz': sm[len(sm) // 2], 'sm_max_mhz': max(mx), 'reasons': sorted(reasons), 'samples': len(sm)}
+
+
+# ---- our arm ------------------------------------------------------------------------------------
+def build_block(cfg, device):
+    import grand_b200
+    opt = make_opt(cfg)
+    block = grand_b200.set_block(opt)(grand_b200.set_function(opt), [], opt, device,
+                                      t=torch.tensor([0., T_END])).to(device)
+    block.train()
+    g = torch.Generator().manual_seed(7)
+    with torch.no_grad():                       # random-init weights of the named architecture (N(0, 1/d))
+        for layer in (block.odefunc.multihead_att_layer, block.multihead_att_layer):
+            for lin in (layer.Q, layer.K):
+                lin.weight.copy_((torch.randn(lin.weight.shape, generator=g) / cfg['d'] ** 0.5).to(device))
+        block.odefunc.alpha_train.fill_(0.3)
+        block.odefunc.beta_train.fill_(0.1)
+    return block
+
+
+def train_pass(block, data, x_dev, g_dev):
+    """one step: forward integrate + adjoint backward; returns (evals, loss tensor)"""
+    func = block.odefunc
+    func.nfe = 0
+    x = x_dev.detach().requires_grad_(True)
+    block.set_x0(x)
+    z = block(x, data)
+    loss = (z * g_dev).sum()
+    params = [p for p in block.parameters() if p.requires_grad]
+    for p in params:
+        p.grad = None
+    loss.backward()
+    return func.nfe, loss
+
+
+def run_ours(args):
+    import grand_b200
+    from grand_b200 import synth, _lib
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    torch.cuda.set_device(local)
+    device = torch.device('cuda', local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group('nccl', device_id=device)
+    name = args.workload
+    cfg = dict(synth.CONFIGS[name])
+    if world > 1:
+        return run_partitioned(args, cfg, device, rank, world)
+    ei, n = synth.make_graph(name, device)
+    data = grand_b200.GraphData()
+    data.new_graph(ei, n)
+    d = cfg['d']
+    gen = torch.Generator(device=device).manual_seed(99)
+    x_dev = torch.randn(n, d, generator=gen, device=device)
+    g_dev = torch.randn(n, d, generator=gen, device=device)
+    x_host = x_dev.cpu().pin_memory()
+    block = build_block(cfg, device)
+
+    for _ in range(max(args.warmup, 3)):
+        evals, loss = train_pass(block, data, x_dev, g_dev)
+    torch.cuda.synchronize()
+    e_prime = int(block.odefunc.edge_index.shape[-1])
+
+    # ---- device-resident timing (value) + per-kernel event timing (roofline) ---------------------
+    launches0 = _lib.launch_count()
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clocks, _lib.Profiler() as prof:
+        torch.cuda.synchronize()
+        start.record()
+        total_evals = 0
+        for _ in range(args.steps):
+            evals, loss = train_pass(block, data, x_dev, g_dev)
+            total_evals += evals
+        stop.record()
+        torch.cuda.synchronize()
+        kernels = prof.results()
+    ms = start.elapsed_time(stop)
+    launches = _lib.launch_count() - launches0
+
+    # ---- end-to-end timing: pinned host state -> device, pass, loss + dL/dx back to host --------
+    gx_host = torch.empty(n, d).pin_memory()
+    s2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    s2.record()
+    evals_e2e = 0
+    for _ in range(args.steps):
+        xin = x_host.to(device, non_blocking=True)
+        func = block.odefunc
+        func.nfe = 0
+        xg = xin.requires_grad_(True)
+        block.set_x0(xg)
+        z = block(xg, data)
+        loss = (z * g_dev).sum()
+        gx, = torch.autograd.grad(loss, xg)
+        gx_host.copy_(gx, non_blocking=True)
+        loss_host = float(loss)                    # device -> host read of the step's result
+        evals_e2e += func.nfe
+    e2.record()
+    torch.cuda.synchronize()
+    ms_e2e = s2.elapsed_time(e2)
+
+    # ---- roofline of the dominant kernel ---------------------------------------------------------
+    peak, peak_src = read_peaks()
+    alg = algorithmic_bytes(n, e_prime, d, cfg['adim'], cfg['heads'])
+    top = max(kernels.items(), key=lambda kv: kv[1]['ms'])
+    kname, kstat = top
+    per_launch_ms = kstat['ms'] / kstat['launches']
+    achieved = alg.get(kname, 0) / (per_launch_ms * 1e-3) / 1e9 if per_launch_ms > 0 else 0.0
+    ksum = sum(v['ms'] for v in kernels.values())
+    roofline = {'bound': 'hbm', 'kernel': kname, 'achieved': round(achieved, 1), 'peak': peak, 'unit': 'GB/s',
+                'frac': round(achieved / peak, 4), 'traffic': None, 'peak_source': peak_src,
+                'algorithmic_bytes_per_launch': alg.get(kname, 0), 'avg_launch_ms': round(per_launch_ms, 4),
+                'share_of_kernel_time': round(kstat['ms'] / ksum, 4) if ksum else None,
+                'kernels': {k: {'ms_per_launch': round(v['ms'] / v['launches'], 4), 'launches': v['launches'],
+                                'share': round(v['ms'] / ksum, 4),
+                                'alg_GBps': round(alg[k] / (v['ms'] / v['launches'] * 1e-3) / 1e9, 1) if k in alg else None}
+                            for k, v in sorted(kernels.items(), key=lambda kv: -kv[1]['ms'])}}
+
+    line = {
+        'metric': 'ODE-func evals/sec (fwd + adjoint bwd)', 'value': round(total_evals / (ms * 1e-3), 3),
+        'unit': 'evals/s', 'n_gpus': 1, 'steps': args.steps, 'warmup': max(args.warmup, 3),
+        'ms_per_step': round(ms / args.steps, 3), 'higher_is_better': True, 'scaling': 'strong',
+        'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': {'workload': f"{name}: GRAND-nl ({cfg['desc']}), N={n}, E'={e_prime}, d={d}, heads={cfg['heads']}, "
+                               f"attention_dim={cfg['adim']}, AttODEblock + ODEFuncTransformerAtt, rk4 step {STEP_SIZE} "
+                               f"T={T_END}, odeint_adjoint (rk4)",
+                   'evals_per_step': evals, 'l2': 'inputs larger than L2 (no flush)' if name in ('c4', 'c5')
+                   else 'working set partly L2-resident; no flush (state reused across evaluations as in the solver)'},
+        'e2e': {'value': round(evals_e2e / (ms_e2e * 1e-3), 3), 'unit': 'evals/s',
+                'h2d_bytes_per_step': n * d * 4, 'd2h_bytes_per_step': n * d * 4 + 4,
+                'ms_per_step': round(ms_e2e / args.steps, 3)},
+        'gpu_launches': int(launches), 'clocks': clocks.summary(), 'roofline': roofline,
+    }
+    if args.cpu_baseline:
+        line['cpu_baseline'] = cpu_baseline(name, cfg, steps=1, warmup=0)
+    print(json.dumps(line))
+
+
+def run_partitioned(args, cfg, device, rank, world):
+    raise SystemExit('bench.py --gpus N>1: the row-partitioned path is not wired yet (see DESIGN.md section e)')
+
+
+# ---- CPU baseline / reference arm (the only place bench.py executes oracle/) ----------------------
+def cpu_pass(state):
+    """one forward evaluation + one adjoint-dynamics evaluation (f recomputed + VJP) of the oracle port"""
+    from oracle import funcs
+    x, ei, wq, bq, wk, bk, x0, g, heads = state
+    with torch.no_grad():
+        funcs.transformer_f(x, ei, wq, bq, wk, bk, heads, state.alpha, state.beta, x0)
+    xs = x.detach().requires_grad_(True)
+    f = funcs.transformer_f(xs, ei, wq, bq, wk, bk, heads, state.alpha, state.beta, x0)
+    torch.autograd.grad(f, (xs, wq, bq, wk, bk, state.alpha, state.beta), g)
+    return 2
+
+
+class CpuState(tuple):
+    pass
+
+
+def make_cpu_state(name, cfg, scale_div):
+    from oracle import graph as og
+    import numpy as np
+    if name == 'c5':
+        import math
+        ei = og.rmat_graph(24 - int(round(math.log2(scale_div))), 16, 1234)
+        n = 1 << (24 - int(round(math.log2(scale_div))))
+    else:
+        n = cfg['n'] // scale_div
+        ei = og.shaped_graph(n, (cfg['e'] // scale_div) // 2 * 2, 1234)
+    ei, _ = og.reset_graph_data(ei, None, n, 'rw', 1.0)
+    d, a = cfg['d'], cfg['adim']
+    g = torch.Generator().manual_seed(5)
+    mk = lambda *s: torch.randn(*s, generator=g)
+    st = CpuState((mk(n, d), torch.tensor(ei), (mk(a, d) / d ** 0.5).requires_grad_(True), mk(a).requires_grad_(True),
+                   (mk(a, d) / d ** 0.5).requires_grad_(True), mk(a).requires_grad_(True), mk(n, d), mk(n, d),
+                   cfg['heads']))
+    st.alpha = torch.tensor(0.3, requires_grad=True)
+    st.beta = torch.tensor(0.1, requires_grad=True)
+    st.n, st.e = n, ei.shape[1]
+    return st
+
+
+CPU_SCALE = {'c1': 1, 'c2': 1, 'c3': 4, 'c4': 64, 'c5': 256}     # keeps the CPU leg at ~10-30 s
+
+
+def cpu_baseline(name, cfg, steps=1, warmup=1):
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    div = CPU_SCALE[name]
+    st = make_cpu_state(name, cfg, div)
+    for _ in range(warmup):
+        cpu_pass(st)
+    t0 = time.perf_counter()
+    evals = 0
+    for _ in range(steps):
+        evals += cpu_pass(st)
+    dt = time.perf_counter() - t0
+    return {'value': round(evals / dt / div, 4), 'unit': 'evals/s', 'cores': cores, 'kind': 'port',
+            'sample': f'oracle port (torch CPU fp32, upstream-semantics sparse restatement) on the {name} shape scaled '
+                      f'1/{div} (N={st.n}, E\'={st.e}); {steps} x (1 forward eval + 1 adjoint eval); evals/s divided '
+                      f'by {div} (linear-cost extrapolation to the full shape)',
+            'seconds': round(dt, 2)}
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    from grand_b200 import synth
+    cfg = dict(synth.CONFIGS[args.workload])
+    base = cpu_baseline(args.workload, cfg, steps=max(1, args.steps), warmup=max(1, min(args.warmup, 1)))
+    line = {'impl': 'reference', 'metric': 'ODE-func evals/sec (fwd + adjoint bwd)', 'value': base['value'],
+            'unit': 'evals/s', 'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
+            'ms_per_step': round(base['seconds'] / max(1, args.steps) * 1e3, 3), 'higher_is_better': True,
+            'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': {'workload': f"{args.workload}: GRAND-nl ({cfg['desc']}) - CPU port of the reference path"},
+            'cpu_baseline': base,
+            'e2e': {'value': base['value'], 'unit': 'evals/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--workload', default='c4', choices=['c1', 'c2', 'c3', 'c4', 'c5'])
+    ap.add_argument('--no-cpu-baseline', dest='cpu_baseline', action='store_false')
+    args = ap.parse_args()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == '__main__':
+    main()

@@ -54,7 +54,13 @@ def add_remaining_self_loops(edge_index, edge_attr, fill_value, num_nodes):
         loop_w = torch.full((num_nodes,), float(fill_value), dtype=ew.dtype, device=ew.device)
         inv = ~mask
         if bool(inv.any()):
-            loop_w[row[inv]] = ew[inv]
+            # several self-loops on one node: the LAST one wins (CPU index-assignment order), made
+            # deterministic on the GPU with an integer max-reduction over edge ids
+            ids = torch.nonzero(inv, as_tuple=False).reshape(-1)
+            last = torch.full((num_nodes,), -1, dtype=torch.int64, device=ei.device)
+            last.scatter_reduce_(0, row[ids], ids, reduce='amax', include_self=True)
+            has = last >= 0
+            loop_w[has] = ew[last[has]]
         new_w = torch.cat([ew[mask], loop_w])
     return _rebatch(batched, new_index, new_w)
 

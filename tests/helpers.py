@@ -29,12 +29,13 @@ def normalized_graph(n, e, seed):
     return og.reset_graph_data(ei, None, n, 'rw', 1.0)
 
 
-def assert_close(got, ref, rtol, what=''):
-    """|got - ref| <= rtol * (|ref| + max|ref|): elementwise relative with a floor at the tensor's scale"""
+def assert_close(got, ref, rtol, what='', floor=0.0):
+    """|got - ref| <= rtol * (|ref| + max(max|ref|, floor)): elementwise relative with a floor at the tensor's
+    scale; `floor` is for quantities that are mathematically zero (e.g. the K-bias gradient under row softmax)"""
     got = torch.as_tensor(got).detach().double().cpu()
     ref = torch.as_tensor(ref).detach().double().cpu()
     assert got.shape == ref.shape, f'{what}: shape {tuple(got.shape)} vs {tuple(ref.shape)}'
-    scale = float(ref.abs().max()) if ref.numel() else 0.0
+    scale = max(float(ref.abs().max()) if ref.numel() else 0.0, floor)
     err = (got - ref).abs()
     bound = rtol * (ref.abs() + scale) + 1e-30
     worst = float((err / bound).max()) if ref.numel() else 0.0

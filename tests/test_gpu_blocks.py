@@ -68,7 +68,11 @@ def test_constant_block_laplacian_rk4(adjoint, method):
     a, b = t64(0.4).requires_grad_(True), t64(0.2).requires_grad_(True)
     x0 = t64(x)
     f = lambda t, y: funcs.laplacian_f(y, torch.tensor(ei_n), t64(w), a, b, x0)
-    zo = oint.odeint(f, xo, [0., T], method, 1.0)[1]
+    # adjoint gradients are optimise-then-discretise: compare with the oracle's adjoint, not with backprop
+    if adjoint:
+        zo = oint.odeint_adjoint(f, xo, [0., T], method, 1.0, adjoint_params=(a, b))[1]
+    else:
+        zo = oint.odeint(f, xo, [0., T], method, 1.0)[1]
     ro = torch.autograd.grad(zo, (xo, a, b), t64(gout))
     assert_close(z, zo, 1e-4, 'z(T)')
     for g, r, name in zip((gx, ga, gb), ro, ('gx', 'galpha', 'gbeta')):
@@ -99,11 +103,15 @@ def test_attention_block_transformer_function(adjoint):
     x0 = t64(x)
     f = lambda t, y: funcs.transformer_f(y, torch.tensor(ei_n), leaves[3], leaves[4], leaves[5], leaves[6], 4,
                                          leaves[1], leaves[2], x0)
-    zo = oint.odeint(f, leaves[0], [0., T], 'rk4', 1.0)[1]
+    if adjoint:
+        zo = oint.odeint_adjoint(f, leaves[0], [0., T], 'rk4', 1.0, adjoint_params=tuple(leaves[1:]))[1]
+    else:
+        zo = oint.odeint(f, leaves[0], [0., T], 'rk4', 1.0)[1]
     ro = torch.autograd.grad(zo, leaves, t64(gout))
     assert_close(z, zo, 1e-4, 'z(T)')
+    bias_scale = max(float(ro[4].abs().max()), float(ro[6].abs().max()))
     for g, r, name in zip(grads, ro, ('gx', 'galpha', 'gbeta', 'gwq', 'gbq', 'gwk', 'gbk')):
-        assert_close(g, r, 1e-4, name)
+        assert_close(g, r, 1e-4, name, floor=bias_scale if name in ('gbq', 'gbk') else 0.0)
 
 
 def test_attention_block_laplacian_function_trains_block_attention_without_adjoint():
@@ -131,8 +139,9 @@ def test_attention_block_laplacian_function_trains_block_attention_without_adjoi
     zo = oint.odeint(f, leaves[0], [0., T], 'rk4', 1.0)[1]
     ro = torch.autograd.grad(zo, leaves, t64(gout))
     assert_close(z, zo, 1e-4, 'z(T)')
+    bias_scale = max(float(ro[2].abs().max()), float(ro[4].abs().max()))
     for g, r, name in zip(grads, ro, ('gx', 'gwq', 'gbq', 'gwk', 'gbk')):
-        assert_close(g, r, 1e-4, name)
+        assert_close(g, r, 1e-4, name, floor=bias_scale if name in ('gbq', 'gbk') else 0.0)
 
 
 def test_dopri5_block_runs_and_matches_oracle_loosely():
