@@ -68,6 +68,12 @@ SIGNATURES = {
     'gb_edge_softmax_fwd': (C.c_int, [_G, _I32, _P, _I32, _P, _I32, _I32, _I32, _I32, _P, _P, _P, _P, _P, _P]),
     'gb_sddmm': (C.c_int, [_G, _P, _I32, _P, _I32, _I32, _P, _I32, _P, _P]),
     'gb_edge_softmax_bwd': (C.c_int, [_G, _I32, _P, _P, _P, _I32, _P, _P, _P]),
+    'gb_att_fused_supported': (C.c_int, [_P, _I32, _P, _I32, _I32, _I32, _P, _I32, _I32]),
+    'gb_att_fwd_fused': (C.c_int, [_G, _I32, _P, _I32, _P, _I32, _I32, _I32, _I32, _P, _P, _P, _P, _P, _I32,
+                                   _P, _I32, _P, _I32, _P, _I32, _P, _I32, _P, _I32, C.POINTER(GbStage), _P]),
+    'gb_att_bwd_fused_partials': (_SZ, [_G]),
+    'gb_att_bwd_fused': (C.c_int, [_G, _P, _I32, _P, _I32, _I32, _I32, _P, _P, _P, _I32, _P, _I32, _P, _I32, _P,
+                                   _I32, _I32, _P, _P, _P, _I32, _P, _I32, _P, _I32, _P, _P, _P]),
     'gb_edge_score_bwd': (C.c_int, [_G, _P, _P, _I32, _P, _I32, _I32, _I32, _I32, _P, _P, _P, _I32, _P, _I32, _P, _P, _P]),
 }
 

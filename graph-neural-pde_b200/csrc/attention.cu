@@ -15,85 +15,9 @@
 // exactly 0.5).  Raw scores are parked in the output buffer between phases (L1/L2 resident).
 //
 // Roofline: HBM.  Algorithmic bytes per forward launch: 8NA (q,k read once) + 4E (index) + 4EH + 4E.
-#include "vec.cuh"
+#include "att_common.cuh"
 
 namespace gb {
-
-constexpr int kAttThreads = 256;
-
-struct AttArgs {
-  const int32_t* ptr;      // segment pointer (rowptr for norm_idx 0, colptr for 1)
-  const int32_t* idx;      // the other endpoint of slot p in segment order
-  const int32_t* perm;     // nullptr (segment order == CSR order) or tperm (CSC slot -> CSR slot)
-  const float* own;        // matrix indexed by the segment id   (q for norm 0, k for norm 1)
-  int32_t ldown;
-  const float* oth;        // matrix gathered through idx        (k for norm 0, q for norm 1)
-  int32_t ldoth;
-  int32_t n, heads, dk, att_type, long_threshold;
-  const float* edge_w;     // optional [E] (CSR order) multiplier of the raw score
-  const float* kparams;    // [output_var, lengthscale] for exp_kernel
-  float* att;              // [E,H] CSR order
-  float* abar;             // [E]
-  float* prods;            // optional [E,H]
-  const int32_t* long_list;
-};
-
-template <int LPR>
-__device__ __forceinline__ unsigned group_mask() {
-  if (LPR == 32) return 0xffffffffu;
-  const unsigned base = (threadIdx.x & 31) / LPR * LPR;
-  return ((1u << (LPR & 31)) - 1u) << base;
-}
-
-// Sum `v` over the lanes of one head.  LH > 0: heads are aligned blocks of LH (power of two) lanes ->
-// segmented butterfly.  LH == 0: generic layout -> one masked group reduction per head.
-template <int LPR, int LH>
-__device__ __forceinline__ float head_sum(float v, int my_head, int heads, unsigned mask) {
-  if (LH > 0) {
-#pragma unroll
-    for (int o = LH / 2; o > 0; o >>= 1) v += __shfl_xor_sync(mask, v, o, LPR);
-    return v;
-  }
-  float mine = 0.f;
-  for (int h = 0; h < heads; ++h) {
-    float c = my_head == h ? v : 0.f;
-#pragma unroll
-    for (int o = LPR / 2; o > 0; o >>= 1) c += __shfl_xor_sync(mask, c, o, LPR);
-    if (my_head == h) mine = c;
-  }
-  return mine;
-}
-
-// raw score of one (edge, head) from the lane-local chunks; result valid in every lane of the head
-template <int V, int LPR, int LH>
-__device__ __forceinline__ float edge_score(const AttArgs& a, const Vec<V>& qo, const Vec<V>& kg, int my_head,
-                                            unsigned mask, float inv_sqrt_dk, float ov2, float inv_2l2) {
-  if (a.att_type == GB_ATT_SCALED_DOT) {
-    // sum(src * dst_k) / sqrt(dk)
-    return head_sum<LPR, LH>(qo.dot(kg), my_head, a.heads, mask) * inv_sqrt_dk;
-  }
-  if (a.att_type == GB_ATT_EXP_KERNEL) {
-    const Vec<V> df = Vec<V>::map2(qo, kg, [](float p, float q) { return p - q; });
-    const float d2 = head_sum<LPR, LH>(df.dot(df), my_head, a.heads, mask);
-    return ov2 * expf(-d2 * inv_2l2);
-  }
-  Vec<V> u = qo, w = kg;
-  if (a.att_type == GB_ATT_PEARSON) {
-    const float inv_dk = 1.0f / (float)a.dk;
-    const float mu = head_sum<LPR, LH>(qo.sum(), my_head, a.heads, mask) * inv_dk;
-    const float mw = head_sum<LPR, LH>(kg.sum(), my_head, a.heads, mask) * inv_dk;
-    const Vec<V> mu_v = Vec<V>::map2(qo, qo, [mu](float, float) { return mu; });
-    const Vec<V> mw_v = Vec<V>::map2(kg, kg, [mw](float, float) { return mw; });
-    u = Vec<V>::map2(qo, mu_v, [](float p, float q) { return p - q; });
-    w = Vec<V>::map2(kg, mw_v, [](float p, float q) { return p - q; });
-  }
-  // torch.nn.CosineSimilarity(eps=1e-5): (x1 / max(|x1|, eps)) . (x2 / max(|x2|, eps))
-  const float uu = head_sum<LPR, LH>(u.dot(u), my_head, a.heads, mask);
-  const float ww = head_sum<LPR, LH>(w.dot(w), my_head, a.heads, mask);
-  const float uw = head_sum<LPR, LH>(u.dot(w), my_head, a.heads, mask);
-  const float nu = fmaxf(sqrtf(uu), 1e-5f), nw = fmaxf(sqrtf(ww), 1e-5f);
-  return uw / (nu * nw);
-}
 
 // One softmax segment per LPR-lane group (LONG == false) or per CTA (LONG == true).
 template <int V, int LPR, int LH, bool LONG>
@@ -199,19 +123,6 @@ __global__ void __launch_bounds__(kAttThreads) edge_softmax_fwd_kernel(const Att
 // ================================ backward ====================================================
 
 // ---- (1) SDDMM: dabar[s] = alpha * <gout[row_s,:], x[col_s,:]>  over CSR rows ------------------
-struct SddmmArgs {
-  const int32_t* ptr;
-  const int32_t* idx;
-  const float* own;        // gout (indexed by the row)
-  int32_t ldown;
-  const float* oth;        // x (gathered through colidx)
-  int32_t ldoth;
-  int32_t n, dv, long_threshold, accumulate;
-  const float* alpha_train;
-  int32_t alpha_sigmoid;
-  float* dabar;
-  const int32_t* long_list;
-};
 
 template <int V, int LPR, int CPL, bool LONG>
 __global__ void __launch_bounds__(kAttThreads) sddmm_kernel(const SddmmArgs a) {
@@ -270,17 +181,6 @@ __global__ void __launch_bounds__(kAttThreads) sddmm_kernel(const SddmmArgs a) {
 }
 
 // ---- (2) softmax backward over the softmax segments --------------------------------------------
-struct SmBwdArgs {
-  const int32_t* ptr;
-  const int32_t* perm;     // nullptr or tperm
-  const float* att;        // [E,H]
-  const float* dabar;      // optional [E]   dL/d(mean_h att)
-  const float* datt;       // optional [E,H] dL/d att (CSR order), added to dabar/H
-  const float* edge_w;     // optional
-  float* ds;               // [E,H] dL/d(raw score)
-  int32_t n, heads, long_threshold;
-  const int32_t* long_list;
-};
 
 __device__ __forceinline__ float sm_da(const SmBwdArgs& a, int slot, int h, float inv_h) {
   float v = 0.f;
@@ -346,19 +246,6 @@ __global__ void __launch_bounds__(256) softmax_bwd_long_kernel(const SmBwdArgs a
 
 // ---- (3) multi-head SpMM: out[seg, c] = scale * sum_p ds[slot_p, head(c)] * src[idx_p, c] -------
 // dq over CSR rows (src = k, perm = nullptr); dk over CSC columns (src = q, perm = tperm).
-struct MhArgs {
-  const int32_t* ptr;
-  const int32_t* idx;
-  const int32_t* perm;
-  const float* ds;         // [E,H] CSR order
-  const float* src;
-  int32_t lds;
-  float* out;
-  int32_t ldo;
-  int32_t n, heads, dk, long_threshold;
-  float scale;
-  const int32_t* long_list;
-};
 
 template <int V, int LPR, bool LONG>
 __global__ void __launch_bounds__(kAttThreads) mh_spmm_kernel(const MhArgs a) {
@@ -444,7 +331,6 @@ int att_vec(const float* a, int lda, const float* b, int ldb, int width, int dk)
   return v;
 }
 
-inline int lpr_for(int chunks) { return chunks <= 8 ? 8 : (chunks <= 16 ? 16 : 32); }
 inline bool is_pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
 
 template <int V, int LPR, int LH>
@@ -524,6 +410,64 @@ int dispatch_mh(const MhArgs& a, int n_long, int kid, cudaStream_t stream) {
 }
 
 }  // namespace
+
+
+namespace gb {
+
+int att_long_fwd(const AttArgs& a, int v, int n_long, cudaStream_t stream) {
+  if (n_long <= 0) return GB_OK;
+  const int chunks = a.heads * a.dk / v;
+  LaunchScope ls(K_EDGE_SOFTMAX_FWD_LONG, stream);
+#define GB_ATT_LONG(VV, LL) edge_softmax_fwd_kernel<VV, LL, 0, true><<<n_long, kAttThreads, 0, stream>>>(a)
+  const int lpr = lpr_for(chunks);
+  if (v == 4) { if (lpr == 8) GB_ATT_LONG(4, 8); else if (lpr == 16) GB_ATT_LONG(4, 16); else GB_ATT_LONG(4, 32); }
+  else if (v == 2) { if (lpr == 8) GB_ATT_LONG(2, 8); else if (lpr == 16) GB_ATT_LONG(2, 16); else GB_ATT_LONG(2, 32); }
+  else { if (lpr == 8) GB_ATT_LONG(1, 8); else if (lpr == 16) GB_ATT_LONG(1, 16); else GB_ATT_LONG(1, 32); }
+#undef GB_ATT_LONG
+  return check_launch("att_long_fwd");
+}
+
+template <int V>
+static int sddmm_long_v(const SddmmArgs& a, int n_long, cudaStream_t stream) {
+  const RowShape rs = row_shape(a.dv);
+  if (rs.lpr == 8 && rs.cpl == 1) sddmm_kernel<V, 8, 1, true><<<n_long, kAttThreads, 0, stream>>>(a);
+  else if (rs.lpr == 16) sddmm_kernel<V, 16, 1, true><<<n_long, kAttThreads, 0, stream>>>(a);
+  else if (rs.lpr == 8 && rs.cpl == 3) sddmm_kernel<V, 8, 3, true><<<n_long, kAttThreads, 0, stream>>>(a);
+  else if (rs.cpl == 1) sddmm_kernel<V, 32, 1, true><<<n_long, kAttThreads, 0, stream>>>(a);
+  else if (rs.cpl == 2) sddmm_kernel<V, 32, 2, true><<<n_long, kAttThreads, 0, stream>>>(a);
+  else if (rs.cpl == 3) sddmm_kernel<V, 32, 3, true><<<n_long, kAttThreads, 0, stream>>>(a);
+  else sddmm_kernel<V, 32, 4, true><<<n_long, kAttThreads, 0, stream>>>(a);
+  return check_launch("sddmm_long");
+}
+
+int sddmm_long(const SddmmArgs& a, int v, int n_long, cudaStream_t stream) {
+  if (n_long <= 0) return GB_OK;
+  LaunchScope ls(K_SDDMM, stream);
+  if (v == 4) return sddmm_long_v<4>(a, n_long, stream);
+  if (v == 2) return sddmm_long_v<2>(a, n_long, stream);
+  return sddmm_long_v<1>(a, n_long, stream);
+}
+
+int softmax_bwd_long(const SmBwdArgs& a, int n_long, cudaStream_t stream) {
+  if (n_long <= 0) return GB_OK;
+  LaunchScope ls(K_EDGE_SOFTMAX_BWD, stream);
+  softmax_bwd_long_kernel<<<n_long, 256, 0, stream>>>(a);
+  return check_launch("softmax_bwd_long");
+}
+
+int mh_spmm_long(const MhArgs& a, int v, int n_long, int kernel_id, cudaStream_t stream) {
+  if (n_long <= 0) return GB_OK;
+  LaunchScope ls(kernel_id, stream);
+  const int lpr = lpr_for(a.heads * a.dk / v);
+#define GB_MH_LONG(VV, LL) mh_spmm_kernel<VV, LL, true><<<n_long, kAttThreads, 0, stream>>>(a)
+  if (v == 4) { if (lpr == 8) GB_MH_LONG(4, 8); else if (lpr == 16) GB_MH_LONG(4, 16); else GB_MH_LONG(4, 32); }
+  else if (v == 2) { if (lpr == 8) GB_MH_LONG(2, 8); else if (lpr == 16) GB_MH_LONG(2, 16); else GB_MH_LONG(2, 32); }
+  else { if (lpr == 8) GB_MH_LONG(1, 8); else if (lpr == 16) GB_MH_LONG(1, 16); else GB_MH_LONG(1, 32); }
+#undef GB_MH_LONG
+  return check_launch("mh_spmm_long");
+}
+
+}  // namespace gb
 
 extern "C" {
 

@@ -16,91 +16,9 @@
 // shared memory in a fixed order.  No atomics anywhere: results are bit-reproducible run to run.
 //
 // Roofline: HBM.  Algorithmic bytes per forward launch: 8E + 12Nd + 4N.
-#include "vec.cuh"
+#include "spmm_common.cuh"
 
 namespace gb {
-
-constexpr int kSpmmThreads = 256;
-constexpr int kRowTiles = 4;   // consecutive row tiles per CTA
-constexpr int kMidFloats = 2 * 1024 * 2;   // level-1 reduction results: 2 x 1024 doubles
-
-struct SpmmArgs {
-  const int32_t* ptr;
-  const int32_t* idx;
-  const int32_t* perm;     // nullptr: vals[p]; else vals[perm[p]]
-  const float* vals;
-  int32_t n, dv, long_threshold;
-  const float* src;        // gathered matrix; also the "- self" term
-  int32_t lds;
-  const float* alpha_train;
-  int32_t alpha_sigmoid;
-  // forward epilogue
-  const float* x0;
-  int32_t ldx0;
-  const float* beta_train;
-  float* out;
-  int32_t ldo;
-  int32_t has_stage;
-  gb_stage stage;
-  // backward epilogue
-  const float* x;
-  int32_t ldx;
-  int32_t accumulate;
-  float* partials;         // [blocks][2]
-  const int32_t* long_list;
-  int32_t partial_base;    // first partial slot of this launch
-};
-
-__device__ __forceinline__ float load_alpha(const SpmmArgs& a) {
-  const float v = __ldg(a.alpha_train);
-  return a.alpha_sigmoid ? sigmoidf_(v) : v;
-}
-
-// epilogue of one vector chunk of one row
-template <int V, bool BWD>
-__device__ __forceinline__ void row_epilogue(const SpmmArgs& a, int row, int col, const Vec<V>& acc, float alpha,
-                                             float beta, float& s1, float& s2) {
-  const Vec<V> self = Vec<V>::load_stream(a.src + (size_t)row * a.lds + col);
-  Vec<V> t = Vec<V>::map2(acc, self, [](float p, float q) { return p - q; });
-  if (!BWD) {
-    Vec<V> f = Vec<V>::map2(t, t, [alpha](float p, float) { return alpha * p; });
-    if (a.x0 != nullptr) {
-      const Vec<V> s = Vec<V>::load_stream(a.x0 + (size_t)row * a.ldx0 + col);
-      f = Vec<V>::map2(f, s, [beta](float p, float q) { return fmaf(beta, q, p); });
-    }
-    if (!a.has_stage || a.stage.write_f) f.store_stream(a.out + (size_t)row * a.ldo + col);
-    if (a.has_stage) {
-      const size_t off = (size_t)row * a.stage.ld + col;
-      Vec<V> y = Vec<V>::load_stream(a.stage.y + off);
-      for (int j = 0; j < a.stage.n_prev; ++j) {
-        const float c = a.stage.c[j];
-        if (c != 0.f) y.fma(c, Vec<V>::load_stream(a.stage.k[j] + off));
-      }
-      y.fma(a.stage.c[a.stage.n_prev], f);
-      y.store_stream(a.stage.ynext + off);
-    }
-  } else {
-    float* dxp = a.out + (size_t)row * a.ldo + col;
-    Vec<V> dx = Vec<V>::map2(t, t, [alpha](float p, float) { return alpha * p; });
-    if (a.accumulate) {
-      const Vec<V> old = Vec<V>::load_rw(dxp);
-      dx = Vec<V>::map2(dx, old, [](float p, float q) { return p + q; });
-    }
-    dx.store_stream(dxp);
-    if (a.x != nullptr) s1 += Vec<V>::load_stream(a.x + (size_t)row * a.ldx + col).dot(t);
-    if (a.x0 != nullptr) s2 += Vec<V>::load_stream(a.x0 + (size_t)row * a.ldx0 + col).dot(self);
-  }
-}
-
-__device__ __forceinline__ void write_partials(const SpmmArgs& a, float s1, float s2, int slot) {
-  __shared__ float red[64];
-  const float r1 = block_sum(s1, red);
-  const float r2 = block_sum(s2, red + 32);
-  if (threadIdx.x == 0) {
-    a.partials[2 * (size_t)slot] = r1;
-    a.partials[2 * (size_t)slot + 1] = r2;
-  }
-}
 
 template <int V, int LPR, int CPL, bool BWD>
 __global__ void __launch_bounds__(kSpmmThreads) spmm_rows(const SpmmArgs a) {
@@ -270,6 +188,24 @@ __global__ void __launch_bounds__(256) reduce_partials_l2(const double* __restri
 
 }  // namespace gb
 
+namespace gb {
+
+// partials = [kMidFloats floats of level-1 doubles][slots][2]; fixed-order two-level reduction -> dparams[2]
+int reduce_partials_launch(float* partials, int slots, const float* alpha_train, int alpha_sigmoid, float* dparams,
+                           cudaStream_t stream) {
+  double* mid = reinterpret_cast<double*>(partials);
+  int l1_blocks = min_int(1024, (slots + 255) / 256);
+  if (l1_blocks < 1) l1_blocks = 1;
+  const int per_block = (slots + l1_blocks - 1) / l1_blocks;
+  LaunchScope ls(K_REDUCE_PARTIALS, stream);
+  reduce_partials_l1<<<l1_blocks, 256, 0, stream>>>(partials + kMidFloats, slots, per_block, mid);
+  reduce_partials_l2<<<1, 256, 0, stream>>>(mid, l1_blocks, alpha_train, alpha_sigmoid, dparams);
+  return check_launch("reduce_partials");
+}
+
+}  // namespace gb
+
+
 using namespace gb;
 
 namespace {
@@ -350,6 +286,32 @@ int check_graph(const gb_graph* g, const char* who) {
 
 }  // namespace
 
+
+namespace gb {
+
+template <int V, bool BWD>
+static int spmm_long_v(const SpmmArgs& a, int n_long, cudaStream_t stream) {
+  const RowShape rs = row_shape(a.dv);
+  if (rs.lpr == 8 && rs.cpl == 1) spmm_long<V, 8, 1, BWD><<<n_long, kSpmmThreads, 0, stream>>>(a);
+  else if (rs.lpr == 16) spmm_long<V, 16, 1, BWD><<<n_long, kSpmmThreads, 0, stream>>>(a);
+  else if (rs.lpr == 8 && rs.cpl == 3) spmm_long<V, 8, 3, BWD><<<n_long, kSpmmThreads, 0, stream>>>(a);
+  else if (rs.cpl == 1) spmm_long<V, 32, 1, BWD><<<n_long, kSpmmThreads, 0, stream>>>(a);
+  else if (rs.cpl == 2) spmm_long<V, 32, 2, BWD><<<n_long, kSpmmThreads, 0, stream>>>(a);
+  else if (rs.cpl == 3) spmm_long<V, 32, 3, BWD><<<n_long, kSpmmThreads, 0, stream>>>(a);
+  else spmm_long<V, 32, 4, BWD><<<n_long, kSpmmThreads, 0, stream>>>(a);
+  return check_launch("spmm_long_only");
+}
+
+int spmm_long_only(const SpmmArgs& a, int v, bool bwd, int n_long, cudaStream_t stream) {
+  if (n_long <= 0) return GB_OK;
+  LaunchScope ls(bwd ? K_SPMM_BWD_LONG : K_SPMM_FWD_LONG, stream);
+  if (v == 4) return bwd ? spmm_long_v<4, true>(a, n_long, stream) : spmm_long_v<4, false>(a, n_long, stream);
+  if (v == 2) return bwd ? spmm_long_v<2, true>(a, n_long, stream) : spmm_long_v<2, false>(a, n_long, stream);
+  return bwd ? spmm_long_v<1, true>(a, n_long, stream) : spmm_long_v<1, false>(a, n_long, stream);
+}
+
+}  // namespace gb
+
 extern "C" {
 
 int gb_spmm_fwd(const gb_graph* g, const float* vals, const float* x, int32_t ldx, const float* x0, int32_t ldx0,
@@ -419,15 +381,7 @@ int gb_spmm_bwd(const gb_graph* g, const float* vals, const float* gout, int32_t
   a.long_list = g->long_cols;
   int slots = 0;
   if (int rc = run_spmm<true>(a, d, v, n_long, stream, &slots)) return rc;
-  if (dparams) {
-    int l1_blocks = min_int(1024, (slots + 255) / 256);
-    if (l1_blocks < 1) l1_blocks = 1;
-    const int per_block = (slots + l1_blocks - 1) / l1_blocks;
-    LaunchScope ls(K_REDUCE_PARTIALS, stream);
-    reduce_partials_l1<<<l1_blocks, 256, 0, stream>>>(a.partials, slots, per_block, mid);
-    reduce_partials_l2<<<1, 256, 0, stream>>>(mid, l1_blocks, alpha_train, alpha_sigmoid, dparams);
-    return check_launch("reduce_partials");
-  }
+  if (dparams) return reduce_partials_launch(partials, slots, alpha_train, alpha_sigmoid, dparams, stream);
   return GB_OK;
 }
 

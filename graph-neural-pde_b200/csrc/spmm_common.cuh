@@ -1,0 +1,94 @@
+// spmm_common.cuh - argument block and fused diffusion epilogue shared by spmm.cu and fused_att.cu
+#pragma once
+#include "vec.cuh"
+
+namespace gb {
+
+constexpr int kSpmmThreads = 256;
+constexpr int kRowTiles = 4;   // consecutive row tiles per CTA
+constexpr int kMidFloats = 2 * 1024 * 2;   // level-1 reduction results: 2 x 1024 doubles
+
+struct SpmmArgs {
+  const int32_t* ptr;
+  const int32_t* idx;
+  const int32_t* perm;     // nullptr: vals[p]; else vals[perm[p]]
+  const float* vals;
+  int32_t n, dv, long_threshold;
+  const float* src;        // gathered matrix; also the "- self" term
+  int32_t lds;
+  const float* alpha_train;
+  int32_t alpha_sigmoid;
+  // forward epilogue
+  const float* x0;
+  int32_t ldx0;
+  const float* beta_train;
+  float* out;
+  int32_t ldo;
+  int32_t has_stage;
+  gb_stage stage;
+  // backward epilogue
+  const float* x;
+  int32_t ldx;
+  int32_t accumulate;
+  float* partials;         // [blocks][2]
+  const int32_t* long_list;
+  int32_t partial_base;    // first partial slot of this launch
+};
+
+__device__ __forceinline__ float load_alpha(const SpmmArgs& a) {
+  const float v = __ldg(a.alpha_train);
+  return a.alpha_sigmoid ? sigmoidf_(v) : v;
+}
+
+// epilogue of one vector chunk of one row
+template <int V, bool BWD>
+__device__ __forceinline__ void row_epilogue(const SpmmArgs& a, int row, int col, const Vec<V>& acc, float alpha,
+                                             float beta, float& s1, float& s2) {
+  const Vec<V> self = Vec<V>::load_stream(a.src + (size_t)row * a.lds + col);
+  Vec<V> t = Vec<V>::map2(acc, self, [](float p, float q) { return p - q; });
+  if (!BWD) {
+    Vec<V> f = Vec<V>::map2(t, t, [alpha](float p, float) { return alpha * p; });
+    if (a.x0 != nullptr) {
+      const Vec<V> s = Vec<V>::load_stream(a.x0 + (size_t)row * a.ldx0 + col);
+      f = Vec<V>::map2(f, s, [beta](float p, float q) { return fmaf(beta, q, p); });
+    }
+    if (!a.has_stage || a.stage.write_f) f.store_stream(a.out + (size_t)row * a.ldo + col);
+    if (a.has_stage) {
+      const size_t off = (size_t)row * a.stage.ld + col;
+      Vec<V> y = Vec<V>::load_stream(a.stage.y + off);
+      for (int j = 0; j < a.stage.n_prev; ++j) {
+        const float c = a.stage.c[j];
+        if (c != 0.f) y.fma(c, Vec<V>::load_stream(a.stage.k[j] + off));
+      }
+      y.fma(a.stage.c[a.stage.n_prev], f);
+      y.store_stream(a.stage.ynext + off);
+    }
+  } else {
+    float* dxp = a.out + (size_t)row * a.ldo + col;
+    Vec<V> dx = Vec<V>::map2(t, t, [alpha](float p, float) { return alpha * p; });
+    if (a.accumulate) {
+      const Vec<V> old = Vec<V>::load_rw(dxp);
+      dx = Vec<V>::map2(dx, old, [](float p, float q) { return p + q; });
+    }
+    dx.store_stream(dxp);
+    if (a.x != nullptr) s1 += Vec<V>::load_stream(a.x + (size_t)row * a.ldx + col).dot(t);
+    if (a.x0 != nullptr) s2 += Vec<V>::load_stream(a.x0 + (size_t)row * a.ldx0 + col).dot(self);
+  }
+}
+
+static __device__ __forceinline__ void write_partials(const SpmmArgs& a, float s1, float s2, int slot) {
+  __shared__ float red[64];
+  const float r1 = block_sum(s1, red);
+  const float r2 = block_sum(s2, red + 32);
+  if (threadIdx.x == 0) {
+    a.partials[2 * (size_t)slot] = r1;
+    a.partials[2 * (size_t)slot + 1] = r2;
+  }
+}
+
+int reduce_partials_launch(float* partials, int slots, const float* alpha_train, int alpha_sigmoid, float* dparams,
+                           cudaStream_t stream);
+// launches only the CTA-per-row kernel over `a.long_list` (used by fused_att.cu); defined in spmm.cu
+int spmm_long_only(const SpmmArgs& a, int v, bool bwd, int n_long, cudaStream_t stream);
+
+}  // namespace gb

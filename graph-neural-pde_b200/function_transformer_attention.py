@@ -20,7 +20,7 @@ from torch import nn
 from .base_classes import ODEFunc
 from . import _lib
 from . import plan as _plan
-from .ops import QKProjFn, EdgeSoftmaxFn, DiffusionFn, ToCooOrderFn
+from .ops import QKProjFn, EdgeSoftmaxFn, DiffusionFn, ToCooOrderFn, FusedTransformerFn, fused_transformer_supported
 
 
 class SpGraphTransAttentionLayer(nn.Module):
@@ -85,6 +85,20 @@ class SpGraphTransAttentionLayer(nn.Module):
                                       'function, function_transformer_attention.py:264); softmax only')
         return _lib.GB_ATT[att_type]
 
+    def qk_weights(self):
+        """[Wq;Wk], [bq;bk] concatenated once per parameter version (parameters change once per
+        optimiser step, evaluations happen NFE times per step)"""
+        key = (self.Q.weight._version, self.Q.bias._version, self.K.weight._version, self.K.bias._version,
+               self.Q.weight.data_ptr(), self.K.weight.data_ptr())
+        hit = getattr(self, '_wb_cache', None)
+        if hit is None or hit[0] != key:
+            with torch.no_grad():
+                w = torch.cat([self.Q.weight, self.K.weight], dim=0).contiguous()
+                b = torch.cat([self.Q.bias, self.K.bias], dim=0).contiguous()
+            hit = (key, (w, b))
+            self._wb_cache = hit
+        return hit[1]
+
     def attention_csr(self, x2, plan):
         """(att [E,H], abar [E], prods [E,H]) in CSR-slot order for an un-batched state x2 [N,d]"""
         att_type = self._check_supported()
@@ -133,11 +147,23 @@ class ODEFuncTransformerAtt(ODEFunc):
                                       '(function_transformer_attention.py:23-32,49-50) and not implemented')
         x2 = self._as_2d(x)
         plan = self._plan(x2.shape[0])
-        _att, abar, _prods = self.multihead_att_layer.attention_csr(x2, plan)
         source = bool(self.opt['add_source'])
         x0 = self._as_2d(self.x0) if (source and self.x0 is not None) else None
-        f = DiffusionFn.apply(x2, abar, self.alpha_train, self.beta_train if x0 is not None else None, x0, plan,
-                              not self.opt['no_alpha_sigmoid'], None)
+        L = self.multihead_att_layer
+        att_type = L._check_supported()
+        edge_w = L.edge_weights if self.opt.get('reweight_attention', False) else None
+        if fused_transformer_supported(plan, x2, L.h, L.attention_dim, att_type, int(self.opt['attention_norm_idx']),
+                                       edge_w):
+            kparams = None
+            if att_type == _lib.GB_ATT['exp_kernel']:
+                kparams = torch.cat([L.output_var.detach(), L.lengthscale.detach()]).to(torch.float32).contiguous()
+            f = FusedTransformerFn.apply(x2, L.Q.weight, L.Q.bias, L.K.weight, L.K.bias, self.alpha_train,
+                                         self.beta_train if x0 is not None else None, x0, plan, L.h, att_type,
+                                         not self.opt['no_alpha_sigmoid'], kparams, L.qk_weights(), None)
+        else:
+            _att, abar, _prods = L.attention_csr(x2, plan)
+            f = DiffusionFn.apply(x2, abar, self.alpha_train, self.beta_train if x0 is not None else None, x0, plan,
+                                  not self.opt['no_alpha_sigmoid'], None)
         return f.view_as(x)
 
     def __repr__(self):

@@ -77,9 +77,17 @@ class EdgeSoftmaxFn(torch.autograd.Function):
         att = torch.empty(plan.e, heads, dtype=torch.float32, device=qk.device)
         abar = torch.empty(plan.e, dtype=torch.float32, device=qk.device)
         prods = torch.empty(plan.e, heads, dtype=torch.float32, device=qk.device)
-        _lib.check(lib.gb_edge_softmax_fwd(plan.c, norm_idx, qk.data_ptr(), a2, qk.data_ptr() + 4 * a, a2, heads, dk,
-                                           att_type, _lib.ptr(edge_w), _lib.ptr(kparams), att.data_ptr(),
-                                           abar.data_ptr(), prods.data_ptr(), _lib.stream()), 'gb_edge_softmax_fwd')
+        if plan.long_threshold == 256 and lib.gb_att_fused_supported(qk.data_ptr(), a2, qk.data_ptr() + 4 * a, a2,
+                                                                     heads, dk, None, 0, 0):
+            _lib.check(lib.gb_att_fwd_fused(plan.c, norm_idx, qk.data_ptr(), a2, qk.data_ptr() + 4 * a, a2, heads, dk,
+                                            att_type, _lib.ptr(edge_w), _lib.ptr(kparams), att.data_ptr(),
+                                            abar.data_ptr(), prods.data_ptr(), 1, None, 0, None, 0, None, 0, None, 0,
+                                            None, 0, None, _lib.stream()), 'gb_att_fwd_fused')
+        else:
+            _lib.check(lib.gb_edge_softmax_fwd(plan.c, norm_idx, qk.data_ptr(), a2, qk.data_ptr() + 4 * a, a2, heads,
+                                               dk, att_type, _lib.ptr(edge_w), _lib.ptr(kparams), att.data_ptr(),
+                                               abar.data_ptr(), prods.data_ptr(), _lib.stream()),
+                       'gb_edge_softmax_fwd')
         ctx.save_for_backward(qk, att)
         ctx.plan, ctx.heads, ctx.dk, ctx.att_type, ctx.norm_idx, ctx.edge_w, ctx.kparams = \
             plan, heads, dk, att_type, norm_idx, edge_w, kparams
@@ -162,6 +170,104 @@ class DiffusionFn(torch.autograd.Function):
         if ctx.needs_input_grad[3] and ctx.source:
             dbeta = dparams[1].reshape(())
         return (dx if ctx.needs_input_grad[0] else None), dvals, dalpha, dbeta, None, None, None, None
+
+
+def fused_transformer_supported(plan, x, heads, adim, att_type, norm_idx, edge_w):
+    """can FusedTransformerFn take this evaluation? (else the composite QKProj/EdgeSoftmax/Diffusion path runs)"""
+    if norm_idx != 0 or edge_w is not None or plan.long_threshold != 256 or adim % heads != 0:
+        return False
+    if x.dtype != torch.float32 or not x.is_cuda:
+        return False
+    n, d = x.shape
+    # q|k live in one [N, 2A] buffer: row stride 2A floats, k offset A floats
+    fake = 256                                       # any 16-byte aligned address: only alignment is inspected
+    return bool(_lib.load().gb_att_fused_supported(fake, 2 * adim, fake + 4 * adim, 2 * adim, heads, adim // heads,
+                                                   x.data_ptr() if x.is_contiguous() else fake, d, d))
+
+
+class FusedTransformerFn(torch.autograd.Function):
+    """One GRAND-nl evaluation (ODEFuncTransformerAtt.forward, function_transformer_attention.py:44-59):
+    projection GEMM + ONE fused graph kernel (score, segment softmax, head mean, SpMM, epilogue).
+    The VJP is projection-GEMM transposes + two fused graph kernels (rows: SDDMM, softmax backward,
+    dq; columns: transpose SpMM, dk, dalpha/dbeta partial sums)."""
+
+    @staticmethod
+    def forward(ctx, x, wq, bq, wk, bk, alpha_train, beta_train, x0, plan, heads, att_type, alpha_sigmoid, kparams,
+                wb_cache, stage):
+        lib = _lib.load()
+        _lib.require_cuda(x, wq, bq, wk, bk, alpha_train, beta_train, x0)
+        x = _f32c(x)
+        n, d = x.shape
+        a = wq.shape[0]
+        dk = a // heads
+        if wb_cache is not None:
+            w, b = wb_cache
+        else:
+            w = torch.cat([wq, wk], dim=0).contiguous()
+            b = torch.cat([bq, bk], dim=0).contiguous()
+        source = beta_train is not None and x0 is not None
+        if source:
+            x0 = _f32c(x0)
+        qk = torch.empty(n, 2 * a, dtype=torch.float32, device=x.device)
+        _lib.check(lib.gb_linear_fwd(x.data_ptr(), d, n, d, w.data_ptr(), b.data_ptr(), 2 * a, qk.data_ptr(),
+                                     2 * a, _lib.stream()), 'gb_linear_fwd')
+        store = any(ctx.needs_input_grad[:7])
+        need_buf = store or plan.long_rows.numel() > 0
+        att = torch.empty(plan.e, heads, dtype=torch.float32, device=x.device) if need_buf else None
+        abar = torch.empty(plan.e, dtype=torch.float32, device=x.device) if need_buf else None
+        out = torch.empty_like(x)
+        _lib.check(lib.gb_att_fwd_fused(plan.c, 0, qk.data_ptr(), 2 * a, qk.data_ptr() + 4 * a, 2 * a, heads, dk,
+                                        att_type, None, _lib.ptr(kparams), _lib.ptr(att), _lib.ptr(abar), None,
+                                        int(store), x.data_ptr(), d, _lib.ptr(x0) if source else None, d,
+                                        alpha_train.data_ptr(), int(alpha_sigmoid),
+                                        beta_train.data_ptr() if source else None, d, out.data_ptr(), d, stage,
+                                        _lib.stream()), 'gb_att_fwd_fused')
+        if store:
+            ctx.save_for_backward(x, w, qk, att, abar, alpha_train, x0 if source else None)
+        ctx.plan, ctx.heads, ctx.dk, ctx.att_type, ctx.alpha_sigmoid, ctx.source = \
+            plan, heads, dk, att_type, int(alpha_sigmoid), source
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gout):
+        lib = _lib.load()
+        if ctx.att_type != _lib.GB_ATT['scaled_dot']:
+            raise NotImplementedError('backward of attention types other than scaled_dot is not implemented')
+        x, w, qk, att, abar, alpha_train, x0 = ctx.saved_tensors
+        plan, heads, dk = ctx.plan, ctx.heads, ctx.dk
+        n, d = x.shape
+        a2 = qk.shape[1]
+        a = a2 // 2
+        gout = _f32c(gout)
+        dev = x.device
+        ds = torch.empty(plan.e, heads, dtype=torch.float32, device=dev)
+        dabar = torch.empty(plan.e, dtype=torch.float32, device=dev) if plan.long_rows.numel() > 0 else None
+        dqk = torch.empty_like(qk)
+        dx = torch.empty_like(x)
+        want_params = ctx.needs_input_grad[5] or ctx.needs_input_grad[6]
+        partials = torch.empty(int(lib.gb_att_bwd_fused_partials(plan.c)), dtype=torch.float32, device=dev)
+        dparams = torch.empty(2, dtype=torch.float32, device=dev) if want_params else None
+        _lib.check(lib.gb_att_bwd_fused(plan.c, qk.data_ptr(), a2, qk.data_ptr() + 4 * a, a2, heads, dk,
+                                        att.data_ptr(), abar.data_ptr(), gout.data_ptr(), d, x.data_ptr(), d,
+                                        _lib.ptr(x0), d, alpha_train.data_ptr(), ctx.alpha_sigmoid, d, ds.data_ptr(),
+                                        _lib.ptr(dabar), dqk.data_ptr(), a2, dqk.data_ptr() + 4 * a, a2,
+                                        dx.data_ptr(), d, partials.data_ptr(), _lib.ptr(dparams), _lib.stream()),
+                   'gb_att_bwd_fused')
+        # dense tail: dx += [dq|dk] [Wq;Wk] ; d[Wq;Wk] = [dq|dk]^T x ; d[bq;bk] = column sums
+        _lib.check(lib.gb_linear_bwd_x(dqk.data_ptr(), a2, n, a2, w.data_ptr(), d, dx.data_ptr(), d, 1,
+                                       _lib.stream()), 'gb_linear_bwd_x')
+        dwq = dbq = dwk = dbk = None
+        if any(ctx.needs_input_grad[1:5]):
+            dw = torch.empty(a2, d, dtype=torch.float32, device=dev)
+            db = torch.empty(a2, dtype=torch.float32, device=dev)
+            ws = torch.empty(int(lib.gb_linear_bwd_w_workspace_bytes(n, d, a2)), dtype=torch.uint8, device=dev)
+            _lib.check(lib.gb_linear_bwd_w(dqk.data_ptr(), a2, x.data_ptr(), d, n, d, a2, dw.data_ptr(), db.data_ptr(),
+                                           ws.data_ptr(), ws.numel(), _lib.stream()), 'gb_linear_bwd_w')
+            dwq, dbq, dwk, dbk = dw[:a], db[:a], dw[a:], db[a:]
+        dalpha = dparams[0].reshape(alpha_train.shape) if ctx.needs_input_grad[5] else None
+        dbeta = dparams[1].reshape(()) if (ctx.needs_input_grad[6] and ctx.source) else None
+        return (dx if ctx.needs_input_grad[0] else None, dwq, dbq, dwk, dbk, dalpha, dbeta) + (None,) * 8
 
 
 class HeadMeanToCsrFn(torch.autograd.Function):

@@ -11,7 +11,7 @@ import torch
 
 from . import _lib
 
-LONG_THRESHOLD = 2048      # segments longer than this get one CTA each instead of a sub-warp group
+LONG_THRESHOLD = 256       # segments longer than this get one CTA each instead of a sub-warp group
 
 
 def _as_2xE(edge_index):

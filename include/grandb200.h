@@ -202,6 +202,38 @@ int gb_edge_score_bwd(const gb_graph* g, const float* ds, const float* q, int32_
                       const float* prods, float* dq, int32_t lddq, float* dk_out, int32_t lddk,
                       float* dkparams_partials, float* dkparams, void* stream);
 
+/* ---- fused GRAND-nl evaluation (warp-per-row kernels, csrc/fused_att.cu) -------------------------
+ * gb_att_fused_supported: 1 when the shapes/alignment fit the fused kernels (heads a power of two <= 8,
+ * dk/4 a power of two, attention_dim <= 128, 16-byte aligned rows, d % 4 == 0, d <= 512; pass x == NULL to
+ * ask about the attention-only mode).  The plan's long_threshold must be 256.
+ *
+ * gb_att_fwd_fused: score + segment softmax + head mean (+ when x != NULL, attention_norm_idx 0: the SpMM
+ * and the diffusion epilogue of gb_spmm_fwd with the freshly computed abar) in ONE kernel.
+ *   store != 0 : att [E,H] / abar [E] are written for every edge (a backward pass will follow)
+ *   store == 0 : they are only used as scratch for segments longer than 256 edges (may be NULL if the
+ *                plan has none); x == NULL requires store semantics (att and abar are the outputs). */
+int gb_att_fused_supported(const float* q, int32_t ldq, const float* k, int32_t ldk, int32_t heads, int32_t dk,
+                           const float* x, int32_t ldx, int32_t d);
+int gb_att_fwd_fused(const gb_graph* g, int32_t norm_idx, const float* q, int32_t ldq, const float* k, int32_t ldk,
+                     int32_t heads, int32_t dk, int32_t att_type, const float* edge_w, const float* kparams,
+                     float* att, float* abar, float* prods, int32_t store,
+                     const float* x, int32_t ldx, const float* x0, int32_t ldx0, const float* alpha_train,
+                     int32_t alpha_sigmoid, const float* beta_train, int32_t d, float* out, int32_t ldo,
+                     const gb_stage* stage, void* stream);
+/* VJP of the fused evaluation (scaled_dot, attention_norm_idx 0) given gout = dL/df:
+ *   rows   : dabar = alpha <g_i, x[col]>, softmax backward -> ds [E,H], dq [N,A]
+ *   columns: dx = alpha (A^T g - g) (direct part only; add dq Wq + dk Wk with gb_linear_bwd_x),
+ *            dk [N,A], dparams = {dalpha_train, dbeta_train} (fixed-order reductions)
+ * ds [E,H] and dabar_scratch [E] (needed only when the plan has long rows) are caller scratch;
+ * partials needs gb_att_bwd_fused_partials(g) floats, 8-byte aligned. */
+size_t gb_att_bwd_fused_partials(const gb_graph* g);
+int gb_att_bwd_fused(const gb_graph* g, const float* q, int32_t ldq, const float* k, int32_t ldk, int32_t heads,
+                     int32_t dk, const float* att, const float* abar, const float* gout, int32_t ldg,
+                     const float* x, int32_t ldx, const float* x0, int32_t ldx0, const float* alpha_train,
+                     int32_t alpha_sigmoid, int32_t d, float* ds, float* dabar_scratch, float* dq, int32_t lddq,
+                     float* dk_out, int32_t lddk, float* dx, int32_t lddx, float* partials, float* dparams,
+                     void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -187,3 +187,45 @@ def test_unsupported_options_raise():
         func.edge_index, func.x0 = ei, x
         with pytest.raises(NotImplementedError):
             func(0.0, x)
+
+
+@pytest.mark.parametrize('d,heads,adim', [(64, 4, 64), (128, 4, 64), (96, 4, 64), (80, 8, 128), (32, 1, 16)])
+def test_fused_path_matches_composite_path_and_is_deterministic(d, heads, adim, monkeypatch):
+    """the warp-per-row fused kernels and the general composite kernels are two implementations of the
+    same evaluation: compare them with each other (tight) in addition to the oracle comparisons above"""
+    import grand_b200
+    from grand_b200 import function_transformer_attention as fta
+    n, e = 3000, 30000
+    ei = rand_graph(n, e, 12, hub=(7, 1200))                                # includes > 256-edge segments
+    rng = np.random.default_rng(5)
+    x, x0, gout = (rng.standard_normal((n, d)).astype(np.float32) for _ in range(3))
+    opt = dict(BASE_OPT, heads=heads, attention_dim=adim, hidden_dim=d)
+    func = grand_b200.ODEFuncTransformerAtt(d, d, opt, torch.device('cuda')).cuda()
+    g = torch.Generator().manual_seed(1)
+    L = func.multihead_att_layer
+    with torch.no_grad():
+        for lin in (L.Q, L.K):
+            lin.weight.copy_((torch.randn(lin.weight.shape, generator=g) / d ** 0.5).cuda())
+        func.alpha_train.fill_(0.2)
+        func.beta_train.fill_(-0.1)
+    func.edge_index, func.x0 = dev(ei), dev(x0)
+    params = [L.Q.weight, L.Q.bias, L.K.weight, L.K.bias, func.alpha_train, func.beta_train]
+
+    def run():
+        xg = dev(x).requires_grad_(True)
+        out = func(0.0, xg)
+        return [out.detach()] + list(torch.autograd.grad(out, [xg] + params, dev(gout)))
+
+    assert fta.fused_transformer_supported(grand_b200.get_plan(func.edge_index, n), dev(x), heads, adim, 0, 0, None)
+    fused_a, fused_b = run(), run()
+    for a, b in zip(fused_a, fused_b):
+        assert torch.equal(a, b)                                             # bit-reproducible
+    with torch.no_grad():
+        nograd = func(0.0, dev(x))                                           # store == 0 variant of the kernel
+    assert torch.equal(nograd, fused_a[0])
+    monkeypatch.setattr(fta, 'fused_transformer_supported', lambda *a, **k: False)
+    comp = run()
+    names = ('f', 'gx', 'gwq', 'gbq', 'gwk', 'gbk', 'galpha', 'gbeta')
+    bias_scale = max(float(comp[3].abs().max()), float(comp[5].abs().max()))
+    for a, b, name in zip(fused_a, comp, names):
+        assert_close(a, b, 2e-5, name, floor=bias_scale if name in ('gbq', 'gbk') else 0.0)
