@@ -64,7 +64,31 @@ def algorithmic_bytes(n, e, d, a, h):
         'linear_fwd': 4 * n * d + 8 * n * a,
         'linear_bwd_x': 4 * n * d + 8 * n * a,
         'linear_bwd_w': 4 * n * d + 8 * n * a,
+        # fused GRAND-nl kernels (csrc/fused_att.cu).  Forward: the no-store figure (forward integration);
+        # the adjoint's recompute launches also write att [E,H] + abar [E] (+ 4EH + 4E).
+        'fused_att_spmm_fwd': 8 * n * a + 4 * n + 4 * e + 12 * n * d,
+        'fused_att_bwd_row': 8 * n * d + 8 * n * a + 4 * e + 8 * e * h + 4 * n,
+        'fused_att_bwd_col': 16 * n * d + 8 * n * a + 12 * e + 4 * e * h + 4 * n,
     }
+
+
+def gather_bytes(n, e, d, a, h):
+    """no-reuse gather model: every edge fetches its endpoint's rows from HBM.  Added to the
+    algorithmic bytes minus the one compulsory read of those matrices."""
+    extra = 4 * (e - n) * (a + d)
+    return {'fused_att_spmm_fwd': extra, 'fused_att_bwd_row': extra, 'fused_att_bwd_col': extra,
+            'spmm_fwd': 4 * (e - n) * d, 'spmm_bwd': 4 * (e - n) * d}
+
+
+def measured_traffic(workload, kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` on `workload`, from the committed
+    `ncu --set full` summary (profiles/traffic.json, written by hand from the .ncu-rep); None if not captured"""
+    path = os.path.join(ROOT, 'profiles', 'traffic.json')
+    try:
+        with open(path) as fh:
+            return json.load(fh).get(workload, {}).get(kernel)
+    except (OSError, ValueError):
+        return None
 
 
 class ClockSampler:
@@ -208,7 +232,7 @@ def run_ours(args):
         loss = (z * g_dev).sum()
         gx, = torch.autograd.grad(loss, xg)
         gx_host.copy_(gx, non_blocking=True)
-        loss_host = float(loss)                    # device -> host read of the step's result
+        loss_host = float(loss.detach())                    # device -> host read of the step's result
         evals_e2e += func.nfe
     e2.record()
     torch.cuda.synchronize()
@@ -217,18 +241,21 @@ def run_ours(args):
     # ---- roofline of the dominant kernel ---------------------------------------------------------
     peak, peak_src = read_peaks()
     alg = algorithmic_bytes(n, e_prime, d, cfg['adim'], cfg['heads'])
+    gat = gather_bytes(n, e_prime, d, cfg['adim'], cfg['heads'])
     top = max(kernels.items(), key=lambda kv: kv[1]['ms'])
     kname, kstat = top
     per_launch_ms = kstat['ms'] / kstat['launches']
     achieved = alg.get(kname, 0) / (per_launch_ms * 1e-3) / 1e9 if per_launch_ms > 0 else 0.0
     ksum = sum(v['ms'] for v in kernels.values())
     roofline = {'bound': 'hbm', 'kernel': kname, 'achieved': round(achieved, 1), 'peak': peak, 'unit': 'GB/s',
-                'frac': round(achieved / peak, 4), 'traffic': None, 'peak_source': peak_src,
+                'frac': round(achieved / peak, 4), 'traffic': measured_traffic(name, kname), 'peak_source': peak_src,
                 'algorithmic_bytes_per_launch': alg.get(kname, 0), 'avg_launch_ms': round(per_launch_ms, 4),
                 'share_of_kernel_time': round(kstat['ms'] / ksum, 4) if ksum else None,
                 'kernels': {k: {'ms_per_launch': round(v['ms'] / v['launches'], 4), 'launches': v['launches'],
                                 'share': round(v['ms'] / ksum, 4),
-                                'alg_GBps': round(alg[k] / (v['ms'] / v['launches'] * 1e-3) / 1e9, 1) if k in alg else None}
+                                'alg_GBps': round(alg[k] / (v['ms'] / v['launches'] * 1e-3) / 1e9, 1) if k in alg else None,
+                                'gather_model_GBps': round((alg[k] + gat[k]) / (v['ms'] / v['launches'] * 1e-3) / 1e9, 1)
+                                if k in alg and k in gat else None}
                             for k, v in sorted(kernels.items(), key=lambda kv: -kv[1]['ms'])}}
 
     line = {
