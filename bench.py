@@ -69,6 +69,9 @@ def algorithmic_bytes(n, e, d, a, h):
         'fused_att_spmm_fwd': 8 * n * a + 4 * n + 4 * e + 12 * n * d,
         'fused_att_bwd_row': 8 * n * d + 8 * n * a + 4 * e + 8 * e * h + 4 * n,
         'fused_att_bwd_col': 16 * n * d + 8 * n * a + 12 * e + 4 * e * h + 4 * n,
+        # single-gather kernels (csrc/nl_kernels.cuh)
+        'nl_fwd': 4 * e + 4 * n + 4 * n * a + 12 * n * d,
+        'nl_adj_rows': 4 * e + 4 * n + 8 * n * a + 16 * n * d + 4 * e * h + 4 * e,
     }
 
 
@@ -76,7 +79,7 @@ def gather_bytes(n, e, d, a, h):
     """no-reuse gather model: every edge fetches its endpoint's rows from HBM.  Added to the
     algorithmic bytes minus the one compulsory read of those matrices."""
     extra = 4 * (e - n) * (a + d)
-    return {'fused_att_spmm_fwd': extra, 'fused_att_bwd_row': extra, 'fused_att_bwd_col': extra,
+    return {'nl_fwd': 4 * (e - n) * d, 'nl_adj_rows': 4 * (e - n) * d, 'fused_att_spmm_fwd': extra, 'fused_att_bwd_row': extra, 'fused_att_bwd_col': extra,
             'spmm_fwd': 4 * (e - n) * d, 'spmm_bwd': 4 * (e - n) * d}
 
 

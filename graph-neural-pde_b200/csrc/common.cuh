@@ -54,6 +54,10 @@ enum KernelId {
   K_FUSED_ATT_BWD_COL,
   K_LINEAR_TC,
   K_STAGE_AXPY,
+  K_NL_FWD,
+  K_NL_FWD_LONG,
+  K_NL_ADJ_ROWS,
+  K_NL_ADJ_LONG,
   K_NUM_KERNELS
 };
 

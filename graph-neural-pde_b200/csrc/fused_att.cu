@@ -16,8 +16,14 @@
 // att/abar are stored).
 #include "att_common.cuh"
 #include "spmm_common.cuh"
+#include "nl_kernels.cuh"
 
 namespace gb {
+int nl_fill_args(NlArgs& a, const gb_graph* g, int row_lo, int row_hi, const float* x, int ldx, const float* q,
+                 int ldq, const float* wk, int ldwk, int heads, int dk, int d, const float* x0, int ldx0,
+                 const float* alpha_train, int alpha_sigmoid, const float* beta_train, float* out, int ldo,
+                 const gb_stage* stage, void* workspace, const char* who);
+
 
 constexpr int kFusedWarps = 4;
 constexpr int kFusedThreads = kFusedWarps * 32;
@@ -641,6 +647,71 @@ int gb_att_bwd_fused(const gb_graph* g, const float* q, int32_t ldq, const float
   // columns: transpose SpMM (dx, partial sums) + dk
   if (int rc = dispatch_bwd(a, stream, true)) return rc;
   int slots = (g->n + kFusedWarps - 1) / kFusedWarps;
+  if (nlc > 0) {
+    SpmmArgs lsp = sp;
+    lsp.partial_base = slots;
+    if (int rc = spmm_long_only(lsp, 4, true, nlc, stream)) return rc;
+    slots += nlc;
+    MhArgs mh{};
+    mh.ptr = g->colptr; mh.idx = g->rowidx; mh.perm = g->tperm; mh.ds = ds; mh.src = q; mh.lds = ldq;
+    mh.out = dk_out; mh.ldo = lddk; mh.n = g->n; mh.heads = heads; mh.dk = dk; mh.long_threshold = kFusedCap;
+    mh.scale = 1.0f / sqrtf((float)dk); mh.long_list = g->long_cols;
+    if (int rc = mh_spmm_long(mh, 4, nlc, K_EDGE_SCORE_BWD_K, stream)) return rc;
+  }
+  if (dparams) return reduce_partials_launch(partials, slots, alpha_train, alpha_sigmoid, dparams, stream);
+  return GB_OK;
+}
+
+int gb_nl_adjoint(const gb_graph* g, int32_t row_lo, int32_t row_hi, const float* x, int32_t ldx, const float* q,
+                  int32_t ldq, const float* wk, int32_t ldwk, int32_t heads, int32_t dk, int32_t d, const float* x0,
+                  int32_t ldx0, const float* alpha_train, int32_t alpha_sigmoid, const float* beta_train,
+                  const float* gout, int32_t ldg, float* out, int32_t ldo, float* ds, float* dabar_scratch,
+                  float* abar, float* dq, int32_t lddq, float* dk_out, int32_t lddk, float* dx, int32_t lddx,
+                  float* partials, float* dparams, void* workspace, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  NlArgs a;
+  if (int rc = nl_fill_args(a, g, row_lo, row_hi, x, ldx, q, ldq, wk, ldwk, heads, dk, d, x0, ldx0, alpha_train,
+                            alpha_sigmoid, beta_train, out, ldo, nullptr, workspace, "gb_nl_adjoint"))
+    return rc;
+  GB_REQUIRE(gout && ds && dabar_scratch && abar && dq && dk_out && dx && partials, "gb_nl_adjoint: null pointer");
+  GB_REQUIRE(g->colptr && (g->e == 0 || (g->rowidx && g->tperm)), "gb_nl_adjoint: graph without CSC arrays");
+  GB_REQUIRE(ldg >= d && lddx >= d && vec_width(gout, ldg, d) == 4 && vec_width(dx, lddx, d) == 4,
+             "gb_nl_adjoint: gout / dx rows must be 16-byte aligned");
+  const int adim = heads * dk;
+  GB_REQUIRE(lddq >= adim && lddk >= adim && vec_width(dk_out, lddk, adim) == 4 && vec_width(q, ldq, adim) == 4,
+             "gb_nl_adjoint: q / dk rows must be 16-byte aligned");
+  GB_REQUIRE(reinterpret_cast<uintptr_t>(partials) % 8 == 0, "gb_nl_adjoint: partials must be 8-byte aligned");
+  const bool use_long = g->long_threshold > 0;
+  GB_REQUIRE(!use_long || g->long_threshold == kFusedCap, "gb_nl_adjoint: plan long_threshold must be %d", kFusedCap);
+  GB_REQUIRE(use_long || g->e <= kFusedCap, "gb_nl_adjoint: plan without long-segment lists");
+  a.write_f = out != nullptr;
+  a.g = gout; a.ldg = ldg; a.ds = ds; a.dabar = dabar_scratch; a.abar = abar; a.dq = dq; a.lddq = lddq;
+  // rows: evaluation + SDDMM + softmax backward + dq in one gather pass
+  if (int rc = nl_dispatch_adj(a, heads, use_long ? g->n_long_rows : 0, stream)) return rc;
+
+  // columns: transpose SpMM (dx, dalpha / dbeta partial sums) + dk over the edges this rank holds
+  const bool part = !(row_lo == 0 && row_hi == g->n);
+  FusedBwdArgs b{};
+  b.rowptr = g->rowptr; b.colidx = g->colidx; b.colptr = g->colptr; b.rowidx = g->rowidx; b.tperm = g->tperm;
+  b.n = g->n; b.heads = heads; b.dk = dk; b.lh = dk / 4;
+  b.q = q; b.ldq = ldq; b.k = nullptr; b.ldk = 0; b.att = nullptr; b.abar = abar;
+  b.g = gout; b.ldg = ldg; b.x = x; b.ldx = ldx; b.xdv = d / 4;
+  b.ds = ds; b.dq = dq; b.lddq = lddq; b.dk_out = dk_out; b.lddk = lddk;
+  SpmmArgs& sp = b.sp;
+  sp.ptr = g->colptr; sp.idx = g->rowidx; sp.perm = g->tperm; sp.vals = abar; sp.n = g->n; sp.dv = d / 4;
+  sp.long_threshold = kFusedCap; sp.src = gout; sp.lds = ldg; sp.alpha_train = alpha_train;
+  sp.alpha_sigmoid = alpha_sigmoid; sp.x0 = (dparams && beta_train) ? x0 : nullptr; sp.ldx0 = ldx0;
+  sp.x = dparams ? x : nullptr; sp.ldx = ldx; sp.out = dx; sp.ldo = lddx; sp.accumulate = 0;
+  sp.partials = partials + kMidFloats; sp.partial_base = 0; sp.long_list = g->long_cols;
+  if (part) { sp.part_lo = row_lo; sp.part_hi = row_hi; }
+  const char* why = "";
+  if (!fused_supported(q, ldq, q, ldq, heads, dk, &why)) {
+    set_error("gb_nl_adjoint: column pass does not support this shape (%s)", why);
+    return GB_ERR_UNSUPPORTED;
+  }
+  if (int rc = dispatch_bwd(b, stream, true)) return rc;
+  int slots = (g->n + kFusedWarps - 1) / kFusedWarps;
+  const int nlc = use_long ? g->n_long_cols : 0;
   if (nlc > 0) {
     SpmmArgs lsp = sp;
     lsp.partial_base = slots;

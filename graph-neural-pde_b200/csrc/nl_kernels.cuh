@@ -1,0 +1,544 @@
+// nl_kernels.cuh - single-gather GRAND-nl kernels (ODEFuncTransformerAtt.forward,
+// src/function_transformer_attention.py:44-59, scaled_dot scores, attention_norm_idx 0) and their VJP.
+//
+// Why these exist: on graphs without locality the evaluation is bound by the per-edge row gathers
+// (ncu, profiles/r01c: 49 GB of DRAM reads per forward launch on the ogbn-products shape = E' x (A + d) x 4 B).
+// They gather ONE row per edge - x[col] - instead of k[col] and x[col]:
+//
+//   score[e,h] = <q[i,h,:], k[j,h,:]> / sqrt(dk),   k[j] = Wk x[j] + bk
+//              = <p[i,h,:], x[j,:]> + const(i,h),   p[i,h,:] = Wk_h^T q[i,h,:] / sqrt(dk)        (d-vector per head)
+//   and the softmax over the edges of row i is invariant to const(i,h), so the K projection is never formed.
+//
+//   forward   one pass over the row's edges with an ONLINE softmax per head (running max m_h, running sum l_h,
+//             running sum T1_h = sum_e exp(s_eh - m_h) x_j):   (A x)_i = 1/H sum_h T1_h / l_h
+//   adjoint   the same pass also carries dabar_e = alpha <g_i, x_j> and T2_h = sum_e exp(s_eh - m_h) dabar_e x_j,
+//             D_h = sum_e exp(s_eh - m_h) dabar_e, which give without a second gather
+//                 dot_h = D_h / (H l_h)                     (= sum_e att_eh dabar_e / H)
+//                 u_h   = T2_h / (H l_h) - dot_h T1_h / l_h (= sum_e ds_eh x_j)
+//                 dq[i,h,:] = Wk_h u_h / sqrt(dk)
+//             raw scores / dabar are parked per edge and turned into ds[e,h] = att (dabar/H - dot_h) and
+//             abar[e] in a coalesced second sweep over the row's own slots (no gather).
+//
+// Work decomposition: persistent CTAs of 8 warps, Wk staged once per CTA in shared memory, rows handed out
+// by a dynamic (integer atomic) scheduler in chunks; a warp owns a row; XL lanes span the d columns
+// (128-bit chunks), 32/XL edge groups run side by side, each lane keeps U gathers in flight.  Per-head dot
+// products are reduced with a transposing butterfly (31 shuffles for 32 values).  Rows longer than the plan's
+// long threshold get one CTA each (warps stride the batches; partial online-softmax states merged in a
+// fixed order).  No float atomics: results are bit-reproducible run to run.
+//
+// Roofline: HBM.  Algorithmic bytes per launch (perfect reuse of gathered rows):
+//   forward  4E + 4N + 4NA (q) + 12Nd (x, x0, out)
+//   adjoint  4E + 4N + 8NA (q, dq) + 8Nd (x, g) [+ 8Nd when f is emitted] + 20E (ds [E,H] + abar [E] out;
+//            the parked scores are re-read from L2)
+// Gather model (no reuse): + 4 (E - N) d.
+#pragma once
+#include <math_constants.h>
+#include "spmm_common.cuh"
+
+namespace gb {
+
+constexpr int kNlWarps = 8;
+constexpr int kNlThreads = kNlWarps * 32;
+constexpr int kNlChunkRows = 4;          // rows per scheduler grab
+constexpr unsigned kFullMask = 0xffffffffu;
+
+struct NlArgs {
+  const int32_t* rowptr;
+  const int32_t* colidx;
+  int32_t row_lo, row_hi;    // rows evaluated by this launch (1-D row partition; [0, n) on one GPU)
+  int32_t dv;                // d / 4
+  int32_t adim, dk;          // attention_dim = heads * dk
+  const float* q;            // [*, A] indexed by the global row id
+  int32_t ldq;
+  const float* wk;           // [A, d] (torch Linear.weight layout)
+  int32_t ldwk;
+  SpmmArgs sp;               // x (src/lds), diffusion epilogue, optional Runge-Kutta stage
+  int32_t write_f;           // adjoint: also emit f (the adjoint solver needs it)
+  // adjoint only
+  const float* g;            // dL/df, indexed by the global row id
+  int32_t ldg;
+  float* ds;                 // [E,H]  out: dL/d raw score (parked raw scores in between)
+  float* dabar;              // [E]    scratch: alpha <g_i, x_j>
+  float* abar;               // [E]    out: mean_h att
+  float* dq;                 // [*, A] out
+  int32_t lddq;
+  int32_t* counter;          // scheduler counter, zeroed before the launch
+  const int32_t* long_list;
+  int32_t long_threshold;
+};
+
+constexpr int ilog2_c(int v) { return v <= 1 ? 0 : 1 + ilog2_c(v / 2); }
+
+__device__ __forceinline__ float4 f4_zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
+__device__ __forceinline__ void f4_scale(float4& a, float s) {
+  a.x *= s; a.y *= s; a.z *= s; a.w *= s;
+}
+__device__ __forceinline__ float4 f4_shfl_xor(const float4& a, int o) {
+  return make_float4(__shfl_xor_sync(kFullMask, a.x, o), __shfl_xor_sync(kFullMask, a.y, o),
+                     __shfl_xor_sync(kFullMask, a.z, o), __shfl_xor_sync(kFullMask, a.w, o));
+}
+__device__ __forceinline__ void f4_add(float4& a, const float4& b) {
+  a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+}
+
+// Transposing butterfly: every lane of an XL-lane group holds NV partial sums (NV <= XL, powers of two);
+// on return v[0] of lane xl is the group total of value index (xl >> (log2 XL - log2 NV)).
+// O = first xor offset (XL/2).  Costs NV-1 + (log2 XL - log2 NV) shuffles instead of NV log2 XL.
+template <int NV, int O>
+struct ReduceT {
+  static __device__ __forceinline__ void run(float* v, int xl) {
+    if constexpr (O >= 1) {
+      if constexpr (NV > 1) {
+        constexpr int HN = NV / 2;
+        const bool up = (xl & O) != 0;
+#pragma unroll
+        for (int i = 0; i < HN; ++i) {
+          const float send = up ? v[i] : v[i + HN];
+          const float keep = up ? v[i + HN] : v[i];
+          v[i] = keep + __shfl_xor_sync(kFullMask, send, O);
+        }
+        ReduceT<HN, O / 2>::run(v, xl);
+      } else {
+        v[0] += __shfl_xor_sync(kFullMask, v[0], O);
+        ReduceT<1, O / 2>::run(v, xl);
+      }
+    }
+  }
+};
+
+template <int H>
+struct NlStats {
+  float mh[H], lh[H], dh[H];     // per head: running max, sum of exp, sum of exp * dabar
+};
+
+// Register state of one warp working on (part of) one row.
+template <int XL, int H, bool ADJ>
+struct NlRow {
+  static constexpr int EPI = 32 / XL;                       // edge groups per warp
+  static constexpr int U = (XL / H) < 8 ? (XL / H) : 8;     // edges in flight per group
+  static constexpr int NV = U * H;                          // scores per group batch (<= XL)
+  static constexpr int SH = ilog2_c(XL) - ilog2_c(NV);      // score index of lane xl = xl >> SH
+  static constexpr int SHU = ilog2_c(XL) - ilog2_c(U);
+  static constexpr int BATCH = EPI * U;                     // edges per warp batch
+  static constexpr int HA = ADJ ? H : 1;
+  static_assert(H <= XL && NV <= XL && 32 % H == 0, "unsupported head count");
+
+  float m, l, dsum;          // online softmax state of (this lane's head, this lane's edge slots)
+  float4 acc1[H];            // T1_h, this lane's 4 columns
+  float4 acc2[HA];           // T2_h
+  float4 p[H];               // Wk_h^T q_ih / sqrt(dk), this lane's 4 columns
+  float4 gi;                 // g_i chunk (adjoint)
+  int xl, es, gbase, myh, myu;
+
+  __device__ __forceinline__ void init_lane(int lane) {
+    xl = lane % XL;
+    es = lane / XL;
+    gbase = lane - xl;
+    const int idx = xl >> SH;
+    myh = idx % H;
+    myu = idx / H;
+  }
+
+  __device__ __forceinline__ void reset() {
+    m = -CUDART_INF_F;
+    l = 0.f;
+    dsum = 0.f;
+#pragma unroll
+    for (int h = 0; h < H; ++h) acc1[h] = f4_zero();
+#pragma unroll
+    for (int h = 0; h < HA; ++h) acc2[h] = f4_zero();
+  }
+
+  // p[h] = Wk_h^T q_ih / sqrt(dk); wk_s = staged Wk [A][ldw], q_s = this row's q [A] (shared memory)
+  __device__ __forceinline__ void load_p(const NlArgs& a, const float* wk_s, int ldw, const float* q_s) {
+    const float scale = 1.0f / sqrtf((float)a.dk);
+    const bool act = xl < a.dv;
+    const float* wcol = wk_s + 4 * (act ? xl : 0);
+#pragma unroll
+    for (int h = 0; h < H; ++h) {
+      float4 acc = f4_zero();
+      for (int t = 0; t < a.dk; t += 4) {
+        const int j = h * a.dk + t;
+        const float4 qv = *reinterpret_cast<const float4*>(q_s + j);
+        fma4(acc, qv.x, *reinterpret_cast<const float4*>(wcol + (size_t)(j + 0) * ldw));
+        fma4(acc, qv.y, *reinterpret_cast<const float4*>(wcol + (size_t)(j + 1) * ldw));
+        fma4(acc, qv.z, *reinterpret_cast<const float4*>(wcol + (size_t)(j + 2) * ldw));
+        fma4(acc, qv.w, *reinterpret_cast<const float4*>(wcol + (size_t)(j + 3) * ldw));
+      }
+      f4_scale(acc, act ? scale : 0.f);
+      p[h] = acc;
+    }
+  }
+
+  // one warp batch: edges [base, base + BATCH) of a row ending at `end`
+  __device__ __forceinline__ void batch(const NlArgs& a, int base, int end, int lane, float alpha) {
+    int cmine = -1;
+    if (lane < BATCH && base + lane < end) cmine = ld_stream_i32(a.colidx + base + lane);
+    const bool act = xl < a.dv;
+    float4 xr[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int c = __shfl_sync(kFullMask, cmine, es * U + u);
+      xr[u] = (c >= 0 && act) ? ldg4(a.sp.src + (size_t)c * a.sp.lds + 4 * xl) : f4_zero();
+    }
+    float v[NV];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+#pragma unroll
+      for (int h = 0; h < H; ++h) v[u * H + h] = dot4(p[h], xr[u]);
+    ReduceT<NV, XL / 2>::run(v, xl);
+    const int pos = base + es * U + myu;
+    const bool valid = pos < end;
+    const float s = valid ? v[0] : -CUDART_INF_F;
+    float dab = 0.f;
+    if constexpr (ADJ) {
+      float w[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) w[u] = dot4(gi, xr[u]);
+      ReduceT<U, XL / 2>::run(w, xl);
+      dab = alpha * __shfl_sync(kFullMask, w[0], gbase + (myu << SHU));
+      if (valid && (xl & ((1 << SH) - 1)) == 0) {           // park the raw score / dabar of this edge
+        a.ds[(size_t)pos * H + myh] = s;
+        if (myh == 0) a.dabar[pos] = dab;
+      }
+    }
+    float mb = s;
+#pragma unroll
+    for (int o = H << SH; o < XL; o <<= 1) mb = fmaxf(mb, __shfl_xor_sync(kFullMask, mb, o));
+    const float mnew = fmaxf(m, mb);
+    const float corr = (mnew == -CUDART_INF_F) ? 1.f : expf(m - mnew);
+    const float pe = valid ? expf(s - mnew) : 0.f;
+    m = mnew;
+    l = fmaf(l, corr, pe);
+    if constexpr (ADJ) dsum = fmaf(dsum, corr, pe * dab);
+    if (__any_sync(kFullMask, corr != 1.f)) {               // some head's running max moved: rescale
+#pragma unroll
+      for (int h = 0; h < H; ++h) {
+        const float c = __shfl_sync(kFullMask, corr, gbase + (h << SH));
+        f4_scale(acc1[h], c);
+        if constexpr (ADJ) f4_scale(acc2[h], c);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const float du = ADJ ? __shfl_sync(kFullMask, dab, gbase + ((u * H) << SH)) : 0.f;
+#pragma unroll
+      for (int h = 0; h < H; ++h) {
+        const float pu = __shfl_sync(kFullMask, pe, gbase + ((u * H + h) << SH));
+        fma4(acc1[h], pu, xr[u]);
+        if constexpr (ADJ) fma4(acc2[h], pu * du, xr[u]);
+      }
+    }
+  }
+
+  // combine the lanes / edge groups of the warp: afterwards every lane holds the per-head statistics and
+  // (for its 4 columns) the merged accumulators.  Fixed order -> deterministic.
+  __device__ __forceinline__ void warp_merge(NlStats<H>& st) {
+#pragma unroll
+    for (int o = H << SH; o < XL; o <<= 1) {
+      l += __shfl_xor_sync(kFullMask, l, o);
+      if constexpr (ADJ) dsum += __shfl_xor_sync(kFullMask, dsum, o);
+    }
+#pragma unroll
+    for (int h = 0; h < H; ++h) {
+      st.mh[h] = __shfl_sync(kFullMask, m, gbase + (h << SH));
+      st.lh[h] = __shfl_sync(kFullMask, l, gbase + (h << SH));
+      st.dh[h] = ADJ ? __shfl_sync(kFullMask, dsum, gbase + (h << SH)) : 0.f;
+    }
+    if (EPI > 1) {
+#pragma unroll
+      for (int h = 0; h < H; ++h) {
+        float mx = st.mh[h];
+#pragma unroll
+        for (int o = XL; o < 32; o <<= 1) mx = fmaxf(mx, __shfl_xor_sync(kFullMask, mx, o));
+        const float sc = (st.mh[h] == -CUDART_INF_F) ? 0.f : expf(st.mh[h] - mx);
+        st.mh[h] = mx;
+        st.lh[h] *= sc;
+        st.dh[h] *= sc;
+        f4_scale(acc1[h], sc);
+        if constexpr (ADJ) f4_scale(acc2[h], sc);
+#pragma unroll
+        for (int o = XL; o < 32; o <<= 1) {
+          st.lh[h] += __shfl_xor_sync(kFullMask, st.lh[h], o);
+          st.dh[h] += __shfl_xor_sync(kFullMask, st.dh[h], o);
+          f4_add(acc1[h], f4_shfl_xor(acc1[h], o));
+          if constexpr (ADJ) f4_add(acc2[h], f4_shfl_xor(acc2[h], o));
+        }
+      }
+    }
+  }
+
+  // f (diffusion epilogue) and dq of the row from the merged state; executed by one warp.
+  // u_s: [H][4*XL] floats of shared memory private to the warp.
+  __device__ __forceinline__ void emit(const NlArgs& a, int row, int lane, const NlStats<H>& st, float alpha,
+                                       float beta, float* u_s, const float* wk_s, int ldw) {
+    float inv[H];
+#pragma unroll
+    for (int h = 0; h < H; ++h) inv[h] = st.lh[h] > 0.f ? 1.0f / st.lh[h] : 0.f;
+    const float inv_h = 1.0f / (float)H;
+    if (!ADJ || a.write_f) {
+      float4 ax = f4_zero();
+#pragma unroll
+      for (int h = 0; h < H; ++h) fma4(ax, inv[h], acc1[h]);
+      f4_scale(ax, inv_h);
+      if (es == 0 && xl < a.dv) {
+        float s1 = 0.f, s2 = 0.f;
+        row_epilogue<4, false>(a.sp, row, 4 * xl, Vec<4>{ax}, alpha, beta, s1, s2);
+      }
+    }
+    if constexpr (ADJ) {
+#pragma unroll
+      for (int h = 0; h < H; ++h) {
+        const float dot = st.dh[h] * inv[h] * inv_h;
+        const float c2 = inv[h] * inv_h, c1 = inv[h] * dot;
+        float4 uh;
+        uh.x = acc2[h].x * c2 - acc1[h].x * c1;
+        uh.y = acc2[h].y * c2 - acc1[h].y * c1;
+        uh.z = acc2[h].z * c2 - acc1[h].z * c1;
+        uh.w = acc2[h].w * c2 - acc1[h].w * c1;
+        if (es == 0) *reinterpret_cast<float4*>(u_s + h * (4 * XL) + 4 * xl) = uh;
+      }
+      __syncwarp();
+      const float scale = 1.0f / sqrtf((float)a.dk);
+      for (int j = lane; j < a.adim; j += 32) {              // dq[i, j] = <Wk[j, :], u_{head(j)}> / sqrt(dk)
+        const float* wr = wk_s + (size_t)j * ldw;
+        const float* ur = u_s + (j / a.dk) * (4 * XL);
+        float acc = 0.f;
+        for (int c = 0; c < a.dv; ++c)
+          acc += dot4(*reinterpret_cast<const float4*>(wr + 4 * c), *reinterpret_cast<const float4*>(ur + 4 * c));
+        a.dq[(size_t)row * a.lddq + j] = acc * scale;
+      }
+    }
+  }
+};
+
+// second sweep of the adjoint over the row's own slots [first, end) with stride `step` (in (edge, head) pairs,
+// multiples of 32): parked raw score / dabar -> ds[e,h] = att (dabar/H - dot_h), abar[e] = mean_h att
+template <int H>
+__device__ __forceinline__ void nl_sweep_ds(const NlArgs& a, int start, int end, int lane, const NlStats<H>& st,
+                                            int first, int step) {
+  const int hsel = lane % H;
+  float msel = st.mh[0], lsel = st.lh[0], dsel = st.dh[0];
+#pragma unroll
+  for (int h = 1; h < H; ++h)
+    if (hsel == h) { msel = st.mh[h]; lsel = st.lh[h]; dsel = st.dh[h]; }
+  const float inv = lsel > 0.f ? 1.0f / lsel : 0.f;
+  const float inv_h = 1.0f / (float)H;
+  const float dot = dsel * inv * inv_h;
+  const int pairs = (end - start) * H;
+  float* dsr = a.ds + (size_t)start * H;
+  for (int p0 = first; p0 < pairs; p0 += step) {
+    const int pp = p0 + lane;
+    const bool ok = pp < pairs;
+    const int e = pp / H;
+    float att = 0.f, dab = 0.f;
+    if (ok) {
+      att = expf(dsr[pp] - msel) * inv;
+      dab = a.dabar[start + e];
+    }
+    float tot = att;
+#pragma unroll
+    for (int o = 1; o < H; o <<= 1) tot += __shfl_xor_sync(kFullMask, tot, o);
+    if (ok) {
+      dsr[pp] = att * (dab * inv_h - dot);
+      if (hsel == 0) a.abar[start + e] = tot * inv_h;
+    }
+  }
+}
+
+// shared-memory layout of both kernels: [A][ldw] staged Wk | per-warp q [W][A] | per-warp u [W][H][4*XL] | (long kernel) partials
+__host__ __device__ inline int nl_ldw(int dv) { return 4 * dv + 4; }
+
+template <int XL, int H>
+inline size_t nl_smem_rows(int adim, int dv) {
+  return sizeof(float) * ((size_t)adim * nl_ldw(dv) + (size_t)kNlWarps * adim + (size_t)kNlWarps * H * 4 * XL);
+}
+// long kernel: + per-warp stats [W][3][H] and accumulators [W][2][H][4*XL]
+template <int XL, int H>
+inline size_t nl_smem_long(int adim, int dv) {
+  return nl_smem_rows<XL, H>(adim, dv) + sizeof(float) * ((size_t)kNlWarps * 3 * H + (size_t)kNlWarps * 2 * H * 4 * XL);
+}
+
+__device__ __forceinline__ void nl_stage_wk(const NlArgs& a, float* wk_s, int ldw) {
+  const int total = a.adim * a.dv;
+  for (int i = threadIdx.x; i < total; i += blockDim.x) {
+    const int j = i / a.dv, c = i - j * a.dv;
+    *reinterpret_cast<float4*>(wk_s + (size_t)j * ldw + 4 * c) = ldg4(a.wk + (size_t)j * a.ldwk + 4 * c);
+  }
+}
+
+// persistent kernel: warps pull chunks of rows from an atomic counter
+template <int XL, int H, bool ADJ>
+__global__ void __launch_bounds__(kNlThreads, 2) nl_rows_kernel(const NlArgs a) {
+  extern __shared__ __align__(16) float smem[];
+  using Row = NlRow<XL, H, ADJ>;
+  const int ldw = nl_ldw(a.dv);
+  float* wk_s = smem;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* q_s = wk_s + (size_t)a.adim * ldw + (size_t)warp * a.adim;
+  float* u_s = wk_s + (size_t)a.adim * ldw + (size_t)kNlWarps * a.adim + (size_t)warp * H * 4 * XL;
+  nl_stage_wk(a, wk_s, ldw);
+  __syncthreads();
+  Row r;
+  r.init_lane(lane);
+  const float alpha = load_alpha(a.sp);
+  const float beta = a.sp.beta_train != nullptr ? __ldg(a.sp.beta_train) : 0.f;
+  const int nrows = a.row_hi - a.row_lo;
+  for (;;) {
+    int r0 = 0;
+    if (lane == 0) r0 = atomicAdd(a.counter, kNlChunkRows);
+    r0 = __shfl_sync(kFullMask, r0, 0);
+    if (r0 >= nrows) break;
+    const int r1 = min(r0 + kNlChunkRows, nrows);
+    for (int rr = r0; rr < r1; ++rr) {
+      const int row = a.row_lo + rr;
+      const int start = __ldg(a.rowptr + row), end = __ldg(a.rowptr + row + 1);
+      if (end - start > a.long_threshold) continue;          // nl_long_kernel takes these
+      for (int j = lane; j < a.adim; j += 32) q_s[j] = __ldg(a.q + (size_t)row * a.ldq + j);
+      __syncwarp();
+      r.load_p(a, wk_s, ldw, q_s);
+      if constexpr (ADJ)
+        r.gi = r.xl < a.dv ? ldg4(a.g + (size_t)row * a.ldg + 4 * r.xl) : f4_zero();
+      r.reset();
+      for (int base = start; base < end; base += Row::BATCH) r.batch(a, base, end, lane, alpha);
+      NlStats<H> st;
+      r.warp_merge(st);
+      r.emit(a, row, lane, st, alpha, beta, u_s, wk_s, ldw);
+      if constexpr (ADJ) {
+        __syncwarp();
+        nl_sweep_ds<H>(a, start, end, lane, st, 0, 32);
+      }
+      __syncwarp();                                          // q_s / u_s are reused by the next row
+    }
+  }
+}
+
+// one CTA per long row: warps stride the batches, partial states merged through shared memory in warp order
+template <int XL, int H, bool ADJ>
+__global__ void __launch_bounds__(kNlThreads, 1) nl_long_kernel(const NlArgs a) {
+  extern __shared__ __align__(16) float smem[];
+  using Row = NlRow<XL, H, ADJ>;
+  const int ldw = nl_ldw(a.dv);
+  float* wk_s = smem;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* q_s = wk_s + (size_t)a.adim * ldw;                                    // one copy (warp 0's slot)
+  float* u_s = wk_s + (size_t)a.adim * ldw + (size_t)kNlWarps * a.adim;        // warp 0's slot
+  float* pst = u_s + (size_t)kNlWarps * H * 4 * XL;                            // [W][3][H]
+  float* pacc = pst + kNlWarps * 3 * H;                                        // [W][2][H][4*XL]
+  const int row = __ldg(a.long_list + blockIdx.x);
+  if (row < a.row_lo || row >= a.row_hi) return;
+  const int start = __ldg(a.rowptr + row), end = __ldg(a.rowptr + row + 1);
+  nl_stage_wk(a, wk_s, ldw);
+  for (int j = threadIdx.x; j < a.adim; j += blockDim.x) q_s[j] = __ldg(a.q + (size_t)row * a.ldq + j);
+  __syncthreads();
+  Row r;
+  r.init_lane(lane);
+  const float alpha = load_alpha(a.sp);
+  const float beta = a.sp.beta_train != nullptr ? __ldg(a.sp.beta_train) : 0.f;
+  r.load_p(a, wk_s, ldw, q_s);
+  if constexpr (ADJ) r.gi = r.xl < a.dv ? ldg4(a.g + (size_t)row * a.ldg + 4 * r.xl) : f4_zero();
+  r.reset();
+  for (int base = start + warp * Row::BATCH; base < end; base += kNlWarps * Row::BATCH)
+    r.batch(a, base, end, lane, alpha);
+  NlStats<H> st;
+  r.warp_merge(st);
+  if (lane == 0) {
+#pragma unroll
+    for (int h = 0; h < H; ++h) {
+      pst[(warp * 3 + 0) * H + h] = st.mh[h];
+      pst[(warp * 3 + 1) * H + h] = st.lh[h];
+      pst[(warp * 3 + 2) * H + h] = st.dh[h];
+    }
+  }
+  if (r.es == 0) {
+#pragma unroll
+    for (int h = 0; h < H; ++h) {
+      *reinterpret_cast<float4*>(pacc + ((size_t)(warp * 2 + 0) * H + h) * 4 * XL + 4 * r.xl) = r.acc1[h];
+      if constexpr (ADJ)
+        *reinterpret_cast<float4*>(pacc + ((size_t)(warp * 2 + 1) * H + h) * 4 * XL + 4 * r.xl) = r.acc2[h];
+    }
+  }
+  __syncthreads();
+  // every warp forms the same merged statistics; warp 0 also merges the accumulators and emits the row
+#pragma unroll
+  for (int h = 0; h < H; ++h) {
+    float mx = -CUDART_INF_F;
+    for (int w = 0; w < kNlWarps; ++w) mx = fmaxf(mx, pst[(w * 3 + 0) * H + h]);
+    float ls = 0.f, dsum = 0.f;
+    for (int w = 0; w < kNlWarps; ++w) {
+      const float mw = pst[(w * 3 + 0) * H + h];
+      const float sc = mw == -CUDART_INF_F ? 0.f : expf(mw - mx);
+      ls = fmaf(pst[(w * 3 + 1) * H + h], sc, ls);
+      dsum = fmaf(pst[(w * 3 + 2) * H + h], sc, dsum);
+    }
+    st.mh[h] = mx;
+    st.lh[h] = ls;
+    st.dh[h] = dsum;
+  }
+  if (warp == 0) {
+#pragma unroll
+    for (int h = 0; h < H; ++h) {
+      float4 t1 = f4_zero(), t2 = f4_zero();
+      for (int w = 0; w < kNlWarps; ++w) {
+        const float mw = pst[(w * 3 + 0) * H + h];
+        const float sc = mw == -CUDART_INF_F ? 0.f : expf(mw - st.mh[h]);
+        fma4(t1, sc, *reinterpret_cast<const float4*>(pacc + ((size_t)(w * 2 + 0) * H + h) * 4 * XL + 4 * r.xl));
+        if constexpr (ADJ)
+          fma4(t2, sc, *reinterpret_cast<const float4*>(pacc + ((size_t)(w * 2 + 1) * H + h) * 4 * XL + 4 * r.xl));
+      }
+      r.acc1[h] = t1;
+      if constexpr (ADJ) r.acc2[h] = t2;
+    }
+    r.emit(a, row, lane, st, alpha, beta, u_s, wk_s, ldw);
+  }
+  if constexpr (ADJ) nl_sweep_ds<H>(a, start, end, lane, st, warp * 32, kNlWarps * 32);
+}
+
+template <int XL, int H, bool ADJ>
+int nl_launch(const NlArgs& a, int n_long, cudaStream_t stream) {
+  static bool configured = false;
+  const size_t smem_rows = nl_smem_rows<XL, H>(a.adim, a.dv), smem_long = nl_smem_long<XL, H>(a.adim, a.dv);
+  if (smem_long > 200 * 1024) {
+    set_error("nl kernels: attention_dim x d too large for shared memory (%zu bytes)", smem_long);
+    return GB_ERR_UNSUPPORTED;
+  }
+  if (!configured) {
+    GB_CUDA(cudaFuncSetAttribute(nl_rows_kernel<XL, H, ADJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    GB_CUDA(cudaFuncSetAttribute(nl_long_kernel<XL, H, ADJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    configured = true;
+  }
+  const int nrows = a.row_hi - a.row_lo;
+  if (nrows <= 0) return GB_OK;
+  GB_CUDA(cudaMemsetAsync(a.counter, 0, sizeof(int32_t), stream));
+  const int want = (nrows + kNlWarps * kNlChunkRows - 1) / (kNlWarps * kNlChunkRows);
+  const int blocks = min_int(want, 2 * sm_count());
+  {
+    LaunchScope ls(ADJ ? K_NL_ADJ_ROWS : K_NL_FWD, stream);
+    nl_rows_kernel<XL, H, ADJ><<<blocks, kNlThreads, smem_rows, stream>>>(a);
+  }
+  if (int rc = check_launch("nl_rows_kernel")) return rc;
+  if (n_long > 0) {
+    LaunchScope ls(ADJ ? K_NL_ADJ_LONG : K_NL_FWD_LONG, stream);
+    nl_long_kernel<XL, H, ADJ><<<n_long, kNlThreads, smem_long, stream>>>(a);
+    return check_launch("nl_long_kernel");
+  }
+  return GB_OK;
+}
+
+template <bool ADJ>
+int nl_dispatch(const NlArgs& a, int heads, int n_long, cudaStream_t stream) {
+#define GB_NL_CASE(XLV, HV) \
+  if (xl == XLV && heads == HV) return nl_launch<XLV, HV, ADJ>(a, n_long, stream);
+  const int xl = a.dv <= 16 ? 16 : 32;
+  GB_NL_CASE(32, 4) GB_NL_CASE(32, 8) GB_NL_CASE(32, 2) GB_NL_CASE(32, 1)
+  GB_NL_CASE(16, 4) GB_NL_CASE(16, 8) GB_NL_CASE(16, 2) GB_NL_CASE(16, 1)
+#undef GB_NL_CASE
+  set_error("nl kernels: unsupported heads=%d", heads);
+  return GB_ERR_UNSUPPORTED;
+}
+
+// defined in nl_fwd.cu / nl_adj.cu (one translation unit per direction: they compile in parallel)
+int nl_dispatch_fwd(const NlArgs& a, int heads, int n_long, cudaStream_t stream);
+int nl_dispatch_adj(const NlArgs& a, int heads, int n_long, cudaStream_t stream);
+
+}  // namespace gb

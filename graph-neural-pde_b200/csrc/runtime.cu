@@ -26,7 +26,8 @@ static const char* kNames[K_NUM_KERNELS] = {
     "linear_fwd",         "linear_bwd_x",      "linear_bwd_w",      "linear_bwd_w_reduce", "edge_softmax_fwd",
     "edge_softmax_fwd_long", "sddmm",          "edge_softmax_bwd",  "edge_score_bwd_q",  "edge_score_bwd_k",
     "plan",               "edge_util",         "fused_att_spmm_fwd", "fused_att_bwd_row", "fused_att_bwd_col",
-    "linear_tc",          "stage_axpy"};
+    "linear_tc",          "stage_axpy",        "nl_fwd",            "nl_fwd_long",       "nl_adj_rows",
+    "nl_adj_long"};
 
 void set_error(const char* fmt, ...) {
   char buf[1024];

@@ -33,6 +33,9 @@ struct SpmmArgs {
   float* partials;         // [blocks][2]
   const int32_t* long_list;
   int32_t partial_base;    // first partial slot of this launch
+  // 1-D row partition (backward only): segments outside [part_lo, part_hi) are columns this rank does not
+  // own - it contributes sum_e a_e g[row_e] but not the "- g[j]" self term nor <g_j, x0_j>.  0,0 = own all.
+  int32_t part_lo, part_hi;
 };
 
 __device__ __forceinline__ float load_alpha(const SpmmArgs& a) {
@@ -44,7 +47,8 @@ __device__ __forceinline__ float load_alpha(const SpmmArgs& a) {
 template <int V, bool BWD>
 __device__ __forceinline__ void row_epilogue(const SpmmArgs& a, int row, int col, const Vec<V>& acc, float alpha,
                                              float beta, float& s1, float& s2) {
-  const Vec<V> self = Vec<V>::load_stream(a.src + (size_t)row * a.lds + col);
+  const bool owned = !BWD || a.part_hi == 0 || (row >= a.part_lo && row < a.part_hi);
+  const Vec<V> self = owned ? Vec<V>::load_stream(a.src + (size_t)row * a.lds + col) : Vec<V>::zero();
   Vec<V> t = Vec<V>::map2(acc, self, [](float p, float q) { return p - q; });
   if (!BWD) {
     Vec<V> f = Vec<V>::map2(t, t, [alpha](float p, float) { return alpha * p; });
@@ -72,7 +76,7 @@ __device__ __forceinline__ void row_epilogue(const SpmmArgs& a, int row, int col
     }
     dx.store_stream(dxp);
     if (a.x != nullptr) s1 += Vec<V>::load_stream(a.x + (size_t)row * a.ldx + col).dot(t);
-    if (a.x0 != nullptr) s2 += Vec<V>::load_stream(a.x0 + (size_t)row * a.ldx0 + col).dot(self);
+    if (a.x0 != nullptr && owned) s2 += Vec<V>::load_stream(a.x0 + (size_t)row * a.ldx0 + col).dot(self);
   }
 }
 

@@ -20,7 +20,8 @@ from torch import nn
 from .base_classes import ODEFunc
 from . import _lib
 from . import plan as _plan
-from .ops import QKProjFn, EdgeSoftmaxFn, DiffusionFn, ToCooOrderFn, FusedTransformerFn, fused_transformer_supported
+from .ops import (QKProjFn, EdgeSoftmaxFn, DiffusionFn, ToCooOrderFn, FusedTransformerFn, fused_transformer_supported,
+                  NlTransformerFn, nl_supported, nl_eval_vjp)
 
 
 class SpGraphTransAttentionLayer(nn.Module):
@@ -152,8 +153,12 @@ class ODEFuncTransformerAtt(ODEFunc):
         L = self.multihead_att_layer
         att_type = L._check_supported()
         edge_w = L.edge_weights if self.opt.get('reweight_attention', False) else None
-        if fused_transformer_supported(plan, x2, L.h, L.attention_dim, att_type, int(self.opt['attention_norm_idx']),
-                                       edge_w):
+        if nl_supported(plan, x2, L.h, L.attention_dim, att_type, int(self.opt['attention_norm_idx']), edge_w):
+            f = NlTransformerFn.apply(x2, L.Q.weight, L.Q.bias, L.K.weight, L.K.bias, self.alpha_train,
+                                      self.beta_train if x0 is not None else None, x0, plan, L.h,
+                                      not self.opt['no_alpha_sigmoid'], None)
+        elif fused_transformer_supported(plan, x2, L.h, L.attention_dim, att_type,
+                                         int(self.opt['attention_norm_idx']), edge_w):
             kparams = None
             if att_type == _lib.GB_ATT['exp_kernel']:
                 kparams = torch.cat([L.output_var.detach(), L.lengthscale.detach()]).to(torch.float32).contiguous()
@@ -165,6 +170,39 @@ class ODEFuncTransformerAtt(ODEFunc):
             f = DiffusionFn.apply(x2, abar, self.alpha_train, self.beta_train if x0 is not None else None, x0, plan,
                                   not self.opt['no_alpha_sigmoid'], None)
         return f.view_as(x)
+
+    def eval_vjp(self, t, x, cot, params):
+        """f(t, x) and the vector-Jacobian products cot^T df/d(x, params) in one fused pass - what the adjoint
+        solver's augmented dynamics need (the reference gets them from `func(t, y)` followed by
+        `autograd.grad`, src/base_classes.py:45-48 via torchdiffeq).  `params`: the tensors the solver wants
+        gradients for; returns (f, vjp_x, [vjp_p or None ...]) or None when the fused path does not apply
+        (the solver then falls back to autograd on forward())."""
+        if self.opt.get('mix_features', False):
+            return None
+        x2 = self._as_2d(x)
+        plan = self._plan(x2.shape[0])
+        L = self.multihead_att_layer
+        att_type = L._check_supported()
+        edge_w = L.edge_weights if self.opt.get('reweight_attention', False) else None
+        if not nl_supported(plan, x2, L.h, L.attention_dim, att_type, int(self.opt['attention_norm_idx']), edge_w):
+            return None
+        self._check_nfe()
+        source = bool(self.opt['add_source'])
+        x0 = self._as_2d(self.x0) if (source and self.x0 is not None) else None
+        named = {'alpha_train': self.alpha_train, 'beta_train': self.beta_train, 'Q.weight': L.Q.weight,
+                 'Q.bias': L.Q.bias, 'K.weight': L.K.weight, 'K.bias': L.K.bias}
+        want_w = any(p is q for p in params for q in (L.Q.weight, L.Q.bias, L.K.weight, L.K.bias))
+        f, dx, grads = nl_eval_vjp(x2, self._as_2d(cot), L.Q.weight, L.Q.bias, L.K.weight, L.K.bias, self.alpha_train,
+                                   self.beta_train if x0 is not None else None, x0, plan, L.h,
+                                   not self.opt['no_alpha_sigmoid'], want_w=want_w)
+        out = []
+        for p in params:
+            g = None
+            for name, q in named.items():
+                if p is q:
+                    g = grads.get(name)
+            out.append(g)
+        return f.view_as(x), dx.view_as(x), out
 
     def __repr__(self):
         return self.__class__.__name__ + ' (' + str(self.in_features) + ' -> ' + str(self.out_features) + ')'

@@ -248,8 +248,18 @@ class _OdeintAdjoint(torch.autograd.Function):
         times = ctx.times
         ys, = ctx.saved_tensors
 
+        fused_vjp = getattr(func, 'eval_vjp', None)
+
         def aug_dynamics(tt, state):
             y, a_y = state[1], state[2]
+            if fused_vjp is not None:
+                # the function evaluates f and cot^T df/d(y, params) in one fused pass (same numbers as
+                # func(t, y) followed by autograd.grad; df/dt == 0 for the autonomous ODE functions)
+                res = fused_vjp(tt, y, -a_y, params)
+                if res is not None:
+                    f, vy, vps = res
+                    vp = [g if g is not None else torch.zeros_like(p) for g, p in zip(vps, params)]
+                    return (torch.zeros_like(tt), f, vy, *vp)
             with torch.enable_grad():
                 tt_ = tt.detach().requires_grad_(True)
                 y_ = y.detach().requires_grad_(True)

@@ -303,3 +303,144 @@ class ToCooOrderFn(torch.autograd.Function):
         if plan.identity_order:
             return g, None
         return g[plan.eperm.long()], None
+
+
+# ---- single-gather GRAND-nl path (csrc/nl_kernels.cuh) --------------------------------------------
+_NL_WS = {}
+
+
+def _nl_workspace(device):
+    ws = _NL_WS.get(device)
+    if ws is None:
+        ws = torch.zeros(int(_lib.load().gb_nl_workspace_bytes()), dtype=torch.uint8, device=device)
+        _NL_WS[device] = ws
+    return ws
+
+
+def nl_supported(plan, x, heads, adim, att_type, norm_idx, edge_w):
+    """can the single-gather kernels take this evaluation?  (scaled_dot, attention_norm_idx 0, no edge
+    reweighting, d <= 128; otherwise the k-gather kernels of fused_att.cu / attention.cu run)"""
+    if norm_idx != 0 or edge_w is not None or att_type != _lib.GB_ATT['scaled_dot'] or adim % heads != 0:
+        return False
+    if plan.long_threshold != 256 or x.dtype != torch.float32 or not x.is_cuda or x.dim() != 2:
+        return False
+    return bool(_lib.load().gb_nl_supported(heads, adim // heads, x.shape[1]))
+
+
+def _nl_vjp(plan, rows, x, q, wq, wk, x0, alpha_train, beta_train, alpha_sigmoid, heads, gout, want_f, want_params,
+            x_row_offset=0):
+    """shared by NlTransformerFn.backward and nl_eval_vjp.  Returns (f|None, dx_direct [Ncols,d], dqk [Nrows?,2A],
+    dparams|None).  All row-indexed tensors are full-height here (one GPU)."""
+    lib = _lib.load()
+    n, d = x.shape
+    a = wq.shape[0]
+    dk = a // heads
+    dev = x.device
+    ds = torch.empty(plan.e, heads, dtype=torch.float32, device=dev)
+    dabar = torch.empty(plan.e, dtype=torch.float32, device=dev)
+    abar = torch.empty(plan.e, dtype=torch.float32, device=dev)
+    dqk = torch.empty(n, 2 * a, dtype=torch.float32, device=dev)
+    dx = torch.empty(n, d, dtype=torch.float32, device=dev)
+    out = torch.empty(n, d, dtype=torch.float32, device=dev) if want_f else None
+    partials = torch.empty(int(lib.gb_att_bwd_fused_partials(plan.c)), dtype=torch.float32, device=dev)
+    dparams = torch.empty(2, dtype=torch.float32, device=dev) if want_params else None
+    source = beta_train is not None and x0 is not None
+    _lib.check(lib.gb_nl_adjoint(plan.c, rows[0], rows[1], x.data_ptr(), d, q.data_ptr(), a, wk.data_ptr(), d, heads, dk,
+                                 d, _lib.ptr(x0) if source else None, d, alpha_train.data_ptr(), int(alpha_sigmoid),
+                                 beta_train.data_ptr() if source else None, gout.data_ptr(), d, _lib.ptr(out), d,
+                                 ds.data_ptr(), dabar.data_ptr(), abar.data_ptr(), dqk.data_ptr(), 2 * a,
+                                 dqk.data_ptr() + 4 * a, 2 * a, dx.data_ptr(), d, partials.data_ptr(),
+                                 _lib.ptr(dparams), _nl_workspace(dev).data_ptr(), _lib.stream()), 'gb_nl_adjoint')
+    return out, dx, dqk, dparams
+
+
+def _nl_dense_tail(x, dqk, w_cat, dx, want_w):
+    """dx += [dq|dk] [Wq;Wk];  d[Wq;Wk] = [dq|dk]^T x, d[bq;bk] = column sums"""
+    lib = _lib.load()
+    n, d = x.shape
+    a2 = dqk.shape[1]
+    _lib.check(lib.gb_linear_bwd_x(dqk.data_ptr(), a2, n, a2, w_cat.data_ptr(), d, dx.data_ptr(), d, 1,
+                                   _lib.stream()), 'gb_linear_bwd_x')
+    if not want_w:
+        return None, None
+    dw = torch.empty(a2, d, dtype=torch.float32, device=x.device)
+    db = torch.empty(a2, dtype=torch.float32, device=x.device)
+    ws = torch.empty(int(lib.gb_linear_bwd_w_workspace_bytes(n, d, a2)), dtype=torch.uint8, device=x.device)
+    _lib.check(lib.gb_linear_bwd_w(dqk.data_ptr(), a2, x.data_ptr(), d, n, d, a2, dw.data_ptr(), db.data_ptr(),
+                                   ws.data_ptr(), ws.numel(), _lib.stream()), 'gb_linear_bwd_w')
+    return dw, db
+
+
+def _nl_q(x, wq, bq):
+    lib = _lib.load()
+    n, d = x.shape
+    a = wq.shape[0]
+    q = torch.empty(n, a, dtype=torch.float32, device=x.device)
+    _lib.check(lib.gb_linear_fwd(x.data_ptr(), d, n, d, wq.data_ptr(), bq.data_ptr(), a, q.data_ptr(), a,
+                                 _lib.stream()), 'gb_linear_fwd')
+    return q
+
+
+class NlTransformerFn(torch.autograd.Function):
+    """One GRAND-nl evaluation (ODEFuncTransformerAtt.forward, function_transformer_attention.py:44-59) as the
+    Q projection GEMM + ONE single-gather graph kernel; nothing per-edge is stored for the backward pass,
+    which re-runs the row pass fused with the VJP (the x[col] gather is needed by the SDDMM anyway)."""
+
+    @staticmethod
+    def forward(ctx, x, wq, bq, wk, bk, alpha_train, beta_train, x0, plan, heads, alpha_sigmoid, stage):
+        lib = _lib.load()
+        _lib.require_cuda(x, wq, bq, wk, bk, alpha_train, beta_train, x0)
+        x = _f32c(x)
+        wq, wk, bq = _f32c(wq), _f32c(wk), _f32c(bq)
+        n, d = x.shape
+        a = wq.shape[0]
+        source = beta_train is not None and x0 is not None
+        if source:
+            x0 = _f32c(x0)
+        q = _nl_q(x, wq, bq)
+        out = torch.empty_like(x)
+        _lib.check(lib.gb_nl_fwd(plan.c, 0, n, x.data_ptr(), d, q.data_ptr(), a, wk.data_ptr(), d, heads, a // heads, d,
+                                 _lib.ptr(x0) if source else None, d, alpha_train.data_ptr(), int(alpha_sigmoid),
+                                 beta_train.data_ptr() if source else None, out.data_ptr(), d, stage,
+                                 _nl_workspace(x.device).data_ptr(), _lib.stream()), 'gb_nl_fwd')
+        ctx.save_for_backward(x, wq, wk, q, alpha_train, beta_train if source else None, x0 if source else None)
+        ctx.plan, ctx.heads, ctx.alpha_sigmoid = plan, heads, int(alpha_sigmoid)
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gout):
+        x, wq, wk, q, alpha_train, beta_train, x0 = ctx.saved_tensors
+        n = x.shape[0]
+        a = wq.shape[0]
+        gout = _f32c(gout)
+        want_params = ctx.needs_input_grad[5] or ctx.needs_input_grad[6]
+        _, dx, dqk, dparams = _nl_vjp(ctx.plan, (0, n), x, q, wq, wk, x0, alpha_train, beta_train, ctx.alpha_sigmoid,
+                                      ctx.heads, gout, False, want_params)
+        w_cat = torch.cat([wq, wk], dim=0)
+        dw, db = _nl_dense_tail(x, dqk, w_cat, dx, any(ctx.needs_input_grad[1:5]))
+        dwq = dbq = dwk = dbk = None
+        if dw is not None:
+            dwq, dbq, dwk, dbk = dw[:a], db[:a], dw[a:], db[a:]
+        dalpha = dparams[0].reshape(alpha_train.shape) if ctx.needs_input_grad[5] else None
+        dbeta = dparams[1].reshape(()) if (ctx.needs_input_grad[6] and beta_train is not None) else None
+        return (dx if ctx.needs_input_grad[0] else None, dwq, dbq, dwk, dbk, dalpha, dbeta) + (None,) * 5
+
+
+def nl_eval_vjp(x, gout, wq, bq, wk, bk, alpha_train, beta_train, x0, plan, heads, alpha_sigmoid, want_w=True):
+    """f(x) and the VJP of f at x with cotangent gout in ONE fused pass (what an adjoint solver needs at every
+    stage: torchdiffeq's augmented dynamics evaluate f and then call autograd.grad on it).  Returns
+    (f, dx, {name: grad}) with the parameter gradients keyed like the autograd inputs."""
+    x, gout = _f32c(x.detach()), _f32c(gout.detach())
+    wq_, wk_, bq_ = _f32c(wq.detach()), _f32c(wk.detach()), _f32c(bq.detach())
+    n = x.shape[0]
+    a = wq_.shape[0]
+    source = beta_train is not None and x0 is not None
+    q = _nl_q(x, wq_, bq_)
+    f, dx, dqk, dparams = _nl_vjp(plan, (0, n), x, q, wq_, wk_, _f32c(x0) if source else None, alpha_train.detach(),
+                                  beta_train.detach() if source else None, int(alpha_sigmoid), heads, gout, True, True)
+    dw, db = _nl_dense_tail(x, dqk, torch.cat([wq_, wk_], dim=0), dx, want_w)
+    grads = {'alpha_train': dparams[0].reshape(alpha_train.shape), 'beta_train': dparams[1].reshape(()) if source else None}
+    if dw is not None:
+        grads.update({'Q.weight': dw[:a], 'Q.bias': db[:a], 'K.weight': dw[a:], 'K.bias': db[a:]})
+    return f, dx, grads

@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define GB_ABI_VERSION 1
+#define GB_ABI_VERSION 2
 
 typedef enum {
   GB_OK = 0,
@@ -233,6 +233,37 @@ int gb_att_bwd_fused(const gb_graph* g, const float* q, int32_t ldq, const float
                      int32_t alpha_sigmoid, int32_t d, float* ds, float* dabar_scratch, float* dq, int32_t lddq,
                      float* dk_out, int32_t lddk, float* dx, int32_t lddx, float* partials, float* dparams,
                      void* stream);
+
+/* ---- single-gather GRAND-nl evaluation and VJP (csrc/nl_kernels.cuh; scaled_dot, attention_norm_idx 0) ----
+ * One row gather per edge: scores are formed as <Wk_h^T q_ih / sqrt(dk), x_j> (the per-(row, head) constant
+ * <q_ih, bk_h> cancels in the row softmax), the softmax is online, so neither k = x Wk^T + bk nor the
+ * attention [E,H] is ever materialised in the forward pass.  Replaces, per evaluation,
+ * ODEFuncTransformerAtt.forward (function_transformer_attention.py:44-59) after the Q projection.
+ *
+ * Rows [row_lo, row_hi) are evaluated (1-D row partition; pass 0, g->n on one GPU).  Matrices indexed by the
+ * row (q, x0, out, gout, dq) are addressed with the GLOBAL row id; x is addressed by global column id.
+ * workspace: gb_nl_workspace_bytes() bytes of device memory (scheduler counter). */
+int gb_nl_supported(int32_t heads, int32_t dk, int32_t d);   /* heads in {1,2,4,8}, dk % 4 == 0, d % 4 == 0, d <= 128 */
+size_t gb_nl_workspace_bytes(void);
+int gb_nl_fwd(const gb_graph* g, int32_t row_lo, int32_t row_hi, const float* x, int32_t ldx,
+              const float* q, int32_t ldq, const float* wk, int32_t ldwk, int32_t heads, int32_t dk, int32_t d,
+              const float* x0, int32_t ldx0, const float* alpha_train, int32_t alpha_sigmoid,
+              const float* beta_train, float* out, int32_t ldo, const gb_stage* stage,
+              void* workspace, void* stream);
+/* Evaluation + VJP in one row pass and one column pass, given gout = dL/df (rows [row_lo,row_hi)):
+ *   rows    : [out = f when out != NULL], dq [rows, A], ds [E,H], abar [E]   (dabar_scratch [E] is caller scratch)
+ *   columns : dx[j,:] = alpha (sum_{e: col_e = j} abar_e gout[row_e,:] - [j owned] gout[j,:])   for ALL columns j
+ *             dk[j,:] = sum_e ds[e,:] q[row_e,:] / sqrt(dk)                                      for ALL columns j
+ *             dparams = {dalpha_train, dbeta_train} (this rank's share when partitioned)
+ * The caller finishes with dense GEMMs: dx += dq Wq + dk Wk, dWq = dq^T x, dWk = dk^T x, db = column sums.
+ * partials: gb_att_bwd_fused_partials(g) floats, 8-byte aligned. */
+int gb_nl_adjoint(const gb_graph* g, int32_t row_lo, int32_t row_hi, const float* x, int32_t ldx,
+                  const float* q, int32_t ldq, const float* wk, int32_t ldwk, int32_t heads, int32_t dk, int32_t d,
+                  const float* x0, int32_t ldx0, const float* alpha_train, int32_t alpha_sigmoid,
+                  const float* beta_train, const float* gout, int32_t ldg, float* out, int32_t ldo,
+                  float* ds, float* dabar_scratch, float* abar, float* dq, int32_t lddq,
+                  float* dk_out, int32_t lddk, float* dx, int32_t lddx, float* partials, float* dparams,
+                  void* workspace, void* stream);
 
 #ifdef __cplusplus
 }

@@ -34,7 +34,7 @@ def test_library_exports_every_declared_symbol():
 def test_ctypes_table_matches_header_and_loads():
     import grand_b200
     lib = grand_b200._lib.load()
-    assert lib.gb_abi_version() == 1
+    assert lib.gb_abi_version() == 2
     assert sorted(grand_b200._lib.SIGNATURES) == declared_symbols()
     assert lib.gb_prof_num_kernels() > 0 and lib.gb_prof_name(0) == b'spmm_fwd'
 

@@ -216,16 +216,37 @@ def test_fused_path_matches_composite_path_and_is_deterministic(d, heads, adim, 
         out = func(0.0, xg)
         return [out.detach()] + list(torch.autograd.grad(out, [xg] + params, dev(gout)))
 
-    assert fta.fused_transformer_supported(grand_b200.get_plan(func.edge_index, n), dev(x), heads, adim, 0, 0, None)
+    plan = grand_b200.get_plan(func.edge_index, n)
+    assert fta.fused_transformer_supported(plan, dev(x), heads, adim, 0, 0, None)
+    assert fta.nl_supported(plan, dev(x), heads, adim, 0, 0, None)
+    names = ('f', 'gx', 'gwq', 'gbq', 'gwk', 'gbk', 'galpha', 'gbeta')
+
+    def compare(a_list, b_list, tol):
+        bias_scale = max(float(b_list[3].abs().max()), float(b_list[5].abs().max()))
+        for a, b, name in zip(a_list, b_list, names):
+            assert_close(a, b, tol, name, floor=bias_scale if name in ('gbq', 'gbk') else 0.0)
+
+    # (1) single-gather kernels (nl_kernels.cuh): deterministic, no-grad variant identical, fused eval+VJP identical
+    nl_a, nl_b = run(), run()
+    for a, b in zip(nl_a, nl_b):
+        assert torch.equal(a, b)
+    with torch.no_grad():
+        assert torch.equal(func(0.0, dev(x)), nl_a[0])
+    f2, vx, vps = func.eval_vjp(0.0, dev(x), dev(gout), params)
+    assert_close(f2, nl_a[0], 1e-6, 'f from the adjoint row kernel vs the forward kernel')
+    for a, b in zip([vx] + vps, nl_a[1:]):
+        assert torch.equal(a, b)
+    # (2) k-gather warp-per-row kernels (fused_att.cu)
+    monkeypatch.setattr(fta, 'nl_supported', lambda *a, **k: False)
+    assert func.eval_vjp(0.0, dev(x), dev(gout), params) is None
     fused_a, fused_b = run(), run()
     for a, b in zip(fused_a, fused_b):
         assert torch.equal(a, b)                                             # bit-reproducible
     with torch.no_grad():
         nograd = func(0.0, dev(x))                                           # store == 0 variant of the kernel
     assert torch.equal(nograd, fused_a[0])
+    # (3) general composite kernels
     monkeypatch.setattr(fta, 'fused_transformer_supported', lambda *a, **k: False)
     comp = run()
-    names = ('f', 'gx', 'gwq', 'gbq', 'gwk', 'gbk', 'galpha', 'gbeta')
-    bias_scale = max(float(comp[3].abs().max()), float(comp[5].abs().max()))
-    for a, b, name in zip(fused_a, comp, names):
-        assert_close(a, b, 2e-5, name, floor=bias_scale if name in ('gbq', 'gbk') else 0.0)
+    compare(fused_a, comp, 2e-5)
+    compare(nl_a, comp, 2e-5)
