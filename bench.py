@@ -181,13 +181,15 @@ def run_ours(args):
     local = int(os.environ.get('LOCAL_RANK', '0'))
     torch.cuda.set_device(local)
     device = torch.device('cuda', local)
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group('nccl', device_id=device)
     name = args.workload
     cfg = dict(synth.CONFIGS[name])
     if world > 1:
-        return run_partitioned(args, cfg, device, rank, world)
+        import torch.distributed as dist
+        dist.init_process_group('nccl', device_id=device)
+        try:
+            return run_partitioned(args, cfg, device, rank, world)
+        finally:
+            dist.destroy_process_group()
     ei, n = synth.make_graph(name, device)
     data = grand_b200.GraphData()
     data.new_graph(ei, n)
@@ -282,7 +284,136 @@ def run_ours(args):
 
 
 def run_partitioned(args, cfg, device, rank, world):
-    raise SystemExit('bench.py --gpus N>1: the row-partitioned path is not wired yet (see DESIGN.md section e)')
+    """N > 1: the same training pass with the graph split by rows over the ranks (grand_b200/partition.py):
+    one all-gather of the state per evaluation, one reduce-scatter of dL/dx per VJP, all over NCCL.  Total
+    work is fixed as N grows (strong scaling).  Timed on the device, max over ranks."""
+    import torch.distributed as dist
+    import grand_b200
+    from grand_b200 import synth, _lib
+    name = args.workload
+    local = device.index
+    n = cfg['n'] if name != 'c5' else 1 << 24
+    # rank 0 draws the graph, everybody receives it (identical global graph on every rank)
+    if rank == 0:
+        ei, n = synth.make_graph(name, device)
+        meta = torch.tensor([ei.shape[1], n], device=device)
+    else:
+        meta = torch.zeros(2, dtype=torch.int64, device=device)
+    dist.broadcast(meta, 0)
+    if rank != 0:
+        ei = torch.empty(2, int(meta[0]), dtype=torch.int64, device=device)
+    n = int(meta[1])
+    dist.broadcast(ei, 0)
+    data = grand_b200.GraphData()
+    data.new_graph(ei, n)
+    d = cfg['d']
+    part = grand_b200.RowPartition(n, world, rank)
+    halo = grand_b200.Halo(part)
+    gen = torch.Generator(device=device).manual_seed(99 + rank)
+    x_dev = torch.randn(part.slab, d, generator=gen, device=device)
+    g_dev = torch.randn(part.slab, d, generator=gen, device=device)
+    x_dev[part.hi - part.lo:] = 0                       # zero padding rows of the last slab
+    g_dev[part.hi - part.lo:] = 0
+    x_host = x_dev.cpu().pin_memory()
+    block = build_block(cfg, device)
+    block.set_partition(part, halo)
+
+    for _ in range(max(args.warmup, 3)):
+        evals, loss = train_pass(block, data, x_dev, g_dev)
+    torch.cuda.synchronize()
+    del ei
+    e_local = int(block.odefunc.edge_index.shape[-1])
+    e_total = torch.tensor([e_local], device=device)
+    dist.all_reduce(e_total)
+
+    def timed(fn):
+        start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        dist.barrier()
+        torch.cuda.synchronize()
+        start.record()
+        out = fn()
+        stop.record()
+        torch.cuda.synchronize()
+        dist.barrier()
+        ms = torch.tensor([start.elapsed_time(stop)], device=device)
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)       # max over ranks
+        return float(ms), out
+
+    launches0 = _lib.launch_count()
+    halo.bytes_in = 0
+
+    def loop():
+        tot = 0
+        for _ in range(args.steps):
+            ev, _ = train_pass(block, data, x_dev, g_dev)
+            tot += ev
+        return tot
+
+    with ClockSampler(local) as clocks, _lib.Profiler() as prof:
+        ms, total_evals = timed(loop)
+        kernels = prof.results()
+    launches = _lib.launch_count() - launches0
+    halo_bytes = halo.bytes_in
+
+    gx_host = torch.empty(part.slab, d).pin_memory()
+
+    def loop_e2e():
+        tot = 0
+        for _ in range(args.steps):
+            xin = x_host.to(device, non_blocking=True)
+            func = block.odefunc
+            func.nfe = 0
+            xg = xin.requires_grad_(True)
+            block.set_x0(xg)
+            z = block(xg, data)
+            loss = (z * g_dev).sum()
+            gx, = torch.autograd.grad(loss, xg)
+            gx_host.copy_(gx, non_blocking=True)
+            float(loss.detach())
+            tot += func.nfe
+        return tot
+
+    ms_e2e, evals_e2e = timed(loop_e2e)
+    if rank != 0:
+        return
+    peak, peak_src = read_peaks()
+    rows = part.hi - part.lo
+    alg = algorithmic_bytes(rows, e_local, d, cfg['adim'], cfg['heads'])
+    gat = gather_bytes(rows, e_local, d, cfg['adim'], cfg['heads'])
+    kname, kstat = max(kernels.items(), key=lambda kv: kv[1]['ms'])
+    per_launch_ms = kstat['ms'] / kstat['launches']
+    achieved = alg.get(kname, 0) / (per_launch_ms * 1e-3) / 1e9 if per_launch_ms > 0 else 0.0
+    ksum = sum(v['ms'] for v in kernels.values())
+    roofline = {'bound': 'hbm', 'kernel': kname, 'achieved': round(achieved, 1), 'peak': peak, 'unit': 'GB/s',
+                'frac': round(achieved / peak, 4), 'traffic': None, 'peak_source': peak_src,
+                'algorithmic_bytes_per_launch': alg.get(kname, 0), 'avg_launch_ms': round(per_launch_ms, 4),
+                'note': "rank 0's kernels on its row slab (algorithmic bytes of the slab)",
+                'kernels': {k: {'ms_per_launch': round(v['ms'] / v['launches'], 4), 'launches': v['launches'],
+                                'share': round(v['ms'] / ksum, 4),
+                                'gather_model_GBps': round((alg[k] + gat[k]) / (v['ms'] / v['launches'] * 1e-3) / 1e9, 1)
+                                if k in alg and k in gat else None}
+                            for k, v in sorted(kernels.items(), key=lambda kv: -kv[1]['ms'])}}
+    line = {
+        'metric': 'ODE-func evals/sec (fwd + adjoint bwd)', 'value': round(total_evals / (ms * 1e-3), 3),
+        'unit': 'evals/s', 'n_gpus': world, 'steps': args.steps, 'warmup': max(args.warmup, 3),
+        'ms_per_step': round(ms / args.steps, 3), 'higher_is_better': True, 'scaling': 'strong',
+        'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': {'workload': f"{name}: GRAND-nl ({cfg['desc']}), N={n}, E'={int(e_total)}, d={d}, heads={cfg['heads']}, "
+                               f"attention_dim={cfg['adim']}, AttODEblock + ODEFuncTransformerAtt, rk4 step {STEP_SIZE} "
+                               f"T={T_END}, odeint_adjoint (rk4)",
+                   'parallelism': f'1-D row partition over {world} GPUs ({part.slab} rows each), all-gather of the '
+                                  f'state per evaluation + reduce-scatter of dL/dx per VJP (NCCL)',
+                   'evals_per_step': evals, 'l2': 'inputs larger than L2 (no flush)'},
+        'e2e': {'value': round(evals_e2e / (ms_e2e * 1e-3), 3), 'unit': 'evals/s',
+                'h2d_bytes_per_step': world * part.slab * d * 4, 'd2h_bytes_per_step': world * (part.slab * d * 4 + 4),
+                'ms_per_step': round(ms_e2e / args.steps, 3)},
+        'gpu_launches': int(launches), 'clocks': clocks.summary(), 'roofline': roofline,
+        'nvlink': {'bytes_in_per_rank_per_step': halo_bytes // args.steps,
+                   'GBps_in_per_rank_if_serial': round(halo_bytes / (ms * 1e-3) / 1e9, 1), 'peak_GBps': 770.0,
+                   'note': 'received bytes of the all-gathers / reduce-scatters divided by the WHOLE step time '
+                           '(the exchanges are not overlapped with compute yet)'},
+    }
+    print(json.dumps(line))
 
 
 # ---- CPU baseline / reference arm (the only place bench.py executes oracle/) ----------------------

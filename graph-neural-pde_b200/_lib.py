@@ -59,8 +59,12 @@ SIGNATURES = {
     'gb_head_mean_gather': (C.c_int, [_P, _I32, _P, _I64, _P, _P]),
     'gb_scatter_rows_f32': (C.c_int, [_P, _I32, _P, _I64, _P, _P]),
     'gb_spmm_fwd': (C.c_int, [_G, _P, _P, _I32, _P, _I32, _P, _I32, _P, _I32, _P, _I32, C.POINTER(GbStage), _P]),
+    'gb_spmm_fwd_part': (C.c_int, [_G, _I32, _I32, _P, _P, _I32, _P, _I32, _P, _I32, _P, _I32, _P, _I32,
+                                   C.POINTER(GbStage), _P]),
     'gb_spmm_bwd_partials': (_SZ, [_G, _I32]),
     'gb_spmm_bwd': (C.c_int, [_G, _P, _P, _I32, _P, _I32, _P, _I32, _P, _I32, _I32, _P, _I32, _I32, _P, _P, _P]),
+    'gb_spmm_bwd_part': (C.c_int, [_G, _I32, _I32, _P, _P, _I32, _P, _I32, _P, _I32, _P, _I32, _I32, _P, _I32, _I32, _P,
+                                   _P, _P]),
     'gb_linear_fwd': (C.c_int, [_P, _I32, _I32, _I32, _P, _P, _I32, _P, _I32, _P]),
     'gb_linear_bwd_x': (C.c_int, [_P, _I32, _I32, _I32, _P, _I32, _P, _I32, _I32, _P]),
     'gb_linear_bwd_w_workspace_bytes': (_SZ, [_I32, _I32, _I32]),

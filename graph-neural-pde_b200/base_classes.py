@@ -60,6 +60,9 @@ class ODEFunc(nn.Module):
         self.nfe = 0
         self.alpha_sc = nn.Parameter(torch.ones(1))
         self.beta_sc = nn.Parameter(torch.ones(1))
+        # (RowPartition, Halo) when the graph is split by rows over several GPUs (partition.py); the
+        # state is then this rank's [S, d] slab and edge_index holds the edges whose row it owns
+        self.partition = None
 
     # ---- helpers shared by the two ODE functions ------------------------------------------------
     @staticmethod
@@ -103,6 +106,14 @@ class ODEblock(nn.Module):
         self.test_integrator = None
         self.set_tol()
         self._graph_cache = None
+        self.partition = None
+
+    def set_partition(self, part, halo):
+        """split the graph by rows over the ranks of `halo` (partition.py): forward() then takes and returns
+        this rank's [S, d] slab of the state; `graph_data` stays the GLOBAL graph on every rank."""
+        self.partition = (part, halo)
+        self.odefunc.partition = self.partition
+        self._graph_cache = None
 
     def set_x0(self, x0):
         self.odefunc.x0 = x0.clone().detach()
@@ -142,6 +153,11 @@ class ODEblock(nn.Module):
                 if self.opt['self_loop_weight'] > 0:
                     edge_index, edge_weight = add_remaining_self_loops(
                         edge_index, edge_weight, fill_value=self.opt['self_loop_weight'], num_nodes=data.num_nodes)
+                if self.partition is not None:               # keep the edges whose row this rank owns
+                    batched = edge_index.dim() == 3
+                    edge_index, edge_weight = self.partition[0].local_edges(edge_index, edge_weight)
+                    if batched:
+                        edge_index, edge_weight = edge_index[None], edge_weight[None]
                 self._graph_cache = (key, ei, edge_index, edge_weight)
             _, _, edge_index, edge_weight = self._graph_cache
             self.data_edge_index = edge_index

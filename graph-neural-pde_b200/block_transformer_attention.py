@@ -24,5 +24,12 @@ class AttODEblock(ODEblock):
 
     def forward(self, x, graph_data, y=None):
         self.reset_graph_data(graph_data, x.dtype, y)
+        if self.partition is not None:
+            # row-partitioned graph: the block-level attention is only read by LaplacianODEFunc; with
+            # opt['function'] == 'transformer' the reference computes and discards it
+            if self.opt['function'] != 'transformer':
+                raise NotImplementedError("block 'attention' with a row-partitioned graph needs function 'transformer'")
+            self.odefunc.attention_weights = None
+            return self._integrate(x)
         self.odefunc.attention_weights = self.get_attention_weights(x)
         return self._integrate(x)

@@ -31,7 +31,7 @@ __global__ void __launch_bounds__(kSpmmThreads) spmm_rows(const SpmmArgs a) {
   float s1 = 0.f, s2 = 0.f;
 #pragma unroll 1
   for (int tile = 0; tile < kRowTiles; ++tile) {
-    const int row = (blockIdx.x * kRowTiles + tile) * RPT + grp;
+    const int row = a.row0 + (blockIdx.x * kRowTiles + tile) * RPT + grp;
     if (row >= a.n) break;
     const int start = __ldg(a.ptr + row), end = __ldg(a.ptr + row + 1);
     if (end - start > a.long_threshold) continue;    // handled by spmm_long
@@ -213,8 +213,8 @@ namespace {
 template <int V, int LPR, int CPL, bool BWD>
 int launch_shape(const SpmmArgs& a, int n_long, cudaStream_t stream) {
   constexpr int RPT = kSpmmThreads / LPR;
-  const int blocks = (a.n + RPT * kRowTiles - 1) / (RPT * kRowTiles);
-  {
+  const int blocks = (a.n - a.row0 + RPT * kRowTiles - 1) / (RPT * kRowTiles);
+  if (blocks > 0) {
     LaunchScope ls(BWD ? K_SPMM_BWD : K_SPMM_FWD, stream);
     spmm_rows<V, LPR, CPL, BWD><<<blocks, kSpmmThreads, 0, stream>>>(a);
   }
@@ -317,14 +317,23 @@ extern "C" {
 int gb_spmm_fwd(const gb_graph* g, const float* vals, const float* x, int32_t ldx, const float* x0, int32_t ldx0,
                 const float* alpha_train, int32_t alpha_sigmoid, const float* beta_train, int32_t d, float* out,
                 int32_t ldo, const gb_stage* stage, void* stream_) {
+  return gb_spmm_fwd_part(g, 0, g ? g->n : 0, vals, x, ldx, x0, ldx0, alpha_train, alpha_sigmoid, beta_train, d, out,
+                          ldo, stage, stream_);
+}
+
+int gb_spmm_fwd_part(const gb_graph* g, int32_t row_lo, int32_t row_hi, const float* vals, const float* x,
+                     int32_t ldx, const float* x0, int32_t ldx0, const float* alpha_train, int32_t alpha_sigmoid,
+                     const float* beta_train, int32_t d, float* out, int32_t ldo, const gb_stage* stage,
+                     void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   if (int rc = check_graph(g, "gb_spmm_fwd")) return rc;
+  GB_REQUIRE(row_lo >= 0 && row_lo <= row_hi && row_hi <= g->n, "gb_spmm_fwd: bad row range [%d, %d)", row_lo, row_hi);
   GB_REQUIRE(x && out && alpha_train && d > 0, "gb_spmm_fwd: null pointer or d <= 0");
   GB_REQUIRE(g->e == 0 || vals, "gb_spmm_fwd: null vals");
   GB_REQUIRE(ldx >= d && ldo >= d, "gb_spmm_fwd: leading dimension smaller than d");
   SpmmArgs a{};
   a.ptr = g->rowptr; a.idx = g->colidx; a.perm = nullptr; a.vals = vals;
-  a.n = g->n; a.long_threshold = g->long_threshold > 0 ? g->long_threshold : 0x7fffffff;
+  a.n = row_hi; a.row0 = row_lo; a.long_threshold = g->long_threshold > 0 ? g->long_threshold : 0x7fffffff;
   a.src = x; a.lds = ldx; a.alpha_train = alpha_train; a.alpha_sigmoid = alpha_sigmoid;
   const bool source = (x0 != nullptr && beta_train != nullptr);
   a.x0 = source ? x0 : nullptr; a.ldx0 = ldx0; a.beta_train = source ? beta_train : nullptr;
@@ -356,6 +365,14 @@ size_t gb_spmm_bwd_partials(const gb_graph* g, int32_t d) {
 int gb_spmm_bwd(const gb_graph* g, const float* vals, const float* gout, int32_t ldg, const float* x, int32_t ldx,
                 const float* x0, int32_t ldx0, const float* alpha_train, int32_t alpha_sigmoid, int32_t d, float* dx,
                 int32_t lddx, int32_t accumulate, float* partials, float* dparams, void* stream_) {
+  return gb_spmm_bwd_part(g, 0, 0, vals, gout, ldg, x, ldx, x0, ldx0, alpha_train, alpha_sigmoid, d, dx, lddx,
+                          accumulate, partials, dparams, stream_);
+}
+
+int gb_spmm_bwd_part(const gb_graph* g, int32_t own_lo, int32_t own_hi, const float* vals, const float* gout,
+                     int32_t ldg, const float* x, int32_t ldx, const float* x0, int32_t ldx0,
+                     const float* alpha_train, int32_t alpha_sigmoid, int32_t d, float* dx, int32_t lddx,
+                     int32_t accumulate, float* partials, float* dparams, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   if (int rc = check_graph(g, "gb_spmm_bwd")) return rc;
   GB_REQUIRE(gout && dx && alpha_train && d > 0, "gb_spmm_bwd: null pointer or d <= 0");
@@ -369,6 +386,7 @@ int gb_spmm_bwd(const gb_graph* g, const float* vals, const float* gout, int32_t
   a.x0 = dparams ? x0 : nullptr; a.ldx0 = ldx0;
   a.x = dparams ? x : nullptr; a.ldx = ldx;
   a.out = dx; a.ldo = lddx; a.accumulate = accumulate;
+  a.part_lo = own_lo; a.part_hi = own_hi;
   int v = min_int(vec_width(gout, ldg, d), vec_width(dx, lddx, d));
   if (a.x) v = min_int(v, vec_width(x, ldx, d));
   if (a.x0) v = min_int(v, vec_width(x0, ldx0, d));

@@ -36,6 +36,7 @@ struct SpmmArgs {
   // 1-D row partition (backward only): segments outside [part_lo, part_hi) are columns this rank does not
   // own - it contributes sum_e a_e g[row_e] but not the "- g[j]" self term nor <g_j, x0_j>.  0,0 = own all.
   int32_t part_lo, part_hi;
+  int32_t row0;            // first segment processed by the launch (forward row partition); segments [row0, n)
 };
 
 __device__ __forceinline__ float load_alpha(const SpmmArgs& a) {

@@ -51,9 +51,28 @@ class LaplacianODEFunc(ODEFunc):
             return flat if plan.identity_order else flat[plan.eperm.long()]
         return _plan.cached_per_edge(plan, src, 'w', lambda t: plan.to_csr_order(t.detach()))
 
+    def _partitioned(self, x, x2):
+        """row-partitioned evaluation (partition.py): x2 is this rank's [S, d] slab, edge_index / edge_weight
+        hold the edges whose row this rank owns"""
+        from . import partition as P
+        part, halo = self.partition
+        if self.opt['block'] != 'constant':
+            raise NotImplementedError("the row-partitioned GRAND-l path supports block 'constant' (fixed edge weights)")
+        if x2.shape[0] != part.slab:
+            raise ValueError(f'partitioned state must be the [{part.slab}, d] slab of this rank, got {tuple(x2.shape)}')
+        plan = self._plan(part.n_pad)
+        vals = self._edge_values(plan)
+        source = bool(self.opt['add_source'])
+        x0 = self._as_2d(self.x0).contiguous() if (source and self.x0 is not None) else None
+        f = P.PartDiffusionFn.apply(x2, vals, self.alpha_train, self.beta_train if x0 is not None else None, x0, part,
+                                    halo, plan, not self.opt['no_alpha_sigmoid'])
+        return f.view_as(x)
+
     def forward(self, t, x):  # the t param is needed by the ODE solver.
         self._check_nfe()
         x2 = self._as_2d(x)
+        if self.partition is not None:
+            return self._partitioned(x, x2)
         plan = self._plan(x2.shape[0])
         vals = self._edge_values(plan)
         source = bool(self.opt['add_source'])

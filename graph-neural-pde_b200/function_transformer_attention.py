@@ -147,6 +147,8 @@ class ODEFuncTransformerAtt(ODEFunc):
             raise NotImplementedError("opt['mix_features'] is broken in the reference "
                                       '(function_transformer_attention.py:23-32,49-50) and not implemented')
         x2 = self._as_2d(x)
+        if self.partition is not None:
+            return self._partitioned(x, x2, None)
         plan = self._plan(x2.shape[0])
         source = bool(self.opt['add_source'])
         x0 = self._as_2d(self.x0) if (source and self.x0 is not None) else None
@@ -171,6 +173,47 @@ class ODEFuncTransformerAtt(ODEFunc):
                                   not self.opt['no_alpha_sigmoid'], None)
         return f.view_as(x)
 
+    def _partitioned(self, x, x2, vjp):
+        """row-partitioned evaluation (partition.py): x2 is this rank's [S, d] slab.  vjp = None: autograd
+        forward; vjp = (cot, params): fused f + VJP for the adjoint solver."""
+        from . import partition as P
+        part, halo = self.partition
+        L = self.multihead_att_layer
+        att_type = L._check_supported()
+        edge_w = L.edge_weights if self.opt.get('reweight_attention', False) else None
+        if x2.shape[0] != part.slab:
+            raise ValueError(f'partitioned state must be the [{part.slab}, d] slab of this rank, got {tuple(x2.shape)}')
+        plan = self._plan(part.n_pad)
+        if not nl_supported(plan, x2, L.h, L.attention_dim, att_type, int(self.opt['attention_norm_idx']), edge_w):
+            raise NotImplementedError('the row-partitioned path supports scaled_dot attention with attention_norm_idx 0, '
+                                      'heads in {1,2,4,8}, d <= 128 (single-gather kernels)')
+        source = bool(self.opt['add_source'])
+        x0 = self._as_2d(self.x0).contiguous() if (source and self.x0 is not None) else None
+        sig = not self.opt['no_alpha_sigmoid']
+        if vjp is None:
+            f = P.PartNlFn.apply(x2, L.Q.weight, L.Q.bias, L.K.weight, L.K.bias, self.alpha_train,
+                                 self.beta_train if x0 is not None else None, x0, part, halo, plan, L.h, sig)
+            return f.view_as(x)
+        cot, params = vjp
+        self._check_nfe()
+        a, d = L.Q.weight.shape
+        f, dx, grads = P.nl_eval_vjp_part(part, halo, plan, x2.detach(), self._as_2d(cot).detach(),
+                                          L.Q.weight.detach().contiguous(), L.Q.bias.detach().contiguous(),
+                                          L.K.weight.detach().contiguous(), self.alpha_train.detach(),
+                                          self.beta_train.detach() if x0 is not None else None, x0, L.h, sig)
+        halo.all_reduce_(grads)
+        dalpha, dbeta, dwq, dwk, dbq, dbk = P.unpack_nl_grads(grads, a, d)
+        named = ((self.alpha_train, dalpha.reshape(self.alpha_train.shape)), (self.beta_train, dbeta.reshape(())),
+                 (L.Q.weight, dwq), (L.Q.bias, dbq), (L.K.weight, dwk), (L.K.bias, dbk))
+        out = []
+        for p in params:
+            g = None
+            for q, gq in named:
+                if p is q:
+                    g = gq
+            out.append(g)
+        return f.view_as(x), dx.view_as(x), out
+
     def eval_vjp(self, t, x, cot, params):
         """f(t, x) and the vector-Jacobian products cot^T df/d(x, params) in one fused pass - what the adjoint
         solver's augmented dynamics need (the reference gets them from `func(t, y)` followed by
@@ -180,6 +223,8 @@ class ODEFuncTransformerAtt(ODEFunc):
         if self.opt.get('mix_features', False):
             return None
         x2 = self._as_2d(x)
+        if self.partition is not None:
+            return self._partitioned(x, x2, (cot, params))
         plan = self._plan(x2.shape[0])
         L = self.multihead_att_layer
         att_type = L._check_supported()

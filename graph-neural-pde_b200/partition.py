@@ -1,0 +1,301 @@
+"""1-D row partition of the diffusion operator over the GPUs of one node.
+
+The reference has no model-parallel mode (its only multi-GPU path is nn.DataParallel replicas); graphs
+too large for one GPU are split here by contiguous row slabs, one process per GPU:
+
+    rank p owns nodes [p*S, min(N, (p+1)*S)),  S = ceil(N / P);  states / gradients live as [S, d] slabs
+    (zero padded on the last rank), the plan of rank p holds the edges whose ROW it owns, with global
+    column ids, over N_pad = P*S nodes.
+
+One exchange per evaluation, none inside the kernels:
+    forward   x_full  = all_gather(x_slab)                       (NCCL over NVLink, (P-1)/P * 4 N d bytes in)
+              f_slab  = rows [lo, hi) of the fused kernels on (plan_p, x_full)
+    backward  every rank forms its share of dx for ALL columns (transpose pass over its own edges; only the
+              owner adds the "- g_j" self term), dx_slab = reduce_scatter(dx_share); parameter gradients
+              (tiny) are all-reduced.  g is never gathered: a rank's edges only touch its own rows of g.
+
+`RowPartition` and `Halo` are plain torch / torch.distributed and run on any backend (the world_size-2
+gloo tests exercise them on CPU); the compute entry points below call the CUDA library and need a GPU.
+"""
+import torch
+
+from . import _lib
+
+
+class RowPartition:
+    """contiguous equal-height row slabs of an n-node graph over `world` ranks"""
+
+    def __init__(self, n, world, rank):
+        if not (0 <= rank < world):
+            raise ValueError(f'rank {rank} outside world of {world}')
+        self.n, self.world, self.rank = int(n), int(world), int(rank)
+        self.slab = -(-self.n // self.world)                 # S = ceil(N / P)
+        self.n_pad = self.slab * self.world
+        self.lo = min(self.rank * self.slab, self.n)
+        self.hi = min(self.lo + self.slab, self.n)
+
+    def bounds(self, rank):
+        lo = min(rank * self.slab, self.n)
+        return lo, min(lo + self.slab, self.n)
+
+    def local_edges(self, edge_index, edge_weight=None):
+        """edges whose row this rank owns (global ids kept), in their original relative order"""
+        ei = edge_index[0] if edge_index.dim() == 3 else edge_index
+        keep = (ei[0] >= self.lo) & (ei[0] < self.hi)
+        ei_loc = ei[:, keep].contiguous()
+        ew_loc = None
+        if edge_weight is not None:
+            ew_loc = edge_weight.reshape(-1)[keep].contiguous()
+        return ei_loc, ew_loc
+
+    def to_slab(self, full):
+        """[N, d] (or [N_pad, d]) global matrix -> this rank's zero-padded [S, d] slab"""
+        out = full.new_zeros((self.slab,) + tuple(full.shape[1:]))
+        out[:self.hi - self.lo] = full[self.lo:self.hi]
+        return out
+
+    def __repr__(self):
+        return f'RowPartition(n={self.n}, world={self.world}, rank={self.rank}, rows=[{self.lo}, {self.hi}))'
+
+
+class Halo:
+    """the collectives of the partitioned path over a torch.distributed process group"""
+
+    def __init__(self, part, group=None):
+        import torch.distributed as dist
+        self.part, self.group, self.dist = part, group, dist
+        if dist.get_world_size(group) != part.world or dist.get_rank(group) != part.rank:
+            raise ValueError('process group does not match the partition')
+        self.backend = dist.get_backend(group)
+        self.bytes_in = 0                                     # bytes received so far (bench accounting)
+
+    def all_gather_rows(self, slab):
+        """[S, d] slab of every rank -> [N_pad, d] on every rank"""
+        slab = slab.contiguous()
+        full = slab.new_empty((self.part.n_pad,) + tuple(slab.shape[1:]))
+        self.dist.all_gather_into_tensor(full, slab, group=self.group)
+        self.bytes_in += (self.part.world - 1) * slab.numel() * slab.element_size()
+        return full
+
+    def reduce_scatter_rows(self, full):
+        """sum over ranks of [N_pad, d], rank p keeps rows [p*S, (p+1)*S)"""
+        full = full.contiguous()
+        out = full.new_empty((self.part.slab,) + tuple(full.shape[1:]))
+        if self.backend == 'gloo':                            # gloo has no reduce_scatter: all_reduce + slice
+            self.dist.all_reduce(full, group=self.group)
+            out.copy_(full[self.part.rank * self.part.slab:(self.part.rank + 1) * self.part.slab])
+        else:
+            self.dist.reduce_scatter_tensor(out, full, group=self.group)
+        self.bytes_in += (self.part.world - 1) * out.numel() * out.element_size()
+        return out
+
+    def all_reduce_(self, t):
+        self.dist.all_reduce(t, group=self.group)
+        return t
+
+
+class LoopbackHalo:
+    """world == 1 stand-in (no process group needed): the collectives are identities"""
+
+    def __init__(self, part):
+        if part.world != 1:
+            raise ValueError('LoopbackHalo is for a world of 1')
+        self.part, self.bytes_in = part, 0
+
+    def all_gather_rows(self, slab):
+        return slab.contiguous()
+
+    def reduce_scatter_rows(self, full):
+        return full.contiguous()
+
+    def all_reduce_(self, t):
+        return t
+
+
+def _virt(t, lo, ld):
+    """device address such that row `lo` of a GLOBAL-row-indexed matrix lands on row 0 of the slab tensor
+    (the kernels only touch owned rows of row-indexed matrices)"""
+    return None if t is None else t.data_ptr() - 4 * lo * ld
+
+
+# ---- local compute of one rank (CUDA) ---------------------------------------------------------------
+def nl_local_forward(part, plan, x_full, x_slab, wq, bq, wk, alpha_train, beta_train, x0_slab, heads, alpha_sigmoid):
+    """rows [lo, hi) of one GRAND-nl evaluation given the gathered state: returns (f_slab [S,d], q_slab [S,A])"""
+    from .ops import _nl_q, _nl_workspace
+    lib = _lib.load()
+    s, d = x_slab.shape
+    a = wq.shape[0]
+    q = _nl_q(x_slab, wq, bq)
+    out = torch.zeros_like(x_slab) if part.hi - part.lo < s else torch.empty_like(x_slab)
+    source = beta_train is not None and x0_slab is not None
+    _lib.check(lib.gb_nl_fwd(plan.c, part.lo, part.hi, x_full.data_ptr(), d, _virt(q, part.lo, a), a, wk.data_ptr(), d,
+                             heads, a // heads, d, _virt(x0_slab, part.lo, d) if source else None, d,
+                             alpha_train.data_ptr(), int(alpha_sigmoid), beta_train.data_ptr() if source else None,
+                             _virt(out, part.lo, d), d, None, _nl_workspace(x_slab.device).data_ptr(), _lib.stream()),
+               'gb_nl_fwd')
+    return out, q
+
+
+def nl_local_vjp(part, plan, x_full, q, wq, wk, alpha_train, beta_train, x0_slab, heads, alpha_sigmoid, g_slab,
+                 want_f, want_w):
+    """this rank's share of the VJP.  Returns (f_slab|None, dx_share [N_pad,d] (to be reduce-scattered),
+    dx_own [S,d] (owner-only term dq Wq, added after the reduce-scatter), grads [2 + 2A(d+1)] flat share of
+    (dalpha, dbeta, dWq, dWk, dbq, dbk) or None) - sums over ranks give the single-GPU numbers."""
+    from .ops import _nl_workspace
+    lib = _lib.load()
+    n_pad, d = x_full.shape
+    s = part.slab
+    a = wq.shape[0]
+    dev = x_full.device
+    f32 = dict(dtype=torch.float32, device=dev)
+    ds = torch.empty(plan.e, heads, **f32)
+    dabar = torch.empty(plan.e, **f32)
+    abar = torch.empty(plan.e, **f32)
+    dq = torch.zeros(s, a, **f32) if part.hi - part.lo < s else torch.empty(s, a, **f32)
+    dk = torch.empty(n_pad, a, **f32)
+    dx = torch.empty(n_pad, d, **f32)
+    out = None
+    if want_f:
+        out = torch.zeros(s, d, **f32) if part.hi - part.lo < s else torch.empty(s, d, **f32)
+    partials = torch.empty(int(lib.gb_att_bwd_fused_partials(plan.c)), **f32)
+    dparams = torch.empty(2, **f32)
+    source = beta_train is not None and x0_slab is not None
+    _lib.check(lib.gb_nl_adjoint(plan.c, part.lo, part.hi, x_full.data_ptr(), d, _virt(q, part.lo, a), a,
+                                 wk.data_ptr(), d, heads, a // heads, d,
+                                 _virt(x0_slab, part.lo, d) if source else None, d, alpha_train.data_ptr(),
+                                 int(alpha_sigmoid), beta_train.data_ptr() if source else None,
+                                 _virt(g_slab, part.lo, d), d, _virt(out, part.lo, d), d, ds.data_ptr(),
+                                 dabar.data_ptr(), abar.data_ptr(), _virt(dq, part.lo, a), a, dk.data_ptr(), a,
+                                 dx.data_ptr(), d, partials.data_ptr(), dparams.data_ptr(),
+                                 _nl_workspace(dev).data_ptr(), _lib.stream()), 'gb_nl_adjoint')
+    # dx_share += dk_share Wk (linear, so it can go through the reduce-scatter)
+    _lib.check(lib.gb_linear_bwd_x(dk.data_ptr(), a, n_pad, a, wk.data_ptr(), d, dx.data_ptr(), d, 1, _lib.stream()),
+               'gb_linear_bwd_x')
+    x_slab = x_full[part.rank * s:(part.rank + 1) * s]
+    dx_own = torch.empty(s, d, **f32)
+    _lib.check(lib.gb_linear_bwd_x(dq.data_ptr(), a, s, a, wq.data_ptr(), d, dx_own.data_ptr(), d, 0, _lib.stream()),
+               'gb_linear_bwd_x')
+    grads = None
+    if want_w:
+        grads = torch.empty(2 + 2 * a * d + 2 * a, **f32)
+        grads[:2] = dparams
+        dwq, dwk = grads[2:2 + a * d].view(a, d), grads[2 + a * d:2 + 2 * a * d].view(a, d)
+        dbq, dbk = grads[2 + 2 * a * d:2 + 2 * a * d + a], grads[2 + 2 * a * d + a:]
+        for dy, xx, rows, dw, db in ((dq, x_slab, s, dwq, dbq), (dk, x_full, n_pad, dwk, dbk)):
+            ws = torch.empty(int(lib.gb_linear_bwd_w_workspace_bytes(rows, d, a)), dtype=torch.uint8, device=dev)
+            dw_t, db_t = torch.empty(a, d, **f32), torch.empty(a, **f32)
+            _lib.check(lib.gb_linear_bwd_w(dy.data_ptr(), a, xx.data_ptr(), d, rows, d, a, dw_t.data_ptr(),
+                                           db_t.data_ptr(), ws.data_ptr(), ws.numel(), _lib.stream()),
+                       'gb_linear_bwd_w')
+            dw.copy_(dw_t)
+            db.copy_(db_t)
+    else:
+        grads = dparams
+    return out, dx, dx_own, grads
+
+
+def diffusion_local_forward(part, plan, vals, x_full, x0_slab, alpha_train, beta_train, alpha_sigmoid):
+    """rows [lo, hi) of alpha (A x - x) + beta x0 (GRAND-l) given the gathered state -> [S, d]"""
+    lib = _lib.load()
+    n_pad, d = x_full.shape
+    s = part.slab
+    out = torch.zeros(s, d, dtype=torch.float32, device=x_full.device) if part.hi - part.lo < s else \
+        torch.empty(s, d, dtype=torch.float32, device=x_full.device)
+    source = beta_train is not None and x0_slab is not None
+    _lib.check(lib.gb_spmm_fwd_part(plan.c, part.lo, part.hi, vals.data_ptr(), x_full.data_ptr(), d,
+                                    _virt(x0_slab, part.lo, d) if source else None, d, alpha_train.data_ptr(),
+                                    int(alpha_sigmoid), beta_train.data_ptr() if source else None, d,
+                                    _virt(out, part.lo, d), d, None, _lib.stream()), 'gb_spmm_fwd_part')
+    return out
+
+
+def diffusion_local_vjp(part, plan, vals, x_full, x0_slab, alpha_train, alpha_sigmoid, g_slab):
+    """this rank's share of dx for all columns [N_pad, d] and of (dalpha_train, dbeta_train) [2]"""
+    lib = _lib.load()
+    n_pad, d = x_full.shape
+    dev = x_full.device
+    dx = torch.empty(n_pad, d, dtype=torch.float32, device=dev)
+    partials = torch.empty(int(lib.gb_spmm_bwd_partials(plan.c, d)), dtype=torch.float32, device=dev)
+    dparams = torch.empty(2, dtype=torch.float32, device=dev)
+    own_hi = part.hi if part.hi > 0 else -1                  # (0, 0) means "own everything" to the library
+    _lib.check(lib.gb_spmm_bwd_part(plan.c, part.lo, own_hi, vals.data_ptr(), _virt(g_slab, part.lo, d), d,
+                                    x_full.data_ptr(), d, _virt(x0_slab, part.lo, d), d, alpha_train.data_ptr(),
+                                    int(alpha_sigmoid), d, dx.data_ptr(), d, 0, partials.data_ptr(),
+                                    dparams.data_ptr(), _lib.stream()), 'gb_spmm_bwd_part')
+    return dx, dparams
+
+
+# ---- autograd over the exchange + local compute -------------------------------------------------------
+from torch.autograd.function import once_differentiable  # noqa: E402
+
+
+class PartNlFn(torch.autograd.Function):
+    """partitioned ODEFuncTransformerAtt.forward: slab in, slab out"""
+
+    @staticmethod
+    def forward(ctx, x_slab, wq, bq, wk, bk, alpha_train, beta_train, x0_slab, part, halo, plan, heads, alpha_sigmoid):
+        x_slab = x_slab.contiguous()
+        x_full = halo.all_gather_rows(x_slab)
+        out, q = nl_local_forward(part, plan, x_full, x_slab, wq.contiguous(), bq.contiguous(), wk.contiguous(),
+                                  alpha_train, beta_train, x0_slab, heads, alpha_sigmoid)
+        ctx.save_for_backward(x_full, q, wq, wk, alpha_train, beta_train, x0_slab)
+        ctx.part, ctx.halo, ctx.plan, ctx.heads, ctx.alpha_sigmoid = part, halo, plan, heads, alpha_sigmoid
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g_slab):
+        x_full, q, wq, wk, alpha_train, beta_train, x0_slab = ctx.saved_tensors
+        a, d = wq.shape
+        _, dx_share, dx_own, grads = nl_local_vjp(ctx.part, ctx.plan, x_full, q, wq.contiguous(), wk.contiguous(),
+                                                  alpha_train, beta_train, x0_slab, ctx.heads, ctx.alpha_sigmoid,
+                                                  g_slab.contiguous(), False, True)
+        dx = ctx.halo.reduce_scatter_rows(dx_share).add_(dx_own)
+        ctx.halo.all_reduce_(grads)
+        dalpha, dbeta, dwq, dwk, dbq, dbk = unpack_nl_grads(grads, a, d)
+        return (dx, dwq, dbq, dwk, dbk, dalpha.reshape(alpha_train.shape),
+                dbeta.reshape(()) if beta_train is not None else None) + (None,) * 6
+
+
+def unpack_nl_grads(grads, a, d):
+    return (grads[0], grads[1], grads[2:2 + a * d].view(a, d), grads[2 + a * d:2 + 2 * a * d].view(a, d),
+            grads[2 + 2 * a * d:2 + 2 * a * d + a], grads[2 + 2 * a * d + a:])
+
+
+class PartDiffusionFn(torch.autograd.Function):
+    """partitioned LaplacianODEFunc.forward with fixed edge values (constant block)"""
+
+    @staticmethod
+    def forward(ctx, x_slab, vals, alpha_train, beta_train, x0_slab, part, halo, plan, alpha_sigmoid):
+        x_full = halo.all_gather_rows(x_slab.contiguous())
+        out = diffusion_local_forward(part, plan, vals, x_full, x0_slab, alpha_train, beta_train, alpha_sigmoid)
+        ctx.save_for_backward(x_full, vals, alpha_train, beta_train, x0_slab)
+        ctx.part, ctx.halo, ctx.plan, ctx.alpha_sigmoid = part, halo, plan, alpha_sigmoid
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g_slab):
+        x_full, vals, alpha_train, beta_train, x0_slab = ctx.saved_tensors
+        if ctx.needs_input_grad[1]:
+            raise NotImplementedError('gradients w.r.t. edge values are not available on the partitioned path')
+        dx_share, dparams = diffusion_local_vjp(ctx.part, ctx.plan, vals, x_full,
+                                                x0_slab if beta_train is not None else None, alpha_train,
+                                                ctx.alpha_sigmoid, g_slab.contiguous())
+        dx = ctx.halo.reduce_scatter_rows(dx_share)
+        ctx.halo.all_reduce_(dparams)
+        return (dx, None, dparams[0].reshape(alpha_train.shape),
+                dparams[1].reshape(()) if beta_train is not None else None) + (None,) * 5
+
+
+def nl_eval_vjp_part(part, halo, plan, x_slab, g_slab, wq, bq, wk, alpha_train, beta_train, x0_slab, heads,
+                     alpha_sigmoid):
+    """partitioned f and VJP in one fused pass (adjoint solver): (f_slab, dx_slab, flat parameter gradients)"""
+    x_slab = x_slab.contiguous()
+    x_full = halo.all_gather_rows(x_slab)
+    from .ops import _nl_q
+    q = _nl_q(x_slab, wq, bq)
+    f, dx_share, dx_own, grads = nl_local_vjp(part, plan, x_full, q, wq, wk, alpha_train, beta_train, x0_slab, heads,
+                                              alpha_sigmoid, g_slab.contiguous(), True, True)
+    dx = halo.reduce_scatter_rows(dx_share).add_(dx_own)
+    return f, dx, grads

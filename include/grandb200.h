@@ -146,6 +146,13 @@ int gb_spmm_fwd(const gb_graph* g, const float* vals, const float* x, int32_t ld
                 const float* beta_train, int32_t d, float* out, int32_t ldo,
                 const gb_stage* stage, void* stream);
 
+/* Row-partitioned form: only rows [row_lo, row_hi) are evaluated (1-D row partition); x is
+ * addressed by global column id, x0 / out / stage buffers by global row id. */
+int gb_spmm_fwd_part(const gb_graph* g, int32_t row_lo, int32_t row_hi, const float* vals, const float* x,
+                     int32_t ldx, const float* x0, int32_t ldx0, const float* alpha_train, int32_t alpha_sigmoid,
+                     const float* beta_train, int32_t d, float* out, int32_t ldo, const gb_stage* stage,
+                     void* stream);
+
 /* ---- K5a: transpose (CSC) SpMM + parameter-gradient reductions (VJP of K1 w.r.t. x, alpha_train,
  *      beta_train).  gout = dL/df.
  *   t[j,:]  = sum_{p in col j} vals[tperm[p]] * gout[rowidx[p],:] - gout[j,:]
@@ -160,6 +167,15 @@ int gb_spmm_bwd(const gb_graph* g, const float* vals, const float* gout, int32_t
                 const float* alpha_train, int32_t alpha_sigmoid, int32_t d,
                 float* dx, int32_t lddx, int32_t accumulate,
                 float* partials, float* dparams, void* stream);
+
+/* Row-partitioned form: the plan holds only this rank's rows; every column j gets this rank's share
+ * sum_e a_e gout[row_e,:], and only columns in [own_lo, own_hi) also get the "- gout[j,:]" self term and
+ * contribute <gout_j, x0_j> to dbeta (own_lo == own_hi == 0: all columns owned).  Summing dx / dparams over
+ * the ranks (reduce-scatter / all-reduce) gives the single-GPU result. */
+int gb_spmm_bwd_part(const gb_graph* g, int32_t own_lo, int32_t own_hi, const float* vals, const float* gout,
+                     int32_t ldg, const float* x, int32_t ldx, const float* x0, int32_t ldx0,
+                     const float* alpha_train, int32_t alpha_sigmoid, int32_t d, float* dx, int32_t lddx,
+                     int32_t accumulate, float* partials, float* dparams, void* stream);
 
 /* ---- K3: Q/K projection (nn.Linear x2, function_transformer_attention.py:224-225)
  *   out[i, j] = sum_c x[i,c] * w[j,c] + b[j],  j < nout   (w is torch's Linear.weight layout [nout, d];
