@@ -280,7 +280,7 @@ def run_ours(args):
     }
     if args.cpu_baseline:
         line['cpu_baseline'] = cpu_baseline(name, cfg, steps=1, warmup=0)
-    print(json.dumps(line))
+    emit(line)
 
 
 def run_partitioned(args, cfg, device, rank, world):
@@ -413,7 +413,7 @@ def run_partitioned(args, cfg, device, rank, world):
                    'note': 'received bytes of the all-gathers / reduce-scatters divided by the WHOLE step time '
                            '(the exchanges are not overlapped with compute yet)'},
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 # ---- CPU baseline / reference arm (the only place bench.py executes oracle/) ----------------------
@@ -492,10 +492,23 @@ def run_reference(args):
             'config': {'workload': f"{args.workload}: GRAND-nl ({cfg['desc']}) - CPU port of the reference path"},
             'cpu_baseline': base,
             'e2e': {'value': base['value'], 'unit': 'evals/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
-    print(json.dumps(line))
+    emit(line)
+
+
+def emit(line):
+    """the ONE JSON line goes to the real stdout; everything else (NCCL banners, library chatter written to
+    fd 1) was redirected to stderr by main()"""
+    os.write(_REAL_STDOUT, (json.dumps(line) + '\n').encode())
+
+
+_REAL_STDOUT = 1
 
 
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=5)

@@ -1,0 +1,75 @@
+// stage.cu - Runge-Kutta stage combination  out = y + sum_j c[j] * k[j]  in ONE pass over the state
+// (torchdiffeq forms it as a chain of axpy kernels, one [N,d] read-modify-write per term).
+// Roofline: HBM, (nk + 2) * 4 bytes per element.
+#include "common.cuh"
+
+namespace gb {
+
+struct CombineArgs {
+  const float* y;
+  const float* k[7];
+  float c[7];
+  int32_t nk;
+  float* out;
+  int64_t count4;     // number of float4 elements
+  int64_t count;      // total floats
+};
+
+template <int NK>
+__global__ void __launch_bounds__(256) stage_combine_kernel(const CombineArgs a) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.count4; i += stride) {
+    float4 acc = ld_stream4(a.y + 4 * i);
+#pragma unroll
+    for (int j = 0; j < NK; ++j) fma4(acc, a.c[j], ld_stream4(a.k[j] + 4 * i));
+    st_stream4(a.out + 4 * i, acc);
+  }
+  // scalar tail (count % 4 elements)
+  const int64_t tail0 = a.count4 * 4;
+  const int64_t t = tail0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < a.count) {
+    float acc = a.y[t];
+#pragma unroll
+    for (int j = 0; j < NK; ++j) acc = fmaf(a.c[j], a.k[j][t], acc);
+    a.out[t] = acc;
+  }
+}
+
+}  // namespace gb
+
+using namespace gb;
+
+extern "C" int gb_stage_combine(const float* y, const float* const* k_host, const float* c_host, int32_t nk,
+                                int64_t count, float* out, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  GB_REQUIRE(y && out && count >= 0 && nk >= 0 && nk <= 7, "gb_stage_combine: bad arguments");
+  GB_REQUIRE(nk == 0 || (k_host && c_host), "gb_stage_combine: null k / c");
+  if (count == 0) return GB_OK;
+  CombineArgs a{};
+  a.y = y; a.out = out; a.nk = nk; a.count = count;
+  bool aligned = reinterpret_cast<uintptr_t>(y) % 16 == 0 && reinterpret_cast<uintptr_t>(out) % 16 == 0;
+  for (int j = 0; j < nk; ++j) {
+    GB_REQUIRE(k_host[j] != nullptr, "gb_stage_combine: null k[%d]", j);
+    a.k[j] = k_host[j];
+    a.c[j] = c_host[j];
+    aligned = aligned && reinterpret_cast<uintptr_t>(k_host[j]) % 16 == 0;
+  }
+  a.count4 = aligned ? count / 4 : 0;
+  const int64_t work = a.count4 > 0 ? a.count4 : count;
+  int64_t blocks = (work + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 16;
+  if (a.count4 > 0 && blocks > cap) blocks = cap;
+  if (a.count4 == 0) blocks = (count + 255) / 256;           // unaligned: every element goes through the tail path
+  LaunchScope ls(K_STAGE_AXPY, stream);
+  switch (nk) {
+    case 0: stage_combine_kernel<0><<<(unsigned)blocks, 256, 0, stream>>>(a); break;
+    case 1: stage_combine_kernel<1><<<(unsigned)blocks, 256, 0, stream>>>(a); break;
+    case 2: stage_combine_kernel<2><<<(unsigned)blocks, 256, 0, stream>>>(a); break;
+    case 3: stage_combine_kernel<3><<<(unsigned)blocks, 256, 0, stream>>>(a); break;
+    case 4: stage_combine_kernel<4><<<(unsigned)blocks, 256, 0, stream>>>(a); break;
+    case 5: stage_combine_kernel<5><<<(unsigned)blocks, 256, 0, stream>>>(a); break;
+    case 6: stage_combine_kernel<6><<<(unsigned)blocks, 256, 0, stream>>>(a); break;
+    default: stage_combine_kernel<7><<<(unsigned)blocks, 256, 0, stream>>>(a); break;
+  }
+  return check_launch("stage_combine");
+}

@@ -16,9 +16,10 @@ with f evaluated under enable_grad and autograd.grad(f, (t, y, *params), -a_y, a
 decreasing time is handled by negating t and f, as torchdiffeq does.  NFE is whatever `func`
 counts: one per call.
 
-Stage combinations y + dt*sum(b_j k_j) use one fused multi-tensor pass per component
-(`torch._foreach`-free: a single `torch.add(..., alpha=)` chain) - the SpMM-epilogue fusion of
-those passes lives in fused_rk.py and is used when the function advertises `fused_stage`.
+Stage combinations y + dt*sum(b_j k_j) are ONE pass over the state (csrc/stage.cu, gb_stage_combine) for
+fp32 CUDA tensors instead of torchdiffeq's chain of axpy kernels, and the reverse-time / adjoint minus
+signs ride on the stage coefficients instead of negating [N,d] tensors.  A function may expose
+`eval_vjp(t, y, cot, params)` (fused f + VJP); the adjoint driver uses it when present.
 """
 import math
 
@@ -43,16 +44,39 @@ _DP = dict(
 _AH = dict(alpha=[1.], beta=[[1.]], c_sol=[0.5, 0.5], c_err=[0.5, -0.5], c_mid=None, order=2, fsal=False)
 
 
-def _combine(y, dt, ks, coeffs):
-    """y + dt * sum_j coeffs[j] * ks[j], per tuple component"""
+_FUSE_MIN = 1 << 14        # below this many elements the launch overhead of either form is the same
+
+
+def _combine_one(yi, terms):
+    """yi + sum_j c_j * k_j: ONE pass (csrc/stage.cu) for fp32 CUDA tensors, else torchdiffeq's axpy chain"""
+    terms = [(k, c) for k, c in terms if c != 0]
+    if not terms:
+        return yi
+    if (yi.is_cuda and yi.dtype == torch.float32 and yi.numel() >= _FUSE_MIN and len(terms) <= 7 and yi.is_contiguous()
+            and all(k.shape == yi.shape and k.dtype == yi.dtype and k.is_contiguous() for k, _ in terms)):
+        import ctypes as C
+        from . import _lib
+        lib = _lib.load()
+        out = torch.empty_like(yi)
+        ks = (C.c_void_p * len(terms))(*[k.data_ptr() for k, _ in terms])
+        cs = (C.c_float * len(terms))(*[float(c) for _, c in terms])
+        _lib.check(lib.gb_stage_combine(yi.data_ptr(), ks, cs, len(terms), yi.numel(), out.data_ptr(), _lib.stream()),
+                   'gb_stage_combine')
+        return out
+    acc = yi
+    for k, c in terms:
+        acc = torch.add(acc, k, alpha=c)
+    return acc
+
+
+def _combine(y, dt, ks, coeffs, signs=None):
+    """y + dt * sum_j coeffs[j] * ks[j], per tuple component; signs[i] (+-1) multiplies component i's
+    derivatives (reverse-time / adjoint sign conventions folded into the coefficients instead of
+    negating whole tensors)"""
     out = []
     for i, yi in enumerate(y):
-        acc = None
-        for k, c in zip(ks, coeffs):
-            if c == 0:
-                continue
-            acc = torch.add(yi if acc is None else acc, k[i], alpha=dt * c)
-        out.append(yi if acc is None else acc)
+        sg = 1.0 if signs is None else signs[i]
+        out.append(_combine_one(yi, [(k[i], dt * c * sg) for k, c in zip(ks, coeffs)]))
     return tuple(out)
 
 
@@ -81,18 +105,28 @@ class _Problem:
         self.times = [self.sign * v for v in self.times]
         self.dtype, self.device = ref.dtype, ref.device
         self._func = func
+        self.comp_signs = None           # set by the adjoint driver: func returns raw VJPs (see _OdeintAdjoint)
 
     def tensor_time(self, s):
         return torch.full((), self.sign * s, dtype=self.dtype, device=self.device)
 
-    def f(self, s, state):
-        """derivative in the internal (forward) time s"""
+    def f_raw(self, s, state):
+        """func at internal time s, as returned (no sign applied)"""
         t = self.tensor_time(s)
         out = self._func(t, state) if self.is_tuple else (self._func(t, state[0]),)
-        out = tuple(out)
+        return tuple(out)
+
+    def f(self, s, state):
+        """derivative in the internal (forward) time s"""
+        out = self.f_raw(s, state)
         if self.sign < 0:
             out = tuple(-o for o in out)
         return out
+
+    def signs(self, n):
+        """per-component factor turning f_raw into the internal-time derivative"""
+        comp = self.comp_signs if self.comp_signs is not None else (1.0,) * n
+        return tuple(self.sign * c for c in comp)
 
 
 def _fixed_grid(t0, t1, step_size):
@@ -103,18 +137,19 @@ def _fixed_grid(t0, t1, step_size):
 
 
 def _fixed_step(prob, method, t0, dt, t1, y):
-    f = prob.f
+    f = prob.f_raw                      # signs (reverse time, adjoint conventions) ride on the coefficients
+    sg = prob.signs(len(y))
     if method == 'euler':
-        return _combine(y, dt, [f(t0, y)], [1.0])
+        return _combine(y, dt, [f(t0, y)], [1.0], sg)
     if method == 'midpoint':
         k1 = f(t0, y)
-        k2 = f(t0 + 0.5 * dt, _combine(y, dt, [k1], [0.5]))
-        return _combine(y, dt, [k2], [1.0])
+        k2 = f(t0 + 0.5 * dt, _combine(y, dt, [k1], [0.5], sg))
+        return _combine(y, dt, [k2], [1.0], sg)
     k1 = f(t0, y)
-    k2 = f(t0 + dt / 3, _combine(y, dt, [k1], [1 / 3]))
-    k3 = f(t0 + dt * 2 / 3, _combine(y, dt, [k1, k2], [-1 / 3, 1.0]))
-    k4 = f(t1, _combine(y, dt, [k1, k2, k3], [1.0, -1.0, 1.0]))
-    return _combine(y, dt, [k1, k2, k3, k4], [0.125, 0.375, 0.375, 0.125])
+    k2 = f(t0 + dt / 3, _combine(y, dt, [k1], [1 / 3], sg))
+    k3 = f(t0 + dt * 2 / 3, _combine(y, dt, [k1, k2], [-1 / 3, 1.0], sg))
+    k4 = f(t1, _combine(y, dt, [k1, k2, k3], [1.0, -1.0, 1.0], sg))
+    return _combine(y, dt, [k1, k2, k3, k4], [0.125, 0.375, 0.375, 0.125], sg)
 
 
 def _solve_fixed(prob, method, step_size):
@@ -210,17 +245,16 @@ def _solve_adaptive(prob, method, rtol, atol, max_num_steps=2 ** 31 - 1):
     return sols
 
 
-def odeint(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, event_fn=None):
+def odeint(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, event_fn=None, _comp_signs=None):
     if event_fn is not None:
         raise NotImplementedError('event handling is not part of the reference call sites')
     method = method or 'dopri5'
     options = dict(options or {})
     prob = _Problem(func, y0, t)
-    fused = getattr(func, 'fused_odeint', None)
-    if fused is not None and not prob.is_tuple and method in _FIXED:
-        res = fused(prob, method, options.get('step_size'))
-        if res is not None:
-            return res
+    if _comp_signs is not None:
+        if method not in _FIXED:
+            raise ValueError('_comp_signs is only meaningful for the fixed-grid solvers')
+        prob.comp_signs = tuple(_comp_signs)
     if method in _FIXED:
         sols = _solve_fixed(prob, method, options.get('step_size'))
     elif method in _ADAPTIVE:
@@ -249,13 +283,19 @@ class _OdeintAdjoint(torch.autograd.Function):
         ys, = ctx.saved_tensors
 
         fused_vjp = getattr(func, 'eval_vjp', None)
+        fixed = cfg['adjoint_method'] in _FIXED
+        # Real-time augmented dynamics (torchdiffeq): d/dt (vjp_t, y, a_y, a_p) = (-a.df/dt, f, -a.df/dy, -a.df/dp).
+        # Fixed-grid solves take the RAW products (cotangent +a_y) and carry the minus signs on the stage
+        # coefficients (comp_signs) - no negated copies of [N,d] tensors; adaptive solves get signed values.
+        comp_signs = (-1.0, 1.0, -1.0) + (-1.0,) * len(params)
 
         def aug_dynamics(tt, state):
             y, a_y = state[1], state[2]
+            cot = a_y if fixed else -a_y
             if fused_vjp is not None:
                 # the function evaluates f and cot^T df/d(y, params) in one fused pass (same numbers as
                 # func(t, y) followed by autograd.grad; df/dt == 0 for the autonomous ODE functions)
-                res = fused_vjp(tt, y, -a_y, params)
+                res = fused_vjp(tt, y, cot, params)
                 if res is not None:
                     f, vy, vps = res
                     vp = [g if g is not None else torch.zeros_like(p) for g, p in zip(vps, params)]
@@ -264,7 +304,7 @@ class _OdeintAdjoint(torch.autograd.Function):
                 tt_ = tt.detach().requires_grad_(True)
                 y_ = y.detach().requires_grad_(True)
                 f = func(tt_, y_)
-                grads = torch.autograd.grad(f, (tt_, y_) + tuple(params), -a_y, allow_unused=True)
+                grads = torch.autograd.grad(f, (tt_, y_) + tuple(params), cot, allow_unused=True)
             vt = grads[0] if grads[0] is not None else torch.zeros_like(tt)
             vy = grads[1] if grads[1] is not None else torch.zeros_like(y)
             vp = [g if g is not None else torch.zeros_like(p) for g, p in zip(grads[2:], params)]
@@ -275,7 +315,8 @@ class _OdeintAdjoint(torch.autograd.Function):
                     [torch.zeros_like(p) for p in params]
             for i in range(len(times) - 1, 0, -1):
                 sol = odeint(aug_dynamics, tuple(state), [times[i], times[i - 1]], rtol=cfg['adjoint_rtol'],
-                             atol=cfg['adjoint_atol'], method=cfg['adjoint_method'], options=cfg['adjoint_options'])
+                             atol=cfg['adjoint_atol'], method=cfg['adjoint_method'], options=cfg['adjoint_options'],
+                             _comp_signs=comp_signs if fixed else None)
                 state = [s[1] for s in sol]
                 state[1] = ys[i - 1]
                 state[2] = state[2] + grad_ys[i - 1]

@@ -250,6 +250,13 @@ int gb_att_bwd_fused(const gb_graph* g, const float* q, int32_t ldq, const float
                      float* dk_out, int32_t lddk, float* dx, int32_t lddx, float* partials, float* dparams,
                      void* stream);
 
+/* ---- Runge-Kutta stage combination (replaces torchdiffeq's chain of axpy kernels in the fixed-grid solvers,
+ *      rk4_alt_step_func / _runge_kutta_step; third-party, call sites src/base_classes.py:45-48):
+ *   out[i] = y[i] + sum_{j < nk} c_host[j] * k_host[j][i],  nk <= 7, one pass over `count` floats.
+ *   k_host: HOST array of nk device pointers; c_host: HOST array of nk coefficients (already times dt). */
+int gb_stage_combine(const float* y, const float* const* k_host, const float* c_host, int32_t nk, int64_t count,
+                     float* out, void* stream);
+
 /* ---- single-gather GRAND-nl evaluation and VJP (csrc/nl_kernels.cuh; scaled_dot, attention_norm_idx 0) ----
  * One row gather per edge: scores are formed as <Wk_h^T q_ih / sqrt(dk), x_j> (the per-(row, head) constant
  * <q_ih, bk_h> cancels in the row softmax), the softmax is online, so neither k = x Wk^T + bk nor the
