@@ -151,15 +151,34 @@ static int choose_splits(int n, int nout, int d) {
 
 }  // namespace gb
 
+namespace gb {
+struct TcArgs {
+  const float* a; int64_t lda; const float* w; int64_t ldw; const float* bias; float* out; int64_t ldo;
+  int32_t rows, no, k; int32_t trans_w, accumulate, stages;
+};
+bool tc_gemm_supported(const void* a, int64_t lda, const void* w, int64_t ldw, const void* out, int64_t ldo, int no,
+                       int k, int trans_w);
+int tc_gemm_launch(const TcArgs& a, int kernel_id, cudaStream_t stream);
+}  // namespace gb
+
 using namespace gb;
 
 extern "C" {
+
+int gb_linear_tc_eligible(const float* a, int32_t lda, const float* w, int32_t ldw, const float* out, int32_t ldo,
+                          int32_t nout, int32_t k, int32_t trans_w) {
+  return tc_gemm_supported(a, lda, w, ldw, out, ldo, nout, k, trans_w) ? 1 : 0;
+}
 
 int gb_linear_fwd(const float* x, int32_t ldx, int32_t n, int32_t d, const float* w, const float* b, int32_t nout,
                   float* out, int32_t ldo, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   GB_REQUIRE(x && w && out && n > 0 && d > 0 && nout > 0, "gb_linear_fwd: bad arguments");
   GB_REQUIRE(ldx >= d && ldo >= nout, "gb_linear_fwd: leading dimension too small");
+  if (tc_gemm_supported(x, ldx, w, d, out, ldo, nout, d, 0)) {       // tcgen05 3xTF32 path (linear_tc.cu)
+    TcArgs t{x, ldx, w, d, b, out, ldo, n, nout, d, 0, 0, 0};
+    return tc_gemm_launch(t, K_LINEAR_FWD, stream);
+  }
   dim3 grid((n + BM - 1) / BM, (nout + BN - 1) / BN);
   LaunchScope ls(K_LINEAR_FWD, stream);
   sgemm_rowA<<<grid, GT, 0, stream>>>(x, ldx, n, d, w, 1, d, nout, b, out, ldo, 0);
@@ -171,6 +190,10 @@ int gb_linear_bwd_x(const float* dy, int32_t lddy, int32_t n, int32_t nout, cons
   cudaStream_t stream = (cudaStream_t)stream_;
   GB_REQUIRE(dy && w && dx && n > 0 && d > 0 && nout > 0, "gb_linear_bwd_x: bad arguments");
   GB_REQUIRE(lddy >= nout && lddx >= d, "gb_linear_bwd_x: leading dimension too small");
+  if (tc_gemm_supported(dy, lddy, w, d, dx, lddx, d, nout, 1)) {      // dx = dy . W: W [nout, d] is B^T, staged transposed
+    TcArgs t{dy, lddy, w, d, nullptr, dx, lddx, n, d, nout, 1, accumulate != 0, 0};
+    return tc_gemm_launch(t, K_LINEAR_BWD_X, stream);
+  }
   dim3 grid((n + BM - 1) / BM, (d + BN - 1) / BN);
   LaunchScope ls(K_LINEAR_BWD_X, stream);
   sgemm_rowA<<<grid, GT, 0, stream>>>(dy, lddy, n, nout, w, d, 1, d, nullptr, dx, lddx, accumulate);

@@ -180,6 +180,12 @@ int gb_spmm_bwd_part(const gb_graph* g, int32_t own_lo, int32_t own_hi, const fl
 /* ---- K3: Q/K projection (nn.Linear x2, function_transformer_attention.py:224-225)
  *   out[i, j] = sum_c x[i,c] * w[j,c] + b[j],  j < nout   (w is torch's Linear.weight layout [nout, d];
  *   pass Q and K weights concatenated along dim 0 to get [q | k] rows in one pass) */
+/* Tensor-core path (csrc/linear_tc.cu): tcgen05.mma kind::tf32 with a 3-term hi/lo split (fp32-accurate), TMEM
+ * accumulators, persistent warp-specialised CTAs.  Taken by gb_linear_fwd / gb_linear_bwd_x when the reduction
+ * length is a multiple of 32 and <= 128, the output width a multiple of 16 and <= 128, rows 16-byte aligned
+ * (every GRAND-nl configuration of BASELINE.json); other shapes run the CUDA-core SGEMM.  Returns 1 / 0. */
+int gb_linear_tc_eligible(const float* a, int32_t lda, const float* w, int32_t ldw, const float* out, int32_t ldo,
+                          int32_t nout, int32_t k, int32_t trans_w);
 int gb_linear_fwd(const float* x, int32_t ldx, int32_t n, int32_t d, const float* w, const float* b,
                   int32_t nout, float* out, int32_t ldo, void* stream);
 /* dx[i,c] (+)= sum_j dy[i,j] * w[j,c] */
