@@ -159,6 +159,10 @@ struct TcArgs {
 bool tc_gemm_supported(const void* a, int64_t lda, const void* w, int64_t ldw, const void* out, int64_t ldo, int no,
                        int k, int trans_w);
 int tc_gemm_launch(const TcArgs& a, int kernel_id, cudaStream_t stream);
+bool tc_gemm_tn_supported(const void* dy, int64_t lddy, const void* x, int64_t ldx, int nout, int d);
+size_t tc_gemm_tn_workspace_bytes(int d);
+int tc_gemm_tn_launch(const float* dy, int64_t lddy, const float* x, int64_t ldx, int rows, int d, float* dw, float* db,
+                      void* workspace, cudaStream_t stream);
 }  // namespace gb
 
 using namespace gb;
@@ -203,7 +207,12 @@ int gb_linear_bwd_x(const float* dy, int32_t lddy, int32_t n, int32_t nout, cons
 size_t gb_linear_bwd_w_workspace_bytes(int32_t n, int32_t d, int32_t nout) {
   if (n <= 0 || d <= 0 || nout <= 0) return 0;
   const size_t s = (size_t)choose_splits(n, nout, d);
-  return s * ((size_t)nout * d + nout) * sizeof(float) + 256;
+  size_t bytes = s * ((size_t)nout * d + nout) * sizeof(float) + 256;
+  if (nout == 128 && d % 32 == 0 && d <= 128) {               // tensor-core path: one partial per SM
+    const size_t tc = tc_gemm_tn_workspace_bytes(d);
+    if (tc > bytes) bytes = tc;
+  }
+  return bytes;
 }
 
 int gb_linear_bwd_w(const float* dy, int32_t lddy, const float* x, int32_t ldx, int32_t n, int32_t d, int32_t nout,
@@ -214,6 +223,8 @@ int gb_linear_bwd_w(const float* dy, int32_t lddy, const float* x, int32_t ldx, 
     set_error("gb_linear_bwd_w: workspace too small");
     return GB_ERR_WORKSPACE;
   }
+  if (db != nullptr && tc_gemm_tn_supported(dy, lddy, x, ldx, nout, d))      // tcgen05 3xTF32 path (linear_tc.cu)
+    return tc_gemm_tn_launch(dy, lddy, x, ldx, n, d, dw, db, workspace, stream);
   const int splits = choose_splits(n, nout, d);
   int rows = (n + splits - 1) / splits;
   rows = (rows + BK - 1) / BK * BK;

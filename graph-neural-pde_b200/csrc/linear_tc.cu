@@ -318,6 +318,233 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_gemm_rows_kernel(const TcArg
   }
 }
 
+// ==================================================================================================
+// dW[M=128, d] = dY^T X, db[M] = column sums of dY  (weight gradient of the packed Q|K projection):
+// the reduction runs over the NODES, so both operands are "MN-major" in memory (the M / N index is the
+// contiguous one).  For 32-bit MN-major operands the only UMMA layout is SWIZZLE_128B_BASE32B (cute::UMMA
+// Layout_MN_SW128_32B_Atom, Swizzle<2,5,2>; canonical form ((8,n),(4,k)):((1,LBO),(8,SBO)) in 16-byte units):
+// atoms of 4 K-rows x 128 bytes (32 consecutive features of 4 consecutive nodes) whose 32-byte chunks are
+// XOR-ed with (K-row & 3) - a row-major block of the source matrix, re-chunked - LBO = byte stride between
+// the atoms along M/N, SBO = byte stride between the 4-row K-groups.  One tcgen05.mma (K = 8) spans two
+// K-groups; a K-block is 32 nodes = 8 K-groups.
+// The bias gradient rides along as 16 extra B columns holding 1.0 (N = d + 16).
+// Every CTA accumulates ALL its K-blocks (static interleave) in one TMEM accumulator and writes one partial
+// [128, d + 16]; a second kernel adds the partials in CTA order (deterministic).
+struct TcTnArgs {
+  const float* dy;       // [rows, 128]
+  int64_t lddy;
+  const float* x;        // [rows, d]
+  int64_t ldx;
+  float* part;           // [gridDim.x][128][d + 16]
+  int32_t rows, d, stages;
+};
+
+struct TcTnSmem {
+  uint32_t a_hi, a_lo, b_hi, b_lo;   // per stage: A 16 KB, B (d/32 + 1 atoms) x 4 KB
+  uint32_t ready, empty, tfull, tmem_ptr, total;
+  uint32_t a_stage, b_stage;         // bytes per stage
+};
+
+__host__ __device__ inline TcTnSmem tc_tn_layout(int d, int stages) {
+  TcTnSmem s{};
+  s.a_stage = 4u * 4096u;                                   // 4 M-atoms x (4 K-groups x 1024 B)
+  s.b_stage = (uint32_t)(d / 32 + 1) * 4096u;               // N-atoms of x + the ones atom
+  uint32_t off = 0;
+  s.a_hi = off; off += stages * s.a_stage;
+  s.a_lo = off; off += stages * s.a_stage;
+  s.b_hi = off; off += stages * s.b_stage;
+  s.b_lo = off; off += stages * s.b_stage;
+  s.ready = off; off += 8u * kTcMaxStages;
+  s.empty = off; off += 8u * kTcMaxStages;
+  s.tfull = off; off += 16u;
+  s.tmem_ptr = off; off += 16u;
+  s.total = off;
+  return s;
+}
+
+// MN-major SWIZZLE_128B_BASE32B descriptor: LBO = 4096 B between M/N atoms, SBO = 512 B between 4-row K-groups
+__device__ __forceinline__ uint64_t umma_desc_mn128(uint32_t smem_addr) {
+  return (uint64_t)((smem_addr >> 4) & 0x3fffu) | (256ull << 16) | (32ull << 32) | (1ull << 46) | (1ull << 61);
+}
+// byte offset of (node 0..31, 16-byte chunk c 0..7) inside one M/N atom column [8 K-groups][4 rows][128 B]
+__device__ __forceinline__ uint32_t sw128_32b(int node, int c) {
+  const int c32 = ((c >> 1) ^ (node & 3));                  // 32-byte chunk XOR K-row within the atom
+  return (uint32_t)(node >> 2) * 512u + (uint32_t)(node & 3) * 128u + (uint32_t)(c32 << 5) + (uint32_t)((c & 1) << 4);
+}
+
+__global__ void __launch_bounds__(kTcThreads, 1) tc_gemm_tn_kernel(const TcTnArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  uint8_t* gen = smem_raw + (base - raw);
+  const TcTnSmem L = tc_tn_layout(a.d, a.stages);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_mma = a.d + 16;                               // x columns + ones columns
+  const int nkb = (a.rows + kTcKBlock - 1) / kTcKBlock;     // K-blocks of 32 nodes
+  const int xatoms = a.d / 32;
+  const uint32_t tmem_cols = n_mma <= 32 ? 32u : (n_mma <= 64 ? 64u : (n_mma <= 128 ? 128u : 256u));
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < a.stages; ++s) {
+      mbar_init(base + L.ready + 8 * s, 4 * 32);
+      mbar_init(base + L.empty + 8 * s, 1);
+    }
+    mbar_init(base + L.tfull, 1);
+    fence_barrier_init();
+  }
+  if (warp == kTcProducerWarps) tmem_alloc(base + L.tmem_ptr, tmem_cols);
+  // the ones atom of B (hi = 1 in the first 16 columns, lo = 0) is constant: fill it once in every stage
+  for (int idx = threadIdx.x; idx < a.stages * 256; idx += kTcThreads) {      // 256 chunks of 16 B per atom
+    const int s = idx / 256, r = idx % 256;
+    const int node = r / 8, c = r % 8;
+    const float one = c < 4 ? 1.f : 0.f;                                      // columns d .. d+15
+    const uint32_t off = (uint32_t)s * L.b_stage + (uint32_t)xatoms * 4096u + sw128_32b(node, c);
+    *reinterpret_cast<float4*>(gen + L.b_hi + off) = make_float4(one, one, one, one);
+    *reinterpret_cast<float4*>(gen + L.b_lo + off) = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(gen + L.tmem_ptr);
+
+  if (warp < kTcProducerWarps) {
+    const int grp = warp >> 2;
+    const int t = threadIdx.x & 127;
+    const int c = t & 7;                                    // 16-byte chunk inside a 128-byte atom row
+    int it = 0;
+    for (int kb = blockIdx.x; kb < nkb; kb += gridDim.x, ++it) {
+      if ((it & 1) != grp) continue;
+      const int s = it % a.stages;
+      const uint32_t ph = (uint32_t)(it / a.stages) & 1u;
+      // (atom, node) pairs: t / 8 runs over 16 of them per step; A has 4 atoms x 32 nodes = 128 pairs (8 steps)
+      float4 va[8], vb[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int pr = (t >> 3) + 16 * i;                   // 0 .. 127
+        const int atom = pr >> 5, node = pr & 31;
+        const int row = kb * kTcKBlock + node;
+        const bool ok = row < a.rows;
+        va[i] = ok ? ld_stream4(a.dy + (int64_t)row * a.lddy + 32 * atom + 4 * c) : make_float4(0.f, 0.f, 0.f, 0.f);
+        vb[i] = (ok && atom < xatoms) ? ld_stream4(a.x + (int64_t)row * a.ldx + 32 * atom + 4 * c)
+                                      : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      mbar_wait(base + L.empty + 8 * s, ph ^ 1u);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int pr = (t >> 3) + 16 * i;
+        const int atom = pr >> 5, node = pr & 31;
+        const uint32_t off = (uint32_t)atom * 4096u + sw128_32b(node, c);
+        float4 hi, lo;
+        split_tf32(va[i], hi, lo);
+        *reinterpret_cast<float4*>(gen + L.a_hi + (uint32_t)s * L.a_stage + off) = hi;
+        *reinterpret_cast<float4*>(gen + L.a_lo + (uint32_t)s * L.a_stage + off) = lo;
+        if (atom < xatoms) {
+          split_tf32(vb[i], hi, lo);
+          *reinterpret_cast<float4*>(gen + L.b_hi + (uint32_t)s * L.b_stage + off) = hi;
+          *reinterpret_cast<float4*>(gen + L.b_lo + (uint32_t)s * L.b_stage + off) = lo;
+        }
+      }
+      fence_proxy_async();
+      mbar_arrive(base + L.ready + 8 * s);
+    }
+  } else if (warp == kTcProducerWarps) {
+    if (lane == 0) {
+      // D = F32, A = B = TF32, both MN-major (bits 15, 16), M = 128, N = d + 16
+      const uint32_t idesc = umma_idesc_tf32(n_mma) | (1u << 15) | (1u << 16);
+      int it = 0;
+      for (int kb = blockIdx.x; kb < nkb; kb += gridDim.x, ++it) {
+        const int s = it % a.stages;
+        const uint32_t ph = (uint32_t)(it / a.stages) & 1u;
+        mbar_wait(base + L.ready + 8 * s, ph);
+        tc_fence_after();
+        const uint32_t ahi = base + L.a_hi + (uint32_t)s * L.a_stage, alo = base + L.a_lo + (uint32_t)s * L.a_stage;
+        const uint32_t bhi = base + L.b_hi + (uint32_t)s * L.b_stage, blo = base + L.b_lo + (uint32_t)s * L.b_stage;
+#pragma unroll
+        for (int kg = 0; kg < 4; ++kg) {                    // one tcgen05.mma = 8 nodes = two 4-row K-groups
+          const uint32_t ko = 1024u * kg;
+          umma_tf32(tmem_base, umma_desc_mn128(ahi + ko), umma_desc_mn128(bhi + ko), idesc, (it | kg) != 0);
+          umma_tf32(tmem_base, umma_desc_mn128(ahi + ko), umma_desc_mn128(blo + ko), idesc, 1u);
+          umma_tf32(tmem_base, umma_desc_mn128(alo + ko), umma_desc_mn128(bhi + ko), idesc, 1u);
+        }
+        umma_commit(base + L.empty + 8 * s);
+      }
+      umma_commit(base + L.tfull);
+    }
+  } else {
+    const int q = warp & 3;
+    mbar_wait(base + L.tfull, 0u);
+    tc_fence_after();
+    const int m = 32 * q + lane;
+    float* prow = a.part + ((int64_t)blockIdx.x * kTcTileM + m) * n_mma;
+    const bool any = (int)blockIdx.x < nkb;                 // a CTA without work leaves TMEM undefined: write zeros
+    for (int c0 = 0; c0 < n_mma; c0 += 16) {
+      float v[16];
+      tmem_ld16(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)c0, v);
+#pragma unroll
+      for (int j = 0; j < 16; j += 4)
+        *reinterpret_cast<float4*>(prow + c0 + j) = any ? make_float4(v[j], v[j + 1], v[j + 2], v[j + 3])
+                                                        : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kTcProducerWarps) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, tmem_cols);
+  }
+}
+
+// dw[m, c] = sum_cta part[cta][m][c] (c < d), db[m] = sum_cta part[cta][m][d]; fixed CTA order
+__global__ void __launch_bounds__(256) tc_tn_reduce_kernel(const float* __restrict__ part, int ctas, int d,
+                                                         float* __restrict__ dw, float* __restrict__ db) {
+  const int n_mma = d + 16;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= kTcTileM * (d + 1)) return;
+  const int m = idx / (d + 1), c = idx % (d + 1);
+  float acc = 0.f;
+  for (int b = 0; b < ctas; ++b) acc += part[((int64_t)b * kTcTileM + m) * n_mma + c];
+  if (c < d) dw[(int64_t)m * d + c] = acc;
+  else if (db) db[m] = acc;
+}
+
+bool tc_gemm_tn_supported(const void* dy, int64_t lddy, const void* x, int64_t ldx, int nout, int d) {
+  static const bool disabled = getenv("GRANDB200_NO_TC") != nullptr;
+  if (disabled) return false;
+  auto al = [](const void* p) { return reinterpret_cast<uintptr_t>(p) % 16 == 0; };
+  return nout == kTcTileM && d % 32 == 0 && d >= 32 && d <= 128 && al(dy) && al(x) && lddy % 4 == 0 && ldx % 4 == 0;
+}
+
+size_t tc_gemm_tn_workspace_bytes(int d) { return (size_t)sm_count() * kTcTileM * (d + 16) * sizeof(float) + 256; }
+
+int tc_gemm_tn_launch(const float* dy, int64_t lddy, const float* x, int64_t ldx, int rows, int d, float* dw, float* db,
+                      void* workspace, cudaStream_t stream) {
+  TcTnArgs a{};
+  a.dy = dy; a.lddy = lddy; a.x = x; a.ldx = ldx; a.rows = rows; a.d = d;
+  a.part = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(workspace) + 15) & ~(uintptr_t)15);
+  a.stages = 3;
+  while (a.stages > 2 && tc_tn_layout(d, a.stages).total + 1024 > 220 * 1024) --a.stages;
+  const size_t smem = tc_tn_layout(d, a.stages).total + 1024;
+  static bool configured = false;
+  if (!configured) {
+    GB_CUDA(cudaFuncSetAttribute(tc_gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    configured = true;
+  }
+  const int nkb = (rows + kTcKBlock - 1) / kTcKBlock;
+  const int blocks = min(nkb, sm_count());
+  {
+    LaunchScope ls(K_LINEAR_BWD_W, stream);
+    tc_gemm_tn_kernel<<<blocks, kTcThreads, smem, stream>>>(a);
+  }
+  if (int rc = check_launch("tc_gemm_tn_kernel")) return rc;
+  {
+    LaunchScope ls(K_LINEAR_BWD_W_REDUCE, stream);
+    const int total = kTcTileM * (d + 1);
+    tc_tn_reduce_kernel<<<(total + 255) / 256, 256, 0, stream>>>(a.part, blocks, d, dw, db);
+  }
+  return check_launch("tc_tn_reduce_kernel");
+}
+
 // can the tensor-core path take out[rows, no] (+)= a[rows, k] . w + bias ?
 bool tc_gemm_supported(const void* a, int64_t lda, const void* w, int64_t ldw, const void* out, int64_t ldo, int no,
                        int k, int trans_w) {

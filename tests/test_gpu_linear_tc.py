@@ -66,3 +66,31 @@ def test_strided_operands_and_fallback_shapes():
     _close(buf[:, a:], x.double() @ w.double().t() + b.double(), 'strided out')
     assert float(buf[:, :a].abs().max()) == 0.0
     assert lib.gb_linear_tc_eligible(x.data_ptr(), 6, w.data_ptr(), 6, buf.data_ptr(), 6, 6, 6, 0) == 0
+
+
+@pytest.mark.parametrize('rows,d', [(1000, 128), (777, 96), (31, 64), (300001, 128), (4097, 32), (1, 128)])
+def test_linear_bwd_w_tensor_core(rows, d):
+    """dW = dY^T X and db = column sums on the tensor cores (MN-major operands, per-SM partials added in a
+    fixed order); the packed Q|K projection has nout = 2 * attention_dim = 128"""
+    from grand_b200 import _lib
+    lib = _lib.load()
+    nout = 128
+    g = torch.Generator(device='cuda').manual_seed(rows + d)
+    dy = torch.randn(rows, nout, device='cuda', generator=g)
+    x = torch.randn(rows, d, device='cuda', generator=g)
+    dw = torch.full((nout, d), float('nan'), device='cuda')
+    db = torch.full((nout,), float('nan'), device='cuda')
+    ws = torch.empty(int(lib.gb_linear_bwd_w_workspace_bytes(rows, d, nout)), dtype=torch.uint8, device='cuda')
+    for _ in range(2):
+        _lib.check(lib.gb_linear_bwd_w(dy.data_ptr(), nout, x.data_ptr(), d, rows, d, nout, dw.data_ptr(), db.data_ptr(),
+                                       ws.data_ptr(), ws.numel(), _lib.stream()), 'gb_linear_bwd_w')
+    torch.cuda.synchronize()
+    ref_w = dy.double().t() @ x.double()
+    ref_b = dy.double().sum(0)
+    scale = float((dy.double().abs().t() @ x.double().abs()).max())          # sum of |terms|: the fp32 accumulation scale
+    assert float((dw.double() - ref_w).abs().max()) <= 2e-6 * scale
+    assert float((db.double() - ref_b).abs().max()) <= 2e-6 * float(dy.double().abs().sum(0).max())
+    dw2, db2 = torch.empty_like(dw), torch.empty_like(db)
+    _lib.check(lib.gb_linear_bwd_w(dy.data_ptr(), nout, x.data_ptr(), d, rows, d, nout, dw2.data_ptr(), db2.data_ptr(),
+                                   ws.data_ptr(), ws.numel(), _lib.stream()), 'gb_linear_bwd_w')
+    assert torch.equal(dw, dw2) and torch.equal(db, db2)
