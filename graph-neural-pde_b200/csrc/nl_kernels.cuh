@@ -170,10 +170,14 @@ struct NlRow {
     }
   }
 
-  // one warp batch: edges [base, base + BATCH) of a row ending at `end`
-  __device__ __forceinline__ void batch(const NlArgs& a, int base, int end, int lane, float alpha) {
-    int cmine = -1;
-    if (lane < BATCH && base + lane < end) cmine = ld_stream_i32(a.colidx + base + lane);
+  // column index of edge base + lane (lanes < BATCH), -1 past the end of the row
+  __device__ __forceinline__ int load_cols(const NlArgs& a, int base, int end, int lane) const {
+    return (lane < BATCH && base + lane < end) ? ld_stream_i32(a.colidx + base + lane) : -1;
+  }
+
+  // one warp batch: edges [base, base + BATCH) of a row ending at `end`; `cmine` = load_cols(base), issued by
+  // the caller one batch ahead so that the index load is off the critical path of the gather
+  __device__ __forceinline__ void batch(const NlArgs& a, int base, int end, int lane, float alpha, int cmine) {
     const bool act = xl < a.dv;
     float4 xr[U];
 #pragma unroll
@@ -390,17 +394,24 @@ __global__ void __launch_bounds__(kNlThreads, 2) nl_rows_kernel(const NlArgs a) 
     r0 = __shfl_sync(kFullMask, r0, 0);
     if (r0 >= nrows) break;
     const int r1 = min(r0 + kNlChunkRows, nrows);
+    // the chunk's row pointers in one load (lanes 0 .. kNlChunkRows), handed out by shuffles
+    const int rp = (lane <= kNlChunkRows && r0 + lane <= nrows) ? __ldg(a.rowptr + a.row_lo + r0 + lane) : 0;
     for (int rr = r0; rr < r1; ++rr) {
       const int row = a.row_lo + rr;
-      const int start = __ldg(a.rowptr + row), end = __ldg(a.rowptr + row + 1);
+      const int start = __shfl_sync(kFullMask, rp, rr - r0), end = __shfl_sync(kFullMask, rp, rr - r0 + 1);
       if (end - start > a.long_threshold) continue;          // nl_long_kernel takes these
+      int cols = r.load_cols(a, start, end, lane);           // in flight while q is staged and p is formed
       for (int j = lane; j < a.adim; j += 32) q_s[j] = __ldg(a.q + (size_t)row * a.ldq + j);
       __syncwarp();
       r.load_p(a, wk_s, ldw, q_s);
       if constexpr (ADJ)
         r.gi = r.xl < a.dv ? ldg4(a.g + (size_t)row * a.ldg + 4 * r.xl) : f4_zero();
       r.reset();
-      for (int base = start; base < end; base += Row::BATCH) r.batch(a, base, end, lane, alpha);
+      for (int base = start; base < end; base += Row::BATCH) {
+        const int cnext = r.load_cols(a, base + Row::BATCH, end, lane);
+        r.batch(a, base, end, lane, alpha, cols);
+        cols = cnext;
+      }
       NlStats<H> st;
       r.warp_merge(st);
       r.emit(a, row, lane, st, alpha, beta, u_s, wk_s, ldw);
@@ -438,8 +449,14 @@ __global__ void __launch_bounds__(kNlThreads, 1) nl_long_kernel(const NlArgs a) 
   r.load_p(a, wk_s, ldw, q_s);
   if constexpr (ADJ) r.gi = r.xl < a.dv ? ldg4(a.g + (size_t)row * a.ldg + 4 * r.xl) : f4_zero();
   r.reset();
-  for (int base = start + warp * Row::BATCH; base < end; base += kNlWarps * Row::BATCH)
-    r.batch(a, base, end, lane, alpha);
+  {
+    int cols = r.load_cols(a, start + warp * Row::BATCH, end, lane);
+    for (int base = start + warp * Row::BATCH; base < end; base += kNlWarps * Row::BATCH) {
+      const int cnext = r.load_cols(a, base + kNlWarps * Row::BATCH, end, lane);
+      r.batch(a, base, end, lane, alpha, cols);
+      cols = cnext;
+    }
+  }
   NlStats<H> st;
   r.warp_merge(st);
   if (lane == 0) {
