@@ -47,6 +47,7 @@ __global__ void __launch_bounds__(kAttThreads) edge_softmax_fwd_kernel(const Att
   }
   const int start = __ldg(a.ptr + seg), end = __ldg(a.ptr + seg + 1);
   if (!LONG && end - start > a.long_threshold) return;
+  if (LONG && end - start <= a.long_threshold) return;      // listed, but taken by a warp-level kernel (block-uniform)
   const int first = LONG ? start + grp : start;
   const int step = LONG ? G : 1;
   const Vec<V> qo = active ? Vec<V>::load(a.own + (size_t)seg * a.ldown + gl * V) : Vec<V>::zero();
@@ -265,6 +266,7 @@ __global__ void __launch_bounds__(kAttThreads) mh_spmm_kernel(const MhArgs a) {
   }
   const int start = __ldg(a.ptr + seg), end = __ldg(a.ptr + seg + 1);
   if (!LONG && end - start > a.long_threshold) return;
+  if (LONG && end - start <= a.long_threshold) return;      // listed, but taken by a warp-level kernel (block-uniform)
   const int first = LONG ? start + grp : start;
   const int step = LONG ? G : 1;
   Vec<V> acc = Vec<V>::zero();

@@ -28,6 +28,8 @@ int nl_fill_args(NlArgs& a, const gb_graph* g, int row_lo, int row_hi, const flo
 constexpr int kFusedWarps = 4;
 constexpr int kFusedThreads = kFusedWarps * 32;
 constexpr int kFusedCap = 256;          // max edges per segment handled here (== plan long threshold)
+constexpr int kColCap = 256;            // gb_nl_adjoint: longer columns go to the CTA-per-column kernels (measured: a single warp
+                                        // on a 4096-edge column costs more than it saves on the C4 and RMAT shapes)
 
 struct FusedFwdArgs {
   AttArgs att;            // segment structure, projections, outputs (att / abar / prods may be null)
@@ -195,6 +197,7 @@ struct FusedBwdArgs {
   const float* g; int32_t ldg;
   const float* x; int32_t ldx;
   int32_t xdv;             // vector chunks per state row
+  int32_t col_cap;         // columns up to this many edges are taken by att_col_bwd_kernel
   // outputs
   float* ds;               // [E,H] scratch: dL/d(raw score), CSR order
   float* dq; int32_t lddq;
@@ -306,7 +309,9 @@ __global__ void __launch_bounds__(kFusedThreads) att_row_bwd_kernel(const FusedB
   }
 }
 
-// one warp per CSC column: transpose SpMM (dx, dalpha/dbeta partials) + dk
+// one warp per CSC column: transpose SpMM (dx, dalpha/dbeta partials) + dk.  The column's per-edge scalars are
+// staged through shared memory in chunks of kFusedCap edges; the accumulators live in registers across the
+// chunks, so columns up to `a.col_cap` edges stay in this kernel (longer ones: CTA-per-column kernels).
 template <int V, int LPE, int XL, int XCPL>
 __global__ void __launch_bounds__(kFusedThreads) att_col_bwd_kernel(const FusedBwdArgs a) {
   extern __shared__ __align__(16) float smem[];
@@ -318,36 +323,43 @@ __global__ void __launch_bounds__(kFusedThreads) att_col_bwd_kernel(const FusedB
   if (seg < a.n) {
     start = __ldg(a.colptr + seg);
     deg = __ldg(a.colptr + seg + 1) - start;
-    if (deg > kFusedCap) deg = -1;                    // long column: handled elsewhere
+    if (deg > a.col_cap) deg = -1;                    // long column: handled elsewhere
   }
   if (deg >= 0) {
-    float* sS = smem + (size_t)warp * kFusedCap * (H + 2);   // ds of the column's edges
+    float* sS = smem + (size_t)warp * kFusedCap * (H + 2);   // ds of the chunk's edges
     float* sA = sS + kFusedCap * H;                           // abar
     int* sC = reinterpret_cast<int*>(sA + kFusedCap);         // row of each edge
-    // ---- pass 1: stage per-edge scalars (coalesced over the column's CSC slots) ----------------
-    for (int e = lane; e < deg; e += 32) {
-      const int slot = ld_stream_i32(a.tperm + start + e);
-      sC[e] = ld_stream_i32(a.rowidx + start + e);
-      sA[e] = __ldg(a.abar + slot);
-      for (int h = 0; h < H; ++h) sS[e * H + h] = __ldg(a.ds + (size_t)slot * H + h);
-    }
-    __syncwarp();
-    // ---- pass 2: t = sum_e abar_e g[row_e,:] - g[j,:] ; dx = alpha t ; partial sums -------------
-    {
-      const SpmmArgs& sp = a.sp;
-      constexpr int EPX = 32 / XL;
-      const int xl = lane % XL, xg = lane / XL;
-      Vec<V> acc[XCPL];
+    const SpmmArgs& sp = a.sp;
+    constexpr int EPX = 32 / XL;
+    const int xl = lane % XL, xg = lane / XL;
+    constexpr int EPI = 32 / LPE;
+    const int el = lane / LPE, cl = lane % LPE;
+    const int width = H * a.dk;
+    const bool active = cl * V < width;
+    const int my_head = active ? (cl * V) / a.dk : 0;
+    Vec<V> acc[XCPL];
 #pragma unroll
-      for (int j = 0; j < XCPL; ++j) acc[j] = Vec<V>::zero();
+    for (int j = 0; j < XCPL; ++j) acc[j] = Vec<V>::zero();
+    Vec<V> acck = Vec<V>::zero();
+    for (int c0 = 0; c0 < deg; c0 += kFusedCap) {
+      const int cn = min(kFusedCap, deg - c0);
+      // ---- stage per-edge scalars (coalesced over the column's CSC slots) -------------------------
+      for (int e = lane; e < cn; e += 32) {
+        const int slot = ld_stream_i32(a.tperm + start + c0 + e);
+        sC[e] = ld_stream_i32(a.rowidx + start + c0 + e);
+        sA[e] = __ldg(a.abar + slot);
+        for (int h = 0; h < H; ++h) sS[e * H + h] = __ldg(a.ds + (size_t)slot * H + h);
+      }
+      __syncwarp();
+      // ---- t += sum_e abar_e g[row_e,:] ----------------------------------------------------------
       constexpr int UX = XCPL == 1 ? 4 : 2;
-      for (int base = 0; base < deg; base += EPX * UX) {
+      for (int base = 0; base < cn; base += EPX * UX) {
         float w[UX];
         Vec<V> r[UX][XCPL];
 #pragma unroll
         for (int u = 0; u < UX; ++u) {
           const int e = base + u * EPX + xg;
-          const bool ok = e < deg;
+          const bool ok = e < cn;
           const int c = ok ? sC[e] : 0;
           w[u] = ok ? sA[e] : 0.f;
 #pragma unroll
@@ -361,48 +373,42 @@ __global__ void __launch_bounds__(kFusedThreads) att_col_bwd_kernel(const FusedB
 #pragma unroll
           for (int j = 0; j < XCPL; ++j) acc[j].fma(w[u], r[u][j]);
       }
-#pragma unroll
-      for (int j = 0; j < XCPL; ++j)
-        for (int o = XL; o < 32; o <<= 1)
-          acc[j] = Vec<V>::map2(acc[j], acc[j], [o](float p, float) { return p + __shfl_xor_sync(0xffffffffu, p, o); });
-      if (xg == 0) {
-        const float alpha = load_alpha(sp);
-#pragma unroll
-        for (int j = 0; j < XCPL; ++j) {
-          const int ch = xl + j * XL;
-          if (ch < sp.dv) row_epilogue<V, true>(sp, seg, ch * V, acc[j], alpha, 0.f, s1, s2);
-        }
-      }
-    }
-    // ---- pass 3: dk[j,h,:] = scale * sum_e ds[e,h] q[row_e,h,:] ---------------------------------
-    {
-      constexpr int EPI = 32 / LPE;
-      const int el = lane / LPE, cl = lane % LPE;
-      const int width = H * a.dk;
-      const bool active = cl * V < width;
-      const int my_head = active ? (cl * V) / a.dk : 0;
-      Vec<V> acc = Vec<V>::zero();
+      // ---- dk[j,h,:] += sum_e ds[e,h] q[row_e,h,:] -------------------------------------------------
       constexpr int U = 4;
-      for (int base = 0; base < deg; base += EPI * U) {
+      for (int base = 0; base < cn; base += EPI * U) {
         float w[U];
         Vec<V> r[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           const int e = base + u * EPI + el;
-          const bool ok = e < deg && active;
+          const bool ok = e < cn && active;
           w[u] = ok ? sS[e * H + my_head] : 0.f;
           r[u] = ok ? Vec<V>::load(a.q + (size_t)sC[e] * a.ldq + cl * V) : Vec<V>::zero();
         }
 #pragma unroll
-        for (int u = 0; u < U; ++u) acc.fma(w[u], r[u]);
+        for (int u = 0; u < U; ++u) acck.fma(w[u], r[u]);
       }
-      for (int o = LPE; o < 32; o <<= 1)
-        acc = Vec<V>::map2(acc, acc, [o](float p, float) { return p + __shfl_xor_sync(0xffffffffu, p, o); });
-      if (el == 0 && active) {
-        const float scale = 1.0f / sqrtf((float)a.dk);
-        acc = Vec<V>::map2(acc, acc, [scale](float p, float) { return p * scale; });
-        acc.store(a.dk_out + (size_t)seg * a.lddk + cl * V);
+      __syncwarp();                                   // the next chunk overwrites the staging buffers
+    }
+    // fixed-order combine of the edge sub-groups, epilogues
+#pragma unroll
+    for (int j = 0; j < XCPL; ++j)
+      for (int o = XL; o < 32; o <<= 1)
+        acc[j] = Vec<V>::map2(acc[j], acc[j], [o](float p, float) { return p + __shfl_xor_sync(0xffffffffu, p, o); });
+    if (xg == 0) {
+      const float alpha = load_alpha(sp);
+#pragma unroll
+      for (int j = 0; j < XCPL; ++j) {
+        const int ch = xl + j * XL;
+        if (ch < sp.dv) row_epilogue<V, true>(sp, seg, ch * V, acc[j], alpha, 0.f, s1, s2);
       }
+    }
+    for (int o = LPE; o < 32; o <<= 1)
+      acck = Vec<V>::map2(acck, acck, [o](float p, float) { return p + __shfl_xor_sync(0xffffffffu, p, o); });
+    if (el == 0 && active) {
+      const float scale = 1.0f / sqrtf((float)a.dk);
+      acck = Vec<V>::map2(acck, acck, [scale](float p, float) { return p * scale; });
+      acck.store(a.dk_out + (size_t)seg * a.lddk + cl * V);
     }
   }
   write_partials(a.sp, s1, s2, a.sp.partial_base + blockIdx.x);
@@ -617,7 +623,7 @@ int gb_att_bwd_fused(const gb_graph* g, const float* q, int32_t ldq, const float
   a.n = g->n; a.heads = heads; a.dk = dk; a.lh = dk / 4;
   a.q = q; a.ldq = ldq; a.k = k; a.ldk = ldk; a.att = att; a.abar = abar;
   a.g = gout; a.ldg = ldg; a.x = x; a.ldx = ldx; a.xdv = d / 4;
-  a.ds = ds; a.dq = dq; a.lddq = lddq; a.dk_out = dk_out; a.lddk = lddk;
+  a.ds = ds; a.dq = dq; a.lddq = lddq; a.dk_out = dk_out; a.lddk = lddk; a.col_cap = kFusedCap;
   SpmmArgs& sp = a.sp;
   sp.ptr = g->colptr; sp.idx = g->rowidx; sp.perm = g->tperm; sp.vals = abar; sp.n = g->n; sp.dv = d / 4;
   sp.long_threshold = kFusedCap; sp.src = gout; sp.lds = ldg; sp.alpha_train = alpha_train;
@@ -696,7 +702,7 @@ int gb_nl_adjoint(const gb_graph* g, int32_t row_lo, int32_t row_hi, const float
   b.n = g->n; b.heads = heads; b.dk = dk; b.lh = dk / 4;
   b.q = q; b.ldq = ldq; b.k = nullptr; b.ldk = 0; b.att = nullptr; b.abar = abar;
   b.g = gout; b.ldg = ldg; b.x = x; b.ldx = ldx; b.xdv = d / 4;
-  b.ds = ds; b.dq = dq; b.lddq = lddq; b.dk_out = dk_out; b.lddk = lddk;
+  b.ds = ds; b.dq = dq; b.lddq = lddq; b.dk_out = dk_out; b.lddk = lddk; b.col_cap = kColCap;
   SpmmArgs& sp = b.sp;
   sp.ptr = g->colptr; sp.idx = g->rowidx; sp.perm = g->tperm; sp.vals = abar; sp.n = g->n; sp.dv = d / 4;
   sp.long_threshold = kFusedCap; sp.src = gout; sp.lds = ldg; sp.alpha_train = alpha_train;
@@ -715,11 +721,12 @@ int gb_nl_adjoint(const gb_graph* g, int32_t row_lo, int32_t row_hi, const float
   if (nlc > 0) {
     SpmmArgs lsp = sp;
     lsp.partial_base = slots;
+    lsp.long_threshold = kColCap;                         // shorter listed columns were done above
     if (int rc = spmm_long_only(lsp, 4, true, nlc, stream)) return rc;
     slots += nlc;
     MhArgs mh{};
     mh.ptr = g->colptr; mh.idx = g->rowidx; mh.perm = g->tperm; mh.ds = ds; mh.src = q; mh.lds = ldq;
-    mh.out = dk_out; mh.ldo = lddk; mh.n = g->n; mh.heads = heads; mh.dk = dk; mh.long_threshold = kFusedCap;
+    mh.out = dk_out; mh.ldo = lddk; mh.n = g->n; mh.heads = heads; mh.dk = dk; mh.long_threshold = kColCap;
     mh.scale = 1.0f / sqrtf((float)dk); mh.long_list = g->long_cols;
     if (int rc = mh_spmm_long(mh, 4, nlc, K_EDGE_SCORE_BWD_K, stream)) return rc;
   }

@@ -23,7 +23,7 @@ int nl_fill_args(NlArgs& a, const gb_graph* g, int row_lo, int row_hi, const flo
   a.dv = d / 4; a.adim = heads * dk; a.dk = dk; a.q = q; a.ldq = ldq; a.wk = wk; a.ldwk = ldwk;
   a.counter = static_cast<int32_t*>(workspace);
   a.long_list = g->long_rows;
-  a.long_threshold = g->long_threshold > 0 ? g->long_threshold : 0x7fffffff;
+  a.long_threshold = g->long_threshold > 0 ? (g->long_threshold > kNlLongRow ? g->long_threshold : kNlLongRow) : 0x7fffffff;
   SpmmArgs& sp = a.sp;
   sp.src = x; sp.lds = ldx; sp.alpha_train = alpha_train; sp.alpha_sigmoid = alpha_sigmoid; sp.n = g->n; sp.dv = d / 4;
   const bool source = x0 != nullptr && beta_train != nullptr;

@@ -40,6 +40,9 @@ namespace gb {
 constexpr int kNlWarps = 8;
 constexpr int kNlThreads = kNlWarps * 32;
 constexpr int kNlChunkRows = 4;          // rows per scheduler grab
+constexpr int kNlLongRow = 2048;         // rows longer than this get a whole CTA (the online softmax needs no
+                                         // per-edge shared memory, so a warp can take rows far beyond the plan's
+                                         // 256-edge list threshold; the scheduler balances them)
 constexpr unsigned kFullMask = 0xffffffffu;
 
 struct NlArgs {
@@ -439,6 +442,7 @@ __global__ void __launch_bounds__(kNlThreads, 1) nl_long_kernel(const NlArgs a) 
   const int row = __ldg(a.long_list + blockIdx.x);
   if (row < a.row_lo || row >= a.row_hi) return;
   const int start = __ldg(a.rowptr + row), end = __ldg(a.rowptr + row + 1);
+  if (end - start <= a.long_threshold) return;              // listed by the plan (> 256) but taken by a warp
   nl_stage_wk(a, wk_s, ldw);
   for (int j = threadIdx.x; j < a.adim; j += blockDim.x) q_s[j] = __ldg(a.q + (size_t)row * a.ldq + j);
   __syncthreads();

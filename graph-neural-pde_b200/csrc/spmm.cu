@@ -82,6 +82,10 @@ __global__ void __launch_bounds__(kSpmmThreads) spmm_long(const SpmmArgs a) {
   const int grp = threadIdx.x / LPR;
   const int row = __ldg(a.long_list + blockIdx.x);
   const int start = __ldg(a.ptr + row), end = __ldg(a.ptr + row + 1);
+  if (end - start <= a.long_threshold) {                    // listed, but taken by a warp-level kernel (block-uniform)
+    if (BWD) write_partials(a, 0.f, 0.f, a.partial_base + blockIdx.x);
+    return;
+  }
   const float alpha = load_alpha(a);
   const float beta = (!BWD && a.beta_train != nullptr) ? __ldg(a.beta_train) : 0.f;
   Vec<V> acc[CPL];
