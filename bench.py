@@ -39,8 +39,8 @@ def read_peaks():
     return 6650.0, 'fallback (B200_PROFILING.md)'
 
 
-def make_opt(cfg, adjoint=True):
-    return {'hidden_dim': cfg['d'], 'block': 'attention', 'function': 'transformer', 'max_nfe': 10 ** 9,
+def make_opt(cfg, adjoint=True, function='transformer'):
+    return {'hidden_dim': cfg['d'], 'block': 'attention' if function == 'transformer' else 'constant', 'function': function, 'max_nfe': 10 ** 9,
             'no_alpha_sigmoid': False, 'add_source': True, 'augment': False, 'adjoint': adjoint, 'tol_scale': 1.0,
             'tol_scale_adjoint': 1.0, 'data_norm': 'rw', 'self_loop_weight': 1.0, 'method': 'rk4',
             'step_size': STEP_SIZE, 'max_iters': 100, 'adjoint_method': 'rk4', 'adjoint_step_size': STEP_SIZE,
@@ -142,20 +142,32 @@ class ClockSampler:
 
 
 # ---- our arm ------------------------------------------------------------------------------------
+FUNCTION = 'transformer'      # --function: transformer = GRAND-nl (headline), laplacian = GRAND-l (constant block)
+
+
 def build_block(cfg, device):
     import grand_b200
-    opt = make_opt(cfg)
+    opt = make_opt(cfg, function=FUNCTION)
     block = grand_b200.set_block(opt)(grand_b200.set_function(opt), [], opt, device,
                                       t=torch.tensor([0., T_END])).to(device)
     block.train()
     g = torch.Generator().manual_seed(7)
     with torch.no_grad():                       # random-init weights of the named architecture (N(0, 1/d))
-        for layer in (block.odefunc.multihead_att_layer, block.multihead_att_layer):
-            for lin in (layer.Q, layer.K):
-                lin.weight.copy_((torch.randn(lin.weight.shape, generator=g) / cfg['d'] ** 0.5).to(device))
+        if FUNCTION == 'transformer':
+            for layer in (block.odefunc.multihead_att_layer, block.multihead_att_layer):
+                for lin in (layer.Q, layer.K):
+                    lin.weight.copy_((torch.randn(lin.weight.shape, generator=g) / cfg['d'] ** 0.5).to(device))
         block.odefunc.alpha_train.fill_(0.3)
         block.odefunc.beta_train.fill_(0.1)
     return block
+
+
+def model_name():
+    return 'GRAND-nl' if FUNCTION == 'transformer' else 'GRAND-l'
+
+
+def block_name():
+    return 'AttODEblock + ODEFuncTransformerAtt' if FUNCTION == 'transformer' else 'ConstantODEblock + LaplacianODEFunc'
 
 
 def train_pass(block, data, x_dev, g_dev):
@@ -268,8 +280,8 @@ def run_ours(args):
         'unit': 'evals/s', 'n_gpus': 1, 'steps': args.steps, 'warmup': max(args.warmup, 3),
         'ms_per_step': round(ms / args.steps, 3), 'higher_is_better': True, 'scaling': 'strong',
         'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-        'config': {'workload': f"{name}: GRAND-nl ({cfg['desc']}), N={n}, E'={e_prime}, d={d}, heads={cfg['heads']}, "
-                               f"attention_dim={cfg['adim']}, AttODEblock + ODEFuncTransformerAtt, rk4 step {STEP_SIZE} "
+        'config': {'workload': f"{name}: {model_name()} ({cfg['desc']}), N={n}, E'={e_prime}, d={d}, heads={cfg['heads']}, "
+                               f"attention_dim={cfg['adim']}, {block_name()}, rk4 step {STEP_SIZE} "
                                f"T={T_END}, odeint_adjoint (rk4)",
                    'evals_per_step': evals, 'l2': 'inputs larger than L2 (no flush)' if name in ('c4', 'c5')
                    else 'working set partly L2-resident; no flush (state reused across evaluations as in the solver)'},
@@ -278,6 +290,12 @@ def run_ours(args):
                 'ms_per_step': round(ms_e2e / args.steps, 3)},
         'gpu_launches': int(launches), 'clocks': clocks.summary(), 'roofline': roofline,
     }
+    if args.gpu_reference:
+        try:
+            line['gpu_reference'] = gpu_reference(name, cfg, device)
+            line['gpu_reference']['speedup_of_value'] = round(line['value'] / line['gpu_reference']['value'], 1)
+        except torch.cuda.OutOfMemoryError as exc:                       # the comparator's temporaries, not ours
+            line['gpu_reference'] = {'unavailable': f'out of memory in the torch-ops comparator: {str(exc)[:80]}'}
     if args.cpu_baseline:
         line['cpu_baseline'] = cpu_baseline(name, cfg, steps=1, warmup=0)
     emit(line)
@@ -398,8 +416,8 @@ def run_partitioned(args, cfg, device, rank, world):
         'unit': 'evals/s', 'n_gpus': world, 'steps': args.steps, 'warmup': max(args.warmup, 3),
         'ms_per_step': round(ms / args.steps, 3), 'higher_is_better': True, 'scaling': 'strong',
         'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-        'config': {'workload': f"{name}: GRAND-nl ({cfg['desc']}), N={n}, E'={int(e_total)}, d={d}, heads={cfg['heads']}, "
-                               f"attention_dim={cfg['adim']}, AttODEblock + ODEFuncTransformerAtt, rk4 step {STEP_SIZE} "
+        'config': {'workload': f"{name}: {model_name()} ({cfg['desc']}), N={n}, E'={int(e_total)}, d={d}, heads={cfg['heads']}, "
+                               f"attention_dim={cfg['adim']}, {block_name()}, rk4 step {STEP_SIZE} "
                                f"T={T_END}, odeint_adjoint (rk4)",
                    'parallelism': f'1-D row partition over {world} GPUs ({part.slab} rows each), all-gather of the '
                                   f'state per evaluation + reduce-scatter of dL/dx per VJP (NCCL)',
@@ -416,11 +434,84 @@ def run_partitioned(args, cfg, device, rank, world):
     emit(line)
 
 
+# ---- GPU comparator: the upstream-semantics path with stock torch CUDA ops -----------------------------
+GPU_REF_SCALE = {'c1': 1, 'c2': 1, 'c3': 1, 'c4': 8, 'c5': 32}
+
+
+def gpu_reference(name, cfg, device):
+    """SURVEY.md 8d comparator (3): what the reference's GPU path does when its sparse dependencies are present -
+    index_select gathers, [E,d] temporaries, scatter_add / scatter_max (float atomics), autograd backward -
+    written with plain torch CUDA ops (torch_sparse / torch_scatter / PyG are not installable here; they
+    lower to exactly these kernels).  Timed on a down-scaled sample of the same shape (its [E,d] temporaries do
+    not fit otherwise), 1 forward evaluation + 1 adjoint evaluation, extrapolated linearly.  None of our kernels."""
+    import math
+    from grand_b200 import synth
+    div = GPU_REF_SCALE[name]
+    ei, n = synth.make_graph(name, device, seed=77, scale_div=div)
+    loops = torch.arange(n, device=device)
+    ei = torch.cat([ei[:, ei[0] != ei[1]], torch.stack([loops, loops])], dim=1)
+    row, col = ei[0], ei[1]
+    d, a, h = cfg['d'], cfg['adim'], cfg['heads']
+    dk = a // h
+    g = torch.Generator(device=device).manual_seed(3)
+    mk = lambda *shape: torch.randn(*shape, generator=g, device=device)
+    x, x0, gout = mk(n, d), mk(n, d), mk(n, d)
+    wq, wk = (mk(a, d) / d ** 0.5).requires_grad_(True), (mk(a, d) / d ** 0.5).requires_grad_(True)
+    bq, bk = mk(a).requires_grad_(True), mk(a).requires_grad_(True)
+    alpha, beta = torch.tensor(0.3, device=device, requires_grad=True), torch.tensor(0.1, device=device, requires_grad=True)
+
+    def f_eval(xx):
+        if FUNCTION == 'transformer':
+            q, k = xx @ wq.t() + bq, xx @ wk.t() + bk
+            prods = (q.view(n, h, dk)[row] * k.view(n, h, dk)[col]).sum(dim=2) / math.sqrt(dk)
+            idx = row[:, None].expand(-1, h)
+            mx = torch.zeros(n, h, device=device).scatter_reduce(0, idx, prods.detach(), reduce='amax', include_self=False)
+            ex = (prods - mx[row]).exp()
+            den = torch.zeros(n, h, device=device).index_add_(0, row, ex)
+            vals = (ex / (den[row] + 1e-16)).mean(dim=1)
+        else:
+            vals = torch.full((row.numel(),), 0.05, device=device)
+        ax = torch.zeros_like(xx).index_add_(0, row, vals[:, None] * xx[col])
+        return torch.sigmoid(alpha) * (ax - xx) + beta * x0
+
+    params = (wq, bq, wk, bk, alpha, beta) if FUNCTION == 'transformer' else (alpha, beta)
+
+    def one_pass():
+        with torch.no_grad():
+            f_eval(x)
+        xs = x.detach().requires_grad_(True)
+        torch.autograd.grad(f_eval(xs), (xs,) + params, gout)
+
+    one_pass()
+    torch.cuda.synchronize()
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 3
+    start.record()
+    for _ in range(reps):
+        one_pass()
+    stop.record()
+    torch.cuda.synchronize()
+    ms = start.elapsed_time(stop) / reps
+    del x, x0, gout, ei
+    torch.cuda.empty_cache()
+    return {'value': round(2 / (ms * 1e-3) / div, 3), 'unit': 'evals/s', 'kind': 'torch CUDA ops (index_select, [E,d] '
+            'temporaries, scatter_add / scatter_reduce atomics, autograd) = what torch_sparse.spmm + PyG softmax lower to',
+            'sample': f'{name} shape scaled 1/{div} (N={n}, E\'={row.numel()}), 1 forward + 1 adjoint evaluation, '
+                      f'{ms:.2f} ms per pair, evals/s divided by {div}'}
+
+
 # ---- CPU baseline / reference arm (the only place bench.py executes oracle/) ----------------------
 def cpu_pass(state):
     """one forward evaluation + one adjoint-dynamics evaluation (f recomputed + VJP) of the oracle port"""
     from oracle import funcs
     x, ei, wq, bq, wk, bk, x0, g, heads = state
+    if FUNCTION == 'laplacian':
+        with torch.no_grad():
+            funcs.laplacian_f(x, ei, state.w, state.alpha, state.beta, x0)
+        xs = x.detach().requires_grad_(True)
+        f = funcs.laplacian_f(xs, ei, state.w, state.alpha, state.beta, x0)
+        torch.autograd.grad(f, (xs, state.alpha, state.beta), g)
+        return 2
     with torch.no_grad():
         funcs.transformer_f(x, ei, wq, bq, wk, bk, heads, state.alpha, state.beta, x0)
     xs = x.detach().requires_grad_(True)
@@ -443,7 +534,7 @@ def make_cpu_state(name, cfg, scale_div):
     else:
         n = cfg['n'] // scale_div
         ei = og.shaped_graph(n, (cfg['e'] // scale_div) // 2 * 2, 1234)
-    ei, _ = og.reset_graph_data(ei, None, n, 'rw', 1.0)
+    ei, w_rw = og.reset_graph_data(ei, None, n, 'rw', 1.0)
     d, a = cfg['d'], cfg['adim']
     g = torch.Generator().manual_seed(5)
     mk = lambda *s: torch.randn(*s, generator=g)
@@ -453,6 +544,7 @@ def make_cpu_state(name, cfg, scale_div):
     st.alpha = torch.tensor(0.3, requires_grad=True)
     st.beta = torch.tensor(0.1, requires_grad=True)
     st.n, st.e = n, ei.shape[1]
+    st.w = torch.tensor(w_rw)
     return st
 
 
@@ -472,7 +564,7 @@ def cpu_baseline(name, cfg, steps=1, warmup=1):
         evals += cpu_pass(st)
     dt = time.perf_counter() - t0
     return {'value': round(evals / dt / div, 4), 'unit': 'evals/s', 'cores': cores, 'kind': 'port',
-            'sample': f'oracle port (torch CPU fp32, upstream-semantics sparse restatement) on the {name} shape scaled '
+            'sample': f'oracle port (torch CPU fp32, upstream-semantics sparse restatement, {model_name()}) on the {name} shape scaled '
                       f'1/{div} (N={st.n}, E\'={st.e}); {steps} x (1 forward eval + 1 adjoint eval); evals/s divided '
                       f'by {div} (linear-cost extrapolation to the full shape)',
             'seconds': round(dt, 2)}
@@ -489,7 +581,12 @@ def run_reference(args):
             'unit': 'evals/s', 'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
             'ms_per_step': round(base['seconds'] / max(1, args.steps) * 1e3, 3), 'higher_is_better': True,
             'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-            'config': {'workload': f"{args.workload}: GRAND-nl ({cfg['desc']}) - CPU port of the reference path"},
+            'config': {'workload': f"{args.workload}: {model_name()} ({cfg['desc']}), N={cfg['n']}, E'={cfg['e'] + cfg['n']}, "
+                                   f"d={cfg['d']}, heads={cfg['heads']}, attention_dim={cfg['adim']}, {block_name()}, rk4 step "
+                                   f"{STEP_SIZE} T={T_END}, odeint_adjoint (rk4)",
+                       'arm': 'reference path on the host cores (oracle port of the upstream-semantics sparse path; the '
+                              'reference itself needs dense [N,N] memory and uninstallable sparse packages), bounded sample, '
+                              'see cpu_baseline.sample'},
             'cpu_baseline': base,
             'e2e': {'value': base['value'], 'unit': 'evals/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
     emit(line)
@@ -516,7 +613,13 @@ def main():
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--workload', default='c4', choices=['c1', 'c2', 'c3', 'c4', 'c5'])
     ap.add_argument('--no-cpu-baseline', dest='cpu_baseline', action='store_false')
+    ap.add_argument('--no-gpu-reference', dest='gpu_reference', action='store_false',
+                    help='skip the torch-CUDA-ops comparator (N = 1 only)')
+    ap.add_argument('--function', default='transformer', choices=['transformer', 'laplacian'],
+                    help='transformer = GRAND-nl (BASELINE.json headline); laplacian = GRAND-l sweep of config 5')
     args = ap.parse_args()
+    global FUNCTION
+    FUNCTION = args.function
     if args.impl == 'reference':
         run_reference(args)
     else:
