@@ -202,7 +202,7 @@ class ODEFuncTransformerAtt(ODEFunc):
                                           L.K.weight.detach().contiguous(), self.alpha_train.detach(),
                                           self.beta_train.detach() if x0 is not None else None, x0, L.h, sig)
         halo.all_reduce_(grads)
-        dalpha, dbeta, dwq, dwk, dbq, dbk = P.unpack_nl_grads(grads, a, d)
+        dwq, dwk, dbq, dbk, dalpha, dbeta = P.unpack_nl_grads(grads, a, d)
         named = ((self.alpha_train, dalpha.reshape(self.alpha_train.shape)), (self.beta_train, dbeta.reshape(())),
                  (L.Q.weight, dwq), (L.Q.bias, dbq), (L.K.weight, dwk), (L.K.bias, dbk))
         out = []

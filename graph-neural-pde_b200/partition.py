@@ -138,9 +138,10 @@ def nl_local_forward(part, plan, x_full, x_slab, wq, bq, wk, alpha_train, beta_t
 
 def nl_local_vjp(part, plan, x_full, q, wq, wk, alpha_train, beta_train, x0_slab, heads, alpha_sigmoid, g_slab,
                  want_f, want_w):
-    """this rank's share of the VJP.  Returns (f_slab|None, dx_share [N_pad,d] (to be reduce-scattered),
-    dx_own [S,d] (owner-only term dq Wq, added after the reduce-scatter), grads [2 + 2A(d+1)] flat share of
-    (dalpha, dbeta, dWq, dWk, dbq, dbk) or None) - sums over ranks give the single-GPU numbers."""
+    """this rank's share of the VJP.  Returns (f_slab|None, dx_share [N_pad,d] (to be reduce-scattered; already
+    holds dq Wq for the owned rows and dk Wk for every column), grads: flat share of
+    (dWq, dWk, dbq, dbk, dalpha, dbeta) [2A(d+1) + 2], or of (dalpha, dbeta) [2] when want_w is False) -
+    sums over ranks give the single-GPU numbers."""
     from .ops import _nl_workspace
     lib = _lib.load()
     n_pad, d = x_full.shape
@@ -151,47 +152,36 @@ def nl_local_vjp(part, plan, x_full, q, wq, wk, alpha_train, beta_train, x0_slab
     ds = torch.empty(plan.e, heads, **f32)
     dabar = torch.empty(plan.e, **f32)
     abar = torch.empty(plan.e, **f32)
-    dq = torch.zeros(s, a, **f32) if part.hi - part.lo < s else torch.empty(s, a, **f32)
-    dk = torch.empty(n_pad, a, **f32)
+    # [dq | dk] for ALL rows in one buffer: dq is non-zero on the owned rows only, dk is this rank's share for
+    # every column - so ONE tensor-core GEMM each gives dx += [dq|dk] [Wq;Wk] and d[Wq;Wk] = [dq|dk]^T x
+    dqk = torch.empty(n_pad, 2 * a, **f32)
+    dqk[:part.lo, :a].zero_()
+    dqk[part.hi:, :a].zero_()
     dx = torch.empty(n_pad, d, **f32)
     out = None
     if want_f:
         out = torch.zeros(s, d, **f32) if part.hi - part.lo < s else torch.empty(s, d, **f32)
     partials = torch.empty(int(lib.gb_att_bwd_fused_partials(plan.c)), **f32)
-    dparams = torch.empty(2, **f32)
+    grads = torch.empty(2 * a * d + 2 * a + 2 if want_w else 2, **f32)
+    dparams = grads[-2:]
     source = beta_train is not None and x0_slab is not None
     _lib.check(lib.gb_nl_adjoint(plan.c, part.lo, part.hi, x_full.data_ptr(), d, _virt(q, part.lo, a), a,
                                  wk.data_ptr(), d, heads, a // heads, d,
                                  _virt(x0_slab, part.lo, d) if source else None, d, alpha_train.data_ptr(),
                                  int(alpha_sigmoid), beta_train.data_ptr() if source else None,
                                  _virt(g_slab, part.lo, d), d, _virt(out, part.lo, d), d, ds.data_ptr(),
-                                 dabar.data_ptr(), abar.data_ptr(), _virt(dq, part.lo, a), a, dk.data_ptr(), a,
-                                 dx.data_ptr(), d, partials.data_ptr(), dparams.data_ptr(),
+                                 dabar.data_ptr(), abar.data_ptr(), dqk.data_ptr(), 2 * a, dqk.data_ptr() + 4 * a,
+                                 2 * a, dx.data_ptr(), d, partials.data_ptr(), dparams.data_ptr(),
                                  _nl_workspace(dev).data_ptr(), _lib.stream()), 'gb_nl_adjoint')
-    # dx_share += dk_share Wk (linear, so it can go through the reduce-scatter)
-    _lib.check(lib.gb_linear_bwd_x(dk.data_ptr(), a, n_pad, a, wk.data_ptr(), d, dx.data_ptr(), d, 1, _lib.stream()),
-               'gb_linear_bwd_x')
-    x_slab = x_full[part.rank * s:(part.rank + 1) * s]
-    dx_own = torch.empty(s, d, **f32)
-    _lib.check(lib.gb_linear_bwd_x(dq.data_ptr(), a, s, a, wq.data_ptr(), d, dx_own.data_ptr(), d, 0, _lib.stream()),
-               'gb_linear_bwd_x')
-    grads = None
+    w_cat = torch.cat([wq, wk], dim=0)
+    _lib.check(lib.gb_linear_bwd_x(dqk.data_ptr(), 2 * a, n_pad, 2 * a, w_cat.data_ptr(), d, dx.data_ptr(), d, 1,
+                                   _lib.stream()), 'gb_linear_bwd_x')
     if want_w:
-        grads = torch.empty(2 + 2 * a * d + 2 * a, **f32)
-        grads[:2] = dparams
-        dwq, dwk = grads[2:2 + a * d].view(a, d), grads[2 + a * d:2 + 2 * a * d].view(a, d)
-        dbq, dbk = grads[2 + 2 * a * d:2 + 2 * a * d + a], grads[2 + 2 * a * d + a:]
-        for dy, xx, rows, dw, db in ((dq, x_slab, s, dwq, dbq), (dk, x_full, n_pad, dwk, dbk)):
-            ws = torch.empty(int(lib.gb_linear_bwd_w_workspace_bytes(rows, d, a)), dtype=torch.uint8, device=dev)
-            dw_t, db_t = torch.empty(a, d, **f32), torch.empty(a, **f32)
-            _lib.check(lib.gb_linear_bwd_w(dy.data_ptr(), a, xx.data_ptr(), d, rows, d, a, dw_t.data_ptr(),
-                                           db_t.data_ptr(), ws.data_ptr(), ws.numel(), _lib.stream()),
-                       'gb_linear_bwd_w')
-            dw.copy_(dw_t)
-            db.copy_(db_t)
-    else:
-        grads = dparams
-    return out, dx, dx_own, grads
+        ws = torch.empty(int(lib.gb_linear_bwd_w_workspace_bytes(n_pad, d, 2 * a)), dtype=torch.uint8, device=dev)
+        _lib.check(lib.gb_linear_bwd_w(dqk.data_ptr(), 2 * a, x_full.data_ptr(), d, n_pad, d, 2 * a, grads.data_ptr(),
+                                       grads.data_ptr() + 4 * 2 * a * d, ws.data_ptr(), ws.numel(), _lib.stream()),
+                   'gb_linear_bwd_w')
+    return out, dx, grads
 
 
 def diffusion_local_forward(part, plan, vals, x_full, x0_slab, alpha_train, beta_train, alpha_sigmoid):
@@ -247,19 +237,21 @@ class PartNlFn(torch.autograd.Function):
     def backward(ctx, g_slab):
         x_full, q, wq, wk, alpha_train, beta_train, x0_slab = ctx.saved_tensors
         a, d = wq.shape
-        _, dx_share, dx_own, grads = nl_local_vjp(ctx.part, ctx.plan, x_full, q, wq.contiguous(), wk.contiguous(),
-                                                  alpha_train, beta_train, x0_slab, ctx.heads, ctx.alpha_sigmoid,
-                                                  g_slab.contiguous(), False, True)
-        dx = ctx.halo.reduce_scatter_rows(dx_share).add_(dx_own)
+        _, dx_share, grads = nl_local_vjp(ctx.part, ctx.plan, x_full, q, wq.contiguous(), wk.contiguous(), alpha_train,
+                                          beta_train, x0_slab, ctx.heads, ctx.alpha_sigmoid, g_slab.contiguous(),
+                                          False, True)
+        dx = ctx.halo.reduce_scatter_rows(dx_share)
         ctx.halo.all_reduce_(grads)
-        dalpha, dbeta, dwq, dwk, dbq, dbk = unpack_nl_grads(grads, a, d)
+        dwq, dwk, dbq, dbk, dalpha, dbeta = unpack_nl_grads(grads, a, d)
         return (dx, dwq, dbq, dwk, dbk, dalpha.reshape(alpha_train.shape),
                 dbeta.reshape(()) if beta_train is not None else None) + (None,) * 6
 
 
 def unpack_nl_grads(grads, a, d):
-    return (grads[0], grads[1], grads[2:2 + a * d].view(a, d), grads[2 + a * d:2 + 2 * a * d].view(a, d),
-            grads[2 + 2 * a * d:2 + 2 * a * d + a], grads[2 + 2 * a * d + a:])
+    """flat (dWq, dWk, dbq, dbk, dalpha, dbeta) as written by nl_local_vjp"""
+    w = 2 * a * d
+    return (grads[:a * d].view(a, d), grads[a * d:w].view(a, d), grads[w:w + a], grads[w + a:w + 2 * a],
+            grads[w + 2 * a], grads[w + 2 * a + 1])
 
 
 class PartDiffusionFn(torch.autograd.Function):
@@ -295,7 +287,7 @@ def nl_eval_vjp_part(part, halo, plan, x_slab, g_slab, wq, bq, wk, alpha_train, 
     x_full = halo.all_gather_rows(x_slab)
     from .ops import _nl_q
     q = _nl_q(x_slab, wq, bq)
-    f, dx_share, dx_own, grads = nl_local_vjp(part, plan, x_full, q, wq, wk, alpha_train, beta_train, x0_slab, heads,
-                                              alpha_sigmoid, g_slab.contiguous(), True, True)
-    dx = halo.reduce_scatter_rows(dx_share).add_(dx_own)
+    f, dx_share, grads = nl_local_vjp(part, plan, x_full, q, wq, wk, alpha_train, beta_train, x0_slab, heads,
+                                      alpha_sigmoid, g_slab.contiguous(), True, True)
+    dx = halo.reduce_scatter_rows(dx_share)
     return f, dx, grads

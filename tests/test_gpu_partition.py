@@ -52,7 +52,7 @@ def test_nl_ranks_sum_to_single_gpu(world, n, d, heads, adim):
     part0 = P.RowPartition(n, world, 0)
     pad = lambda a: torch.cat([dev(a), torch.zeros(part0.n_pad - n, d, device='cuda')])
     x_full, x0_full, g_full = pad(x), pad(x0), pad(g)
-    f_parts, dx_share, dx_own, grads = [], 0, [], 0
+    f_parts, dx_share, grads = [], 0, 0
     for r in range(world):
         part = P.RowPartition(n, world, r)
         ei_loc, _ = part.local_edges(dev(ei))
@@ -62,21 +62,20 @@ def test_nl_ranks_sum_to_single_gpu(world, n, d, heads, adim):
         out, q = P.nl_local_forward(part, plan, x_full, x_slab, L.Q.weight.detach(), L.Q.bias.detach(),
                                     L.K.weight.detach(), func.alpha_train.detach(), func.beta_train.detach(),
                                     x0_slab, heads, True)
-        f2, share, own, gr = P.nl_local_vjp(part, plan, x_full, q, L.Q.weight.detach(), L.K.weight.detach(),
+        f2, share, gr = P.nl_local_vjp(part, plan, x_full, q, L.Q.weight.detach(), L.K.weight.detach(),
                                             func.alpha_train.detach(), func.beta_train.detach(), x0_slab, heads, True,
                                             g_slab, True, True)
         assert_close(f2, out, 1e-6, 'f of the adjoint kernel vs the forward kernel')
         assert float(out[part.hi - part.lo:].abs().max() if part.hi - part.lo < part.slab else 0.0) == 0.0
         f_parts.append(out)
         dx_share = dx_share + share                                          # reduce-scatter == sum, then slice
-        dx_own.append(own)
         grads = grads + gr                                                   # all-reduce
     f = torch.cat(f_parts)[:n]
-    dx = (dx_share + torch.cat(dx_own))[:n]
+    dx = dx_share[:n]
     assert_close(f, f_ref, 2e-6, 'f')
     assert_close(dx, dx_ref, 1e-5, 'dx')
     a = adim
-    dalpha, dbeta, dwq, dwk, dbq, dbk = P.unpack_nl_grads(grads, a, d)
+    dwq, dwk, dbq, dbk, dalpha, dbeta = P.unpack_nl_grads(grads, a, d)
     bias_scale = float(p_ref[1].abs().max())
     for got, ref, name in ((dwq, p_ref[0], 'dWq'), (dbq, p_ref[1], 'dbq'), (dwk, p_ref[2], 'dWk'),
                            (dbk, p_ref[3], 'dbk'), (dalpha, p_ref[4], 'dalpha'), (dbeta, p_ref[5], 'dbeta')):
