@@ -19,10 +19,11 @@ from .block_transformer_attention import AttODEblock
 from .model_configurations import set_block, set_function
 from . import integrators
 from . import partition
+from .graphed import GraphedPass
 from .partition import RowPartition, Halo, LoopbackHalo
 from .integrators import odeint, odeint_adjoint
 
 __all__ = ['GraphPlan', 'get_plan', 'MaxNFEException', 'get_rw_adj', 'gcn_norm_fill_val',
            'add_remaining_self_loops', 'Meter', 'ODEFunc', 'ODEblock', 'GraphData', 'LaplacianODEFunc',
            'ODEFuncTransformerAtt', 'SpGraphTransAttentionLayer', 'ConstantODEblock', 'AttODEblock',
-           'set_block', 'set_function', 'partition', 'RowPartition', 'Halo', 'LoopbackHalo', 'odeint', 'odeint_adjoint', 'integrators']
+           'set_block', 'set_function', 'partition', 'GraphedPass', 'RowPartition', 'Halo', 'LoopbackHalo', 'odeint', 'odeint_adjoint', 'integrators']

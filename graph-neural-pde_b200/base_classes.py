@@ -170,8 +170,17 @@ class ODEblock(nn.Module):
 
     def _integrate(self, x):
         """the integrator call shared by ConstantODEblock / AttODEblock (block_constant.py:34-58)"""
-        t = self.t.type_as(x)
         integrator = self.train_integrator if self.training else self.test_integrator
+        # the restated solvers read the time grid on the host: keep it a CPU tensor (no device sync per pass,
+        # which also makes the pass capturable in a CUDA graph); torchdiffeq wants it next to the state
+        ours = getattr(integrator, '__module__', '').endswith('integrators')
+        if ours:
+            host = getattr(self, '_t_host', None)
+            if host is None or host[0] is not self.t:              # one device read per time grid, then cached
+                host = self._t_host = (self.t, self.t.detach().cpu())
+            t = host[1].to(x.dtype)
+        else:
+            t = self.t.type_as(x)
         func = self.odefunc
         opt = self.opt
         if opt['adjoint'] and self.training:
