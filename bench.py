@@ -397,7 +397,7 @@ def run_partitioned(args, cfg, device, rank, world):
         return float(ms), out
 
     launches0 = _lib.launch_count()
-    halo.bytes_in = 0
+    halo.bytes_in = halo.n_gathers = halo.n_scatters = 0
 
     def loop():
         tot = 0
@@ -411,6 +411,7 @@ def run_partitioned(args, cfg, device, rank, world):
         kernels = prof.results()
     launches = _lib.launch_count() - launches0
     halo_bytes = halo.bytes_in
+    n_gathers, n_scatters = halo.n_gathers // args.steps, halo.n_scatters // args.steps
 
     gx_host = torch.empty(part.slab, d).pin_memory()
 
@@ -470,7 +471,40 @@ def run_partitioned(args, cfg, device, rank, world):
                    'note': 'received bytes of the all-gathers / reduce-scatters divided by the WHOLE step time '
                            '(the exchanges are not overlapped with compute yet)'},
     }
+    line['nvlink'].update(exchange_times(halo, part, d, device, n_gathers, n_scatters, ms / args.steps))
     emit(line)
+
+
+def exchange_times(halo, part, d, device, n_gathers, n_scatters, step_ms):
+    """the two collectives of the partitioned path timed alone (CUDA events, max over ranks), outside the timed
+    region: how much of a step is exchange, and the NVLink rate the exchanges themselves reach"""
+    import torch.distributed as dist
+    slab = torch.zeros(part.slab, d, device=device)
+    full = torch.zeros(part.n_pad, d, device=device)
+    out = {}
+    for key, fn in (('all_gather_ms', lambda: halo.all_gather_rows(slab)),
+                    ('reduce_scatter_ms', lambda: halo.reduce_scatter_rows(full))):
+        for _ in range(3):
+            fn()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        dist.barrier()
+        torch.cuda.synchronize()
+        a.record()
+        for _ in range(10):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([a.elapsed_time(b) / 10], device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out[key] = round(float(t), 3)
+    recv = (part.world - 1) * part.slab * d * 4
+    out['all_gather_GBps_in'] = round(recv / (out['all_gather_ms'] * 1e-3) / 1e9, 1)
+    out['reduce_scatter_GBps_in'] = round(recv / (out['reduce_scatter_ms'] * 1e-3) / 1e9, 1)
+    out['exchanges_per_step'] = {'all_gather': n_gathers, 'reduce_scatter': n_scatters}
+    ex = n_gathers * out['all_gather_ms'] + n_scatters * out['reduce_scatter_ms']
+    out['exchange_ms_per_step'] = round(ex, 2)
+    out['exchange_share_of_step'] = round(ex / step_ms, 3)
+    return out
 
 
 # ---- GPU comparator: the upstream-semantics path with stock torch CUDA ops -----------------------------

@@ -73,8 +73,37 @@ struct NlArgs {
 constexpr int ilog2_c(int v) { return v <= 1 ? 0 : 1 + ilog2_c(v / 2); }
 
 __device__ __forceinline__ float4 f4_zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
+
+// Packed fp32 (sm_100: fma/mul.rn.f32x2 -> FFMA2 / FMUL2).  The row kernels are bound by instruction issue,
+// not by the fma pipe: one FFMA2 takes one issue slot for two FMAs, and its scalar-broadcast operand form
+// (R.F32) makes "scalar x pair" free.  Results are the same IEEE fma per component as the scalar code.
+__device__ __forceinline__ unsigned long long pk2(float2 v) { return *reinterpret_cast<unsigned long long*>(&v); }
+__device__ __forceinline__ float2 unpk2(unsigned long long r) { return *reinterpret_cast<float2*>(&r); }
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) {
+  unsigned long long r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(pk2(a)), "l"(pk2(b)), "l"(pk2(c)));
+  return unpk2(r);
+}
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) {
+  unsigned long long r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk2(a)), "l"(pk2(b)));
+  return unpk2(r);
+}
+__device__ __forceinline__ float2 bc2(float s) { return make_float2(s, s); }
+// acc += s * v, two FFMA2
+__device__ __forceinline__ void fma4p(float4& acc, float s, const float4& v) {
+  const float2 lo = fma2(bc2(s), make_float2(v.x, v.y), make_float2(acc.x, acc.y));
+  const float2 hi = fma2(bc2(s), make_float2(v.z, v.w), make_float2(acc.z, acc.w));
+  acc = make_float4(lo.x, lo.y, hi.x, hi.y);
+}
+// <a, b> over 4 columns: FMUL2 + FFMA2 + FADD
+__device__ __forceinline__ float dot4p(const float4& a, const float4& b) {
+  const float2 t = fma2(make_float2(a.z, a.w), make_float2(b.z, b.w), mul2(make_float2(a.x, a.y), make_float2(b.x, b.y)));
+  return t.x + t.y;
+}
 __device__ __forceinline__ void f4_scale(float4& a, float s) {
-  a.x *= s; a.y *= s; a.z *= s; a.w *= s;
+  const float2 lo = mul2(bc2(s), make_float2(a.x, a.y)), hi = mul2(bc2(s), make_float2(a.z, a.w));
+  a = make_float4(lo.x, lo.y, hi.x, hi.y);
 }
 __device__ __forceinline__ float4 f4_shfl_xor(const float4& a, int o) {
   return make_float4(__shfl_xor_sync(kFullMask, a.x, o), __shfl_xor_sync(kFullMask, a.y, o),
@@ -129,7 +158,9 @@ struct NlRow {
   float m, l, dsum;          // online softmax state of (this lane's head, this lane's edge slots)
   float4 acc1[H];            // T1_h, this lane's 4 columns
   float4 acc2[HA];           // T2_h
-  float4 p[H];               // Wk_h^T q_ih / sqrt(dk), this lane's 4 columns
+  static constexpr bool PAIRS = (H % 2 == 0);               // heads paired in FFMA2 score products
+  float4 p[PAIRS ? 1 : H];   // Wk_h^T q_ih / sqrt(dk), this lane's 4 columns (odd head counts)
+  float2 pp[PAIRS ? 2 * H : 1];   // the same as head pairs: pp[(h/2)*4 + c] = (p[h][c], p[h+1][c])
   float4 gi;                 // g_i chunk (adjoint)
   int xl, es, gbase, myh, myu;
 
@@ -157,19 +188,37 @@ struct NlRow {
     const float scale = 1.0f / sqrtf((float)a.dk);
     const bool act = xl < a.dv;
     const float* wcol = wk_s + 4 * (act ? xl : 0);
+    float4 ph[H];
 #pragma unroll
     for (int h = 0; h < H; ++h) {
       float4 acc = f4_zero();
       for (int t = 0; t < a.dk; t += 4) {
         const int j = h * a.dk + t;
         const float4 qv = *reinterpret_cast<const float4*>(q_s + j);
-        fma4(acc, qv.x, *reinterpret_cast<const float4*>(wcol + (size_t)(j + 0) * ldw));
-        fma4(acc, qv.y, *reinterpret_cast<const float4*>(wcol + (size_t)(j + 1) * ldw));
-        fma4(acc, qv.z, *reinterpret_cast<const float4*>(wcol + (size_t)(j + 2) * ldw));
-        fma4(acc, qv.w, *reinterpret_cast<const float4*>(wcol + (size_t)(j + 3) * ldw));
+        fma4p(acc, qv.x, *reinterpret_cast<const float4*>(wcol + (size_t)(j + 0) * ldw));
+        fma4p(acc, qv.y, *reinterpret_cast<const float4*>(wcol + (size_t)(j + 1) * ldw));
+        fma4p(acc, qv.z, *reinterpret_cast<const float4*>(wcol + (size_t)(j + 2) * ldw));
+        fma4p(acc, qv.w, *reinterpret_cast<const float4*>(wcol + (size_t)(j + 3) * ldw));
       }
-      f4_scale(acc, act ? scale : 0.f);
-      p[h] = acc;
+      ph[h] = acc;
+    }
+    const float2 sc2 = bc2(act ? scale : 0.f);
+    if constexpr (PAIRS) {
+      // the scaling multiply doubles as the transposition to head pairs: its FMUL2 results ARE the register
+      // pairs the score products read (a plain repack is re-done by ptxas with two MOVs at every use)
+#pragma unroll
+      for (int h = 0; h < H; h += 2) {
+        pp[2 * h + 0] = mul2(make_float2(ph[h].x, ph[h + 1].x), sc2);
+        pp[2 * h + 1] = mul2(make_float2(ph[h].y, ph[h + 1].y), sc2);
+        pp[2 * h + 2] = mul2(make_float2(ph[h].z, ph[h + 1].z), sc2);
+        pp[2 * h + 3] = mul2(make_float2(ph[h].w, ph[h + 1].w), sc2);
+      }
+    } else {
+#pragma unroll
+      for (int h = 0; h < H; ++h) {
+        f4_scale(ph[h], sc2.x);
+        p[h] = ph[h];
+      }
     }
   }
 
@@ -190,9 +239,22 @@ struct NlRow {
     }
     float v[NV];
 #pragma unroll
-    for (int u = 0; u < U; ++u)
+    for (int u = 0; u < U; ++u) {
+      if constexpr (PAIRS) {                                  // two heads per FFMA2, x broadcast
 #pragma unroll
-      for (int h = 0; h < H; ++h) v[u * H + h] = dot4(p[h], xr[u]);
+        for (int h = 0; h < H; h += 2) {
+          float2 s2 = mul2(pp[2 * h + 0], bc2(xr[u].x));
+          s2 = fma2(pp[2 * h + 1], bc2(xr[u].y), s2);
+          s2 = fma2(pp[2 * h + 2], bc2(xr[u].z), s2);
+          s2 = fma2(pp[2 * h + 3], bc2(xr[u].w), s2);
+          v[u * H + h] = s2.x;
+          v[u * H + h + 1] = s2.y;
+        }
+      } else {
+#pragma unroll
+        for (int h = 0; h < H; ++h) v[u * H + h] = dot4p(p[h], xr[u]);
+      }
+    }
     ReduceT<NV, XL / 2>::run(v, xl);
     const int pos = base + es * U + myu;
     const bool valid = pos < end;
@@ -201,7 +263,7 @@ struct NlRow {
     if constexpr (ADJ) {
       float w[U];
 #pragma unroll
-      for (int u = 0; u < U; ++u) w[u] = dot4(gi, xr[u]);
+      for (int u = 0; u < U; ++u) w[u] = dot4p(gi, xr[u]);
       ReduceT<U, XL / 2>::run(w, xl);
       dab = alpha * __shfl_sync(kFullMask, w[0], gbase + (myu << SHU));
       if (valid && (xl & ((1 << SH) - 1)) == 0) {           // park the raw score / dabar of this edge
@@ -232,8 +294,8 @@ struct NlRow {
 #pragma unroll
       for (int h = 0; h < H; ++h) {
         const float pu = __shfl_sync(kFullMask, pe, gbase + ((u * H + h) << SH));
-        fma4(acc1[h], pu, xr[u]);
-        if constexpr (ADJ) fma4(acc2[h], pu * du, xr[u]);
+        fma4p(acc1[h], pu, xr[u]);
+        if constexpr (ADJ) fma4p(acc2[h], pu * du, xr[u]);
       }
     }
   }
@@ -310,10 +372,13 @@ struct NlRow {
       for (int j = lane; j < a.adim; j += 32) {              // dq[i, j] = <Wk[j, :], u_{head(j)}> / sqrt(dk)
         const float* wr = wk_s + (size_t)j * ldw;
         const float* ur = u_s + (j / a.dk) * (4 * XL);
-        float acc = 0.f;
-        for (int c = 0; c < a.dv; ++c)
-          acc += dot4(*reinterpret_cast<const float4*>(wr + 4 * c), *reinterpret_cast<const float4*>(ur + 4 * c));
-        a.dq[(size_t)row * a.lddq + j] = acc * scale;
+        float2 acc = make_float2(0.f, 0.f);
+        for (int c = 0; c < a.dv; ++c) {
+          const float4 wv = *reinterpret_cast<const float4*>(wr + 4 * c), uv = *reinterpret_cast<const float4*>(ur + 4 * c);
+          acc = fma2(make_float2(wv.x, wv.y), make_float2(uv.x, uv.y), acc);
+          acc = fma2(make_float2(wv.z, wv.w), make_float2(uv.z, uv.w), acc);
+        }
+        a.dq[(size_t)row * a.lddq + j] = (acc.x + acc.y) * scale;
       }
     }
   }

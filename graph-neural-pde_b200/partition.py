@@ -68,6 +68,7 @@ class Halo:
             raise ValueError('process group does not match the partition')
         self.backend = dist.get_backend(group)
         self.bytes_in = 0                                     # bytes received so far (bench accounting)
+        self.n_gathers = self.n_scatters = 0
 
     def all_gather_rows(self, slab):
         """[S, d] slab of every rank -> [N_pad, d] on every rank"""
@@ -75,6 +76,7 @@ class Halo:
         full = slab.new_empty((self.part.n_pad,) + tuple(slab.shape[1:]))
         self.dist.all_gather_into_tensor(full, slab, group=self.group)
         self.bytes_in += (self.part.world - 1) * slab.numel() * slab.element_size()
+        self.n_gathers += 1
         return full
 
     def reduce_scatter_rows(self, full):
@@ -87,6 +89,7 @@ class Halo:
         else:
             self.dist.reduce_scatter_tensor(out, full, group=self.group)
         self.bytes_in += (self.part.world - 1) * out.numel() * out.element_size()
+        self.n_scatters += 1
         return out
 
     def all_reduce_(self, t):
