@@ -227,6 +227,19 @@ struct NlRow {
     return (lane < BATCH && base + lane < end) ? ld_stream_i32(a.colidx + base + lane) : -1;
   }
 
+  // pull the rows of a coming batch towards the SM: lane -> (edge lane / LPE, 1/LPE of the row), one
+  // prefetch instruction per batch.  `cnext` = load_cols() of that batch.
+  __device__ __forceinline__ void prefetch_rows(const NlArgs& a, int cnext, int lane) const {
+    constexpr int LPE = 32 / BATCH;
+    const int c = __shfl_sync(kFullMask, cnext, lane / LPE);
+    const int row_bytes = 16 * a.dv;
+    const int off = (lane % LPE) * ((row_bytes + LPE - 1) / LPE);
+    if (c >= 0 && off < row_bytes) {
+      const char* ptr = reinterpret_cast<const char*>(a.sp.src + (size_t)c * a.sp.lds) + off;
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(ptr));
+    }
+  }
+
   // one warp batch: edges [base, base + BATCH) of a row ending at `end`; `cmine` = load_cols(base), issued by
   // the caller one batch ahead so that the index load is off the critical path of the gather
   __device__ __forceinline__ void batch(const NlArgs& a, int base, int end, int lane, float alpha, int cmine) {
@@ -475,10 +488,13 @@ __global__ void __launch_bounds__(kNlThreads, 2) nl_rows_kernel(const NlArgs a) 
       if constexpr (ADJ)
         r.gi = r.xl < a.dv ? ldg4(a.g + (size_t)row * a.ldg + 4 * r.xl) : f4_zero();
       r.reset();
+      int cnext = r.load_cols(a, start + Row::BATCH, end, lane);
       for (int base = start; base < end; base += Row::BATCH) {
-        const int cnext = r.load_cols(a, base + Row::BATCH, end, lane);
+        const int cnn = r.load_cols(a, base + 2 * Row::BATCH, end, lane);
+        r.prefetch_rows(a, cnext, lane);
         r.batch(a, base, end, lane, alpha, cols);
         cols = cnext;
+        cnext = cnn;
       }
       NlStats<H> st;
       r.warp_merge(st);
