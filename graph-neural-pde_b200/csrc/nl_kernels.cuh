@@ -192,6 +192,7 @@ struct NlRow {
 #pragma unroll
     for (int h = 0; h < H; ++h) {
       float4 acc = f4_zero();
+#pragma unroll 2
       for (int t = 0; t < a.dk; t += 4) {
         const int j = h * a.dk + t;
         const float4 qv = *reinterpret_cast<const float4*>(q_s + j);
@@ -385,13 +386,14 @@ struct NlRow {
       for (int j = lane; j < a.adim; j += 32) {              // dq[i, j] = <Wk[j, :], u_{head(j)}> / sqrt(dk)
         const float* wr = wk_s + (size_t)j * ldw;
         const float* ur = u_s + (j / a.dk) * (4 * XL);
-        float2 acc = make_float2(0.f, 0.f);
+        float2 acc = make_float2(0.f, 0.f), acc1 = make_float2(0.f, 0.f);
+#pragma unroll 4
         for (int c = 0; c < a.dv; ++c) {
           const float4 wv = *reinterpret_cast<const float4*>(wr + 4 * c), uv = *reinterpret_cast<const float4*>(ur + 4 * c);
           acc = fma2(make_float2(wv.x, wv.y), make_float2(uv.x, uv.y), acc);
-          acc = fma2(make_float2(wv.z, wv.w), make_float2(uv.z, uv.w), acc);
+          acc1 = fma2(make_float2(wv.z, wv.w), make_float2(uv.z, uv.w), acc1);
         }
-        a.dq[(size_t)row * a.lddq + j] = (acc.x + acc.y) * scale;
+        a.dq[(size_t)row * a.lddq + j] = ((acc.x + acc1.x) + (acc.y + acc1.y)) * scale;
       }
     }
   }
