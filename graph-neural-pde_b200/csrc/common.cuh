@@ -75,6 +75,10 @@ int check_launch(const char* name);   // cudaGetLastError -> gb_status
 
 int sm_count();
 
+// fork / join of the per-device side stream (runtime.cu); side_fork returns `main` when unavailable
+cudaStream_t side_fork(cudaStream_t main);
+int side_join(cudaStream_t main, cudaStream_t side);
+
 // ---- device helpers --------------------------------------------------------------------------
 __device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
 __device__ __forceinline__ void fma4(float4& acc, float a, const float4& v) {

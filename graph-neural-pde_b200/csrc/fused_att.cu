@@ -715,21 +715,23 @@ int gb_nl_adjoint(const gb_graph* g, int32_t row_lo, int32_t row_hi, const float
     set_error("gb_nl_adjoint: column pass does not support this shape (%s)", why);
     return GB_ERR_UNSUPPORTED;
   }
-  if (int rc = dispatch_bwd(b, stream, true)) return rc;
   int slots = (g->n + kFusedWarps - 1) / kFusedWarps;
   const int nlc = use_long ? g->n_long_cols : 0;
+  const cudaStream_t side = nlc > 0 ? side_fork(stream) : stream;   // hub columns next to the main column pass
   if (nlc > 0) {
     SpmmArgs lsp = sp;
     lsp.partial_base = slots;
-    lsp.long_threshold = kColCap;                         // shorter listed columns were done above
-    if (int rc = spmm_long_only(lsp, 4, true, nlc, stream)) return rc;
+    lsp.long_threshold = kColCap;                         // shorter listed columns are done by the main kernel
+    if (int rc = spmm_long_only(lsp, 4, true, nlc, side)) return rc;
     slots += nlc;
     MhArgs mh{};
     mh.ptr = g->colptr; mh.idx = g->rowidx; mh.perm = g->tperm; mh.ds = ds; mh.src = q; mh.lds = ldq;
     mh.out = dk_out; mh.ldo = lddk; mh.n = g->n; mh.heads = heads; mh.dk = dk; mh.long_threshold = kColCap;
     mh.scale = 1.0f / sqrtf((float)dk); mh.long_list = g->long_cols;
-    if (int rc = mh_spmm_long(mh, 4, nlc, K_EDGE_SCORE_BWD_K, stream)) return rc;
+    if (int rc = mh_spmm_long(mh, 4, nlc, K_EDGE_SCORE_BWD_K, side)) return rc;
   }
+  if (int rc = dispatch_bwd(b, stream, true)) return rc;
+  if (int rc = side_join(stream, side)) return rc;
   if (dparams) return reduce_partials_launch(partials, slots, alpha_train, alpha_sigmoid, dparams, stream);
   return GB_OK;
 }

@@ -613,6 +613,13 @@ int nl_launch(const NlArgs& a, int n_long, cudaStream_t stream) {
   }
   const int nrows = a.row_hi - a.row_lo;
   if (nrows <= 0) return GB_OK;
+  // hub rows first, on the side stream: their few CTAs run next to the persistent kernel instead of after it
+  const cudaStream_t side = n_long > 0 ? side_fork(stream) : stream;
+  if (n_long > 0) {
+    LaunchScope ls(ADJ ? K_NL_ADJ_LONG : K_NL_FWD_LONG, side);
+    nl_long_kernel<XL, H, ADJ><<<n_long, kNlThreads, smem_long, side>>>(a);
+    if (int rc = check_launch("nl_long_kernel")) return rc;
+  }
   GB_CUDA(cudaMemsetAsync(a.counter, 0, sizeof(int32_t), stream));
   const int want = (nrows + kNlWarps * kNlChunkRows - 1) / (kNlWarps * kNlChunkRows);
   const int blocks = min_int(want, 2 * sm_count());
@@ -621,12 +628,7 @@ int nl_launch(const NlArgs& a, int n_long, cudaStream_t stream) {
     nl_rows_kernel<XL, H, ADJ><<<blocks, kNlThreads, smem_rows, stream>>>(a);
   }
   if (int rc = check_launch("nl_rows_kernel")) return rc;
-  if (n_long > 0) {
-    LaunchScope ls(ADJ ? K_NL_ADJ_LONG : K_NL_FWD_LONG, stream);
-    nl_long_kernel<XL, H, ADJ><<<n_long, kNlThreads, smem_long, stream>>>(a);
-    return check_launch("nl_long_kernel");
-  }
-  return GB_OK;
+  return side_join(stream, side);
 }
 
 template <bool ADJ>

@@ -1,5 +1,6 @@
 // runtime.cu - error reporting, launch accounting and per-kernel event timing of libgrandb200.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <atomic>
 #include <mutex>
 #include <vector>
@@ -63,6 +64,61 @@ int sm_count() {
       return 148;
   }
   return cached;
+}
+
+// ---- side stream: the CTA-per-long-segment kernels run next to the main kernel of the same pass ------------
+// A handful of hub rows / columns (one CTA each, up to ~1 ms for a 20 000-edge hub) would otherwise run alone
+// on a few SMs after the main kernel.  They touch disjoint output rows, so they are launched FIRST on a side
+// stream that is ordered after everything already enqueued on the caller's stream (fork) and joined back
+// before the next dependent launch.  Works under stream capture (the side stream joins the capture through the
+// fork event and leaves it at the join).  GRANDB200_NO_SIDE_STREAM=1 keeps everything on the caller's stream.
+namespace {
+struct SideStream {
+  cudaStream_t s = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr;
+  bool failed = false;
+};
+SideStream g_side[16];
+std::mutex g_side_mu;
+}  // namespace
+
+cudaStream_t side_fork(cudaStream_t main) {
+  static const bool off = [] {
+    const char* e = getenv("GRANDB200_NO_SIDE_STREAM");
+    return e && e[0] && e[0] != '0';
+  }();
+  if (off) return main;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return main;
+  std::lock_guard<std::mutex> lk(g_side_mu);
+  SideStream& ss = g_side[dev];
+  if (ss.failed) return main;
+  if (!ss.s) {
+    if (cudaStreamCreateWithFlags(&ss.s, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ss.fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming) != cudaSuccess) {
+      ss.failed = true;
+      ss.s = nullptr;
+      cudaGetLastError();
+      return main;
+    }
+  }
+  if (cudaEventRecord(ss.fork, main) != cudaSuccess || cudaStreamWaitEvent(ss.s, ss.fork, 0) != cudaSuccess) {
+    cudaGetLastError();
+    return main;
+  }
+  return ss.s;
+}
+
+int side_join(cudaStream_t main, cudaStream_t side) {
+  if (side == main) return GB_OK;
+  int dev = 0;
+  GB_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lk(g_side_mu);
+  SideStream& ss = g_side[dev];
+  GB_CUDA(cudaEventRecord(ss.join, side));
+  GB_CUDA(cudaStreamWaitEvent(main, ss.join, 0));
+  return GB_OK;
 }
 
 LaunchScope::LaunchScope(int kernel_id, cudaStream_t s) : id(kernel_id), stream(s), rec(nullptr) {
