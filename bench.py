@@ -170,6 +170,13 @@ def block_name():
     return 'AttODEblock + ODEFuncTransformerAtt' if FUNCTION == 'transformer' else 'ConstantODEblock + LaplacianODEFunc'
 
 
+def main_kernels(kernels):
+    """kernels timed on the launching stream; the hub-row / hub-column kernels that run on the library's side
+    stream next to the main kernel are left out of shares and of the roofline choice (their event interval
+    includes the wait for free SMs)"""
+    return {k: v for k, v in kernels.items() if not v.get('overlapped')}
+
+
 def train_pass(block, data, x_dev, g_dev):
     """one step: forward integrate + adjoint backward; returns (evals, loss tensor)"""
     func = block.odefunc
@@ -298,17 +305,18 @@ def run_ours(args):
     peak, peak_src = read_peaks()
     alg = algorithmic_bytes(n, e_prime, d, cfg['adim'], cfg['heads'])
     gat = gather_bytes(n, e_prime, d, cfg['adim'], cfg['heads'])
-    top = max(kernels.items(), key=lambda kv: kv[1]['ms'])
+    top = max(main_kernels(kernels).items(), key=lambda kv: kv[1]['ms'])
     kname, kstat = top
     per_launch_ms = kstat['ms'] / kstat['launches']
     achieved = alg.get(kname, 0) / (per_launch_ms * 1e-3) / 1e9 if per_launch_ms > 0 else 0.0
-    ksum = sum(v['ms'] for v in kernels.values())
+    ksum = sum(v['ms'] for v in main_kernels(kernels).values())
     roofline = {'bound': 'hbm', 'kernel': kname, 'achieved': round(achieved, 1), 'peak': peak, 'unit': 'GB/s',
                 'frac': round(achieved / peak, 4), 'traffic': measured_traffic(name, kname), 'peak_source': peak_src,
                 'algorithmic_bytes_per_launch': alg.get(kname, 0), 'avg_launch_ms': round(per_launch_ms, 4),
                 'share_of_kernel_time': round(kstat['ms'] / ksum, 4) if ksum else None,
                 'kernels': {k: {'ms_per_launch': round(v['ms'] / v['launches'], 4), 'launches': v['launches'],
-                                'share': round(v['ms'] / ksum, 4),
+                                'share': None if v.get('overlapped') else round(v['ms'] / ksum, 4),
+                                'overlapped_with_main_kernel': bool(v.get('overlapped')),
                                 'alg_GBps': round(alg[k] / (v['ms'] / v['launches'] * 1e-3) / 1e9, 1) if k in alg else None,
                                 'gather_model_GBps': round((alg[k] + gat[k]) / (v['ms'] / v['launches'] * 1e-3) / 1e9, 1)
                                 if k in alg and k in gat else None}
@@ -438,16 +446,17 @@ def run_partitioned(args, cfg, device, rank, world):
     rows = part.hi - part.lo
     alg = algorithmic_bytes(rows, e_local, d, cfg['adim'], cfg['heads'])
     gat = gather_bytes(rows, e_local, d, cfg['adim'], cfg['heads'])
-    kname, kstat = max(kernels.items(), key=lambda kv: kv[1]['ms'])
+    kname, kstat = max(main_kernels(kernels).items(), key=lambda kv: kv[1]['ms'])
     per_launch_ms = kstat['ms'] / kstat['launches']
     achieved = alg.get(kname, 0) / (per_launch_ms * 1e-3) / 1e9 if per_launch_ms > 0 else 0.0
-    ksum = sum(v['ms'] for v in kernels.values())
+    ksum = sum(v['ms'] for v in main_kernels(kernels).values())
     roofline = {'bound': 'hbm', 'kernel': kname, 'achieved': round(achieved, 1), 'peak': peak, 'unit': 'GB/s',
                 'frac': round(achieved / peak, 4), 'traffic': None, 'peak_source': peak_src,
                 'algorithmic_bytes_per_launch': alg.get(kname, 0), 'avg_launch_ms': round(per_launch_ms, 4),
                 'note': "rank 0's kernels on its row slab (algorithmic bytes of the slab)",
                 'kernels': {k: {'ms_per_launch': round(v['ms'] / v['launches'], 4), 'launches': v['launches'],
-                                'share': round(v['ms'] / ksum, 4),
+                                'share': None if v.get('overlapped') else round(v['ms'] / ksum, 4),
+                                'overlapped_with_main_kernel': bool(v.get('overlapped')),
                                 'gather_model_GBps': round((alg[k] + gat[k]) / (v['ms'] / v['launches'] * 1e-3) / 1e9, 1)
                                 if k in alg and k in gat else None}
                             for k, v in sorted(kernels.items(), key=lambda kv: -kv[1]['ms'])}}

@@ -47,6 +47,7 @@ SIGNATURES = {
     'gb_prof_collect': (C.c_int, []),
     'gb_prof_get': (C.c_int, [C.c_int, C.POINTER(C.c_double), C.POINTER(_I64)]),
     'gb_prof_num_kernels': (C.c_int, []),
+    'gb_prof_overlapped': (C.c_int64, [C.c_int]),
     'gb_prof_name': (C.c_char_p, [C.c_int]),
     'gb_plan_workspace_bytes': (_SZ, [_I32, _I64]),
     'gb_plan_build': (C.c_int, [_P, _P, _I64, _I32, _P, _P, _P, _P, _P, _P, _P, _SZ, _P]),
@@ -160,5 +161,6 @@ class Profiler:
             ms, cnt = C.c_double(0), C.c_int64(0)
             lib.gb_prof_get(i, C.byref(ms), C.byref(cnt))
             if cnt.value:
-                out[lib.gb_prof_name(i).decode()] = {'ms': ms.value, 'launches': cnt.value}
+                out[lib.gb_prof_name(i).decode()] = {'ms': ms.value, 'launches': cnt.value,
+                                                     'overlapped': int(lib.gb_prof_overlapped(i))}
         return out

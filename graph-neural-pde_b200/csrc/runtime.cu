@@ -14,6 +14,7 @@ static std::atomic<int> g_prof_on{0};
 
 struct EventRec {
   int id;
+  bool side;                                   // recorded on the side stream: the interval overlaps the main kernel
   cudaEvent_t start, stop;
 };
 static std::mutex g_prof_mu;
@@ -21,6 +22,7 @@ static std::vector<EventRec*> g_pending;       // recorded, not yet collected
 static std::vector<EventRec*> g_free;          // event pool
 static double g_total_ms[K_NUM_KERNELS];
 static int64_t g_count[K_NUM_KERNELS];
+static int64_t g_side_count[K_NUM_KERNELS];    // launches recorded on the side stream
 
 static const char* kNames[K_NUM_KERNELS] = {
     "spmm_fwd",           "spmm_fwd_long",     "spmm_bwd",          "spmm_bwd_long",     "reduce_partials",
@@ -94,7 +96,9 @@ cudaStream_t side_fork(cudaStream_t main) {
   SideStream& ss = g_side[dev];
   if (ss.failed) return main;
   if (!ss.s) {
-    if (cudaStreamCreateWithFlags(&ss.s, cudaStreamNonBlocking) != cudaSuccess ||
+    int lo = 0, hi = 0;                               // highest priority: the few hub CTAs are placed before the
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);       // main kernel's CTAs fill every SM
+    if (cudaStreamCreateWithPriority(&ss.s, cudaStreamNonBlocking, hi) != cudaSuccess ||
         cudaEventCreateWithFlags(&ss.fork, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming) != cudaSuccess) {
       ss.failed = true;
@@ -108,6 +112,14 @@ cudaStream_t side_fork(cudaStream_t main) {
     return main;
   }
   return ss.s;
+}
+
+static bool is_side_stream(cudaStream_t s) {
+  if (s == nullptr) return false;
+  std::lock_guard<std::mutex> lk(g_side_mu);
+  for (const SideStream& ss : g_side)
+    if (ss.s == s) return true;
+  return false;
 }
 
 int side_join(cudaStream_t main, cudaStream_t side) {
@@ -140,6 +152,7 @@ LaunchScope::LaunchScope(int kernel_id, cudaStream_t s) : id(kernel_id), stream(
     }
   }
   r->id = kernel_id;
+  r->side = is_side_stream(stream);
   cudaEventRecord(r->start, stream);
   rec = r;
 }
@@ -189,6 +202,7 @@ int gb_prof_reset(void) {
   for (int i = 0; i < K_NUM_KERNELS; ++i) {
     g_total_ms[i] = 0.0;
     g_count[i] = 0;
+    g_side_count[i] = 0;
   }
   return GB_OK;
 }
@@ -201,6 +215,7 @@ int gb_prof_collect(void) {
     GB_CUDA(cudaEventElapsedTime(&ms, r->start, r->stop));
     g_total_ms[r->id] += ms;
     g_count[r->id] += 1;
+    if (r->side) g_side_count[r->id] += 1;
     g_free.push_back(r);
   }
   g_pending.clear();
@@ -213,6 +228,12 @@ int gb_prof_get(int kernel_id, double* total_ms_host, int64_t* launches_host) {
   if (total_ms_host) *total_ms_host = g_total_ms[kernel_id];
   if (launches_host) *launches_host = g_count[kernel_id];
   return GB_OK;
+}
+
+int64_t gb_prof_overlapped(int kernel_id) {
+  if (kernel_id < 0 || kernel_id >= K_NUM_KERNELS) return 0;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  return g_side_count[kernel_id];
 }
 
 int gb_prof_num_kernels(void) { return K_NUM_KERNELS; }

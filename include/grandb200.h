@@ -101,6 +101,9 @@ int gb_prof_enable(int on);
 int gb_prof_reset(void);
 int gb_prof_collect(void);                      /* synchronises the recorded events */
 int gb_prof_get(int kernel_id, double* total_ms_host, int64_t* launches_host);
+/* launches of the kernel that ran on the library's side stream next to the main kernel of their pass (hub rows /
+ * columns): their event intervals include the wait for free SMs and overlap the main kernel's */
+int64_t gb_prof_overlapped(int kernel_id);
 int gb_prof_num_kernels(void);
 const char* gb_prof_name(int kernel_id);
 
