@@ -44,6 +44,7 @@ constexpr int kNlLongRow = 2048;         // rows longer than this get a whole CT
                                          // per-edge shared memory, so a warp can take rows far beyond the plan's
                                          // 256-edge list threshold; the scheduler balances them)
 constexpr unsigned kFullMask = 0xffffffffu;
+constexpr size_t kNlSmemLimit = 227 * 1024;   // opt-in dynamic shared memory per CTA on sm_100
 
 struct NlArgs {
   const int32_t* rowptr;
@@ -66,8 +67,9 @@ struct NlArgs {
   float* dq;                 // [*, A] out
   int32_t lddq;
   int32_t* counter;          // scheduler counter, zeroed before the launch
-  const int32_t* long_list;
-  int32_t long_threshold;
+  const int32_t* long_list;  // rows with more edges than the plan's list threshold (256)
+  int32_t n_long;
+  int32_t long_threshold;    // rows with more edges than this are worked by a whole CTA
 };
 
 constexpr int ilog2_c(int v) { return v <= 1 ? 0 : 1 + ilog2_c(v / 2); }
@@ -433,25 +435,109 @@ __device__ __forceinline__ void nl_sweep_ds(const NlArgs& a, int start, int end,
   }
 }
 
-// shared-memory layout of both kernels: [A][ldw] staged Wk | per-warp q [W][A] | per-warp u [W][H][4*XL] | (long kernel) partials
+// shared-memory layout of both kernels: [A][ldw] staged Wk | per-warp q [W][A] | per-warp u [W][H][4*XL]
 __host__ __device__ inline int nl_ldw(int dv) { return 4 * dv + 4; }
 
 template <int XL, int H>
 inline size_t nl_smem_rows(int adim, int dv) {
   return sizeof(float) * ((size_t)adim * nl_ldw(dv) + (size_t)kNlWarps * adim + (size_t)kNlWarps * H * 4 * XL);
 }
-// long kernel: + per-warp stats [W][3][H] and accumulators [W][2][H][4*XL]
-template <int XL, int H>
-inline size_t nl_smem_long(int adim, int dv) {
-  return nl_smem_rows<XL, H>(adim, dv) + sizeof(float) * ((size_t)kNlWarps * 3 * H + (size_t)kNlWarps * 2 * H * 4 * XL);
-}
-
 __device__ __forceinline__ void nl_stage_wk(const NlArgs& a, float* wk_s, int ldw) {
   const int total = a.adim * a.dv;
   for (int i = threadIdx.x; i < total; i += blockDim.x) {
     const int j = i / a.dv, c = i - j * a.dv;
     *reinterpret_cast<float4*>(wk_s + (size_t)j * ldw + 4 * c) = ldg4(a.wk + (size_t)j * a.ldwk + 4 * c);
   }
+}
+
+// A long row (more edges than a.long_threshold) is worked by the whole CTA: warps stride the batches, then the
+// partial online-softmax states are merged in warp order.  No extra shared memory: the per-warp statistics go to
+// the q slots of warps 1.. ([W][3][H] <= 7 A floats), the accumulators are summed warp after warp into the u slots
+// of warps 0-1 ([2][H][4 XL]).  Called by every thread of the CTA.
+template <int XL, int H, bool ADJ>
+__device__ __forceinline__ void nl_long_row(const NlArgs& a, int row, float* wk_s, int ldw, float alpha, float beta) {
+  using Row = NlRow<XL, H, ADJ>;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* q_s = wk_s + (size_t)a.adim * ldw;                                    // warp 0's q slot
+  float* pst = q_s + a.adim;                                                   // [W][3][H]
+  float* u_s = wk_s + (size_t)a.adim * ldw + (size_t)kNlWarps * a.adim;        // warp 0's u slot
+  float* pacc = u_s;                                                           // [2][H][4*XL] (u slots of warps 0-1)
+  const int start = __ldg(a.rowptr + row), end = __ldg(a.rowptr + row + 1);
+  for (int j = threadIdx.x; j < a.adim; j += blockDim.x) q_s[j] = __ldg(a.q + (size_t)row * a.ldq + j);
+  __syncthreads();
+  Row r;
+  r.init_lane(lane);
+  r.load_p(a, wk_s, ldw, q_s);
+  if constexpr (ADJ) r.gi = r.xl < a.dv ? ldg4(a.g + (size_t)row * a.ldg + 4 * r.xl) : f4_zero();
+  r.reset();
+  {
+    int cols = r.load_cols(a, start + warp * Row::BATCH, end, lane);
+    for (int base = start + warp * Row::BATCH; base < end; base += kNlWarps * Row::BATCH) {
+      const int cnext = r.load_cols(a, base + kNlWarps * Row::BATCH, end, lane);
+      r.prefetch_rows(a, cnext, lane);
+      r.batch(a, base, end, lane, alpha, cols);
+      cols = cnext;
+    }
+  }
+  NlStats<H> st;
+  r.warp_merge(st);
+  if (lane == 0) {
+#pragma unroll
+    for (int h = 0; h < H; ++h) {
+      pst[(warp * 3 + 0) * H + h] = st.mh[h];
+      pst[(warp * 3 + 1) * H + h] = st.lh[h];
+      pst[(warp * 3 + 2) * H + h] = st.dh[h];
+    }
+  }
+  __syncthreads();
+  // every warp forms the same merged statistics
+  float scw[H];                                               // this warp's rescale to the merged maximum
+#pragma unroll
+  for (int h = 0; h < H; ++h) {
+    float mx = -CUDART_INF_F;
+    for (int w = 0; w < kNlWarps; ++w) mx = fmaxf(mx, pst[(w * 3 + 0) * H + h]);
+    float ls = 0.f, dsum = 0.f;
+    for (int w = 0; w < kNlWarps; ++w) {
+      const float mw = pst[(w * 3 + 0) * H + h];
+      const float sc = mw == -CUDART_INF_F ? 0.f : expf(mw - mx);
+      ls = fmaf(pst[(w * 3 + 1) * H + h], sc, ls);
+      dsum = fmaf(pst[(w * 3 + 2) * H + h], sc, dsum);
+    }
+    scw[h] = st.mh[h] == -CUDART_INF_F ? 0.f : expf(st.mh[h] - mx);
+    st.mh[h] = mx;
+    st.lh[h] = ls;
+    st.dh[h] = dsum;
+  }
+  // accumulators: warp 0 stores, warps 1.. add in turn (fixed order -> deterministic)
+  for (int w = 0; w < kNlWarps; ++w) {
+    if (warp == w && r.es == 0) {
+#pragma unroll
+      for (int h = 0; h < H; ++h) {
+        float4* d1 = reinterpret_cast<float4*>(pacc + (size_t)h * 4 * XL + 4 * r.xl);
+        float4 t1 = w == 0 ? f4_zero() : *d1;
+        fma4(t1, scw[h], r.acc1[h]);
+        *d1 = t1;
+        if constexpr (ADJ) {
+          float4* d2 = reinterpret_cast<float4*>(pacc + (size_t)(H + h) * 4 * XL + 4 * r.xl);
+          float4 t2 = w == 0 ? f4_zero() : *d2;
+          fma4(t2, scw[h], r.acc2[h]);
+          *d2 = t2;
+        }
+      }
+    }
+    __syncthreads();
+  }
+  if (warp == 0) {
+#pragma unroll
+    for (int h = 0; h < H; ++h) {
+      r.acc1[h] = *reinterpret_cast<const float4*>(pacc + (size_t)h * 4 * XL + 4 * r.xl);
+      if constexpr (ADJ) r.acc2[h] = *reinterpret_cast<const float4*>(pacc + (size_t)(H + h) * 4 * XL + 4 * r.xl);
+    }
+    __syncwarp();                                            // emit() reuses the same shared memory for u
+    r.emit(a, row, lane, st, alpha, beta, u_s, wk_s, ldw);
+  }
+  if constexpr (ADJ) nl_sweep_ds<H>(a, start, end, lane, st, warp * 32, kNlWarps * 32);
+  __syncthreads();                                          // the q / u slots go back to their warps
 }
 
 // persistent kernel: warps pull chunks of rows from an atomic counter
@@ -471,6 +557,14 @@ __global__ void __launch_bounds__(kNlThreads, 2) nl_rows_kernel(const NlArgs a) 
   const float alpha = load_alpha(a.sp);
   const float beta = a.sp.beta_train != nullptr ? __ldg(a.sp.beta_train) : 0.f;
   const int nrows = a.row_hi - a.row_lo;
+  // hub rows first, one CTA each (CTA b takes list entries b, b + grid, ...): they finish long before the
+  // scheduler loop below runs dry, so they cost no tail and no second launch
+  for (int li = blockIdx.x; li < a.n_long; li += gridDim.x) {
+    const int row = __ldg(a.long_list + li);
+    if (row < a.row_lo || row >= a.row_hi) continue;
+    if (__ldg(a.rowptr + row + 1) - __ldg(a.rowptr + row) <= a.long_threshold) continue;   // a warp takes it below
+    nl_long_row<XL, H, ADJ>(a, row, wk_s, ldw, alpha, beta);
+  }
   for (;;) {
     int r0 = 0;
     if (lane == 0) r0 = atomicAdd(a.counter, kNlChunkRows);
@@ -482,7 +576,7 @@ __global__ void __launch_bounds__(kNlThreads, 2) nl_rows_kernel(const NlArgs a) 
     for (int rr = r0; rr < r1; ++rr) {
       const int row = a.row_lo + rr;
       const int start = __shfl_sync(kFullMask, rp, rr - r0), end = __shfl_sync(kFullMask, rp, rr - r0 + 1);
-      if (end - start > a.long_threshold) continue;          // nl_long_kernel takes these
+      if (end - start > a.long_threshold) continue;          // done CTA-wide above
       int cols = r.load_cols(a, start, end, lane);           // in flight while q is staged and p is formed
       for (int j = lane; j < a.adim; j += 32) q_s[j] = __ldg(a.q + (size_t)row * a.ldq + j);
       __syncwarp();
@@ -510,125 +604,29 @@ __global__ void __launch_bounds__(kNlThreads, 2) nl_rows_kernel(const NlArgs a) 
   }
 }
 
-// one CTA per long row: warps stride the batches, partial states merged through shared memory in warp order
 template <int XL, int H, bool ADJ>
-__global__ void __launch_bounds__(kNlThreads, 1) nl_long_kernel(const NlArgs a) {
-  extern __shared__ __align__(16) float smem[];
-  using Row = NlRow<XL, H, ADJ>;
-  const int ldw = nl_ldw(a.dv);
-  float* wk_s = smem;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float* q_s = wk_s + (size_t)a.adim * ldw;                                    // one copy (warp 0's slot)
-  float* u_s = wk_s + (size_t)a.adim * ldw + (size_t)kNlWarps * a.adim;        // warp 0's slot
-  float* pst = u_s + (size_t)kNlWarps * H * 4 * XL;                            // [W][3][H]
-  float* pacc = pst + kNlWarps * 3 * H;                                        // [W][2][H][4*XL]
-  const int row = __ldg(a.long_list + blockIdx.x);
-  if (row < a.row_lo || row >= a.row_hi) return;
-  const int start = __ldg(a.rowptr + row), end = __ldg(a.rowptr + row + 1);
-  if (end - start <= a.long_threshold) return;              // listed by the plan (> 256) but taken by a warp
-  nl_stage_wk(a, wk_s, ldw);
-  for (int j = threadIdx.x; j < a.adim; j += blockDim.x) q_s[j] = __ldg(a.q + (size_t)row * a.ldq + j);
-  __syncthreads();
-  Row r;
-  r.init_lane(lane);
-  const float alpha = load_alpha(a.sp);
-  const float beta = a.sp.beta_train != nullptr ? __ldg(a.sp.beta_train) : 0.f;
-  r.load_p(a, wk_s, ldw, q_s);
-  if constexpr (ADJ) r.gi = r.xl < a.dv ? ldg4(a.g + (size_t)row * a.ldg + 4 * r.xl) : f4_zero();
-  r.reset();
-  {
-    int cols = r.load_cols(a, start + warp * Row::BATCH, end, lane);
-    for (int base = start + warp * Row::BATCH; base < end; base += kNlWarps * Row::BATCH) {
-      const int cnext = r.load_cols(a, base + kNlWarps * Row::BATCH, end, lane);
-      r.batch(a, base, end, lane, alpha, cols);
-      cols = cnext;
-    }
-  }
-  NlStats<H> st;
-  r.warp_merge(st);
-  if (lane == 0) {
-#pragma unroll
-    for (int h = 0; h < H; ++h) {
-      pst[(warp * 3 + 0) * H + h] = st.mh[h];
-      pst[(warp * 3 + 1) * H + h] = st.lh[h];
-      pst[(warp * 3 + 2) * H + h] = st.dh[h];
-    }
-  }
-  if (r.es == 0) {
-#pragma unroll
-    for (int h = 0; h < H; ++h) {
-      *reinterpret_cast<float4*>(pacc + ((size_t)(warp * 2 + 0) * H + h) * 4 * XL + 4 * r.xl) = r.acc1[h];
-      if constexpr (ADJ)
-        *reinterpret_cast<float4*>(pacc + ((size_t)(warp * 2 + 1) * H + h) * 4 * XL + 4 * r.xl) = r.acc2[h];
-    }
-  }
-  __syncthreads();
-  // every warp forms the same merged statistics; warp 0 also merges the accumulators and emits the row
-#pragma unroll
-  for (int h = 0; h < H; ++h) {
-    float mx = -CUDART_INF_F;
-    for (int w = 0; w < kNlWarps; ++w) mx = fmaxf(mx, pst[(w * 3 + 0) * H + h]);
-    float ls = 0.f, dsum = 0.f;
-    for (int w = 0; w < kNlWarps; ++w) {
-      const float mw = pst[(w * 3 + 0) * H + h];
-      const float sc = mw == -CUDART_INF_F ? 0.f : expf(mw - mx);
-      ls = fmaf(pst[(w * 3 + 1) * H + h], sc, ls);
-      dsum = fmaf(pst[(w * 3 + 2) * H + h], sc, dsum);
-    }
-    st.mh[h] = mx;
-    st.lh[h] = ls;
-    st.dh[h] = dsum;
-  }
-  if (warp == 0) {
-#pragma unroll
-    for (int h = 0; h < H; ++h) {
-      float4 t1 = f4_zero(), t2 = f4_zero();
-      for (int w = 0; w < kNlWarps; ++w) {
-        const float mw = pst[(w * 3 + 0) * H + h];
-        const float sc = mw == -CUDART_INF_F ? 0.f : expf(mw - st.mh[h]);
-        fma4(t1, sc, *reinterpret_cast<const float4*>(pacc + ((size_t)(w * 2 + 0) * H + h) * 4 * XL + 4 * r.xl));
-        if constexpr (ADJ)
-          fma4(t2, sc, *reinterpret_cast<const float4*>(pacc + ((size_t)(w * 2 + 1) * H + h) * 4 * XL + 4 * r.xl));
-      }
-      r.acc1[h] = t1;
-      if constexpr (ADJ) r.acc2[h] = t2;
-    }
-    r.emit(a, row, lane, st, alpha, beta, u_s, wk_s, ldw);
-  }
-  if constexpr (ADJ) nl_sweep_ds<H>(a, start, end, lane, st, warp * 32, kNlWarps * 32);
-}
-
-template <int XL, int H, bool ADJ>
-int nl_launch(const NlArgs& a, int n_long, cudaStream_t stream) {
+int nl_launch(NlArgs a, int n_long, cudaStream_t stream) {
   static bool configured = false;
-  const size_t smem_rows = nl_smem_rows<XL, H>(a.adim, a.dv), smem_long = nl_smem_long<XL, H>(a.adim, a.dv);
-  if (smem_long > 200 * 1024) {
-    set_error("nl kernels: attention_dim x d too large for shared memory (%zu bytes)", smem_long);
+  const size_t smem = nl_smem_rows<XL, H>(a.adim, a.dv);
+  if (smem > kNlSmemLimit) {
+    set_error("nl kernels: attention_dim x d too large for shared memory (%zu bytes)", smem);
     return GB_ERR_UNSUPPORTED;
   }
   if (!configured) {
-    GB_CUDA(cudaFuncSetAttribute(nl_rows_kernel<XL, H, ADJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    GB_CUDA(cudaFuncSetAttribute(nl_long_kernel<XL, H, ADJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    GB_CUDA(cudaFuncSetAttribute(nl_rows_kernel<XL, H, ADJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kNlSmemLimit));
     configured = true;
   }
   const int nrows = a.row_hi - a.row_lo;
   if (nrows <= 0) return GB_OK;
-  // hub rows first, on the side stream: their few CTAs run next to the persistent kernel instead of after it
-  const cudaStream_t side = n_long > 0 ? side_fork(stream) : stream;
-  if (n_long > 0) {
-    LaunchScope ls(ADJ ? K_NL_ADJ_LONG : K_NL_FWD_LONG, side);
-    nl_long_kernel<XL, H, ADJ><<<n_long, kNlThreads, smem_long, side>>>(a);
-    if (int rc = check_launch("nl_long_kernel")) return rc;
-  }
+  a.n_long = n_long;
   GB_CUDA(cudaMemsetAsync(a.counter, 0, sizeof(int32_t), stream));
   const int want = (nrows + kNlWarps * kNlChunkRows - 1) / (kNlWarps * kNlChunkRows);
   const int blocks = min_int(want, 2 * sm_count());
   {
     LaunchScope ls(ADJ ? K_NL_ADJ_ROWS : K_NL_FWD, stream);
-    nl_rows_kernel<XL, H, ADJ><<<blocks, kNlThreads, smem_rows, stream>>>(a);
+    nl_rows_kernel<XL, H, ADJ><<<blocks, kNlThreads, smem, stream>>>(a);
   }
-  if (int rc = check_launch("nl_rows_kernel")) return rc;
-  return side_join(stream, side);
+  return check_launch("nl_rows_kernel");
 }
 
 template <bool ADJ>
