@@ -204,7 +204,8 @@ def run_ours(args):
     cfg = dict(synth.CONFIGS[name])
     if world > 1:
         import torch.distributed as dist
-        dist.init_process_group('nccl', device_id=device)
+        import datetime
+        dist.init_process_group('nccl', device_id=device, timeout=datetime.timedelta(seconds=600))
         try:
             return run_partitioned(args, cfg, device, rank, world)
         finally:
@@ -440,6 +441,8 @@ def run_partitioned(args, cfg, device, rank, world):
         return tot
 
     ms_e2e, evals_e2e = timed(loop_e2e)
+    # collective: EVERY rank takes part (before the rank-0-only reporting below)
+    exchange = exchange_times(halo, part, d, device, n_gathers, n_scatters, ms / args.steps)
     if rank != 0:
         return
     peak, peak_src = read_peaks()
@@ -480,7 +483,7 @@ def run_partitioned(args, cfg, device, rank, world):
                    'note': 'received bytes of the all-gathers / reduce-scatters divided by the WHOLE step time '
                            '(the exchanges are not overlapped with compute yet)'},
     }
-    line['nvlink'].update(exchange_times(halo, part, d, device, n_gathers, n_scatters, ms / args.steps))
+    line['nvlink'].update(exchange)
     emit(line)
 
 
@@ -701,9 +704,22 @@ def main():
                     help='skip the torch-CUDA-ops comparator (N = 1 only)')
     ap.add_argument('--function', default='transformer', choices=['transformer', 'laplacian'],
                     help='transformer = GRAND-nl (BASELINE.json headline); laplacian = GRAND-l sweep of config 5')
+    ap.add_argument('--watchdog', type=int, default=1500,
+                    help='seconds after which a still-running bench process kills itself (a rank stuck in a '
+                         'collective must not hold the GPUs)')
     args = ap.parse_args()
     global FUNCTION
     FUNCTION = args.function
+    if args.watchdog > 0:
+        import threading
+
+        def _expired():
+            sys.stderr.write(f'bench.py: watchdog expired after {args.watchdog} s, exiting\n')
+            sys.stderr.flush()
+            os._exit(3)
+        t = threading.Timer(args.watchdog, _expired)
+        t.daemon = True
+        t.start()
     if args.impl == 'reference':
         run_reference(args)
     else:
