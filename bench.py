@@ -345,7 +345,7 @@ def run_ours(args):
         except torch.cuda.OutOfMemoryError as exc:                       # the comparator's temporaries, not ours
             line['gpu_reference'] = {'unavailable': f'out of memory in the torch-ops comparator: {str(exc)[:80]}'}
     if args.cpu_baseline:
-        line['cpu_baseline'] = cpu_baseline(name, cfg, steps=1, warmup=0)
+        line['cpu_baseline'] = cpu_baseline(name, cfg, steps=2, warmup=1)
     emit(line)
 
 
@@ -633,7 +633,7 @@ def make_cpu_state(name, cfg, scale_div):
     return st
 
 
-CPU_SCALE = {'c1': 1, 'c2': 1, 'c3': 4, 'c4': 64, 'c5': 256}     # keeps the CPU leg at ~10-30 s
+CPU_SCALE = {'c1': 1, 'c2': 1, 'c3': 2, 'c4': 16, 'c5': 64}      # keeps the CPU leg at ~10-30 s
 
 
 def cpu_baseline(name, cfg, steps=1, warmup=1):

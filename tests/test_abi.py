@@ -60,3 +60,31 @@ def test_heads_must_divide_attention_dim():
     opt = {'leaky_relu_slope': 0.2, 'heads': 3, 'attention_dim': 32, 'attention_type': 'scaled_dot', 'beltrami': False}
     with pytest.raises(AssertionError):
         grand_b200.SpGraphTransAttentionLayer(6, 6, opt, torch.device('cpu'))
+
+
+def test_product_never_imports_the_oracle():
+    """oracle/ is test infrastructure: no module of the package may import it, and bench.py may do so only
+    inside its CPU-baseline / reference-arm functions"""
+    import ast
+    import glob
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+    def oracle_imports(path):
+        tree = ast.parse(open(path).read())
+        hits = []
+        for node in ast.walk(tree):
+            if isinstance(node, ast.Import) and any(a.name.split('.')[0] == 'oracle' for a in node.names):
+                hits.append(node.lineno)
+            if isinstance(node, ast.ImportFrom) and (node.module or '').split('.')[0] == 'oracle':
+                hits.append(node.lineno)
+        return tree, hits
+
+    for path in glob.glob(os.path.join(root, 'graph-neural-pde_b200', '*.py')) + [os.path.join(root, 'grand_b200.py')]:
+        assert oracle_imports(path)[1] == [], f'{path} imports the oracle'
+    tree, hits = oracle_imports(os.path.join(root, 'bench.py'))
+    allowed = set()
+    for node in ast.walk(tree):
+        if isinstance(node, ast.FunctionDef) and node.name in ('cpu_pass', 'make_cpu_state', 'cpu_baseline', 'run_reference'):
+            allowed.update(range(node.lineno, node.end_lineno + 1))
+    assert all(h in allowed for h in hits), f'bench.py imports the oracle outside the CPU baseline: lines {hits}'
