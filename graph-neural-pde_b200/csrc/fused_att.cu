@@ -28,6 +28,8 @@ int nl_fill_args(NlArgs& a, const gb_graph* g, int row_lo, int row_hi, const flo
 constexpr int kFusedWarps = 4;
 constexpr int kFusedThreads = kFusedWarps * 32;
 constexpr int kFusedCap = 256;          // max edges per segment handled here (== plan long threshold)
+constexpr int kColChunk = 64;           // att_col_bwd_kernel stages this many edges at a time: 6 KB of shared memory per
+                                        // CTA instead of 24 KB, so occupancy is set by registers (12 CTAs/SM), not by smem
 constexpr int kColCap = 256;            // gb_nl_adjoint: longer columns go to the CTA-per-column kernels (measured: a single warp
                                         // on a 4096-edge column costs more than it saves on the C4 and RMAT shapes)
 
@@ -310,7 +312,7 @@ __global__ void __launch_bounds__(kFusedThreads) att_row_bwd_kernel(const FusedB
 }
 
 // one warp per CSC column: transpose SpMM (dx, dalpha/dbeta partials) + dk.  The column's per-edge scalars are
-// staged through shared memory in chunks of kFusedCap edges; the accumulators live in registers across the
+// staged through shared memory in chunks of kColChunk edges; the accumulators live in registers across the
 // chunks, so columns up to `a.col_cap` edges stay in this kernel (longer ones: CTA-per-column kernels).
 template <int V, int LPE, int XL, int XCPL>
 __global__ void __launch_bounds__(kFusedThreads) att_col_bwd_kernel(const FusedBwdArgs a) {
@@ -326,9 +328,9 @@ __global__ void __launch_bounds__(kFusedThreads) att_col_bwd_kernel(const FusedB
     if (deg > a.col_cap) deg = -1;                    // long column: handled elsewhere
   }
   if (deg >= 0) {
-    float* sS = smem + (size_t)warp * kFusedCap * (H + 2);   // ds of the chunk's edges
-    float* sA = sS + kFusedCap * H;                           // abar
-    int* sC = reinterpret_cast<int*>(sA + kFusedCap);         // row of each edge
+    float* sS = smem + (size_t)warp * kColChunk * (H + 2);   // ds of the chunk's edges (16-byte aligned rows)
+    float* sA = sS + kColChunk * H;                           // abar
+    int* sC = reinterpret_cast<int*>(sA + kColChunk);         // row of each edge
     const SpmmArgs& sp = a.sp;
     constexpr int EPX = 32 / XL;
     const int xl = lane % XL, xg = lane / XL;
@@ -341,14 +343,19 @@ __global__ void __launch_bounds__(kFusedThreads) att_col_bwd_kernel(const FusedB
 #pragma unroll
     for (int j = 0; j < XCPL; ++j) acc[j] = Vec<V>::zero();
     Vec<V> acck = Vec<V>::zero();
-    for (int c0 = 0; c0 < deg; c0 += kFusedCap) {
-      const int cn = min(kFusedCap, deg - c0);
+    const bool ds4 = H == 4 && (reinterpret_cast<uintptr_t>(a.ds) & 15) == 0;
+    for (int c0 = 0; c0 < deg; c0 += kColChunk) {
+      const int cn = min(kColChunk, deg - c0);
       // ---- stage per-edge scalars (coalesced over the column's CSC slots) -------------------------
       for (int e = lane; e < cn; e += 32) {
         const int slot = ld_stream_i32(a.tperm + start + c0 + e);
         sC[e] = ld_stream_i32(a.rowidx + start + c0 + e);
         sA[e] = __ldg(a.abar + slot);
-        for (int h = 0; h < H; ++h) sS[e * H + h] = __ldg(a.ds + (size_t)slot * H + h);
+        if (ds4) {                                      // one 16-byte load per edge
+          *reinterpret_cast<float4*>(sS + e * 4) = __ldg(reinterpret_cast<const float4*>(a.ds + (size_t)slot * 4));
+        } else {
+          for (int h = 0; h < H; ++h) sS[e * H + h] = __ldg(a.ds + (size_t)slot * H + h);
+        }
       }
       __syncwarp();
       // ---- t += sum_e abar_e g[row_e,:] ----------------------------------------------------------
@@ -469,7 +476,8 @@ int launch_bwd(const FusedBwdArgs& a, cudaStream_t stream, bool col) {
   const int blocks = (a.n + kFusedWarps - 1) / kFusedWarps;
   LaunchScope ls(col ? K_FUSED_ATT_BWD_COL : K_FUSED_ATT_BWD_ROW, stream);
   if (col)
-    att_col_bwd_kernel<4, LPE, XL, XCPL><<<blocks, kFusedThreads, fused_smem(a.heads), stream>>>(a);
+    att_col_bwd_kernel<4, LPE, XL, XCPL><<<blocks, kFusedThreads,
+                                          (size_t)kFusedWarps * kColChunk * (a.heads + 2) * sizeof(float), stream>>>(a);
   else
     att_row_bwd_kernel<4, LPE, XL, XCPL><<<blocks, kFusedThreads, fused_smem(a.heads), stream>>>(a);
   return check_launch(col ? "att_col_bwd" : "att_row_bwd");
