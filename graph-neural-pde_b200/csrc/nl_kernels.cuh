@@ -40,6 +40,24 @@ namespace gb {
 constexpr int kNlWarps = 8;
 constexpr int kNlThreads = kNlWarps * 32;
 constexpr int kNlChunkRows = 4;          // rows per scheduler grab
+// Tuning knobs (measured on the ogbn-products shape, profiles/r01zi, r01zj): the forward kernel keeps 4 gathers in
+// flight per lane group and fits 80 registers -> 3 CTAs (24 warps) per SM, 3 % faster than 8 gathers at 2 CTAs;
+// the adjoint kernel carries twice the accumulators: 8 gathers at 2 CTAs (125 registers); 4 gathers at 3 CTAs
+// spills and is 12 % slower.
+#ifndef GB_NL_UFWD
+#define GB_NL_UFWD 4
+#endif
+#ifndef GB_NL_CTAS_FWD
+#define GB_NL_CTAS_FWD 3
+#endif
+#ifndef GB_NL_UADJ
+#define GB_NL_UADJ 8
+#endif
+#ifndef GB_NL_CTAS_ADJ
+#define GB_NL_CTAS_ADJ 2
+#endif
+constexpr int kNlUFwd = GB_NL_UFWD, kNlUAdj = GB_NL_UADJ;              // gathers in flight per lane group
+constexpr int kNlCtasFwd = GB_NL_CTAS_FWD, kNlCtasAdj = GB_NL_CTAS_ADJ;  // resident CTAs per SM compiled for
 constexpr int kNlLongRow = 2048;         // rows longer than this get a whole CTA (the online softmax needs no
                                          // per-edge shared memory, so a warp can take rows far beyond the plan's
                                          // 256-edge list threshold; the scheduler balances them)
@@ -149,7 +167,8 @@ struct NlStats {
 template <int XL, int H, bool ADJ>
 struct NlRow {
   static constexpr int EPI = 32 / XL;                       // edge groups per warp
-  static constexpr int U = (XL / H) < 8 ? (XL / H) : 8;     // edges in flight per group
+  static constexpr int UMAX = ADJ ? kNlUAdj : kNlUFwd;
+  static constexpr int U = (XL / H) < UMAX ? (XL / H) : UMAX;   // edges in flight per group
   static constexpr int NV = U * H;                          // scores per group batch (<= XL)
   static constexpr int SH = ilog2_c(XL) - ilog2_c(NV);      // score index of lane xl = xl >> SH
   static constexpr int SHU = ilog2_c(XL) - ilog2_c(U);
@@ -542,7 +561,7 @@ __device__ __forceinline__ void nl_long_row(const NlArgs& a, int row, float* wk_
 
 // persistent kernel: warps pull chunks of rows from an atomic counter
 template <int XL, int H, bool ADJ>
-__global__ void __launch_bounds__(kNlThreads, 2) nl_rows_kernel(const NlArgs a) {
+__global__ void __launch_bounds__(kNlThreads, ADJ ? kNlCtasAdj : kNlCtasFwd) nl_rows_kernel(const NlArgs a) {
   extern __shared__ __align__(16) float smem[];
   using Row = NlRow<XL, H, ADJ>;
   const int ldw = nl_ldw(a.dv);
@@ -621,7 +640,7 @@ int nl_launch(NlArgs a, int n_long, cudaStream_t stream) {
   a.n_long = n_long;
   GB_CUDA(cudaMemsetAsync(a.counter, 0, sizeof(int32_t), stream));
   const int want = (nrows + kNlWarps * kNlChunkRows - 1) / (kNlWarps * kNlChunkRows);
-  const int blocks = min_int(want, 2 * sm_count());
+  const int blocks = min_int(want, (ADJ ? kNlCtasAdj : kNlCtasFwd) * sm_count());
   {
     LaunchScope ls(ADJ ? K_NL_ADJ_ROWS : K_NL_FWD, stream);
     nl_rows_kernel<XL, H, ADJ><<<blocks, kNlThreads, smem, stream>>>(a);
