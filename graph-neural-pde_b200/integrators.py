@@ -223,7 +223,9 @@ def _solve_adaptive(prob, method, rtol, atol, max_num_steps=2 ** 31 - 1):
             tol = tuple(atol + rtol * torch.max(a.abs(), b.abs()) for a, b in zip(y, y1))
             ratio = _mixed_norm(tuple(e / s for e, s in zip(err, tol)))
             if ratio <= 1:
-                f1 = ks[-1] if tab['fsal'] else prob.f(t + dt, y1)
+                # torchdiffeq's _runge_kutta_step returns f1 = k[..., -1] for EVERY tableau (exact for the FSAL
+                # Dormand-Prince pair; for adaptive_heun it is f(t1, y + dt k1), no extra evaluation)
+                f1 = ks[-1]
                 y_mid = _combine(y, dt, ks, tab['c_mid']) if tab['c_mid'] else None
                 win = (t, t + dt, y, y1, y_mid, f0, f1)
                 t, y, f0 = t + dt, y1, f1

@@ -141,7 +141,8 @@ def _adaptive(func, method, y0, t0, t1, rtol, atol, max_steps=100000):
                     x = (t1 - t) / dt
                     y = tuple(a + x * (b - a) for a, b in zip(y, y1))
                 return y
-            t, y, f0 = t_new, y1, ks[-1] if method == 'dopri5' else f(t_new, y1)
+            # torchdiffeq (0.1.x and 0.2.x rk_common._runge_kutta_step): f1 = k[..., -1] for every tableau
+            t, y, f0 = t_new, y1, ks[-1]
         # step-size controller
         if ratio == 0:
             factor = 10.0

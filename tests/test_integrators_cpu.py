@@ -1,0 +1,277 @@
+"""CPU: the product's restated solvers (grand_b200/integrators.py - host logic, plain torch) against the
+oracle's restatement (oracle/integrate.py), closed-form solutions and autograd through the solver.
+The ODE functions here are small dense torch modules: the solvers are generic, the CUDA operators are not
+involved (they have no CPU path)."""
+import math
+
+import pytest
+import torch
+
+from oracle import integrate as oi
+
+torch.manual_seed(0)
+
+
+def product():
+    from grand_b200 import integrators
+    return integrators
+
+
+class Linear(torch.nn.Module):
+    """dy/dt = y A^T + b (autonomous) with an nfe counter like the reference's ODE functions"""
+
+    def __init__(self, d, seed=0, scale=0.3):
+        super().__init__()
+        g = torch.Generator().manual_seed(seed)
+        self.A = torch.nn.Parameter(scale * torch.randn(d, d, generator=g, dtype=torch.float64))
+        self.b = torch.nn.Parameter(0.1 * torch.randn(d, generator=g, dtype=torch.float64))
+        self.nfe = 0
+
+    def forward(self, t, y):
+        self.nfe += 1
+        return y @ self.A.T + self.b
+
+
+class TimeDependent(torch.nn.Module):
+    """dy/dt = -y * w + sin(t): the time argument must reach the function with the right sign and value"""
+
+    def __init__(self):
+        super().__init__()
+        self.w = torch.nn.Parameter(torch.tensor(0.7, dtype=torch.float64))
+
+    def forward(self, t, y):
+        return -y * self.w + torch.sin(t)
+
+
+def exact_linear(func, y0, t):
+    """y(t) for dy/dt = A y + b via the augmented matrix exponential"""
+    d = func.A.shape[0]
+    m = torch.zeros(d + 1, d + 1, dtype=torch.float64)
+    m[:d, :d] = func.A.detach()
+    m[:d, d] = func.b.detach()
+    e = torch.linalg.matrix_exp(m * t)
+    aug = torch.cat([y0, torch.ones(y0.shape[0], 1, dtype=torch.float64)], dim=1)
+    return (aug @ e.T)[:, :d]
+
+
+@pytest.mark.parametrize('method', ['euler', 'midpoint', 'rk4'])
+@pytest.mark.parametrize('t1,step', [(2.0, 1.0), (1.0, 0.3), (2.5, 1.0)])
+def test_fixed_grid_solvers_match_the_oracle_bitwise(method, t1, step):
+    """same grid (incl. the clamped last point), same stage formulas -> identical fp64 results up to the
+    order of the stage sums"""
+    P = product()
+    func = Linear(5)
+    y0 = torch.randn(7, 5, dtype=torch.float64)
+    t = torch.tensor([0.0, t1], dtype=torch.float64)
+    with torch.no_grad():
+        got = P.odeint(func, y0, t, method=method, options=dict(step_size=step))
+        nfe = func.nfe
+        func.nfe = 0
+        ref = oi.odeint(func, y0, [0.0, t1], method, step)
+    assert got.shape == ref.shape == (2, 7, 5)
+    assert torch.equal(got[0], y0)
+    torch.testing.assert_close(got, ref, rtol=1e-13, atol=1e-13)
+    assert nfe == func.nfe                                     # the reference counts one nfe per call
+
+
+@pytest.mark.parametrize('method,order', [('euler', 1), ('midpoint', 2), ('rk4', 4)])
+def test_fixed_grid_convergence_order(method, order):
+    P = product()
+    func = Linear(4, seed=3)
+    y0 = torch.randn(3, 4, dtype=torch.float64)
+    exact = exact_linear(func, y0, 1.0)
+    errs = []
+    with torch.no_grad():
+        for h in (0.1, 0.05):
+            y = P.odeint(func, y0, torch.tensor([0.0, 1.0]), method=method, options=dict(step_size=h))[1]
+            errs.append(float((y - exact).abs().max()))
+    rate = math.log2(errs[0] / errs[1])
+    assert abs(rate - order) < 0.35, (errs, rate)
+
+
+def test_rk4_is_the_three_eighths_rule():
+    """torchdiffeq's fixed-grid rk4 is rk4_alt_step_func (3/8 rule), not the classic tableau: one step on
+    dy/dt = t^3-free test function y' = y gives 1 + h + h^2/2 + h^3/6 + h^4/24 for both, so use y' = t*y"""
+    P = product()
+    f = lambda t, y: t * y
+    y0 = torch.ones(1, dtype=torch.float64)
+    h = 0.5
+    got = P.odeint(f, y0, torch.tensor([0.0, h]), method='rk4', options=dict(step_size=h))[1]
+    k1 = 0.0
+    k2 = (h / 3) * (1 + h * k1 / 3)
+    k3 = (2 * h / 3) * (1 + h * (k2 - k1 / 3))
+    k4 = h * (1 + h * (k1 - k2 + k3))
+    ref = 1 + h * (k1 + 3 * k2 + 3 * k3 + k4) / 8
+    assert abs(float(got) - ref) < 1e-15
+    classic = 1 + h * (0 + 2 * (h / 2) * 1 + 2 * (h / 2) * (1 + h / 2 * (h / 2)) + h * (1 + h * (h / 2) * (1 + h * h / 4))) / 6
+    assert abs(float(got) - classic) > 1e-6
+
+
+def test_time_argument_forward_and_reverse():
+    P = product()
+    func = TimeDependent()
+    y0 = torch.tensor([0.3, -1.2], dtype=torch.float64)
+    with torch.no_grad():
+        fwd = P.odeint(func, y0, torch.tensor([0.0, 1.5]), method='rk4', options=dict(step_size=0.05))
+        back = P.odeint(func, fwd[1], torch.tensor([1.5, 0.0]), method='rk4', options=dict(step_size=0.05))
+        ref = oi.odeint(func, y0, [0.0, 1.5], 'rk4', 0.05)
+    torch.testing.assert_close(fwd, ref, rtol=1e-13, atol=1e-13)
+    torch.testing.assert_close(back[1], y0, rtol=0, atol=1e-6)   # reverse-time solve returns to the start
+
+
+def test_intermediate_times_are_interpolated_on_the_fixed_grid():
+    P = product()
+    func = Linear(3, seed=5)
+    y0 = torch.randn(2, 3, dtype=torch.float64)
+    with torch.no_grad():
+        sol = P.odeint(func, y0, torch.tensor([0.0, 0.25, 1.0]), method='euler', options=dict(step_size=0.5))
+        one = P.odeint(func, y0, torch.tensor([0.0, 0.5]), method='euler', options=dict(step_size=0.5))[1]
+    torch.testing.assert_close(sol[1], y0 + 0.5 * (one - y0), rtol=1e-14, atol=1e-14)
+    assert sol.shape == (3, 2, 3)
+
+
+# ---- adaptive solvers -----------------------------------------------------------------------------
+@pytest.mark.parametrize('method', ['dopri5', 'adaptive_heun'])
+def test_adaptive_solvers_match_the_oracle_and_the_exact_solution(method):
+    P = product()
+    func = Linear(4, seed=11)
+    y0 = torch.randn(5, 4, dtype=torch.float64)
+    rtol, atol = (1e-8, 1e-10) if method == 'dopri5' else (1e-5, 1e-7)
+    with torch.no_grad():
+        got = P.odeint(func, y0, torch.tensor([0.0, 2.0]), method=method, rtol=rtol, atol=atol)
+        nfe = func.nfe
+        func.nfe = 0
+        ref = oi.odeint(func, y0, [0.0, 2.0], method, None, rtol, atol)
+    assert nfe == func.nfe                                     # same accepted / rejected step sequence
+    torch.testing.assert_close(got, ref, rtol=1e-12, atol=1e-12)
+    exact = exact_linear(func, y0, 2.0)
+    tol = 1e-6 if method == 'dopri5' else 1e-3
+    assert float((got[1] - exact).abs().max()) < tol
+
+
+def test_dopri5_lands_on_requested_times_by_dense_output():
+    P = product()
+    func = Linear(3, seed=2)
+    y0 = torch.randn(2, 3, dtype=torch.float64)
+    ts = [0.0, 0.37, 1.0, 1.9]
+    with torch.no_grad():
+        sol = P.odeint(func, y0, torch.tensor(ts), method='dopri5', rtol=1e-9, atol=1e-11)
+    for i, tv in enumerate(ts):
+        assert float((sol[i] - exact_linear(func, y0, tv)).abs().max()) < 1e-6
+
+
+def test_unknown_method_and_bad_time_vectors_raise():
+    P = product()
+    f = lambda t, y: y
+    y0 = torch.ones(2)
+    with pytest.raises(NotImplementedError):
+        P.odeint(f, y0, torch.tensor([0.0, 1.0]), method='implicit_adams')
+    with pytest.raises(ValueError):
+        P.odeint(f, y0, torch.tensor([0.0]), method='rk4')
+    with pytest.raises(ValueError):
+        P.odeint(f, y0, torch.tensor([0.0, 1.0, 0.5]), method='rk4')
+    with pytest.raises(NotImplementedError):
+        P.odeint_adjoint(f, (y0, y0), torch.tensor([0.0, 1.0]), method='rk4')
+
+
+# ---- adjoint --------------------------------------------------------------------------------------
+def _loss_and_grads(solver, func, y0, **kw):
+    y0 = y0.clone().requires_grad_(True)
+    for p in func.parameters():
+        p.grad = None
+    z = solver(func, y0)
+    w = torch.linspace(-1, 1, z[-1].numel(), dtype=z.dtype).view_as(z[-1])
+    loss = (z[-1] * w).sum()
+    loss.backward()
+    return float(loss.detach()), y0.grad.clone(), [p.grad.clone() for p in func.parameters()]
+
+
+@pytest.mark.parametrize('method,step', [('rk4', 0.25), ('euler', 0.1), ('midpoint', 0.2)])
+def test_adjoint_matches_the_oracle_adjoint(method, step):
+    """same augmented reverse solve: identical numbers (sign conventions ride on stage coefficients here, on
+    negated tensors in the oracle - algebraically the same)"""
+    P = product()
+    func = Linear(4, seed=7)
+    y0 = torch.randn(6, 4, dtype=torch.float64)
+    t = torch.tensor([0.0, 1.0], dtype=torch.float64)
+    ours = _loss_and_grads(lambda f, y: P.odeint_adjoint(f, y, t, method=method, options=dict(step_size=step),
+                                                         adjoint_method=method,
+                                                         adjoint_options=dict(step_size=step)), func, y0)
+    ref = _loss_and_grads(lambda f, y: oi.odeint_adjoint(f, y, [0.0, 1.0], method, step), func, y0)
+    assert abs(ours[0] - ref[0]) < 1e-13
+    torch.testing.assert_close(ours[1], ref[1], rtol=1e-12, atol=1e-13)
+    for a, b in zip(ours[2], ref[2]):
+        torch.testing.assert_close(a, b, rtol=1e-12, atol=1e-13)
+
+
+def test_adjoint_gradients_converge_to_backprop_through_the_solver():
+    """continuous adjoint vs discretise-then-differentiate: equal up to the O(h^4) truncation of rk4"""
+    P = product()
+    func = Linear(3, seed=9)
+    y0 = torch.randn(4, 3, dtype=torch.float64)
+    t = torch.tensor([0.0, 1.0], dtype=torch.float64)
+    h = 0.05
+    adj = _loss_and_grads(lambda f, y: P.odeint_adjoint(f, y, t, method='rk4', options=dict(step_size=h)), func, y0)
+    bp = _loss_and_grads(lambda f, y: P.odeint(f, y, t, method='rk4', options=dict(step_size=h)), func, y0)
+    assert abs(adj[0] - bp[0]) < 1e-14
+    torch.testing.assert_close(adj[1], bp[1], rtol=1e-6, atol=1e-8)
+    for a, b in zip(adj[2], bp[2]):
+        torch.testing.assert_close(a, b, rtol=1e-6, atol=1e-8)
+
+
+def test_adjoint_with_time_dependent_function_and_dopri5():
+    P = product()
+    func = TimeDependent()
+    y0 = torch.tensor([0.4, -0.9, 1.3], dtype=torch.float64)
+    t = torch.tensor([0.0, 1.2], dtype=torch.float64)
+    kw = dict(method='dopri5', rtol=1e-9, atol=1e-11)
+    adj = _loss_and_grads(lambda f, y: P.odeint_adjoint(f, y, t, **kw), func, y0)
+    bp = _loss_and_grads(lambda f, y: P.odeint(f, y, t, **kw), func, y0)
+    torch.testing.assert_close(adj[1], bp[1], rtol=1e-6, atol=1e-8)
+    torch.testing.assert_close(adj[2][0], bp[2][0], rtol=1e-6, atol=1e-8)
+
+
+class FusedLinear(Linear):
+    """exposes the fused f + VJP hook of the CUDA functions (ODEFuncTransformerAtt.eval_vjp) with closed-form
+    products, and counts how often each route was taken"""
+
+    def __init__(self, *a, decline=False, **kw):
+        super().__init__(*a, **kw)
+        self.fused_calls, self.decline = 0, decline
+
+    def eval_vjp(self, t, y, cot, params):
+        if self.decline:
+            return None
+        self.fused_calls += 1
+        self.nfe += 1
+        f = y @ self.A.T + self.b
+        grads = {id(self.A): cot.T @ y, id(self.b): cot.sum(0)}
+        return f, cot @ self.A, [grads.get(id(p)) for p in params]
+
+
+@pytest.mark.parametrize('method', ['rk4', 'dopri5'])
+def test_eval_vjp_hook_gives_the_autograd_numbers(method):
+    P = product()
+    y0 = torch.randn(5, 4, dtype=torch.float64)
+    t = torch.tensor([0.0, 1.0], dtype=torch.float64)
+    kw = dict(method=method, options=dict(step_size=0.25), rtol=1e-8, atol=1e-10)
+    plain, fused, declined = Linear(4, seed=1), FusedLinear(4, seed=1), FusedLinear(4, seed=1, decline=True)
+    ref = _loss_and_grads(lambda f, y: P.odeint_adjoint(f, y, t, **kw), plain, y0)
+    got = _loss_and_grads(lambda f, y: P.odeint_adjoint(f, y, t, **kw), fused, y0)
+    dec = _loss_and_grads(lambda f, y: P.odeint_adjoint(f, y, t, **kw), declined, y0)
+    assert fused.fused_calls > 0 and declined.fused_calls == 0
+    assert fused.nfe == plain.nfe == declined.nfe              # one nfe per augmented-dynamics call either way
+    for a, b in ((got, ref), (dec, ref)):
+        torch.testing.assert_close(a[1], b[1], rtol=1e-12, atol=1e-13)
+        for u, v in zip(a[2], b[2]):
+            torch.testing.assert_close(u, v, rtol=1e-12, atol=1e-13)
+
+
+def test_adjoint_params_subset_and_frozen_parameters():
+    P = product()
+    func = Linear(3, seed=4)
+    func.b.requires_grad_(False)
+    y0 = torch.randn(2, 3, dtype=torch.float64, requires_grad=True)
+    z = P.odeint_adjoint(func, y0, torch.tensor([0.0, 1.0]), method='rk4', options=dict(step_size=0.5))
+    z[-1].sum().backward()
+    assert func.A.grad is not None and func.b.grad is None and y0.grad is not None
