@@ -24,6 +24,24 @@ from .ops import (QKProjFn, EdgeSoftmaxFn, DiffusionFn, ToCooOrderFn, FusedTrans
                   NlTransformerFn, nl_supported, nl_eval_vjp)
 
 
+def unit_heads(qk, heads, centre):
+    """[N, 2A] projections q|k -> per-(node, head) unit vectors (mean-centred first when `centre`), the q half
+    multiplied by sqrt(dk).  The scaled_dot kernels applied to the result give the reference's cosine_sim /
+    pearson scores: torch.nn.CosineSimilarity(eps=1e-5) is  <q / max(|q|, eps), k / max(|k|, eps)>  per head
+    (function_transformer_attention.py:251-259), and the kernels' 1/sqrt(dk) cancels the factor put on q.
+    Node-level torch ops ([N, 2A] elementwise), differentiated by autograd: this is how the backward pass of
+    these two attention types is formed (the per-edge work stays in the hand-written scaled_dot VJP kernels)."""
+    n, a2 = qk.shape
+    dk = a2 // (2 * heads)
+    v = qk.reshape(n, 2 * heads, dk)
+    if centre:
+        v = v - v.mean(dim=2, keepdim=True)
+    v = v / v.norm(dim=2, keepdim=True).clamp_min(1e-5)
+    scale = torch.ones(2 * heads, dtype=qk.dtype, device=qk.device)
+    scale[:heads] = float(dk) ** 0.5
+    return (v * scale[None, :, None]).reshape(n, a2)
+
+
 class SpGraphTransAttentionLayer(nn.Module):
     """function_transformer_attention.py:65-270"""
 
@@ -86,6 +104,17 @@ class SpGraphTransAttentionLayer(nn.Module):
                                       'function, function_transformer_attention.py:264); softmax only')
         return _lib.GB_ATT[att_type]
 
+    @property
+    def _UNIT_TYPES(self):
+        return (_lib.GB_ATT['cosine_sim'], _lib.GB_ATT['pearson'])
+
+    def needs_composite_backward(self, att_type, x):
+        """cosine_sim / pearson evaluations that will be differentiated run as projection -> unit_heads ->
+        scaled_dot edge kernels -> SpMM (the fused forward kernels have no VJP for these types)"""
+        if att_type not in self._UNIT_TYPES or not torch.is_grad_enabled():
+            return False
+        return x.requires_grad or any(p.requires_grad for p in (self.Q.weight, self.Q.bias, self.K.weight, self.K.bias))
+
     def qk_weights(self):
         """[Wq;Wk], [bq;bk] concatenated once per parameter version (parameters change once per
         optimiser step, evaluations happen NFE times per step)"""
@@ -110,6 +139,10 @@ class SpGraphTransAttentionLayer(nn.Module):
         kparams = None
         if att_type == _lib.GB_ATT['exp_kernel']:
             kparams = torch.cat([self.output_var.detach(), self.lengthscale.detach()]).to(torch.float32).contiguous()
+        if att_type in self._UNIT_TYPES and torch.is_grad_enabled() and qk.requires_grad:
+            # training: the VJP kernels implement scaled_dot; cosine_sim / pearson are scaled_dot of unit vectors
+            qk = unit_heads(qk, self.h, centre=att_type == _lib.GB_ATT['pearson'])
+            att_type = _lib.GB_ATT['scaled_dot']
         return EdgeSoftmaxFn.apply(qk, plan, self.h, att_type, int(self.opt['attention_norm_idx']), edge_w, kparams)
 
     def forward(self, x, edge, y=None):
@@ -159,8 +192,8 @@ class ODEFuncTransformerAtt(ODEFunc):
             f = NlTransformerFn.apply(x2, L.Q.weight, L.Q.bias, L.K.weight, L.K.bias, self.alpha_train,
                                       self.beta_train if x0 is not None else None, x0, plan, L.h,
                                       not self.opt['no_alpha_sigmoid'], None)
-        elif fused_transformer_supported(plan, x2, L.h, L.attention_dim, att_type,
-                                         int(self.opt['attention_norm_idx']), edge_w):
+        elif not L.needs_composite_backward(att_type, x2) and fused_transformer_supported(
+                plan, x2, L.h, L.attention_dim, att_type, int(self.opt['attention_norm_idx']), edge_w):
             kparams = None
             if att_type == _lib.GB_ATT['exp_kernel']:
                 kparams = torch.cat([L.output_var.detach(), L.lengthscale.detach()]).to(torch.float32).contiguous()
