@@ -109,11 +109,15 @@ class SpGraphTransAttentionLayer(nn.Module):
         return (_lib.GB_ATT['cosine_sim'], _lib.GB_ATT['pearson'])
 
     def needs_composite_backward(self, att_type, x):
-        """cosine_sim / pearson evaluations that will be differentiated run as projection -> unit_heads ->
-        scaled_dot edge kernels -> SpMM (the fused forward kernels have no VJP for these types)"""
-        if att_type not in self._UNIT_TYPES or not torch.is_grad_enabled():
+        """evaluations of the other attention types that will be differentiated run as projection -> edge softmax
+        -> SpMM (the fused forward kernels have no VJP for them): cosine_sim / pearson as scaled_dot of unit_heads,
+        exp_kernel through ops.exp_kernel_score_vjp"""
+        if att_type == _lib.GB_ATT['scaled_dot'] or not torch.is_grad_enabled() or not _lib.unverified_enabled():
             return False
-        return x.requires_grad or any(p.requires_grad for p in (self.Q.weight, self.Q.bias, self.K.weight, self.K.bias))
+        params = [self.Q.weight, self.Q.bias, self.K.weight, self.K.bias]
+        if att_type == _lib.GB_ATT['exp_kernel']:
+            params += [self.output_var, self.lengthscale]
+        return x.requires_grad or any(p.requires_grad for p in params)
 
     def qk_weights(self):
         """[Wq;Wk], [bq;bk] concatenated once per parameter version (parameters change once per
@@ -137,9 +141,11 @@ class SpGraphTransAttentionLayer(nn.Module):
         if self.opt.get('reweight_attention', False) and self.edge_weights is not None:
             edge_w = _plan.cached_per_edge(plan, self.edge_weights, 'rw', lambda t: plan.to_csr_order(t.detach()))
         kparams = None
-        if att_type == _lib.GB_ATT['exp_kernel']:
-            kparams = torch.cat([self.output_var.detach(), self.lengthscale.detach()]).to(torch.float32).contiguous()
-        if att_type in self._UNIT_TYPES and torch.is_grad_enabled() and qk.requires_grad:
+        if att_type == _lib.GB_ATT['exp_kernel']:            # differentiable: EdgeSoftmaxFn returns d(output_var, lengthscale)
+            kparams = torch.cat([self.output_var, self.lengthscale]).to(torch.float32).contiguous()
+            if not _lib.unverified_enabled():
+                kparams = kparams.detach()
+        if att_type in self._UNIT_TYPES and torch.is_grad_enabled() and qk.requires_grad and _lib.unverified_enabled():
             # training: the VJP kernels implement scaled_dot; cosine_sim / pearson are scaled_dot of unit vectors
             qk = unit_heads(qk, self.h, centre=att_type == _lib.GB_ATT['pearson'])
             att_type = _lib.GB_ATT['scaled_dot']

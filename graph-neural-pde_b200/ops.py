@@ -63,6 +63,43 @@ class QKProjFn(torch.autograd.Function):
         return dx, None, None, None, None
 
 
+def _segment_sums(vals, ptr):
+    """[E,H] values laid out segment after segment, ptr [n+1] -> [n,H] sums.  Prefix sums in fp64 (deterministic on
+    every backend; a difference of two prefixes loses ~1e-16 * E relative to the running total)"""
+    cs = torch.zeros(vals.shape[0] + 1, vals.shape[1], dtype=torch.float64, device=vals.device)
+    torch.cumsum(vals.double(), dim=0, out=cs[1:])
+    ptr = ptr.long()
+    return (cs[ptr[1:]] - cs[ptr[:-1]]).to(vals.dtype)
+
+
+def exp_kernel_score_vjp(ds, prods, q, k, kparams, rowptr, colptr, tperm, heads, mh):
+    """VJP of the exp_kernel score  s[e,h] = ov^2 exp(-|q[row_e,h] - k[col_e,h]|^2 / (2 l^2))
+    (function_transformer_attention.py:247-248) given ds = dL/ds [E,H] (CSR-slot order) and the scores themselves:
+
+        c_eh  = ds_eh s_eh / l^2
+        dq[i,h] = sum_{e in row i} c_eh k[col_e,h] - q[i,h] sum_{e in row i} c_eh
+        dk[j,h] = sum_{e in col j} c_eh q[row_e,h] - k[j,h] sum_{e in col j} c_eh
+        d ov = 2/ov sum ds s            d l = sum ds s |q-k|^2 / l^3,  |q-k|^2 = -2 l^2 log(s / ov^2)
+
+    `mh(c)` returns the two gathered sums ([N,A] each) - on the GPU the multi-head SpMM kernels behind
+    gb_edge_score_bwd (scaled_dot form), in the CPU test of this algebra an index_add.  Everything else is
+    elementwise / prefix-sum torch work on [E,H] and [N,A] tensors."""
+    n, a = q.shape
+    dk = a // heads
+    ov, ls = kparams[0], kparams[1]
+    w = ds * prods
+    c = w / (ls * ls)
+    ck, cq = mh(c)
+    rsum = _segment_sums(c, rowptr)
+    csum = _segment_sums(c[tperm.long()], colptr)
+    dq = ck.view(n, heads, dk) - q.view(n, heads, dk) * rsum[:, :, None]
+    dkk = cq.view(n, heads, dk) - k.view(n, heads, dk) * csum[:, :, None]
+    logt = torch.where(prods > 0, torch.log(prods / (ov * ov)), torch.zeros_like(prods))
+    d_ov = w.double().sum() * 2.0 / ov.double()
+    d_ls = (w.double() * (-2.0 * logt.double())).sum() / ls.double()
+    return dq.reshape(n, a), dkk.reshape(n, a), torch.stack([d_ov, d_ls]).to(ds.dtype)
+
+
 class EdgeSoftmaxFn(torch.autograd.Function):
     """qk [N,2A] -> (att [E,H], abar [E], prods [E,H]) in CSR-slot order."""
 
@@ -88,9 +125,9 @@ class EdgeSoftmaxFn(torch.autograd.Function):
                                                dk, att_type, _lib.ptr(edge_w), _lib.ptr(kparams), att.data_ptr(),
                                                abar.data_ptr(), prods.data_ptr(), _lib.stream()),
                        'gb_edge_softmax_fwd')
-        ctx.save_for_backward(qk, att)
-        ctx.plan, ctx.heads, ctx.dk, ctx.att_type, ctx.norm_idx, ctx.edge_w, ctx.kparams = \
-            plan, heads, dk, att_type, norm_idx, edge_w, kparams
+        exp_kernel = att_type == _lib.GB_ATT['exp_kernel']
+        ctx.save_for_backward(qk, att, prods if exp_kernel else None, kparams if exp_kernel else None)
+        ctx.plan, ctx.heads, ctx.dk, ctx.att_type, ctx.norm_idx, ctx.edge_w = plan, heads, dk, att_type, norm_idx, edge_w
         ctx.set_materialize_grads(False)
         ctx.mark_non_differentiable(prods)
         return att, abar, prods
@@ -99,22 +136,44 @@ class EdgeSoftmaxFn(torch.autograd.Function):
     @once_differentiable
     def backward(ctx, datt, dabar, _dprods):
         lib = _lib.load()
-        qk, att = ctx.saved_tensors
+        qk, att, prods, kparams = ctx.saved_tensors
         plan, heads, dk = ctx.plan, ctx.heads, ctx.dk
         n, a2 = qk.shape
         a = a2 // 2
         if datt is None and dabar is None:
             return (None,) * 7
+        if ctx.att_type not in (_lib.GB_ATT['scaled_dot'], _lib.GB_ATT['exp_kernel']):
+            raise NotImplementedError('cosine_sim / pearson are differentiated as scaled_dot of unit vectors '
+                                      '(function_transformer_attention.unit_heads); call through the layer')
+        if ctx.att_type == _lib.GB_ATT['exp_kernel'] and not _lib.unverified_enabled():
+            raise NotImplementedError('backward of attention_type exp_kernel has not run on hardware yet: '
+                                      'set GB_UNVERIFIED=1 to enable it (see _lib.unverified_enabled)')
+        if ctx.att_type == _lib.GB_ATT['exp_kernel'] and ctx.edge_w is not None:
+            raise NotImplementedError('backward of exp_kernel with reweight_attention is not implemented')
         datt = None if datt is None else _f32c(datt)
         dabar = None if dabar is None else _f32c(dabar)
         ds = torch.empty(plan.e, heads, dtype=torch.float32, device=qk.device)
         _lib.check(lib.gb_edge_softmax_bwd(plan.c, ctx.norm_idx, att.data_ptr(), _lib.ptr(dabar), _lib.ptr(datt), heads,
                                            _lib.ptr(ctx.edge_w), ds.data_ptr(), _lib.stream()), 'gb_edge_softmax_bwd')
         dqk = torch.empty_like(qk)
-        _lib.check(lib.gb_edge_score_bwd(plan.c, ds.data_ptr(), qk.data_ptr(), a2, qk.data_ptr() + 4 * a, a2, heads, dk,
-                                         ctx.att_type, _lib.ptr(ctx.kparams), None, dqk.data_ptr(), a2,
-                                         dqk.data_ptr() + 4 * a, a2, None, None, _lib.stream()), 'gb_edge_score_bwd')
-        return dqk, None, None, None, None, None, None
+
+        def mh(c, scale=1.0):
+            """sum_{e in row i} c_eh k[col_e,h] -> dqk[:, :A], sum_{e in col j} c_eh q[row_e,h] -> dqk[:, A:]; the
+            kernels multiply by 1/sqrt(dk) (scaled_dot VJP), `scale` undoes it where the caller needs plain sums"""
+            c = _f32c(c * scale if scale != 1.0 else c)
+            _lib.check(lib.gb_edge_score_bwd(plan.c, c.data_ptr(), qk.data_ptr(), a2, qk.data_ptr() + 4 * a, a2, heads,
+                                             dk, _lib.GB_ATT['scaled_dot'], None, None, dqk.data_ptr(), a2,
+                                             dqk.data_ptr() + 4 * a, a2, None, None, _lib.stream()),
+                       'gb_edge_score_bwd')
+            return dqk[:, :a], dqk[:, a:]
+
+        if ctx.att_type == _lib.GB_ATT['scaled_dot']:
+            mh(ds)
+            return dqk, None, None, None, None, None, None
+        dq, dkk, dkparams = exp_kernel_score_vjp(ds, prods, qk[:, :a], qk[:, a:], kparams, plan.rowptr, plan.colptr,
+                                                 plan.tperm, heads, lambda c: mh(c, float(dk) ** 0.5))
+        return (torch.cat([dq, dkk], dim=1), None, None, None, None, None,
+                dkparams if ctx.needs_input_grad[6] else None)
 
 
 class DiffusionFn(torch.autograd.Function):

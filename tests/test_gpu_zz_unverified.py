@@ -152,3 +152,62 @@ def test_rmat_scale16_parity():
     bias_scale = max(float(rg[2].abs().max()), float(rg[4].abs().max()))
     for g, r, name in zip(grads, rg, ('gx', 'gwq', 'gbq', 'gwk', 'gbk', 'galpha', 'gbeta')):
         assert_close(g, r, G_RTOL, 'GRAND-nl ' + name, floor=bias_scale if name in ('gbq', 'gbk') else 0.0)
+
+
+@pytest.mark.parametrize('path', sorted(glob.glob(os.path.join(GOLD, 'ref_transformer_exp_kernel_*.npz'))))
+def test_exp_kernel_gradients_match_the_reference(path):
+    """training path of attention_type exp_kernel: projection -> edge softmax (exp_kernel forward kernel) -> SpMM,
+    backward through ops.exp_kernel_score_vjp over the multi-head SpMM kernels; incl. output_var / lengthscale"""
+    z = np.load(path)
+    n, d = z['x'].shape
+    opt = dict(BASE_OPT, attention_type='exp_kernel', attention_norm_idx=int(z['attention_norm_idx']), hidden_dim=d,
+               heads=int(z['heads']), attention_dim=int(z['wq'].shape[0]))
+    func = _func(opt, z)
+    L = func.multihead_att_layer
+    with torch.no_grad():
+        L.output_var.fill_(float(z['output_var']))
+        L.lengthscale.fill_(float(z['lengthscale']))
+    func.edge_index, func.x0 = dev(z['edge_index']), dev(z['x0'])
+    xg = dev(z['x']).requires_grad_(True)
+    out = func(0.0, xg)
+    params = [xg, func.alpha_train, func.beta_train, L.Q.weight, L.Q.bias, L.K.weight, L.K.bias, L.output_var,
+              L.lengthscale]
+    grads = torch.autograd.grad(out, params, dev(z['gout']))
+    assert_close(out, z['f'], F_RTOL, 'f')
+    keys = ('gx', 'galpha', 'gbeta', 'gwq', 'gbq', 'gwk', 'gbk', 'goutput_var', 'glengthscale')
+    for g, key in zip(grads, keys):
+        assert_close(g.reshape(-1), np.asarray(z[key]).reshape(-1), G_RTOL, key)
+
+
+def test_exp_kernel_gradients_on_a_graph_with_hub_segments():
+    import grand_b200
+    from helpers import rand_graph
+    n, d, heads, adim = 600, 32, 4, 32
+    ei = rand_graph(n, 5000, 21, hub=(5, 700))                    # > 256-edge row and column: long-segment kernels
+    rng = np.random.default_rng(4)
+    x, x0, gout = (0.5 * rng.standard_normal((n, d)).astype(np.float32) for _ in range(3))
+    z = dict(wq=rng.standard_normal((adim, d)).astype(np.float32) / np.sqrt(d), bq=0.1 * rng.standard_normal(adim).astype(np.float32),
+             wk=rng.standard_normal((adim, d)).astype(np.float32) / np.sqrt(d), bk=0.1 * rng.standard_normal(adim).astype(np.float32),
+             alpha_train=0.3, beta_train=0.1)
+    t64 = lambda a: torch.tensor(np.asarray(a), dtype=torch.float64)
+    for norm_idx in (0, 1):
+        opt = dict(BASE_OPT, attention_type='exp_kernel', attention_norm_idx=norm_idx, hidden_dim=d, heads=heads,
+                   attention_dim=adim)
+        func = _func(opt, z)
+        L = func.multihead_att_layer
+        with torch.no_grad():
+            L.output_var.fill_(1.2)
+            L.lengthscale.fill_(1.5)
+        func.edge_index, func.x0 = dev(ei), dev(x0)
+        xg = dev(x).requires_grad_(True)
+        out = func(0.0, xg)
+        grads = torch.autograd.grad(out, [xg, L.Q.weight, L.K.weight, L.output_var, L.lengthscale], dev(gout))
+        leaves = [t64(v).requires_grad_(True) for v in (x, z['wq'], z['bq'], z['wk'], z['bk'])]
+        ov, ls = t64(1.2).requires_grad_(True), t64(1.5).requires_grad_(True)
+        ref = funcs.transformer_f(leaves[0], torch.tensor(ei), leaves[1], leaves[2], leaves[3], leaves[4], heads,
+                                  t64(0.3), t64(0.1), t64(x0), attention_type='exp_kernel', attention_norm_idx=norm_idx,
+                                  output_var=ov, lengthscale=ls)
+        rg = torch.autograd.grad(ref, [leaves[0], leaves[1], leaves[3], ov, ls], t64(gout))
+        assert_close(out, ref, F_RTOL, f'f norm{norm_idx}')
+        for g, r, name in zip(grads, rg, ('gx', 'gwq', 'gwk', 'goutput_var', 'glengthscale')):
+            assert_close(g.reshape(-1), r.reshape(-1), G_RTOL, f'{name} norm{norm_idx}')
