@@ -376,6 +376,110 @@ def run_ours(args):
     emit(line)
 
 
+def eval_bytes(n, e, d, a, h):
+    """SURVEY.md 8d algorithmic bytes of ONE evaluation (not one kernel launch): GRAND-l / GRAND-nl, forward
+    evaluation and adjoint evaluation (f recomputed + VJP)"""
+    b_l = 8 * e + 12 * n * d + 4 * n
+    b_nl = 16 * n * d + 16 * n * a + 12 * e + 4 * n
+    return {'laplacian': {'forward': b_l, 'adjoint': 16 * e + 24 * n * d + 8 * n},
+            'transformer': {'forward': b_nl, 'adjoint': 2 * b_nl + 8 * e * h}}
+
+
+def run_microbench(args):
+    """--microbench: the isolated per-evaluation measurement of SURVEY.md 8d(i).  One forward evaluation
+    (`func(t, x)` under no_grad) and one adjoint evaluation (f + VJP: `func.eval_vjp`, or forward + autograd.grad
+    where the function has no fused form), each timed alone with CUDA events: `iters` (>= 100) calls after 10
+    warm-ups, once back to back (L2 hot: the state stays wherever the previous call left it) and once with L2
+    flushed before every call (a buffer of 2 x L2 size is overwritten; every call timed with its own event pair)."""
+    import grand_b200
+    from grand_b200 import synth, _lib
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    torch.cuda.set_device(local)
+    device = torch.device('cuda', local)
+    name = args.workload
+    cfg = dict(synth.CONFIGS[name])
+    ei, n = synth.make_graph(name, device)
+    data = grand_b200.GraphData()
+    data.new_graph(ei, n)
+    d = cfg['d']
+    gen = torch.Generator(device=device).manual_seed(99)
+    x = torch.randn(n, d, generator=gen, device=device)
+    g = torch.randn(n, d, generator=gen, device=device)
+    block = build_block(cfg, device)
+    block.reset_graph_data(data, x.dtype)
+    block.set_x0(x)
+    func = block.odefunc
+    if FUNCTION == 'laplacian' and block.opt['block'] == 'attention':
+        func.attention_weights = block.get_attention_weights(x)
+    e_prime = int(func.edge_index.shape[-1])
+    params = [p for p in func.parameters() if p.requires_grad]
+    t0 = torch.zeros((), device=device)
+    iters = max(100, args.steps)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)      # 2 x the 126 MB L2
+
+    def forward_eval():
+        with torch.no_grad():
+            return func(t0, x)
+
+    def adjoint_eval():
+        fused = getattr(func, 'eval_vjp', None)
+        res = fused(t0, x, g, params) if fused is not None else None
+        if res is not None:
+            return res
+        with torch.enable_grad():
+            xg = x.detach().requires_grad_(True)
+            f = func(t0, xg)
+            return f, torch.autograd.grad(f, [xg] + params, g, allow_unused=True)
+
+    def timed(fn):
+        for _ in range(10):
+            fn()
+        torch.cuda.synchronize()
+        l0 = _lib.launch_count()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(iters):
+            fn()
+        e.record()
+        torch.cuda.synchronize()
+        hot_ms = s.elapsed_time(e) / iters
+        launches = (_lib.launch_count() - l0) / iters
+        pairs = []
+        for i in range(iters):
+            flush.fill_(i & 0xff)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            pairs.append((a, b))
+        torch.cuda.synchronize()
+        cold = sorted(a.elapsed_time(b) for a, b in pairs)
+        return {'hot_ms': round(hot_ms, 4), 'flushed_ms': round(sum(cold) / iters, 4),
+                'flushed_ms_median': round(cold[iters // 2], 4), 'kernels_per_eval': round(launches, 1)}
+
+    func.nfe = 0
+    peak, peak_src = read_peaks()
+    with ClockSampler(local) as clocks:
+        out = {'forward': timed(forward_eval), 'adjoint': timed(adjoint_eval)}
+    eb = eval_bytes(n, e_prime, d, cfg['adim'], cfg['heads'])[FUNCTION]
+    for kind, r in out.items():
+        r['algorithmic_bytes'] = eb[kind]
+        for key in ('hot', 'flushed'):
+            gbs = eb[kind] / (r[key + '_ms'] * 1e-3) / 1e9
+            r[f'alg_GBps_{key}'] = round(gbs, 1)
+            r[f'frac_of_peak_{key}'] = round(gbs / peak, 4)
+            r[f'evals_per_s_{key}'] = round(1e3 / r[key + '_ms'], 2)
+    pair_ms = out['forward']['flushed_ms'] + out['adjoint']['flushed_ms']
+    emit({'metric': 'isolated ODE-func evaluations/sec (1 forward + 1 adjoint evaluation, L2 flushed)',
+          'value': round(2e3 / pair_ms, 3), 'unit': 'evals/s', 'n_gpus': 1, 'steps': iters, 'warmup': 10,
+          'ms_per_step': round(pair_ms, 4), 'higher_is_better': True, 'scaling': 'strong', 'vs_baseline': None,
+          'dtype': 'f32', 'data': 'synthetic',
+          'config': {'workload': f"{name}: {model_name()} ({cfg['desc']}), N={n}, E'={e_prime}, d={d}, "
+                                 f"heads={cfg['heads']}, attention_dim={cfg['adim']}, isolated evaluation microbench",
+                     'l2': 'both: back to back (hot) and a 256 MB buffer overwritten before every call (flushed)'},
+          'microbench': out, 'peak_GBps': peak, 'peak_source': peak_src, 'clocks': clocks.summary()})
+
+
 def run_partitioned(args, cfg, device, rank, world):
     """N > 1: the same training pass with the graph split by rows over the ranks (grand_b200/partition.py):
     one all-gather of the state per evaluation, one reduce-scatter of dL/dx per VJP, all over NCCL.  Total
@@ -731,6 +835,9 @@ def main():
                     help='skip the torch-CUDA-ops comparator (N = 1 only)')
     ap.add_argument('--function', default='transformer', choices=['transformer', 'laplacian'],
                     help='transformer = GRAND-nl (BASELINE.json headline); laplacian = GRAND-l sweep of config 5')
+    ap.add_argument('--microbench', action='store_true',
+                    help='isolated per-evaluation timing (SURVEY.md 8d): forward and adjoint evaluation alone, '
+                         'L2 hot and L2 flushed, >= 100 iterations; 1 GPU')
     ap.add_argument('--watchdog', type=int, default=1500,
                     help='seconds after which a still-running bench process kills itself (a rank stuck in a '
                          'collective must not hold the GPUs)')
@@ -749,6 +856,8 @@ def main():
         t.start()
     if args.impl == 'reference':
         run_reference(args)
+    elif args.microbench:
+        run_microbench(args)
     else:
         run_ours(args)
 

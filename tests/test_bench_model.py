@@ -46,3 +46,18 @@ def test_measured_traffic_table_is_readable():
     assert bench.measured_traffic('c4', 'fused_att_bwd_col') > 6e10
     assert bench.measured_traffic('c4', 'no_such_kernel') is None
     json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json')))
+
+
+def test_per_evaluation_bytes_match_the_survey():
+    """SURVEY.md 8d: C2 B_NL = 61.95 MB; C3 B_L = 206.5 MB, B_NL = 450.2 MB; C4 B_NL = 8.305 GB, B_L = 4.286 GB;
+    C5 B_L = 15.23 GB, B_NL = 37.85 GB; adjoint GRAND-l = 16E' + 24Nd + 8N (C5 30.5 GB)"""
+    c2 = bench.eval_bytes(n=19717, e=108365, d=128, a=64, h=4)
+    c3 = bench.eval_bytes(n=169343, e=1335586, d=96, a=64, h=4)
+    c4 = bench.eval_bytes(**C4)
+    c5 = bench.eval_bytes(**C5)
+    assert abs(c2['transformer']['forward'] / 1e6 - 61.95) < 0.01
+    assert abs(c3['laplacian']['forward'] / 1e6 - 206.5) < 0.1 and abs(c3['transformer']['forward'] / 1e6 - 450.2) < 0.1
+    assert abs(c4['transformer']['forward'] / 1e9 - 8.305) < 0.001 and abs(c4['laplacian']['forward'] / 1e9 - 4.286) < 0.001
+    assert abs(c5['laplacian']['forward'] / 1e9 - 15.23) < 0.01 and abs(c5['transformer']['forward'] / 1e9 - 37.85) < 0.01
+    assert abs(c5['laplacian']['adjoint'] / 1e9 - 30.5) < 0.1
+    assert c4['transformer']['adjoint'] == 2 * c4['transformer']['forward'] + 8 * C4['e'] * C4['h']
