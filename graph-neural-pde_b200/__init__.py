@@ -4,7 +4,7 @@ directory name `graph-neural-pde_b200` is not a Python identifier.
 
 Module names mirror the reference's `src/` files so a maintainer can swap imports one for one:
   base_classes, function_laplacian_diffusion, function_transformer_attention, block_constant,
-  block_transformer_attention, model_configurations, utils  (+ integrators: torchdiffeq-compatible
+  block_transformer_attention, block_mixed, block_transformer_hard_attention, model_configurations, utils  (+ integrators: torchdiffeq-compatible
   odeint / odeint_adjoint used when torchdiffeq is not installed).
 All device work goes through libgrandb200.so (csrc/, C ABI in include/grandb200.h).
 """
@@ -16,6 +16,8 @@ from .function_laplacian_diffusion import LaplacianODEFunc
 from .function_transformer_attention import ODEFuncTransformerAtt, SpGraphTransAttentionLayer
 from .block_constant import ConstantODEblock
 from .block_transformer_attention import AttODEblock
+from .block_mixed import MixedODEblock
+from .block_transformer_hard_attention import HardAttODEblock
 from .model_configurations import set_block, set_function
 from . import integrators
 from . import partition
@@ -25,5 +27,5 @@ from .integrators import odeint, odeint_adjoint
 
 __all__ = ['GraphPlan', 'get_plan', 'MaxNFEException', 'get_rw_adj', 'gcn_norm_fill_val',
            'add_remaining_self_loops', 'Meter', 'ODEFunc', 'ODEblock', 'GraphData', 'LaplacianODEFunc',
-           'ODEFuncTransformerAtt', 'SpGraphTransAttentionLayer', 'ConstantODEblock', 'AttODEblock',
+           'ODEFuncTransformerAtt', 'SpGraphTransAttentionLayer', 'ConstantODEblock', 'AttODEblock', 'MixedODEblock', 'HardAttODEblock',
            'set_block', 'set_function', 'partition', 'GraphedPass', 'RowPartition', 'Halo', 'LoopbackHalo', 'odeint', 'odeint_adjoint', 'integrators']

@@ -1,10 +1,12 @@
 """Mirror of the reference's src/model_configurations.py:17-44: the string -> class registry behind
-the `--block` and `--function` flags (src/graph_datasets/run_GNN.py:318-319).  Only the blocks and
-functions on the accelerated path are registered; the others raise, naming the key."""
+the `--block` and `--function` flags (src/graph_datasets/run_GNN.py:318-319).  Blocks: constant, attention, mixed, hard_attention; functions: laplacian, transformer.  The others
+(rewire_attention, GAT) raise, naming the key."""
 from .function_transformer_attention import ODEFuncTransformerAtt
 from .function_laplacian_diffusion import LaplacianODEFunc
 from .block_transformer_attention import AttODEblock
 from .block_constant import ConstantODEblock
+from .block_mixed import MixedODEblock
+from .block_transformer_hard_attention import HardAttODEblock
 
 
 class BlockNotDefined(Exception):
@@ -21,9 +23,13 @@ def set_block(opt):
         block = AttODEblock
     elif ode_str == 'constant':
         block = ConstantODEblock
-    elif ode_str in ('mixed', 'hard_attention', 'rewire_attention'):
-        raise NotImplementedError(f"block '{ode_str}' is outside the accelerated path (SURVEY.md 2.1); "
-                                  "its ODE function is served by LaplacianODEFunc unchanged")
+    elif ode_str == 'mixed':
+        block = MixedODEblock
+    elif ode_str == 'hard_attention':
+        block = HardAttODEblock
+    elif ode_str == 'rewire_attention':
+        raise NotImplementedError("block 'rewire_attention' (block_transformer_rewiring.py: kNN / GDC rewiring inside "
+                                  'the block) is outside the accelerated path (SURVEY.md 2.1)')
     else:
         raise BlockNotDefined
     return block

@@ -211,3 +211,112 @@ def test_exp_kernel_gradients_on_a_graph_with_hub_segments():
         assert_close(out, ref, F_RTOL, f'f norm{norm_idx}')
         for g, r, name in zip(grads, rg, ('gx', 'gwq', 'gwk', 'goutput_var', 'glengthscale')):
             assert_close(g.reshape(-1), r.reshape(-1), G_RTOL, f'{name} norm{norm_idx}')
+
+
+# ---- MixedODEblock / HardAttODEblock (host compositions over the verified kernels) ----------------------------
+BLOCK_OPT = {'hidden_dim': 16, 'block': 'mixed', 'function': 'laplacian', 'max_nfe': 10000, 'no_alpha_sigmoid': False,
+             'add_source': True, 'augment': False, 'adjoint': False, 'tol_scale': 1.0, 'tol_scale_adjoint': 1.0,
+             'data_norm': 'rw', 'self_loop_weight': 1.0, 'method': 'rk4', 'step_size': 1.0, 'max_iters': 100,
+             'adjoint_method': 'rk4', 'adjoint_step_size': 1.0, 'leaky_relu_slope': 0.2, 'heads': 4, 'attention_dim': 16,
+             'attention_norm_idx': 0, 'reweight_attention': False, 'beltrami': False, 'attention_type': 'scaled_dot',
+             'square_plus': False, 'mix_features': False, 'multi_modal': False, 'kinetic_energy': None,
+             'jacobian_norm2': None, 'total_deriv': None, 'directional_penalty': None, 'att_samp_pct': 0.6,
+             'use_flux': False}
+
+
+def _block(opt, n, e, T, seed):
+    import grand_b200
+    block = grand_b200.set_block(opt)(grand_b200.set_function(opt), [], opt, torch.device('cuda'),
+                                      t=torch.tensor([0., T])).cuda()
+    ei = og.shaped_graph(n, e, seed)
+    data = grand_b200.GraphData()
+    data.new_graph(dev(ei), n)
+    g = torch.Generator().manual_seed(seed)
+    with torch.no_grad():
+        L = block.multihead_att_layer
+        for lin in (L.Q, L.K):
+            lin.weight.copy_((torch.randn(lin.weight.shape, generator=g) / lin.weight.shape[1] ** 0.5).cuda())
+            lin.bias.copy_((0.1 * torch.randn(lin.bias.shape, generator=g)).cuda())
+        block.odefunc.alpha_train.fill_(0.4)
+        block.odefunc.beta_train.fill_(0.2)
+    return block, data, ei
+
+
+def _t64(a):
+    return torch.tensor(np.asarray(a.detach().cpu() if torch.is_tensor(a) else a), dtype=torch.float64)
+
+
+def test_mixed_block_state_and_gradients_incl_the_gate():
+    from oracle import integrate as oint
+    n, e, d, T = 250, 1500, 16, 2.0
+    block, data, ei = _block(dict(BLOCK_OPT), n, e, T, 4)
+    block.train()
+    with torch.no_grad():
+        block.gamma.fill_(0.3)
+    x = torch.randn(n, d, device='cuda', requires_grad=True)
+    gout = torch.randn(n, d, device='cuda')
+    block.set_x0(x)
+    z = block(x, data)
+    B = block.multihead_att_layer
+    params = [x, B.Q.weight, B.K.weight, block.gamma, block.odefunc.alpha_train]
+    grads = torch.autograd.grad(z, params, gout)
+    ei_n, w = og.reset_graph_data(ei, None, n, 'rw', 1.0)
+    eit = torch.tensor(ei_n)
+    leaves = [_t64(p).requires_grad_(True) for p in params]
+    att, _ = funcs.attention_layer(leaves[0], eit, leaves[1], _t64(B.Q.bias), leaves[2], _t64(B.K.bias), 4)
+    gate = torch.sigmoid(leaves[3])
+    mixed = att.mean(1) * (1 - gate) + _t64(w) * gate
+    x0 = _t64(x)
+    f = lambda t, y: funcs.laplacian_f(y, eit, mixed, leaves[4], _t64(0.2), x0)
+    zo = oint.odeint(f, leaves[0], [0., T], 'rk4', 1.0)[1]
+    ro = torch.autograd.grad(zo, leaves, _t64(gout))
+    assert_close(z, zo, 1e-4, 'z(T)')
+    for g, r, name in zip(grads, ro, ('gx', 'gwq', 'gwk', 'ggamma', 'galpha')):
+        assert_close(g.reshape(-1), r.reshape(-1), 1e-4, name)
+
+
+@pytest.mark.parametrize('function', ['laplacian', 'transformer'])
+def test_hard_attention_block_samples_edges_while_training(function, capsys):
+    from oracle import integrate as oint
+    n, e, d, T = 300, 2400, 16, 2.0
+    opt = dict(BLOCK_OPT, block='hard_attention', function=function)
+    import grand_b200
+    block = grand_b200.set_block(opt)(grand_b200.set_function(opt), [], opt, torch.device('cuda'),
+                                      t=torch.tensor([0., T])).cuda()
+    ei = og.shaped_graph(n, e, 9)
+    data = grand_b200.GraphData()
+    data.new_graph(dev(ei), n)
+    L = block.multihead_att_layer if function == 'laplacian' else block.odefunc.multihead_att_layer
+    g = torch.Generator().manual_seed(2)
+    with torch.no_grad():
+        for lin in (L.Q, L.K):
+            lin.weight.copy_((torch.randn(lin.weight.shape, generator=g) / 4.0).cuda())
+        block.odefunc.alpha_train.fill_(0.4)
+        block.odefunc.beta_train.fill_(0.2)
+    x = torch.randn(n, d, device='cuda')
+    block.set_x0(x)
+    block.train()
+    z = block(x, data)
+    func = block.odefunc
+    e_full = int(block.data_edge_index.shape[-1])
+    kept = func.edge_index[0] if func.edge_index.dim() == 3 else func.edge_index
+    assert abs(int(kept.shape[1]) - 0.6 * e_full) <= 2
+    assert 'retaining' in capsys.readouterr().out
+    w = func.attention_weights.reshape(-1)
+    sums = torch.zeros(n, device='cuda').index_add_(0, kept[0], w)
+    present = torch.zeros(n, dtype=torch.bool, device='cuda')
+    present[kept[0]] = True
+    assert_close(sums[present], torch.ones(int(present.sum())), 1e-5, 'kept rows sum to one')
+    eit = kept.cpu()
+    x0 = _t64(x)
+    if function == 'laplacian':
+        f = lambda t, y: funcs.laplacian_f(y, eit, _t64(w), _t64(0.4), _t64(0.2), x0)
+    else:
+        f = lambda t, y: funcs.transformer_f(y, eit, _t64(L.Q.weight), _t64(L.Q.bias), _t64(L.K.weight), _t64(L.K.bias), 4,
+                                             _t64(0.4), _t64(0.2), x0)
+    zo = oint.odeint(f, _t64(x), [0., T], 'rk4', 1.0)[1]
+    assert_close(z, zo, 1e-4, 'z(T) on the sampled graph')
+    block.eval()                                                  # eval mode: the full graph, head-mean attention
+    with torch.no_grad():
+        z_eval = block(x, data)
+    assert func.edge_index.shape[-1] == e_full and z_eval.shape == x.shape
