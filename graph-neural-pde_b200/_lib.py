@@ -10,7 +10,8 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libgrandb200.so')
+# GRANDB200_LIB: load a tuning variant (csrc/Makefile `variant`, scripts/sweep_variants.py) instead of the default build
+LIB_PATH = os.environ.get('GRANDB200_LIB') or os.path.join(_HERE, 'libgrandb200.so')
 HEADER_PATH = os.path.join(_HERE, '..', 'include', 'grandb200.h')
 
 GB_ATT = {'scaled_dot': 0, 'cosine_sim': 1, 'pearson': 2, 'exp_kernel': 3}

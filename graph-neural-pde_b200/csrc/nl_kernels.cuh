@@ -19,7 +19,7 @@
 //             raw scores / dabar are parked per edge and turned into ds[e,h] = att (dabar/H - dot_h) and
 //             abar[e] in a coalesced second sweep over the row's own slots (no gather).
 //
-// Work decomposition: persistent CTAs of 8 warps, Wk staged once per CTA in shared memory, rows handed out
+// Work decomposition: persistent CTAs of 8 warps (GB_NL_WARPS_FWD / _ADJ), Wk staged once per CTA in shared memory, rows handed out
 // by a dynamic (integer atomic) scheduler in chunks; a warp owns a row; XL lanes span the d columns
 // (128-bit chunks), 32/XL edge groups run side by side, each lane keeps U gathers in flight.  Per-head dot
 // products are reduced with a transposing butterfly (31 shuffles for 32 values).  Rows longer than the plan's
@@ -37,9 +37,25 @@
 
 namespace gb {
 
-constexpr int kNlWarps = 8;
-constexpr int kNlThreads = kNlWarps * 32;
-constexpr int kNlChunkRows = 4;          // rows per scheduler grab
+// GB_NL_* are the compile-time tuning knobs of these kernels; csrc/Makefile's `variant` target builds a library per
+// setting (scripts/sweep_variants.py runs them side by side on the GPU).  The defaults are the measured optimum.
+#ifndef GB_NL_WARPS
+#define GB_NL_WARPS 8
+#endif
+#ifndef GB_NL_WARPS_FWD
+#define GB_NL_WARPS_FWD GB_NL_WARPS
+#endif
+#ifndef GB_NL_WARPS_ADJ
+#define GB_NL_WARPS_ADJ GB_NL_WARPS
+#endif
+#ifndef GB_NL_CHUNK_ROWS
+#define GB_NL_CHUNK_ROWS 4
+#endif
+template <bool ADJ> constexpr int kNlWarpsOf = ADJ ? GB_NL_WARPS_ADJ : GB_NL_WARPS_FWD;   // warps per CTA
+constexpr int kNlChunkRows = GB_NL_CHUNK_ROWS;   // rows per scheduler grab (<= 31: one lane per row pointer)
+static_assert(kNlChunkRows >= 1 && kNlChunkRows <= 31, "a chunk's row pointers are loaded by one warp instruction");
+static_assert(kNlWarpsOf<false> >= 4 && kNlWarpsOf<false> <= 32 && kNlWarpsOf<true> >= 4 && kNlWarpsOf<true> <= 32,
+              "CTA-wide hub rows park [W][3][H] statistics in the q slots of warps 1.. ((W-1) A floats, dk >= 4)");
 // Tuning knobs (measured on the ogbn-products shape, profiles/r01zi, r01zj): the forward kernel keeps 4 gathers in
 // flight per lane group and fits 80 registers -> 3 CTAs (24 warps) per SM, 3 % faster than 8 gathers at 2 CTAs;
 // the adjoint kernel carries twice the accumulators: 8 gathers at 2 CTAs (125 registers); 4 gathers at 3 CTAs
@@ -457,8 +473,9 @@ __device__ __forceinline__ void nl_sweep_ds(const NlArgs& a, int start, int end,
 // shared-memory layout of both kernels: [A][ldw] staged Wk | per-warp q [W][A] | per-warp u [W][H][4*XL]
 __host__ __device__ inline int nl_ldw(int dv) { return 4 * dv + 4; }
 
-template <int XL, int H>
+template <int XL, int H, bool ADJ>
 inline size_t nl_smem_rows(int adim, int dv) {
+  constexpr int kNlWarps = kNlWarpsOf<ADJ>;
   return sizeof(float) * ((size_t)adim * nl_ldw(dv) + (size_t)kNlWarps * adim + (size_t)kNlWarps * H * 4 * XL);
 }
 __device__ __forceinline__ void nl_stage_wk(const NlArgs& a, float* wk_s, int ldw) {
@@ -476,6 +493,7 @@ __device__ __forceinline__ void nl_stage_wk(const NlArgs& a, float* wk_s, int ld
 template <int XL, int H, bool ADJ>
 __device__ __forceinline__ void nl_long_row(const NlArgs& a, int row, float* wk_s, int ldw, float alpha, float beta) {
   using Row = NlRow<XL, H, ADJ>;
+  constexpr int kNlWarps = kNlWarpsOf<ADJ>;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float* q_s = wk_s + (size_t)a.adim * ldw;                                    // warp 0's q slot
   float* pst = q_s + a.adim;                                                   // [W][3][H]
@@ -561,9 +579,10 @@ __device__ __forceinline__ void nl_long_row(const NlArgs& a, int row, float* wk_
 
 // persistent kernel: warps pull chunks of rows from an atomic counter
 template <int XL, int H, bool ADJ>
-__global__ void __launch_bounds__(kNlThreads, ADJ ? kNlCtasAdj : kNlCtasFwd) nl_rows_kernel(const NlArgs a) {
+__global__ void __launch_bounds__(kNlWarpsOf<ADJ> * 32, ADJ ? kNlCtasAdj : kNlCtasFwd) nl_rows_kernel(const NlArgs a) {
   extern __shared__ __align__(16) float smem[];
   using Row = NlRow<XL, H, ADJ>;
+  constexpr int kNlWarps = kNlWarpsOf<ADJ>;
   const int ldw = nl_ldw(a.dv);
   float* wk_s = smem;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -626,7 +645,8 @@ __global__ void __launch_bounds__(kNlThreads, ADJ ? kNlCtasAdj : kNlCtasFwd) nl_
 template <int XL, int H, bool ADJ>
 int nl_launch(NlArgs a, int n_long, cudaStream_t stream) {
   static bool configured = false;
-  const size_t smem = nl_smem_rows<XL, H>(a.adim, a.dv);
+  constexpr int kNlWarps = kNlWarpsOf<ADJ>;
+  const size_t smem = nl_smem_rows<XL, H, ADJ>(a.adim, a.dv);
   if (smem > kNlSmemLimit) {
     set_error("nl kernels: attention_dim x d too large for shared memory (%zu bytes)", smem);
     return GB_ERR_UNSUPPORTED;
@@ -643,7 +663,7 @@ int nl_launch(NlArgs a, int n_long, cudaStream_t stream) {
   const int blocks = min_int(want, (ADJ ? kNlCtasAdj : kNlCtasFwd) * sm_count());
   {
     LaunchScope ls(ADJ ? K_NL_ADJ_ROWS : K_NL_FWD, stream);
-    nl_rows_kernel<XL, H, ADJ><<<blocks, kNlThreads, smem, stream>>>(a);
+    nl_rows_kernel<XL, H, ADJ><<<blocks, kNlWarps * 32, smem, stream>>>(a);
   }
   return check_launch("nl_rows_kernel");
 }
