@@ -42,8 +42,15 @@ def assert_close(got, ref, rtol, what='', floor=0.0):
     assert worst <= 1.0, f'{what}: max err {float(err.max()):.3e} at scale {scale:.3e} exceeds rtol {rtol} by x{worst:.2f}'
 
 
+DEVICE = 'cuda'      # tests/test_host_plumbing_cpu.py sets 'cpu' while the emulated ABI is installed
+
+
+def device():
+    return torch.device(DEVICE)
+
+
 def dev(a, dtype=None):
     t = torch.as_tensor(np.asarray(a))
     if dtype is not None:
         t = t.to(dtype)
-    return t.cuda()
+    return t.to(DEVICE)

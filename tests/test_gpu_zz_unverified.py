@@ -10,7 +10,7 @@ import pytest
 import torch
 
 from oracle import funcs, graph as og
-from helpers import assert_close, dev
+from helpers import assert_close, dev, device
 
 pytestmark = [pytest.mark.gpu,
               pytest.mark.skipif(os.environ.get('GB_UNVERIFIED') != '1',
@@ -27,7 +27,7 @@ BASE_OPT = {'leaky_relu_slope': 0.2, 'heads': 2, 'attention_dim': 8, 'attention_
 def _func(opt, z):
     import grand_b200
     d = int(opt['hidden_dim'])
-    func = grand_b200.ODEFuncTransformerAtt(d, d, opt, torch.device('cuda')).cuda()
+    func = grand_b200.ODEFuncTransformerAtt(d, d, opt, device()).to(device())
     L = func.multihead_att_layer
     with torch.no_grad():
         for lin, w, b in ((L.Q, 'wq', 'bq'), (L.K, 'wk', 'bk')):
@@ -119,7 +119,7 @@ def test_rmat_scale16_parity():
     eit = torch.tensor(ei)
     # GRAND-l
     lopt = dict(BASE_OPT, function='laplacian', block='constant', hidden_dim=d)
-    lf = grand_b200.LaplacianODEFunc(d, d, lopt, torch.device('cuda')).cuda()
+    lf = grand_b200.LaplacianODEFunc(d, d, lopt, device()).to(device())
     with torch.no_grad():
         lf.alpha_train.fill_(0.3)
         lf.beta_train.fill_(0.1)
@@ -226,8 +226,8 @@ BLOCK_OPT = {'hidden_dim': 16, 'block': 'mixed', 'function': 'laplacian', 'max_n
 
 def _block(opt, n, e, T, seed):
     import grand_b200
-    block = grand_b200.set_block(opt)(grand_b200.set_function(opt), [], opt, torch.device('cuda'),
-                                      t=torch.tensor([0., T])).cuda()
+    block = grand_b200.set_block(opt)(grand_b200.set_function(opt), [], opt, device(),
+                                      t=torch.tensor([0., T])).to(device())
     ei = og.shaped_graph(n, e, seed)
     data = grand_b200.GraphData()
     data.new_graph(dev(ei), n)
@@ -235,8 +235,8 @@ def _block(opt, n, e, T, seed):
     with torch.no_grad():
         L = block.multihead_att_layer
         for lin in (L.Q, L.K):
-            lin.weight.copy_((torch.randn(lin.weight.shape, generator=g) / lin.weight.shape[1] ** 0.5).cuda())
-            lin.bias.copy_((0.1 * torch.randn(lin.bias.shape, generator=g)).cuda())
+            lin.weight.copy_((torch.randn(lin.weight.shape, generator=g) / lin.weight.shape[1] ** 0.5).to(device()))
+            lin.bias.copy_((0.1 * torch.randn(lin.bias.shape, generator=g)).to(device()))
         block.odefunc.alpha_train.fill_(0.4)
         block.odefunc.beta_train.fill_(0.2)
     return block, data, ei
@@ -253,8 +253,8 @@ def test_mixed_block_state_and_gradients_incl_the_gate():
     block.train()
     with torch.no_grad():
         block.gamma.fill_(0.3)
-    x = torch.randn(n, d, device='cuda', requires_grad=True)
-    gout = torch.randn(n, d, device='cuda')
+    x = torch.randn(n, d, device=device(), requires_grad=True)
+    gout = torch.randn(n, d, device=device())
     block.set_x0(x)
     z = block(x, data)
     B = block.multihead_att_layer
@@ -281,8 +281,8 @@ def test_hard_attention_block_samples_edges_while_training(function, capsys):
     n, e, d, T = 300, 2400, 16, 2.0
     opt = dict(BLOCK_OPT, block='hard_attention', function=function)
     import grand_b200
-    block = grand_b200.set_block(opt)(grand_b200.set_function(opt), [], opt, torch.device('cuda'),
-                                      t=torch.tensor([0., T])).cuda()
+    block = grand_b200.set_block(opt)(grand_b200.set_function(opt), [], opt, device(),
+                                      t=torch.tensor([0., T])).to(device())
     ei = og.shaped_graph(n, e, 9)
     data = grand_b200.GraphData()
     data.new_graph(dev(ei), n)
@@ -290,10 +290,10 @@ def test_hard_attention_block_samples_edges_while_training(function, capsys):
     g = torch.Generator().manual_seed(2)
     with torch.no_grad():
         for lin in (L.Q, L.K):
-            lin.weight.copy_((torch.randn(lin.weight.shape, generator=g) / 4.0).cuda())
+            lin.weight.copy_((torch.randn(lin.weight.shape, generator=g) / 4.0).to(device()))
         block.odefunc.alpha_train.fill_(0.4)
         block.odefunc.beta_train.fill_(0.2)
-    x = torch.randn(n, d, device='cuda')
+    x = torch.randn(n, d, device=device())
     block.set_x0(x)
     block.train()
     z = block(x, data)
@@ -303,8 +303,8 @@ def test_hard_attention_block_samples_edges_while_training(function, capsys):
     assert abs(int(kept.shape[1]) - 0.6 * e_full) <= 2
     assert 'retaining' in capsys.readouterr().out
     w = func.attention_weights.reshape(-1)
-    sums = torch.zeros(n, device='cuda').index_add_(0, kept[0], w)
-    present = torch.zeros(n, dtype=torch.bool, device='cuda')
+    sums = torch.zeros(n, device=device()).index_add_(0, kept[0], w)
+    present = torch.zeros(n, dtype=torch.bool, device=device())
     present[kept[0]] = True
     assert_close(sums[present], torch.ones(int(present.sum())), 1e-5, 'kept rows sum to one')
     eit = kept.cpu()
