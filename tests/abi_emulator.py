@@ -243,9 +243,6 @@ class Emulator:
     def gb_att_fused_supported(self, q, ldq, k, ldk, heads, dk, x, ldx, d):
         return 0                                 # the warp-per-row fused kernels are not emulated: composite route
 
-    def gb_nl_supported(self, heads, dk, d):
-        return 0                                 # nor are the single-gather kernels
-
     def gb_nl_workspace_bytes(self):
         return 16
 
@@ -307,4 +304,126 @@ class Emulator:
         np.add.at(gk, G.colidx, DS * Q[G.rows])
         f32(dq, G.n, a, lddq)[:] = gq.reshape(G.n, a)
         f32(dk_out, G.n, a, lddk)[:] = gk.reshape(G.n, a)
+        return 0
+
+    # ---- row-range forms (1-D row partition) and the single-gather GRAND-nl entry points ------------------------
+    # Matrices indexed by the row (q, x0, out, gout, dq) arrive as "virtual" base pointers (slab pointer minus
+    # lo * ld floats, partition._virt): only rows [lo, hi) may be touched.  x is indexed by global column id.
+    @staticmethod
+    def _rows(ptr, lo, hi, cols, ld):
+        return f32(_p(ptr) + 4 * lo * ld, hi - lo, cols, ld)
+
+    nl_enabled = False                            # tests flip this to route evaluations to gb_nl_fwd / gb_nl_adjoint
+
+    def gb_nl_supported(self, heads, dk, d):
+        return int(self.nl_enabled and heads in (1, 2, 4, 8) and dk % 4 == 0 and d % 4 == 0 and d <= 128)
+
+    def gb_spmm_fwd_part(self, g, lo, hi, vals, x, ldx, x0, ldx0, alpha_train, alpha_sigmoid, beta_train, d, out, ldo,
+                         stage, stream):
+        self._note('gb_spmm_fwd_part')
+        G = Graph(g)
+        X = f32(x, G.n, d, ldx).astype(np.float64)
+        ax = np.zeros((G.n, d))
+        np.add.at(ax, G.rows, vec(vals, G.e).astype(np.float64)[:, None] * X[G.colidx])
+        f = _alpha(alpha_train, alpha_sigmoid) * (ax - X)[lo:hi]
+        if _p(x0) and _p(beta_train):
+            f = f + scalar(beta_train) * self._rows(x0, lo, hi, d, ldx0)
+        self._rows(out, lo, hi, d, ldo)[:] = f
+        return 0
+
+    def gb_spmm_bwd_part(self, g, own_lo, own_hi, vals, gout, ldg, x, ldx, x0, ldx0, alpha_train, alpha_sigmoid, d, dx,
+                         lddx, accumulate, partials, dparams, stream):
+        self._note('gb_spmm_bwd_part')
+        G = Graph(g)
+        if own_lo == 0 and own_hi == 0:
+            own_lo, own_hi = 0, G.n
+        own_hi = max(own_hi, own_lo)              # (lo, -1): a rank that owns no rows
+        go = np.zeros((G.n, d))
+        go[own_lo:own_hi] = self._rows(gout, own_lo, own_hi, d, ldg)      # a rank's edges only touch its rows of g
+        t = np.zeros((G.n, d))
+        np.add.at(t, G.colidx, vec(vals, G.e).astype(np.float64)[:, None] * go[G.rows])
+        t[own_lo:own_hi] -= go[own_lo:own_hi]
+        alpha = _alpha(alpha_train, alpha_sigmoid)
+        dxv = f32(dx, G.n, d, lddx)
+        dxv[:] = (dxv if accumulate else 0) + alpha * t
+        if _p(dparams):
+            dp = vec(dparams, 2)
+            dp[0] = (alpha * (1 - alpha) if alpha_sigmoid else 1.0) * float((f32(x, G.n, d, ldx) * t).sum())
+            dp[1] = float((go[own_lo:own_hi] * self._rows(x0, own_lo, own_hi, d, ldx0)).sum()) if _p(x0) else 0.0
+        return 0
+
+    def gb_att_bwd_fused_partials(self, g):
+        return 4
+
+    def _nl_attention(self, G, lo, hi, x, ldx, q, ldq, wk, ldwk, heads, dk, d):
+        """row-softmax scaled_dot attention of the plan's edges with k = Wk x (the bias cancels in the row softmax)"""
+        a = heads * dk
+        X = f32(x, G.n, d, ldx).astype(np.float64)
+        Q = np.zeros((G.n, a))
+        Q[lo:hi] = self._rows(q, lo, hi, a, ldq)
+        K = X @ f32(wk, a, d, ldwk).astype(np.float64).T
+        s = (Q.reshape(G.n, heads, dk)[G.rows] * K.reshape(G.n, heads, dk)[G.colidx]).sum(axis=2) / math.sqrt(dk)
+        m = np.full((G.n, heads), -np.inf)
+        np.maximum.at(m, G.rows, s)
+        p = np.exp(s - m[G.rows])
+        den = np.zeros((G.n, heads))
+        np.add.at(den, G.rows, p)
+        return X, Q, K, p / den[G.rows]
+
+    def gb_nl_fwd(self, g, lo, hi, x, ldx, q, ldq, wk, ldwk, heads, dk, d, x0, ldx0, alpha_train, alpha_sigmoid,
+                  beta_train, out, ldo, stage, workspace, stream):
+        self._note('gb_nl_fwd')
+        if stage is not None:
+            return self._fail('emulator: Runge-Kutta stage fusion is not emulated')
+        G = Graph(g)
+        X, _, _, att = self._nl_attention(G, lo, hi, x, ldx, q, ldq, wk, ldwk, heads, dk, d)
+        ax = np.zeros((G.n, d))
+        np.add.at(ax, G.rows, att.mean(axis=1)[:, None] * X[G.colidx])
+        f = _alpha(alpha_train, alpha_sigmoid) * (ax - X)[lo:hi]
+        if _p(x0) and _p(beta_train):
+            f = f + scalar(beta_train) * self._rows(x0, lo, hi, d, ldx0)
+        self._rows(out, lo, hi, d, ldo)[:] = f
+        return 0
+
+    def gb_nl_adjoint(self, g, lo, hi, x, ldx, q, ldq, wk, ldwk, heads, dk, d, x0, ldx0, alpha_train, alpha_sigmoid,
+                      beta_train, gout, ldg, out, ldo, ds, dabar, abar, dq, lddq, dk_out, lddk, dx, lddx, partials,
+                      dparams, workspace, stream):
+        self._note('gb_nl_adjoint')
+        G = Graph(g)
+        a = heads * dk
+        X, Q, K, att = self._nl_attention(G, lo, hi, x, ldx, q, ldq, wk, ldwk, heads, dk, d)
+        alpha = _alpha(alpha_train, alpha_sigmoid)
+        ab = att.mean(axis=1)
+        if _p(out):
+            ax = np.zeros((G.n, d))
+            np.add.at(ax, G.rows, ab[:, None] * X[G.colidx])
+            f = alpha * (ax - X)[lo:hi]
+            if _p(x0) and _p(beta_train):
+                f = f + scalar(beta_train) * self._rows(x0, lo, hi, d, ldx0)
+            self._rows(out, lo, hi, d, ldo)[:] = f
+        go = np.zeros((G.n, d))
+        go[lo:hi] = self._rows(gout, lo, hi, d, ldg)
+        dab = alpha * (go[G.rows] * X[G.colidx]).sum(axis=1)
+        da = dab[:, None] / heads
+        inner = np.zeros((G.n, heads))
+        np.add.at(inner, G.rows, att * da)
+        dsv = att * (da - inner[G.rows])
+        f32(ds, G.e, heads)[:] = dsv
+        vec(abar, G.e)[:] = ab
+        if _p(dabar):
+            vec(dabar, G.e)[:] = dab
+        w = dsv[:, :, None] / math.sqrt(dk)
+        gq, gk = np.zeros((G.n, heads, dk)), np.zeros((G.n, heads, dk))
+        np.add.at(gq, G.rows, w * K.reshape(G.n, heads, dk)[G.colidx])
+        np.add.at(gk, G.colidx, w * Q.reshape(G.n, heads, dk)[G.rows])
+        self._rows(dq, lo, hi, a, lddq)[:] = gq.reshape(G.n, a)[lo:hi]
+        f32(dk_out, G.n, a, lddk)[:] = gk.reshape(G.n, a)
+        t = np.zeros((G.n, d))
+        np.add.at(t, G.colidx, ab[:, None] * go[G.rows])
+        t[lo:hi] -= go[lo:hi]
+        f32(dx, G.n, d, lddx)[:] = alpha * t
+        if _p(dparams):
+            dp = vec(dparams, 2)
+            dp[0] = (alpha * (1 - alpha) if alpha_sigmoid else 1.0) * float((X * t).sum())
+            dp[1] = float((go[lo:hi] * self._rows(x0, lo, hi, d, ldx0)).sum()) if _p(x0) else 0.0
         return 0
