@@ -537,7 +537,7 @@ def run_partitioned(args, cfg, device, rank, world):
         return float(ms), out
 
     launches0 = _lib.launch_count()
-    halo.bytes_in = halo.n_gathers = halo.n_scatters = 0
+    halo.bytes_in = halo.n_gathers = halo.n_scatters = halo.n_prefetched = 0
 
     def loop():
         tot = 0
@@ -604,15 +604,18 @@ def run_partitioned(args, cfg, device, rank, world):
                                f"T={T_END}, odeint_adjoint (rk4)",
                    'parallelism': f'1-D row partition over {world} GPUs ({part.slab} rows each), all-gather of the '
                                   f'state per evaluation + reduce-scatter of dL/dx per VJP (NCCL)',
-                   'evals_per_step': evals, 'l2': 'inputs larger than L2 (no flush)'},
+                   'evals_per_step': evals, 'l2': 'inputs larger than L2 (no flush)',
+                   'overlapped_exchange': os.environ.get('GRANDB200_OVERLAP') == '1'},
         'e2e': {'value': round(evals_e2e / (ms_e2e * 1e-3), 3), 'unit': 'evals/s',
                 'h2d_bytes_per_step': world * part.slab * d * 4, 'd2h_bytes_per_step': world * (part.slab * d * 4 + 4),
                 'ms_per_step': round(ms_e2e / args.steps, 3)},
         'gpu_launches': int(launches), 'clocks': clocks.summary(), 'roofline': roofline,
         'nvlink': {'bytes_in_per_rank_per_step': halo_bytes // args.steps,
                    'GBps_in_per_rank_if_serial': round(halo_bytes / (ms * 1e-3) / 1e9, 1), 'peak_GBps': 770.0,
-                   'note': 'received bytes of the all-gathers / reduce-scatters divided by the WHOLE step time '
-                           '(the exchanges are not overlapped with compute yet)'},
+                   'prefetched_gathers_per_step': getattr(halo, 'n_prefetched', 0) // args.steps,
+                   'note': 'received bytes of the all-gathers / reduce-scatters divided by the WHOLE step time; with '
+                           'GRANDB200_OVERLAP=1 the all-gather of the next adjoint stage runs under the column pass of '
+                           'the current one (prefetched_gathers_per_step of them), otherwise exchanges are serial'},
     }
     line['nvlink'].update(exchange)
     emit(line)

@@ -88,6 +88,9 @@ SIGNATURES = {
                             _P, _I32, C.POINTER(GbStage), _P, _P]),
     'gb_nl_adjoint': (C.c_int, [_G, _I32, _I32, _P, _I32, _P, _I32, _P, _I32, _I32, _I32, _I32, _P, _I32, _P, _I32,
                                 _P, _P, _I32, _P, _I32, _P, _P, _P, _P, _I32, _P, _I32, _P, _I32, _P, _P, _P, _P]),
+    'gb_nl_adjoint_phase': (C.c_int, [_G, _I32, _I32, _P, _I32, _P, _I32, _P, _I32, _I32, _I32, _I32, _P, _I32, _P,
+                                      _I32, _P, _P, _I32, _P, _I32, _P, _P, _P, _P, _I32, _P, _I32, _P, _I32, _P, _P, _P,
+                                      _I32, _P]),
     'gb_edge_score_bwd': (C.c_int, [_G, _P, _P, _I32, _P, _I32, _I32, _I32, _I32, _P, _P, _P, _I32, _P, _I32, _P, _P, _P]),
 }
 

@@ -682,7 +682,21 @@ int gb_nl_adjoint(const gb_graph* g, int32_t row_lo, int32_t row_hi, const float
                   const float* gout, int32_t ldg, float* out, int32_t ldo, float* ds, float* dabar_scratch,
                   float* abar, float* dq, int32_t lddq, float* dk_out, int32_t lddk, float* dx, int32_t lddx,
                   float* partials, float* dparams, void* workspace, void* stream_) {
+  return gb_nl_adjoint_phase(g, row_lo, row_hi, x, ldx, q, ldq, wk, ldwk, heads, dk, d, x0, ldx0, alpha_train,
+                             alpha_sigmoid, beta_train, gout, ldg, out, ldo, ds, dabar_scratch, abar, dq, lddq, dk_out,
+                             lddk, dx, lddx, partials, dparams, workspace, GB_NL_PHASE_BOTH, stream_);
+}
+
+int gb_nl_adjoint_phase(const gb_graph* g, int32_t row_lo, int32_t row_hi, const float* x, int32_t ldx, const float* q,
+                        int32_t ldq, const float* wk, int32_t ldwk, int32_t heads, int32_t dk, int32_t d,
+                        const float* x0, int32_t ldx0, const float* alpha_train, int32_t alpha_sigmoid,
+                        const float* beta_train, const float* gout, int32_t ldg, float* out, int32_t ldo, float* ds,
+                        float* dabar_scratch, float* abar, float* dq, int32_t lddq, float* dk_out, int32_t lddk,
+                        float* dx, int32_t lddx, float* partials, float* dparams, void* workspace, int32_t phase,
+                        void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
+  GB_REQUIRE(phase == GB_NL_PHASE_BOTH || phase == GB_NL_PHASE_ROWS || phase == GB_NL_PHASE_COLS,
+             "gb_nl_adjoint_phase: bad phase");
   NlArgs a;
   if (int rc = nl_fill_args(a, g, row_lo, row_hi, x, ldx, q, ldq, wk, ldwk, heads, dk, d, x0, ldx0, alpha_train,
                             alpha_sigmoid, beta_train, out, ldo, nullptr, workspace, "gb_nl_adjoint"))
@@ -701,7 +715,10 @@ int gb_nl_adjoint(const gb_graph* g, int32_t row_lo, int32_t row_hi, const float
   a.write_f = out != nullptr;
   a.g = gout; a.ldg = ldg; a.ds = ds; a.dabar = dabar_scratch; a.abar = abar; a.dq = dq; a.lddq = lddq;
   // rows: evaluation + SDDMM + softmax backward + dq in one gather pass
-  if (int rc = nl_dispatch_adj(a, heads, use_long ? g->n_long_rows : 0, stream)) return rc;
+  if (phase != GB_NL_PHASE_COLS) {
+    if (int rc = nl_dispatch_adj(a, heads, use_long ? g->n_long_rows : 0, stream)) return rc;
+  }
+  if (phase == GB_NL_PHASE_ROWS) return GB_OK;
 
   // columns: transpose SpMM (dx, dalpha / dbeta partial sums) + dk over the edges this rank holds
   const bool part = !(row_lo == 0 && row_hi == g->n);

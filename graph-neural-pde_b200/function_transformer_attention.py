@@ -253,6 +253,75 @@ class ODEFuncTransformerAtt(ODEFunc):
             out.append(g)
         return f.view_as(x), dx.view_as(x), out
 
+    # ---- two-phase evaluation + VJP for the row-partitioned adjoint solve ----------------------------------------
+    # The next Runge-Kutta stage's state depends only on f, which the ROW pass produces; its all-gather can therefore
+    # run while the column pass, the dense tail and the reduce-scatter of this evaluation are still at work
+    # (DESIGN.md "Multi-GPU").  integrators._adjoint_fixed_phased drives this protocol when phased_ok() says so.
+    def phased_ok(self, x):
+        """two-phase protocol available?  Row-partitioned, single-gather kernels, and switched on: the overlap has
+        not run on hardware yet, so it is opt-in (GRANDB200_OVERLAP=1)"""
+        import os
+        if self.partition is None or os.environ.get('GRANDB200_OVERLAP') != '1' or self.opt.get('mix_features', False):
+            return False
+        part, _halo = self.partition
+        L = self.multihead_att_layer
+        x2 = self._as_2d(x)
+        edge_w = L.edge_weights if self.opt.get('reweight_attention', False) else None
+        plan = self._plan(part.n_pad)
+        return x2.shape[0] == part.slab and nl_supported(plan, x2, L.h, L.attention_dim, L._check_supported(),
+                                                         int(self.opt['attention_norm_idx']), edge_w)
+
+    def prefetch_state(self, x):
+        """start gathering the slabs of a state that a later eval_vjp_phased(…, prefetched=) call will evaluate"""
+        _part, halo = self.partition
+        pending = halo.all_gather_rows_async(self._as_2d(x).detach())
+        pending.src = x                                            # eval_vjp_phased checks identity against its `x`
+        return pending
+
+    def eval_vjp_phased(self, t, x, cot, params, prefetched=None):
+        """first half of eval_vjp on a row-partitioned graph: gather (or take the prefetched gather of) the state,
+        project q, run the row pass.  Returns (f, finish): f is this rank's slab of f(t, x); finish() runs the column
+        pass, the dense tail and the exchanges and returns (vjp_x, [vjp_p or None ...]) like eval_vjp."""
+        from . import partition as P
+        from .ops import _nl_q
+        part, halo = self.partition
+        L = self.multihead_att_layer
+        x2 = self._as_2d(x).detach().contiguous()
+        self._check_nfe()
+        if prefetched is not None and prefetched.src is x:
+            x_full = prefetched.wait()
+        else:
+            if prefetched is not None:
+                prefetched.wait()                                  # a gather of some other state: complete it, drop it
+            x_full = halo.all_gather_rows(x2)
+        plan = self._plan(part.n_pad)
+        source = bool(self.opt['add_source'])
+        x0 = self._as_2d(self.x0).contiguous() if (source and self.x0 is not None) else None
+        wq, bq, wk = (L.Q.weight.detach().contiguous(), L.Q.bias.detach().contiguous(), L.K.weight.detach().contiguous())
+        q = _nl_q(x2, wq, bq)
+        half = P.nl_local_vjp_rows(part, plan, x_full, q, wq, wk, self.alpha_train.detach(),
+                                   self.beta_train.detach() if x0 is not None else None, x0, L.h,
+                                   not self.opt['no_alpha_sigmoid'], self._as_2d(cot).detach().contiguous(), True)
+        a, d = wq.shape
+
+        def finish():
+            dx_share, grads = P.nl_local_vjp_cols(half)
+            dx = halo.reduce_scatter_rows(dx_share)
+            halo.all_reduce_(grads)
+            dwq, dwk, dbq, dbk, dalpha, dbeta = P.unpack_nl_grads(grads, a, d)
+            named = ((self.alpha_train, dalpha.reshape(self.alpha_train.shape)), (self.beta_train, dbeta.reshape(())),
+                     (L.Q.weight, dwq), (L.Q.bias, dbq), (L.K.weight, dwk), (L.K.bias, dbk))
+            out = []
+            for p in params:
+                g = None
+                for q_, gq in named:
+                    if p is q_:
+                        g = gq
+                out.append(g)
+            return dx.view_as(x), out
+
+        return half.f.view_as(x), finish
+
     def eval_vjp(self, t, x, cot, params):
         """f(t, x) and the vector-Jacobian products cot^T df/d(x, params) in one fused pass - what the adjoint
         solver's augmented dynamics need (the reference gets them from `func(t, y)` followed by

@@ -267,6 +267,55 @@ def odeint(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, even
     return out if prob.is_tuple else out[0]
 
 
+# Butcher tableaus of the fixed-grid methods as (A rows, b, c): stage i > 0 is evaluated at y + dt * sum_j A[i-1][j] k_j
+_TABLEAU = {
+    'euler': ([], [1.0], [0.0]),
+    'midpoint': ([[0.5]], [0.0, 1.0], [0.0, 0.5]),
+    'rk4': ([[1 / 3], [-1 / 3, 1.0], [1.0, -1.0, 1.0]], [0.125, 0.375, 0.375, 0.125], [0.0, 1 / 3, 2 / 3, 1.0]),
+}
+
+
+def _adjoint_fixed_phased(func, params, state, t_hi, t_lo, method, step_size):
+    """The fixed-grid reverse solve of the augmented adjoint state (vjp_t, y, a_y, *a_params) from real time t_hi down
+    to t_lo for a function with the two-phase protocol (`eval_vjp_phased` / `prefetch_state`,
+    ODEFuncTransformerAtt on a row-partitioned graph).  Same arithmetic, in the same order, as
+    odeint(aug_dynamics, ..., _comp_signs=(-1, 1, -1, -1...)) over _fixed_step - only the ORDER OF ISSUE differs: as soon
+    as the row pass of stage i is queued (f known) the y component of stage i+1 is formed and its all-gather started,
+    and only then the column pass / dense tail / reduce-scatter of stage i are queued, so the gather overlaps them."""
+    A, b, c = _TABLEAU[method]
+    ref = state[1]
+    s0, s1 = -float(t_hi), -float(t_lo)                              # internal (increasing) time, as in _Problem
+    grid = [s0, s1] if step_size is None else _fixed_grid(s0, s1, float(step_size))
+    n_state = len(state)
+    sg = (1.0, -1.0) + (1.0,) * (n_state - 2)                       # prob.sign (-1) x comp_signs (-1, 1, -1, -1, ...)
+    state = tuple(state)
+    pre = None
+    for step, (g0, g1) in enumerate(zip(grid[:-1], grid[1:])):
+        dt = g1 - g0
+        last_step = step == len(grid) - 2
+        ks = []
+        y, a_y = state[1], state[2]
+        y_stage, a_stage = y, a_y
+        for i in range(len(b)):
+            s_i = g1 if (method == 'rk4' and i == 3) else g0 + c[i] * dt
+            tt = torch.full((), -s_i, dtype=ref.dtype, device=ref.device)
+            f, finish = func.eval_vjp_phased(tt, y_stage, a_stage, params, prefetched=pre)
+            fs = [k[1] for k in ks] + [f]
+            coeffs = A[i] if i + 1 < len(b) else b
+            y_next = _combine_one(y, [(fk, dt * cf * sg[1]) for fk, cf in zip(fs, coeffs)])
+            pre = None if (i + 1 == len(b) and last_step) else func.prefetch_state(y_next)
+            vy, vps = finish()
+            vp = [g if g is not None else torch.zeros_like(p) for g, p in zip(vps, params)]
+            ks.append((torch.zeros_like(tt), f, vy, *vp))
+            if i + 1 < len(b):
+                y_stage = y_next
+                a_stage = _combine_one(a_y, [(k[2], dt * cf * sg[2]) for k, cf in zip(ks, A[i])])
+        new = list(_combine(state, dt, ks, b, sg))
+        new[1] = y_next                                              # the same sum, already formed for the prefetch
+        state = tuple(new)
+    return list(state)
+
+
 class _OdeintAdjoint(torch.autograd.Function):
 
     @staticmethod
@@ -315,7 +364,14 @@ class _OdeintAdjoint(torch.autograd.Function):
         with torch.no_grad():
             state = [torch.zeros((), dtype=ys.dtype, device=ys.device), ys[-1], grad_ys[-1]] + \
                     [torch.zeros_like(p) for p in params]
+            phased = fixed and getattr(func, 'phased_ok', None) is not None and func.phased_ok(ys[-1])
             for i in range(len(times) - 1, 0, -1):
+                if phased:
+                    state = _adjoint_fixed_phased(func, params, state, times[i], times[i - 1], cfg['adjoint_method'],
+                                                  cfg['adjoint_options'].get('step_size'))
+                    state[1] = ys[i - 1]
+                    state[2] = state[2] + grad_ys[i - 1]
+                    continue
                 sol = odeint(aug_dynamics, tuple(state), [times[i], times[i - 1]], rtol=cfg['adjoint_rtol'],
                              atol=cfg['adjoint_atol'], method=cfg['adjoint_method'], options=cfg['adjoint_options'],
                              _comp_signs=comp_signs if fixed else None)

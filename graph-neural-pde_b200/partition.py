@@ -79,6 +79,18 @@ class Halo:
         self.n_gathers += 1
         return full
 
+    def all_gather_rows_async(self, slab):
+        """start the all-gather of `slab` and return at once: a PendingGather whose wait() hands out the [N_pad, d]
+        matrix.  On NCCL the collective runs on the communicator's own stream (ordered after the work already queued
+        on the current stream), so kernels launched before wait() overlap it."""
+        slab_c = slab.contiguous()
+        full = slab_c.new_empty((self.part.n_pad,) + tuple(slab_c.shape[1:]))
+        work = self.dist.all_gather_into_tensor(full, slab_c, group=self.group, async_op=True)
+        self.bytes_in += (self.part.world - 1) * slab_c.numel() * slab_c.element_size()
+        self.n_gathers += 1
+        self.n_prefetched = getattr(self, 'n_prefetched', 0) + 1
+        return PendingGather(slab, slab_c, full, work)
+
     def reduce_scatter_rows(self, full):
         """sum over ranks of [N_pad, d], rank p keeps rows [p*S, (p+1)*S)"""
         full = full.contiguous()
@@ -97,6 +109,20 @@ class Halo:
         return t
 
 
+class PendingGather:
+    """an all-gather in flight (Halo.all_gather_rows_async).  `src` is the tensor the caller asked to gather: the
+    consumer checks identity before trusting the result."""
+
+    def __init__(self, src, slab, full, work):
+        self.src, self._slab, self._full, self._work = src, slab, full, work
+
+    def wait(self):
+        if self._work is not None:
+            self._work.wait()              # NCCL: the current stream waits for the collective (no host block)
+            self._work = None
+        return self._full
+
+
 class LoopbackHalo:
     """world == 1 stand-in (no process group needed): the collectives are identities"""
 
@@ -107,6 +133,10 @@ class LoopbackHalo:
 
     def all_gather_rows(self, slab):
         return slab.contiguous()
+
+    def all_gather_rows_async(self, slab):
+        c = slab.contiguous()
+        return PendingGather(slab, c, c, None)
 
     def reduce_scatter_rows(self, full):
         return full.contiguous()
@@ -185,6 +215,80 @@ def nl_local_vjp(part, plan, x_full, q, wq, wk, alpha_train, beta_train, x0_slab
                                        grads.data_ptr() + 4 * 2 * a * d, ws.data_ptr(), ws.numel(), _lib.stream()),
                    'gb_linear_bwd_w')
     return out, dx, grads
+
+
+class _NlVjpHalf:
+    """buffers of one evaluation + VJP between its row pass and its column pass (nl_local_vjp_rows / _cols)"""
+    __slots__ = ('part', 'plan', 'x_full', 'q', 'wq', 'wk', 'alpha_train', 'beta_train', 'x0_slab', 'heads', 'sig',
+                 'g_slab', 'f', 'ds', 'dabar', 'abar', 'dqk', 'dx', 'partials', 'grads', 'want_w')
+
+
+def nl_local_vjp_rows(part, plan, x_full, q, wq, wk, alpha_train, beta_train, x0_slab, heads, alpha_sigmoid, g_slab,
+                      want_w):
+    """first half of nl_local_vjp: the row pass only (gb_nl_adjoint_phase, GB_NL_PHASE_ROWS).  On return (i.e. once
+    the launch is queued) `.f` holds f for the owned rows - all the solver needs to form the NEXT stage's state, whose
+    all-gather can then run while nl_local_vjp_cols() works."""
+    from .ops import _nl_workspace
+    lib = _lib.load()
+    n_pad, d = x_full.shape
+    s = part.slab
+    a = wq.shape[0]
+    dev = x_full.device
+    f32 = dict(dtype=torch.float32, device=dev)
+    h = _NlVjpHalf()
+    h.part, h.plan, h.x_full, h.q, h.wq, h.wk = part, plan, x_full, q, wq, wk
+    h.alpha_train, h.beta_train, h.x0_slab, h.heads, h.sig, h.g_slab, h.want_w = \
+        alpha_train, beta_train, x0_slab, heads, int(alpha_sigmoid), g_slab, want_w
+    h.ds = torch.empty(plan.e, heads, **f32)
+    h.dabar = torch.empty(plan.e, **f32)
+    h.abar = torch.empty(plan.e, **f32)
+    h.dqk = torch.empty(n_pad, 2 * a, **f32)
+    h.dqk[:part.lo, :a].zero_()
+    h.dqk[part.hi:, :a].zero_()
+    h.dx = torch.empty(n_pad, d, **f32)
+    h.f = torch.zeros(s, d, **f32) if part.hi - part.lo < s else torch.empty(s, d, **f32)
+    h.partials = torch.empty(int(lib.gb_att_bwd_fused_partials(plan.c)), **f32)
+    h.grads = torch.empty(2 * a * d + 2 * a + 2 if want_w else 2, **f32)
+    _nl_adjoint_phase(lib, h, 1, _nl_workspace(dev))
+    return h
+
+
+def _nl_adjoint_phase(lib, h, phase, workspace):
+    part, plan, x_full = h.part, h.plan, h.x_full
+    d = x_full.shape[1]
+    a = h.wq.shape[0]
+    source = h.beta_train is not None and h.x0_slab is not None
+    dparams = h.grads[-2:]
+    _lib.check(lib.gb_nl_adjoint_phase(plan.c, part.lo, part.hi, x_full.data_ptr(), d, _virt(h.q, part.lo, a), a,
+                                       h.wk.data_ptr(), d, h.heads, a // h.heads, d,
+                                       _virt(h.x0_slab, part.lo, d) if source else None, d, h.alpha_train.data_ptr(),
+                                       h.sig, h.beta_train.data_ptr() if source else None,
+                                       _virt(h.g_slab, part.lo, d), d, _virt(h.f, part.lo, d), d, h.ds.data_ptr(),
+                                       h.dabar.data_ptr(), h.abar.data_ptr(), h.dqk.data_ptr(), 2 * a,
+                                       h.dqk.data_ptr() + 4 * a, 2 * a, h.dx.data_ptr(), d, h.partials.data_ptr(),
+                                       dparams.data_ptr(), workspace.data_ptr(), phase, _lib.stream()),
+               'gb_nl_adjoint_phase')
+
+
+def nl_local_vjp_cols(h):
+    """second half: column pass + the dense tail.  Returns (dx_share [N_pad, d], flat parameter-gradient share), the
+    same values nl_local_vjp returns."""
+    from .ops import _nl_workspace
+    lib = _lib.load()
+    x_full = h.x_full
+    n_pad, d = x_full.shape
+    a = h.wq.shape[0]
+    _nl_adjoint_phase(lib, h, 2, _nl_workspace(x_full.device))
+    w_cat = torch.cat([h.wq, h.wk], dim=0)
+    _lib.check(lib.gb_linear_bwd_x(h.dqk.data_ptr(), 2 * a, n_pad, 2 * a, w_cat.data_ptr(), d, h.dx.data_ptr(), d, 1,
+                                   _lib.stream()), 'gb_linear_bwd_x')
+    if h.want_w:
+        ws = torch.empty(int(lib.gb_linear_bwd_w_workspace_bytes(n_pad, d, 2 * a)), dtype=torch.uint8,
+                         device=x_full.device)
+        _lib.check(lib.gb_linear_bwd_w(h.dqk.data_ptr(), 2 * a, x_full.data_ptr(), d, n_pad, d, 2 * a, h.grads.data_ptr(),
+                                       h.grads.data_ptr() + 4 * 2 * a * d, ws.data_ptr(), ws.numel(), _lib.stream()),
+                   'gb_linear_bwd_w')
+    return h.dx, h.grads
 
 
 def diffusion_local_forward(part, plan, vals, x_full, x0_slab, alpha_train, beta_train, alpha_sigmoid):

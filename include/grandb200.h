@@ -297,6 +297,20 @@ int gb_nl_adjoint(const gb_graph* g, int32_t row_lo, int32_t row_hi, const float
                   float* dk_out, int32_t lddk, float* dx, int32_t lddx, float* partials, float* dparams,
                   void* workspace, void* stream);
 
+/* The same call in two halves, so that a host that exchanges states between devices can start the exchange of the
+ * NEXT stage's state (which depends only on f) while the column pass of this evaluation runs:
+ *   GB_NL_PHASE_ROWS : the row pass only  -> out (f), dq, ds, abar (and the dabar scratch) are complete on return
+ *   GB_NL_PHASE_COLS : the column pass only (same arguments; reads q, abar, ds, gout, x) -> dx, dk, dparams
+ *   GB_NL_PHASE_BOTH : gb_nl_adjoint. */
+enum { GB_NL_PHASE_BOTH = 0, GB_NL_PHASE_ROWS = 1, GB_NL_PHASE_COLS = 2 };
+int gb_nl_adjoint_phase(const gb_graph* g, int32_t row_lo, int32_t row_hi, const float* x, int32_t ldx,
+                        const float* q, int32_t ldq, const float* wk, int32_t ldwk, int32_t heads, int32_t dk,
+                        int32_t d, const float* x0, int32_t ldx0, const float* alpha_train, int32_t alpha_sigmoid,
+                        const float* beta_train, const float* gout, int32_t ldg, float* out, int32_t ldo,
+                        float* ds, float* dabar_scratch, float* abar, float* dq, int32_t lddq,
+                        float* dk_out, int32_t lddk, float* dx, int32_t lddx, float* partials, float* dparams,
+                        void* workspace, int32_t phase, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

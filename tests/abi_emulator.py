@@ -388,35 +388,52 @@ class Emulator:
     def gb_nl_adjoint(self, g, lo, hi, x, ldx, q, ldq, wk, ldwk, heads, dk, d, x0, ldx0, alpha_train, alpha_sigmoid,
                       beta_train, gout, ldg, out, ldo, ds, dabar, abar, dq, lddq, dk_out, lddk, dx, lddx, partials,
                       dparams, workspace, stream):
-        self._note('gb_nl_adjoint')
+        return self.gb_nl_adjoint_phase(g, lo, hi, x, ldx, q, ldq, wk, ldwk, heads, dk, d, x0, ldx0, alpha_train,
+                                        alpha_sigmoid, beta_train, gout, ldg, out, ldo, ds, dabar, abar, dq, lddq, dk_out,
+                                        lddk, dx, lddx, partials, dparams, workspace, 0, stream)
+
+    def gb_nl_adjoint_phase(self, g, lo, hi, x, ldx, q, ldq, wk, ldwk, heads, dk, d, x0, ldx0, alpha_train,
+                            alpha_sigmoid, beta_train, gout, ldg, out, ldo, ds, dabar, abar, dq, lddq, dk_out, lddk, dx,
+                            lddx, partials, dparams, workspace, phase, stream):
+        """phase 0: both halves; 1: row pass (f, dq, ds, abar); 2: column pass, which READS abar / ds back from the
+        caller's buffers (so a host that hands the second half different buffers is caught)"""
+        self._note({0: 'gb_nl_adjoint', 1: 'gb_nl_adjoint_rows', 2: 'gb_nl_adjoint_cols'}[phase])
         G = Graph(g)
         a = heads * dk
-        X, Q, K, att = self._nl_attention(G, lo, hi, x, ldx, q, ldq, wk, ldwk, heads, dk, d)
         alpha = _alpha(alpha_train, alpha_sigmoid)
-        ab = att.mean(axis=1)
-        if _p(out):
-            ax = np.zeros((G.n, d))
-            np.add.at(ax, G.rows, ab[:, None] * X[G.colidx])
-            f = alpha * (ax - X)[lo:hi]
-            if _p(x0) and _p(beta_train):
-                f = f + scalar(beta_train) * self._rows(x0, lo, hi, d, ldx0)
-            self._rows(out, lo, hi, d, ldo)[:] = f
+        X = f32(x, G.n, d, ldx).astype(np.float64)
         go = np.zeros((G.n, d))
         go[lo:hi] = self._rows(gout, lo, hi, d, ldg)
-        dab = alpha * (go[G.rows] * X[G.colidx]).sum(axis=1)
-        da = dab[:, None] / heads
-        inner = np.zeros((G.n, heads))
-        np.add.at(inner, G.rows, att * da)
-        dsv = att * (da - inner[G.rows])
-        f32(ds, G.e, heads)[:] = dsv
-        vec(abar, G.e)[:] = ab
-        if _p(dabar):
-            vec(dabar, G.e)[:] = dab
-        w = dsv[:, :, None] / math.sqrt(dk)
-        gq, gk = np.zeros((G.n, heads, dk)), np.zeros((G.n, heads, dk))
-        np.add.at(gq, G.rows, w * K.reshape(G.n, heads, dk)[G.colidx])
+        if phase != 2:
+            _, Q, K, att = self._nl_attention(G, lo, hi, x, ldx, q, ldq, wk, ldwk, heads, dk, d)
+            ab = att.mean(axis=1)
+            if _p(out):
+                ax = np.zeros((G.n, d))
+                np.add.at(ax, G.rows, ab[:, None] * X[G.colidx])
+                f = alpha * (ax - X)[lo:hi]
+                if _p(x0) and _p(beta_train):
+                    f = f + scalar(beta_train) * self._rows(x0, lo, hi, d, ldx0)
+                self._rows(out, lo, hi, d, ldo)[:] = f
+            dab = alpha * (go[G.rows] * X[G.colidx]).sum(axis=1)
+            da = dab[:, None] / heads
+            inner = np.zeros((G.n, heads))
+            np.add.at(inner, G.rows, att * da)
+            f32(ds, G.e, heads)[:] = att * (da - inner[G.rows])
+            vec(abar, G.e)[:] = ab
+            if _p(dabar):
+                vec(dabar, G.e)[:] = dab
+            gq = np.zeros((G.n, heads, dk))
+            np.add.at(gq, G.rows, f32(ds, G.e, heads).astype(np.float64)[:, :, None] / math.sqrt(dk)
+                      * K.reshape(G.n, heads, dk)[G.colidx])
+            self._rows(dq, lo, hi, a, lddq)[:] = gq.reshape(G.n, a)[lo:hi]
+        if phase == 1:
+            return 0
+        ab = vec(abar, G.e).astype(np.float64)
+        w = f32(ds, G.e, heads).astype(np.float64)[:, :, None] / math.sqrt(dk)
+        Q = np.zeros((G.n, a))
+        Q[lo:hi] = self._rows(q, lo, hi, a, ldq)
+        gk = np.zeros((G.n, heads, dk))
         np.add.at(gk, G.colidx, w * Q.reshape(G.n, heads, dk)[G.rows])
-        self._rows(dq, lo, hi, a, lddq)[:] = gq.reshape(G.n, a)[lo:hi]
         f32(dk_out, G.n, a, lddk)[:] = gk.reshape(G.n, a)
         t = np.zeros((G.n, d))
         np.add.at(t, G.colidx, ab[:, None] * go[G.rows])

@@ -207,7 +207,9 @@ def _make_block(function='transformer'):
     return block
 
 
-def _gloo_worker(rank, world, port, n, d, ret):
+def _gloo_worker(rank, world, port, n, d, ret, overlap=False):
+    if overlap:
+        os.environ['GRANDB200_OVERLAP'] = '1'
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, 'tests'))
     import contextlib
@@ -234,9 +236,18 @@ def _gloo_worker(rank, world, port, n, d, ret):
         halo = grand_b200.Halo(part)
         block = _make_block()
         block.set_partition(part, halo)
+        del emu.calls[:]
         z, grads, nfe = _train_pass(block, data, part.to_slab(x), part.to_slab(gz))
         assert nfe == nfe_ref == 16 and z.shape == (part.slab, d)
         assert halo.n_gathers == 16 and halo.n_scatters == 8          # one gather per evaluation, one scatter per VJP
+        if overlap:
+            # two-phase adjoint: 7 of the 8 adjoint evaluations find their state already gathered, and every row pass
+            # is followed by the next gather BEFORE its own column pass is issued
+            assert getattr(halo, 'n_prefetched', 0) == 7
+            calls = [c for c in emu.calls if c.startswith('gb_nl_adjoint')]
+            assert calls == ['gb_nl_adjoint_rows', 'gb_nl_adjoint_cols'] * 8
+        else:
+            assert getattr(halo, 'n_prefetched', 0) == 0 and 'gb_nl_adjoint_rows' not in emu.calls
         assert_close(z, part.to_slab(z_ref), 2e-5, 'z slab')
         assert_close(grads[0], part.to_slab(g_ref[0]), 1e-4, 'dL/dx slab')
         bias_scale = max(float(g_ref[2].abs().max()), float(g_ref[4].abs().max()))
@@ -252,6 +263,16 @@ def test_two_rank_block_path_over_gloo_matches_the_single_process_block():
     mgr = mp.Manager()
     ret = mgr.dict()
     mp.spawn(_gloo_worker, args=(world, _free_port(), 157, 32, ret), nprocs=world, join=True)
+    assert dict(ret) == {0: 'ok', 1: 'ok'}
+
+
+def test_two_rank_block_path_with_the_overlapped_exchange():
+    """GRANDB200_OVERLAP=1: the phased adjoint solve (integrators._adjoint_fixed_phased) drives eval_vjp_phased /
+    prefetch_state over real async gloo collectives; same numbers as the single-process block"""
+    world = 2
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_gloo_worker, args=(world, _free_port(), 157, 32, ret, True), nprocs=world, join=True)
     assert dict(ret) == {0: 'ok', 1: 'ok'}
 
 

@@ -275,3 +275,73 @@ def test_adjoint_params_subset_and_frozen_parameters():
     z = P.odeint_adjoint(func, y0, torch.tensor([0.0, 1.0]), method='rk4', options=dict(step_size=0.5))
     z[-1].sum().backward()
     assert func.A.grad is not None and func.b.grad is None and y0.grad is not None
+
+
+# ---- two-phase adjoint protocol (row-partitioned graphs: the next stage's exchange overlaps the column pass) -------
+class PhasedLinear(Linear):
+    """mock of ODEFuncTransformerAtt's two-phase protocol with closed-form products; records the order of issue"""
+
+    def __init__(self, *a, **kw):
+        super().__init__(*a, **kw)
+        self.log = []
+
+    def phased_ok(self, y):
+        return True
+
+    def prefetch_state(self, y):
+        self.log.append('prefetch')
+        return ('pending', y)
+
+    def eval_vjp_phased(self, t, y, cot, params, prefetched=None):
+        assert prefetched is None or prefetched[1] is y           # the solver hands back exactly what it prefetched
+        self.log.append('rows' if prefetched is None else 'rows(prefetched)')
+        self.nfe += 1
+        f = y @ self.A.T + self.b
+
+        def finish():
+            self.log.append('cols')
+            grads = {id(self.A): cot.T @ y, id(self.b): cot.sum(0)}
+            return cot @ self.A, [grads.get(id(p)) for p in params]
+        return f, finish
+
+
+@pytest.mark.parametrize('method,step,t1', [('rk4', 0.5, 2.0), ('rk4', 1.0, 2.5), ('midpoint', 0.25, 1.0), ('euler', 0.2, 1.0)])
+def test_phased_adjoint_solve_is_the_plain_adjoint_solve(method, step, t1):
+    P = product()
+    y0 = torch.randn(5, 4, dtype=torch.float64)
+    t = torch.tensor([0.0, t1], dtype=torch.float64)
+    kw = dict(method=method, options=dict(step_size=step))
+    plain, phased = Linear(4, seed=1), PhasedLinear(4, seed=1)
+    ref = _loss_and_grads(lambda f, y: P.odeint_adjoint(f, y, t, **kw), plain, y0)
+    got = _loss_and_grads(lambda f, y: P.odeint_adjoint(f, y, t, **kw), phased, y0)
+    assert phased.nfe == plain.nfe
+    assert torch.equal(got[1], ref[1])                             # same arithmetic in the same order: bit-identical
+    for a, b in zip(got[2], ref[2]):
+        assert torch.equal(a, b)
+    log = phased.log
+    stages = {'rk4': 4, 'midpoint': 2, 'euler': 1}[method]
+    n_evals = log.count('rows') + log.count('rows(prefetched)')
+    assert n_evals == log.count('cols')                            # every first half is finished
+    assert log.count('rows') == 1                                  # only the very first stage has nothing prefetched
+    assert log.count('prefetch') == n_evals - 1                    # ... and nothing is prefetched past the last stage
+    assert n_evals % stages == 0
+    for i, ev in enumerate(log[:-1]):                              # order of issue: rows, prefetch (next state), cols
+        if ev.startswith('rows') and i + 2 < len(log):
+            assert log[i + 1] == 'prefetch' and log[i + 2] == 'cols'
+
+
+def test_phased_adjoint_with_intermediate_output_times():
+    """several requested times: the y component is reset to the stored forward value at every boundary, so the gather
+    prefetched across a boundary is never used"""
+    P = product()
+    y0 = torch.randn(3, 4, dtype=torch.float64)
+    t = torch.tensor([0.0, 1.0, 2.0], dtype=torch.float64)
+    kw = dict(method='rk4', options=dict(step_size=0.5))
+
+    def run(func):
+        y = y0.clone().requires_grad_(True)
+        z = P.odeint_adjoint(func, y, t, **kw)
+        (z[1].sum() + 2 * z[2].sum()).backward()
+        return y.grad, func.A.grad
+    ref, got = run(Linear(4, seed=2)), run(PhasedLinear(4, seed=2))
+    assert torch.equal(got[0], ref[0]) and torch.equal(got[1], ref[1])
