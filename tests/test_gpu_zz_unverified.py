@@ -320,3 +320,41 @@ def test_hard_attention_block_samples_edges_while_training(function, capsys):
     with torch.no_grad():
         z_eval = block(x, data)
     assert func.edge_index.shape[-1] == e_full and z_eval.shape == x.shape
+
+
+def test_two_phase_adjoint_is_bit_identical_to_the_single_call(monkeypatch):
+    """gb_nl_adjoint_phase (row pass, then column pass) through the phased adjoint solve on a 1-rank partition
+    (LoopbackHalo) against the ordinary partitioned solve (gb_nl_adjoint in one call): same kernels, same buffers,
+    same order of arithmetic -> torch.equal"""
+    import grand_b200
+    n, d = 400, 32
+    opt = dict(BLOCK_OPT, block='attention', function='transformer', adjoint=True, hidden_dim=d)
+    ei = dev(og.shaped_graph(n, 2400, 9))
+    g = torch.Generator().manual_seed(0)
+    x, gz = dev(torch.randn(n, d, generator=g).numpy()), dev(torch.randn(n, d, generator=g).numpy())
+    results = []
+    for overlap in (False, True):
+        monkeypatch.setenv('GRANDB200_OVERLAP', '1' if overlap else '0')
+        block = grand_b200.set_block(opt)(grand_b200.set_function(opt), [], opt, device(),
+                                          t=torch.tensor([0., 2.])).to(device())
+        block.train()
+        L = block.odefunc.multihead_att_layer
+        gw = torch.Generator().manual_seed(5)
+        with torch.no_grad():
+            for lin in (L.Q, L.K):
+                lin.weight.copy_((torch.randn(lin.weight.shape, generator=gw) / 6).to(device()))
+                lin.bias.copy_((0.1 * torch.randn(lin.bias.shape, generator=gw)).to(device()))
+            block.odefunc.alpha_train.fill_(0.3)
+            block.odefunc.beta_train.fill_(0.1)
+        part = grand_b200.RowPartition(n, 1, 0)
+        block.set_partition(part, grand_b200.LoopbackHalo(part))
+        data = grand_b200.GraphData()
+        data.new_graph(ei, n)
+        xg = x.clone().requires_grad_(True)
+        block.set_x0(xg)
+        z = block(xg, data)
+        params = [xg, L.Q.weight, L.Q.bias, L.K.weight, L.K.bias, block.odefunc.alpha_train, block.odefunc.beta_train]
+        results.append([z.detach()] + list(torch.autograd.grad((z * gz).sum(), params)))
+        assert block.odefunc.nfe == 16
+    for a, b in zip(*results):
+        assert torch.equal(a, b)
