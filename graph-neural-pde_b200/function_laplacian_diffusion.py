@@ -68,6 +68,58 @@ class LaplacianODEFunc(ODEFunc):
                                     halo, plan, not self.opt['no_alpha_sigmoid'])
         return f.view_as(x)
 
+    # ---- two-phase evaluation + VJP for the row-partitioned adjoint solve (see ODEFuncTransformerAtt.phased_ok) ---
+    def phased_ok(self, x):
+        import os
+        if self.partition is None or os.environ.get('GRANDB200_OVERLAP') != '1' or self.opt['block'] != 'constant':
+            return False
+        return self._as_2d(x).shape[0] == self.partition[0].slab
+
+    def prefetch_state(self, x):
+        pending = self.partition[1].all_gather_rows_async(self._as_2d(x).detach())
+        pending.src = x
+        return pending
+
+    def eval_vjp_phased(self, t, x, cot, params, prefetched=None):
+        """(f, finish) for this rank's slab: the forward SpMM over the gathered state now, the transpose SpMM and the
+        exchanges of dL/dx, d(alpha_train, beta_train) in finish() - so that the solver can start gathering the next
+        stage's state (a function of f only) in between.  Same kernels as PartDiffusionFn forward / backward."""
+        from . import partition as P
+        part, halo = self.partition
+        self._check_nfe()
+        x2 = self._as_2d(x).detach().contiguous()
+        if prefetched is not None and prefetched.src is x:
+            x_full = prefetched.wait()
+        else:
+            if prefetched is not None:
+                prefetched.wait()
+            x_full = halo.all_gather_rows(x2)
+        plan = self._plan(part.n_pad)
+        vals = self._edge_values(plan).detach()
+        source = bool(self.opt['add_source'])
+        x0 = self._as_2d(self.x0).contiguous() if (source and self.x0 is not None) else None
+        sig = not self.opt['no_alpha_sigmoid']
+        alpha, beta = self.alpha_train.detach(), (self.beta_train.detach() if x0 is not None else None)
+        f = P.diffusion_local_forward(part, plan, vals, x_full, x0, alpha, beta, sig)
+        g_slab = self._as_2d(cot).detach().contiguous()
+
+        def finish():
+            dx_share, dparams = P.diffusion_local_vjp(part, plan, vals, x_full, x0, alpha, sig, g_slab)
+            dx = halo.reduce_scatter_rows(dx_share)
+            halo.all_reduce_(dparams)
+            named = ((self.alpha_train, dparams[0].reshape(self.alpha_train.shape)),
+                     (self.beta_train, dparams[1].reshape(()) if x0 is not None else None))
+            out = []
+            for p in params:
+                g = None
+                for q_, gq in named:
+                    if p is q_:
+                        g = gq
+                out.append(g)
+            return dx.view_as(x), out
+
+        return f.view_as(x), finish
+
     def forward(self, t, x):  # the t param is needed by the ODE solver.
         self._check_nfe()
         x2 = self._as_2d(x)

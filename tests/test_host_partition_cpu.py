@@ -185,8 +185,10 @@ def _train_pass(block, data, x, g):
     xg = x.detach().requires_grad_(True)
     block.set_x0(xg)
     z = block(xg, data)
-    L = block.odefunc.multihead_att_layer
-    params = [L.Q.weight, L.Q.bias, L.K.weight, L.K.bias, block.odefunc.alpha_train, block.odefunc.beta_train]
+    params = [block.odefunc.alpha_train, block.odefunc.beta_train]
+    L = getattr(block.odefunc, 'multihead_att_layer', None)
+    if L is not None:
+        params = [L.Q.weight, L.Q.bias, L.K.weight, L.K.bias] + params
     grads = torch.autograd.grad((z * g).sum(), [xg] + params)
     return z.detach(), grads, block.odefunc.nfe
 
@@ -207,7 +209,7 @@ def _make_block(function='transformer'):
     return block
 
 
-def _gloo_worker(rank, world, port, n, d, ret, overlap=False):
+def _gloo_worker(rank, world, port, n, d, ret, overlap=False, function='transformer'):
     if overlap:
         os.environ['GRANDB200_OVERLAP'] = '1'
     sys.path.insert(0, ROOT)
@@ -230,11 +232,11 @@ def _gloo_worker(rank, world, port, n, d, ret, overlap=False):
         data = grand_b200.GraphData()
         data.new_graph(ei, n)
         # single-process truth (same emulated ABI, un-partitioned block)
-        z_ref, g_ref, nfe_ref = _train_pass(_make_block(), data, x, gz)
+        z_ref, g_ref, nfe_ref = _train_pass(_make_block(function), data, x, gz)
         # partitioned: this rank's slab in, this rank's slab out
         part = grand_b200.RowPartition(n, world, rank)
         halo = grand_b200.Halo(part)
-        block = _make_block()
+        block = _make_block(function)
         block.set_partition(part, halo)
         del emu.calls[:]
         z, grads, nfe = _train_pass(block, data, part.to_slab(x), part.to_slab(gz))
@@ -244,14 +246,22 @@ def _gloo_worker(rank, world, port, n, d, ret, overlap=False):
             # two-phase adjoint: 7 of the 8 adjoint evaluations find their state already gathered, and every row pass
             # is followed by the next gather BEFORE its own column pass is issued
             assert getattr(halo, 'n_prefetched', 0) == 7
-            calls = [c for c in emu.calls if c.startswith('gb_nl_adjoint')]
-            assert calls == ['gb_nl_adjoint_rows', 'gb_nl_adjoint_cols'] * 8
+            if function == 'transformer':
+                calls = [c for c in emu.calls if c.startswith('gb_nl_adjoint')]
+                assert calls == ['gb_nl_adjoint_rows', 'gb_nl_adjoint_cols'] * 8
+            else:
+                calls = [c for c in emu.calls if c.startswith('gb_spmm_')][8:]            # after the forward integration
+                assert calls == ['gb_spmm_fwd_part', 'gb_spmm_bwd_part'] * 8
         else:
             assert getattr(halo, 'n_prefetched', 0) == 0 and 'gb_nl_adjoint_rows' not in emu.calls
         assert_close(z, part.to_slab(z_ref), 2e-5, 'z slab')
         assert_close(grads[0], part.to_slab(g_ref[0]), 1e-4, 'dL/dx slab')
-        bias_scale = max(float(g_ref[2].abs().max()), float(g_ref[4].abs().max()))
-        for got, r, name in zip(grads[1:], g_ref[1:], ('dWq', 'dbq', 'dWk', 'dbk', 'dalpha', 'dbeta')):
+        if function == 'transformer':
+            bias_scale = max(float(g_ref[2].abs().max()), float(g_ref[4].abs().max()))
+            names = ('dWq', 'dbq', 'dWk', 'dbk', 'dalpha', 'dbeta')
+        else:
+            bias_scale, names = 0.0, ('dalpha', 'dbeta')
+        for got, r, name in zip(grads[1:], g_ref[1:], names):
             assert_close(got, r, 1e-4, name, floor=bias_scale if name in ('dbq', 'dbk') else 0.0)   # all-reduced: full value
         ret[rank] = 'ok'
     finally:
@@ -273,6 +283,16 @@ def test_two_rank_block_path_with_the_overlapped_exchange():
     mgr = mp.Manager()
     ret = mgr.dict()
     mp.spawn(_gloo_worker, args=(world, _free_port(), 157, 32, ret, True), nprocs=world, join=True)
+    assert dict(ret) == {0: 'ok', 1: 'ok'}
+
+
+@pytest.mark.parametrize('overlap', [False, True])
+def test_two_rank_laplacian_block_path(overlap):
+    """GRAND-l (constant block) on two gloo ranks, serial and overlapped exchange"""
+    world = 2
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_gloo_worker, args=(world, _free_port(), 157, 32, ret, overlap, 'laplacian'), nprocs=world, join=True)
     assert dict(ret) == {0: 'ok', 1: 'ok'}
 
 
