@@ -321,3 +321,48 @@ def test_two_phase_adjoint_equals_the_single_call(host, monkeypatch):
     zz.test_two_phase_adjoint_is_bit_identical_to_the_single_call(monkeypatch)
     calls = [c for c in host.calls if c.startswith('gb_nl_adjoint')]
     assert calls == ['gb_nl_adjoint'] * 8 + ['gb_nl_adjoint_rows', 'gb_nl_adjoint_cols'] * 8
+
+
+@pytest.mark.parametrize('adjoint', [False, True])
+def test_attention_block_transformer_function_vs_the_oracle(host, adjoint):
+    """port of tests/test_gpu_blocks.py::test_attention_block_transformer_function (the headline configuration:
+    AttODEblock + ODEFuncTransformerAtt, rk4, odeint_adjoint with the fused eval_vjp) through the single-gather route"""
+    import grand_b200
+    from oracle import integrate as oint
+    n, e, d, T = 200, 1400, 16, 2.0
+    opt = dict(OPT, hidden_dim=d, adjoint=adjoint)
+    block = grand_b200.set_block(opt)(grand_b200.set_function(opt), [], opt, CPU, t=torch.tensor([0., T]))
+    ei = og.shaped_graph(n, e, 2)
+    data = grand_b200.GraphData()
+    data.new_graph(torch.tensor(ei), n)
+    block.train()
+    func = block.odefunc
+    g = torch.Generator().manual_seed(1)
+    with torch.no_grad():
+        for layer in (func.multihead_att_layer, block.multihead_att_layer):
+            for lin in (layer.Q, layer.K):
+                lin.weight.copy_(torch.randn(lin.weight.shape, generator=g) / 4.0)
+                lin.bias.copy_(0.1 * torch.randn(lin.bias.shape, generator=g))
+        func.alpha_train.fill_(-0.3)
+        func.beta_train.fill_(0.5)
+    x = torch.randn(n, d, generator=g).requires_grad_(True)
+    gout = torch.randn(n, d, generator=g)
+    block.set_x0(x)
+    z = block(x, data)
+    L = func.multihead_att_layer
+    params = [x, func.alpha_train, func.beta_train, L.Q.weight, L.Q.bias, L.K.weight, L.K.bias]
+    grads = torch.autograd.grad(z, params, gout)
+    assert 'gb_nl_adjoint' in host.calls                                 # both modes differentiate through the fused entry point
+    ei_n, _ = og.reset_graph_data(ei, None, n, 'rw', 1.0)
+    leaves = [T64(p).requires_grad_(True) for p in params]
+    f = lambda t, y: funcs.transformer_f(y, torch.tensor(ei_n), leaves[3], leaves[4], leaves[5], leaves[6], 4, leaves[1],
+                                         leaves[2], T64(x))
+    if adjoint:
+        zo = oint.odeint_adjoint(f, leaves[0], [0., T], 'rk4', 1.0, adjoint_params=tuple(leaves[1:]))[1]
+    else:
+        zo = oint.odeint(f, leaves[0], [0., T], 'rk4', 1.0)[1]
+    ro = torch.autograd.grad(zo, leaves, T64(gout))
+    assert_close(z, zo, 1e-4, 'z(T)')
+    bias_scale = max(float(ro[4].abs().max()), float(ro[6].abs().max()))
+    for got, r, name in zip(grads, ro, ('gx', 'galpha', 'gbeta', 'gwq', 'gbq', 'gwk', 'gbk')):
+        assert_close(got, r, 1e-4, name, floor=bias_scale if name in ('gbq', 'gbk') else 0.0)
