@@ -345,3 +345,33 @@ def test_phased_adjoint_with_intermediate_output_times():
         return y.grad, func.A.grad
     ref, got = run(Linear(4, seed=2)), run(PhasedLinear(4, seed=2))
     assert torch.equal(got[0], ref[0]) and torch.equal(got[1], ref[1])
+
+
+def test_dormand_prince_tableau_is_pinned_to_scipy():
+    """torchdiffeq is absent, so the adaptive solver's numbers cannot be pinned to it; its Butcher tableau can be pinned
+    to an independent implementation of the same published method: scipy's RK45.  Nodes, stage matrix and 5th-order
+    weights are identical; the error weights are Shampine's variant (the one torchdiffeq ships), which is -2/3 of the
+    original Dormand-Prince embedded difference that scipy uses - the same error direction, a different scale."""
+    import numpy as np
+    from scipy.integrate._ivp.rk import RK45
+    for tab in (product()._DP, dict(alpha=oi._DP_ALPHA, beta=oi._DP_BETA, c_sol=oi._DP_C_SOL, c_err=oi._DP_C_ERR)):
+        assert np.allclose(RK45.C[1:], tab['alpha'][:5], rtol=0, atol=1e-15) and tab['alpha'][5] == 1.0
+        for i, row in enumerate(tab['beta'][:5]):
+            assert np.allclose(RK45.A[i + 1, :len(row)], row, rtol=0, atol=1e-15)
+        assert np.allclose(RK45.B, tab['beta'][5], rtol=0, atol=1e-15)          # FSAL: last stage row = solution weights
+        assert np.allclose(RK45.B, tab['c_sol'][:6], rtol=0, atol=1e-15) and tab['c_sol'][6] == 0
+        assert np.allclose(np.asarray(tab['c_err']), -2.0 / 3.0 * RK45.E, rtol=0, atol=1e-15)
+
+
+def test_dopri5_agrees_with_scipy_rk45_on_a_linear_system():
+    """different step controllers, same method and tolerances: the two solutions agree to the requested accuracy"""
+    import numpy as np
+    from scipy.integrate import solve_ivp
+    P = product()
+    func = Linear(4, seed=6)
+    y0 = torch.randn(1, 4, dtype=torch.float64)
+    A, b = func.A.detach().numpy(), func.b.detach().numpy()
+    ref = solve_ivp(lambda t, y: A @ y + b, (0.0, 2.0), y0[0].numpy(), method='RK45', rtol=1e-9, atol=1e-11).y[:, -1]
+    with torch.no_grad():
+        got = P.odeint(func, y0, torch.tensor([0.0, 2.0]), method='dopri5', rtol=1e-9, atol=1e-11)[1, 0].numpy()
+    assert np.allclose(got, ref, rtol=1e-7, atol=1e-9)
