@@ -24,8 +24,9 @@ from . import partition
 from .graphed import GraphedPass
 from .partition import RowPartition, Halo, LoopbackHalo
 from .integrators import odeint, odeint_adjoint
+from .early_stop_solver import EarlyStopInt
 
 __all__ = ['GraphPlan', 'get_plan', 'MaxNFEException', 'get_rw_adj', 'gcn_norm_fill_val',
            'add_remaining_self_loops', 'Meter', 'ODEFunc', 'ODEblock', 'GraphData', 'LaplacianODEFunc',
            'ODEFuncTransformerAtt', 'SpGraphTransAttentionLayer', 'ConstantODEblock', 'AttODEblock', 'MixedODEblock', 'HardAttODEblock',
-           'set_block', 'set_function', 'partition', 'GraphedPass', 'RowPartition', 'Halo', 'LoopbackHalo', 'odeint', 'odeint_adjoint', 'integrators']
+           'set_block', 'set_function', 'partition', 'GraphedPass', 'RowPartition', 'Halo', 'LoopbackHalo', 'odeint', 'odeint_adjoint', 'integrators', 'EarlyStopInt']

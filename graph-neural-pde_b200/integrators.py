@@ -152,7 +152,7 @@ def _fixed_step(prob, method, t0, dt, t1, y):
     return _combine(y, dt, [k1, k2, k3, k4], [0.125, 0.375, 0.375, 0.125], sg)
 
 
-def _solve_fixed(prob, method, step_size):
+def _solve_fixed(prob, method, step_size, on_step=None):
     times = prob.times
     if step_size is None:
         grid = list(times)
@@ -163,6 +163,8 @@ def _solve_fixed(prob, method, step_size):
     j = 1
     for g0, g1 in zip(grid[:-1], grid[1:]):
         y1 = _fixed_step(prob, method, g0, g1 - g0, g1, y)
+        if on_step is not None:
+            on_step(prob.sign * g0, prob.sign * g1, y1)
         while j < len(times) and g1 >= times[j]:
             if times[j] == g1:
                 sols.append(y1)
@@ -200,7 +202,10 @@ def _interp4(y0, y1, y_mid, f0, f1, dt, x):
     return tuple(out)
 
 
-def _solve_adaptive(prob, method, rtol, atol, max_num_steps=2 ** 31 - 1):
+def _solve_adaptive(prob, method, rtol, atol, max_num_steps=2 ** 31 - 1, on_step=None, max_attempts=None):
+    """on_step(t0, t1, y1) is called after every ATTEMPTED step with the last accepted state (what the reference's
+    EarlyStopDopri5.advance evaluates, early_stop_solver.py:82-95); max_attempts bounds the attempts per requested
+    time: when it is hit the solution at that time is the last accepted state instead of the dense output."""
     tab = _DP if method == 'dopri5' else _AH
     times = prob.times
     t, y = times[0], prob.y0
@@ -211,7 +216,11 @@ def _solve_adaptive(prob, method, rtol, atol, max_num_steps=2 ** 31 - 1):
     win = None
     steps = 0
     for target in times[1:]:
+        attempts = 0
         while t < target:
+            if max_attempts is not None and attempts >= max_attempts:
+                break
+            attempts += 1
             if steps >= max_num_steps:
                 raise RuntimeError('max_num_steps exceeded')
             steps += 1
@@ -235,9 +244,16 @@ def _solve_adaptive(prob, method, rtol, atol, max_num_steps=2 ** 31 - 1):
                 dfactor = 1.0 if ratio < 1 else 0.2
                 factor = min(10.0, max(0.9 / ratio ** (1.0 / tab['order']), dfactor))
             dt = dt * factor
+            if on_step is not None and win is not None:
+                on_step(prob.sign * win[0], prob.sign * win[1], win[3])
+        if win is None:                               # no step was accepted within the attempt budget
+            sols.append(y)
+            continue
         # t >= target: evaluate the dense output of the last accepted step at `target`
         w0, w1, ya, yb, ym, fa, fb = win
-        if target == w1:
+        if t < target:                                # attempt budget hit: the last accepted state stands in
+            sols.append(yb)
+        elif target == w1:
             sols.append(yb)
         elif ym is not None:
             sols.append(_interp4(ya, yb, ym, fa, fb, w1 - w0, (target - w0) / (w1 - w0)))
@@ -247,7 +263,8 @@ def _solve_adaptive(prob, method, rtol, atol, max_num_steps=2 ** 31 - 1):
     return sols
 
 
-def odeint(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, event_fn=None, _comp_signs=None):
+def odeint(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, event_fn=None, _comp_signs=None,
+           _on_step=None, _max_attempts=None):
     if event_fn is not None:
         raise NotImplementedError('event handling is not part of the reference call sites')
     method = method or 'dopri5'
@@ -258,9 +275,9 @@ def odeint(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, even
             raise ValueError('_comp_signs is only meaningful for the fixed-grid solvers')
         prob.comp_signs = tuple(_comp_signs)
     if method in _FIXED:
-        sols = _solve_fixed(prob, method, options.get('step_size'))
+        sols = _solve_fixed(prob, method, options.get('step_size'), on_step=_on_step)
     elif method in _ADAPTIVE:
-        sols = _solve_adaptive(prob, method, float(rtol), float(atol))
+        sols = _solve_adaptive(prob, method, float(rtol), float(atol), on_step=_on_step, max_attempts=_max_attempts)
     else:
         raise NotImplementedError(f"method '{method}' (supported: {_FIXED + _ADAPTIVE})")
     out = tuple(torch.stack([s[i] for s in sols]) for i in range(len(prob.y0)))
