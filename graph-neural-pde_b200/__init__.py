@@ -25,8 +25,11 @@ from .graphed import GraphedPass
 from .partition import RowPartition, Halo, LoopbackHalo
 from .integrators import odeint, odeint_adjoint
 from .early_stop_solver import EarlyStopInt
+from .base_classes import BaseGNN
+from .GNN import GNN
+from .GNN_early import GNNEarly
 
 __all__ = ['GraphPlan', 'get_plan', 'MaxNFEException', 'get_rw_adj', 'gcn_norm_fill_val',
            'add_remaining_self_loops', 'Meter', 'ODEFunc', 'ODEblock', 'GraphData', 'LaplacianODEFunc',
            'ODEFuncTransformerAtt', 'SpGraphTransAttentionLayer', 'ConstantODEblock', 'AttODEblock', 'MixedODEblock', 'HardAttODEblock',
-           'set_block', 'set_function', 'partition', 'GraphedPass', 'RowPartition', 'Halo', 'LoopbackHalo', 'odeint', 'odeint_adjoint', 'integrators', 'EarlyStopInt']
+           'set_block', 'set_function', 'partition', 'GraphedPass', 'RowPartition', 'Halo', 'LoopbackHalo', 'odeint', 'odeint_adjoint', 'integrators', 'EarlyStopInt', 'BaseGNN', 'GNN', 'GNNEarly']

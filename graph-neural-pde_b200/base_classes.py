@@ -226,3 +226,100 @@ class GraphData(object):
 
     def __repr__(self):
         return self.__class__.__name__
+
+
+class BaseGNN(nn.Module):
+    """base_classes.py:137-186 - encoder / decoder around the ODE block: `m1` (or `mx` + `mp` with opt['beltrami']),
+    optional `m11` / `m12` MLP, `fc`, batch norms and the decoder `m2`.  Same parameter names and the same in-place
+    edits of `opt['hidden_dim']` (beltrami, use_labels) as the reference, so its checkpoints load.  These are dense
+    [N, F] x [F, d] layers executed once per step: torch.nn.Linear (library GEMMs), outside the per-evaluation path."""
+
+    def __init__(self, opt, num_classes, num_features, device=torch.device('cpu')):
+        super(BaseGNN, self).__init__()
+        self.opt = opt
+        self.T = opt['time']
+        self.num_classes = num_classes
+        self.num_features = num_features
+        self.graph_data = GraphData()
+        self.device = device
+        self.fm = Meter()
+        self.bm = Meter()
+        if opt.get('beltrami', False):
+            self.mx = nn.Linear(self.num_features, opt['feat_hidden_dim'])
+            self.mp = nn.Linear(opt['pos_enc_dim'], opt['pos_enc_hidden_dim'])
+            opt['hidden_dim'] = opt['feat_hidden_dim'] + opt['pos_enc_hidden_dim']
+        else:
+            self.m1 = nn.Linear(self.num_features, opt['hidden_dim'])
+        if opt.get('use_mlp', False):
+            self.m11 = nn.Linear(opt['hidden_dim'], opt['hidden_dim'])
+            self.m12 = nn.Linear(opt['hidden_dim'], opt['hidden_dim'])
+        if opt.get('use_labels', False):
+            opt['hidden_dim'] = opt['hidden_dim'] + num_classes
+        self.hidden_dim = opt['hidden_dim']
+        if opt.get('fc_out', False):
+            self.fc = nn.Linear(opt['hidden_dim'], opt['hidden_dim'])
+        self.m2 = nn.Linear(opt['hidden_dim'], num_classes)
+        if opt.get('batch_norm', False):
+            self.bn_in = torch.nn.BatchNorm1d(opt['hidden_dim'])
+            self.bn_out = torch.nn.BatchNorm1d(opt['hidden_dim'])
+        self.regularization_fns, self.regularization_coeffs = create_regularization_fns(self.opt)
+
+    def getNFE(self):
+        return self.odeblock.odefunc.nfe + self.odeblock.reg_odefunc.odefunc.nfe
+
+    def resetNFE(self):
+        self.odeblock.odefunc.nfe = 0
+        self.odeblock.reg_odefunc.odefunc.nfe = 0
+
+    def reset(self):
+        self.m1.reset_parameters()
+        self.m2.reset_parameters()
+
+    # ---- GNN.forward / GNNEarly.forward share everything but one line (GNN.py:17-74, GNN_early.py:42-105) ----------
+    def _encode(self, x, pos_encoding):
+        import torch.nn.functional as F
+        opt = self.opt
+        y = None
+        if opt.get('use_labels', False):
+            y = x[..., -self.num_classes:]
+            x = x[..., :-self.num_classes]
+        if opt.get('beltrami', False):
+            x = self.mx(F.dropout(x, opt['input_dropout'], training=self.training))
+            p = self.mp(F.dropout(pos_encoding, opt['input_dropout'], training=self.training))
+            x = torch.cat([x, p], dim=-1)
+        else:
+            x = self.m1(F.dropout(x, opt['input_dropout'], training=self.training))
+        if opt.get('use_mlp', False):
+            x = F.dropout(x, opt['dropout'], training=self.training)
+            x = F.dropout(x + self.m11(F.relu(x)), opt['dropout'], training=self.training)
+            x = F.dropout(x + self.m12(F.relu(x)), opt['dropout'], training=self.training)
+        if y is not None:
+            x = torch.cat([x, y], dim=-1)
+        if opt.get('batch_norm', False):
+            x = self.bn_in(x.transpose(-1, -2)).transpose(-1, -2) if x.dim() == 3 else self.bn_in(x)
+        if opt.get('augment', False):
+            x = torch.cat([x, torch.zeros_like(x)], dim=-1)
+        return x
+
+    def _decode(self, z, width):
+        import torch.nn.functional as F
+        if self.opt.get('augment', False):
+            z = torch.split(z, width // 2, dim=-1)[0]
+        z = F.relu(z)
+        if self.opt.get('fc_out', False):
+            z = F.relu(self.fc(z))
+        z = F.dropout(z, self.opt['dropout'], training=self.training)
+        return self.m2(z)
+
+    def _forward(self, x, graph_data, x2=None, pos_encoding=None):
+        x = self._encode(x, pos_encoding)
+        self.odeblock.set_x0(x)
+        self.graph_data.new_graph(graph_data, x.shape[-2])
+        if self.training and self.odeblock.nreg > 0:
+            z, self.reg_states = self.odeblock(x, self.graph_data, x2)
+        else:
+            z = self.odeblock(x, self.graph_data, x2)
+        return self._decode(z, x.shape[-1])
+
+    def __repr__(self):
+        return self.__class__.__name__

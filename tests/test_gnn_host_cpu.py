@@ -1,0 +1,123 @@
+"""CPU (emulated C ABI): the model wrappers around the hot path - GNN / GNNEarly (mirrors of the reference's
+src/GNN.py, src/GNN_early.py, src/base_classes.py:137-186): encoder -> ODE block -> relu -> decoder against the
+oracle, and the early-stopping test-time integrator end to end."""
+import types
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+import helpers
+from helpers import assert_close
+from oracle import funcs, graph as og, integrate as oint
+
+CPU = torch.device('cpu')
+T64 = lambda a: torch.tensor(np.asarray(a.detach() if torch.is_tensor(a) else a), dtype=torch.float64)
+
+OPT = {'hidden_dim': 16, 'block': 'constant', 'function': 'laplacian', 'max_nfe': 10000, 'no_alpha_sigmoid': False,
+       'add_source': True, 'augment': False, 'adjoint': False, 'tol_scale': 1.0, 'tol_scale_adjoint': 1.0,
+       'data_norm': 'rw', 'self_loop_weight': 1.0, 'method': 'rk4', 'step_size': 1.0, 'max_iters': 100,
+       'adjoint_method': 'rk4', 'adjoint_step_size': 1.0, 'leaky_relu_slope': 0.2, 'heads': 4, 'attention_dim': 16,
+       'attention_norm_idx': 0, 'reweight_attention': False, 'beltrami': False, 'attention_type': 'scaled_dot',
+       'square_plus': False, 'mix_features': False, 'multi_modal': False, 'kinetic_energy': None,
+       'jacobian_norm2': None, 'total_deriv': None, 'directional_penalty': None, 'time': 3.0, 'use_mlp': False,
+       'use_labels': False, 'fc_out': False, 'batch_norm': False, 'input_dropout': 0.0, 'dropout': 0.0,
+       'max_test_steps': 100, 'earlystopxT': 2.0}
+
+
+@pytest.fixture
+def host(emulated_abi, monkeypatch):
+    monkeypatch.setattr(helpers, 'DEVICE', 'cpu')
+    return emulated_abi
+
+
+@pytest.mark.parametrize('batched', [False, True])
+@pytest.mark.parametrize('adjoint', [False, True])
+def test_gnn_logits_and_gradients_match_the_oracle_composition(host, batched, adjoint):
+    import grand_b200
+    n, e, feats, classes = 120, 800, 20, 4
+    torch.manual_seed(0)
+    model = grand_b200.GNN(dict(OPT, adjoint=adjoint), classes, feats, CPU)
+    model.train()
+    func = model.odeblock.odefunc
+    with torch.no_grad():
+        func.alpha_train.fill_(0.4)
+        func.beta_train.fill_(0.2)
+    ei = og.shaped_graph(n, e, 6)
+    x = torch.randn(n, feats)
+    labels = torch.randint(0, classes, (n,))
+    wrap = (lambda t: t[None]) if batched else (lambda t: t)
+    logits = model(wrap(x), wrap(torch.tensor(ei)))
+    assert logits.shape == ((1, n, classes) if batched else (n, classes))
+    # getNFE adds odefunc.nfe and reg_odefunc.odefunc.nfe, which are the SAME object in the reference too
+    # (base_classes.py:43,174-175): 12 evaluations read as 24
+    assert func.nfe == 12 and model.getNFE() == 24
+    loss = F.cross_entropy(logits.reshape(n, classes), labels)
+    params = [model.m1.weight, model.m1.bias, model.m2.weight, model.m2.bias, func.alpha_train, func.beta_train]
+    grads = torch.autograd.grad(loss, params)
+    # oracle composition in fp64
+    ei_n, w = og.reset_graph_data(ei, None, n, 'rw', 1.0)
+    leaves = [T64(p).requires_grad_(True) for p in params]
+    h0 = T64(x) @ leaves[0].t() + leaves[1]
+    x0 = h0.detach()                                       # ODEblock.set_x0: detached clone (base_classes.py:53-55)
+
+    class Ref(torch.nn.Module):
+        def forward(self, t, y):
+            return funcs.laplacian_f(y, torch.tensor(ei_n), T64(w), leaves[4], leaves[5], x0)
+
+    solve = oint.odeint_adjoint if adjoint else oint.odeint
+    kw = dict(adjoint_params=(leaves[4], leaves[5])) if adjoint else {}
+    z = solve(Ref(), h0, [0., 3.0], 'rk4', 1.0, **kw)[1]
+    ref_logits = F.relu(z) @ leaves[2].t() + leaves[3]
+    ref = torch.autograd.grad(F.cross_entropy(ref_logits, labels), leaves)
+    assert_close(logits.reshape(n, classes), ref_logits, 1e-4, 'logits')
+    for g, r, name in zip(grads, ref, ('dm1.w', 'dm1.b', 'dm2.w', 'dm2.b', 'dalpha', 'dbeta')):
+        assert_close(g, r, 2e-4, name)
+    model.resetNFE()
+    assert model.getNFE() == 0
+
+
+def test_gnn_early_runs_the_early_stop_integrator_at_test_time(host):
+    import grand_b200
+    n, e, feats, classes = 100, 700, 12, 3
+    torch.manual_seed(1)
+    model = grand_b200.GNNEarly(dict(OPT, time=2.0), classes, feats, CPU)
+    ei = torch.tensor(og.shaped_graph(n, e, 2))
+    x = torch.randn(n, feats)
+    labels = torch.randint(0, classes, (n,))
+    idx = torch.randperm(n)
+    masks = [torch.zeros(n, dtype=torch.bool) for _ in range(3)]
+    for m, sl in zip(masks, (idx[:30], idx[30:60], idx[60:])):
+        m[sl] = True
+    data = types.SimpleNamespace(y=labels, train_mask=masks[0], val_mask=masks[1], test_mask=masks[2])
+    model.set_solver_data(data)
+    model.train()
+    out_train = model(x, ei)                               # training: the ordinary integrator over [0, T]
+    assert model.odeblock.test_integrator.solver is None and model.odeblock.odefunc.nfe == 8
+    model.eval()
+    model.resetNFE()
+    with torch.no_grad():
+        out = model(x, ei)                                 # test time: [0, earlystopxT * T] = 4 rk4 steps, decoded after each
+    s = model.odeblock.test_integrator.solver
+    assert out.shape == out_train.shape == (n, classes) and model.odeblock.odefunc.nfe == 16 and s.n_evaluations == 4
+    assert 0 < s.best_time <= 4.0 and 0 <= s.best_test <= 1 and s.best_val > 0
+    assert torch.equal(model.odeblock.test_integrator.m2_weight, model.m2.weight.data)
+
+
+def test_base_gnn_option_branches_build_and_run(host):
+    """beltrami (mx | mp), use_mlp, use_labels, fc_out, batch_norm, augment: shapes and hidden_dim bookkeeping"""
+    import grand_b200
+    n, e, feats, classes = 60, 400, 10, 3
+    opt = dict(OPT, beltrami=True, feat_hidden_dim=8, pos_enc_dim=6, pos_enc_hidden_dim=4, use_mlp=True, use_labels=True,
+               fc_out=True, batch_norm=True, augment=True, time=1.0)
+    model = grand_b200.GNN(opt, classes, feats, CPU)
+    assert opt['hidden_dim'] == 8 + 4 + classes and model.hidden_dim == 15
+    assert model.odeblock.odefunc.in_features == 30                     # augmented: 2 x hidden_dim
+    ei = torch.tensor(og.shaped_graph(n, e, 3))
+    x = torch.cat([torch.randn(n, feats), F.one_hot(torch.randint(0, classes, (n,)), classes).float()], dim=1)
+    model.train()
+    out = model(x, ei, pos_encoding=torch.randn(n, 6))
+    assert out.shape == (n, classes)
+    out.sum().backward()
+    assert model.mx.weight.grad is not None and model.mp.weight.grad is not None and model.fc.weight.grad is not None
