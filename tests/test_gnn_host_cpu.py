@@ -12,8 +12,8 @@ import helpers
 from helpers import assert_close
 from oracle import funcs, graph as og, integrate as oint
 
-CPU = torch.device('cpu')
-T64 = lambda a: torch.tensor(np.asarray(a.detach() if torch.is_tensor(a) else a), dtype=torch.float64)
+T64 = lambda a: torch.tensor(np.asarray(a.detach().cpu() if torch.is_tensor(a) else a), dtype=torch.float64)
+D = lambda t: t.to(helpers.device())          # 'cpu' under the emulated ABI, 'cuda' when the opt-in GPU tests call these
 
 OPT = {'hidden_dim': 16, 'block': 'constant', 'function': 'laplacian', 'max_nfe': 10000, 'no_alpha_sigmoid': False,
        'add_source': True, 'augment': False, 'adjoint': False, 'tol_scale': 1.0, 'tol_scale_adjoint': 1.0,
@@ -38,17 +38,17 @@ def test_gnn_logits_and_gradients_match_the_oracle_composition(host, batched, ad
     import grand_b200
     n, e, feats, classes = 120, 800, 20, 4
     torch.manual_seed(0)
-    model = grand_b200.GNN(dict(OPT, adjoint=adjoint), classes, feats, CPU)
+    model = grand_b200.GNN(dict(OPT, adjoint=adjoint), classes, feats, helpers.device()).to(helpers.device())
     model.train()
     func = model.odeblock.odefunc
     with torch.no_grad():
         func.alpha_train.fill_(0.4)
         func.beta_train.fill_(0.2)
     ei = og.shaped_graph(n, e, 6)
-    x = torch.randn(n, feats)
-    labels = torch.randint(0, classes, (n,))
+    x = D(torch.randn(n, feats))
+    labels = D(torch.randint(0, classes, (n,)))
     wrap = (lambda t: t[None]) if batched else (lambda t: t)
-    logits = model(wrap(x), wrap(torch.tensor(ei)))
+    logits = model(wrap(x), wrap(D(torch.tensor(ei))))
     assert logits.shape == ((1, n, classes) if batched else (n, classes))
     # getNFE adds odefunc.nfe and reg_odefunc.odefunc.nfe, which are the SAME object in the reference too
     # (base_classes.py:43,174-175): 12 evaluations read as 24
@@ -70,7 +70,7 @@ def test_gnn_logits_and_gradients_match_the_oracle_composition(host, batched, ad
     kw = dict(adjoint_params=(leaves[4], leaves[5])) if adjoint else {}
     z = solve(Ref(), h0, [0., 3.0], 'rk4', 1.0, **kw)[1]
     ref_logits = F.relu(z) @ leaves[2].t() + leaves[3]
-    ref = torch.autograd.grad(F.cross_entropy(ref_logits, labels), leaves)
+    ref = torch.autograd.grad(F.cross_entropy(ref_logits, labels.cpu()), leaves)
     assert_close(logits.reshape(n, classes), ref_logits, 1e-4, 'logits')
     for g, r, name in zip(grads, ref, ('dm1.w', 'dm1.b', 'dm2.w', 'dm2.b', 'dalpha', 'dbeta')):
         assert_close(g, r, 2e-4, name)
@@ -82,14 +82,15 @@ def test_gnn_early_runs_the_early_stop_integrator_at_test_time(host):
     import grand_b200
     n, e, feats, classes = 100, 700, 12, 3
     torch.manual_seed(1)
-    model = grand_b200.GNNEarly(dict(OPT, time=2.0), classes, feats, CPU)
-    ei = torch.tensor(og.shaped_graph(n, e, 2))
-    x = torch.randn(n, feats)
-    labels = torch.randint(0, classes, (n,))
+    model = grand_b200.GNNEarly(dict(OPT, time=2.0), classes, feats, helpers.device()).to(helpers.device())
+    ei = D(torch.tensor(og.shaped_graph(n, e, 2)))
+    x = D(torch.randn(n, feats))
+    labels = D(torch.randint(0, classes, (n,)))
     idx = torch.randperm(n)
     masks = [torch.zeros(n, dtype=torch.bool) for _ in range(3)]
     for m, sl in zip(masks, (idx[:30], idx[30:60], idx[60:])):
         m[sl] = True
+    masks = [D(m) for m in masks]
     data = types.SimpleNamespace(y=labels, train_mask=masks[0], val_mask=masks[1], test_mask=masks[2])
     model.set_solver_data(data)
     model.train()
@@ -111,13 +112,13 @@ def test_base_gnn_option_branches_build_and_run(host):
     n, e, feats, classes = 60, 400, 10, 3
     opt = dict(OPT, beltrami=True, feat_hidden_dim=8, pos_enc_dim=6, pos_enc_hidden_dim=4, use_mlp=True, use_labels=True,
                fc_out=True, batch_norm=True, augment=True, time=1.0)
-    model = grand_b200.GNN(opt, classes, feats, CPU)
+    model = grand_b200.GNN(opt, classes, feats, helpers.device()).to(helpers.device())
     assert opt['hidden_dim'] == 8 + 4 + classes and model.hidden_dim == 15
     assert model.odeblock.odefunc.in_features == 30                     # augmented: 2 x hidden_dim
-    ei = torch.tensor(og.shaped_graph(n, e, 3))
-    x = torch.cat([torch.randn(n, feats), F.one_hot(torch.randint(0, classes, (n,)), classes).float()], dim=1)
+    ei = D(torch.tensor(og.shaped_graph(n, e, 3)))
+    x = D(torch.cat([torch.randn(n, feats), F.one_hot(torch.randint(0, classes, (n,)), classes).float()], dim=1))
     model.train()
-    out = model(x, ei, pos_encoding=torch.randn(n, 6))
+    out = model(x, ei, pos_encoding=D(torch.randn(n, 6)))
     assert out.shape == (n, classes)
     out.sum().backward()
     assert model.mx.weight.grad is not None and model.mp.weight.grad is not None and model.fc.weight.grad is not None

@@ -358,3 +358,17 @@ def test_two_phase_adjoint_is_bit_identical_to_the_single_call(monkeypatch):
         assert block.odefunc.nfe == 16
     for a, b in zip(*results):
         assert torch.equal(a, b)
+
+
+# ---- model wrappers (GNN / GNNEarly): the CPU tests of tests/test_gnn_host_cpu.py on the device -------------------
+@pytest.mark.parametrize('batched', [False, True])
+@pytest.mark.parametrize('adjoint', [False, True])
+def test_gnn_logits_and_gradients(batched, adjoint):
+    import test_gnn_host_cpu as tg
+    tg.test_gnn_logits_and_gradients_match_the_oracle_composition(None, batched, adjoint)
+
+
+def test_gnn_early_and_option_branches():
+    import test_gnn_host_cpu as tg
+    tg.test_gnn_early_runs_the_early_stop_integrator_at_test_time(None)
+    tg.test_base_gnn_option_branches_build_and_run(None)
