@@ -3,7 +3,7 @@
 
     python scripts/sweep_variants.py build            # here (no GPU): compile every variant, print registers / spills
     python scripts/sweep_variants.py run [--workload c4] [--steps 3]   # on the GPU box, ONE gpurun call:
-        for every built variant: a parity spot check (tests/test_gpu_transformer.py -k fused_path), then
+        for every built variant: (with --check) a parity spot check (tests/test_gpu_transformer.py), then
         bench.py with GRANDB200_LIB pointing at it; lines land in gpurun_out/sweep_<workload>_<tag>.json and a
         table in gpurun_out/sweep_<workload>.md
 
@@ -88,7 +88,7 @@ def build(tags):
         print('| ' + ' | '.join(r) + ' |')
 
 
-def run(tags, workload, steps):
+def run(tags, workload, steps, check=False):
     out_dir = os.path.join(ROOT, 'gpurun_out')
     os.makedirs(out_dir, exist_ok=True)
     table = ['| variant | parity spot check | ms/step | evals/s | nl_fwd ms | nl_adj_rows ms |', '|---|---|---|---|---|---|']
@@ -98,13 +98,15 @@ def run(tags, workload, steps):
             table.append(f'| {tag} | library not built | | | | |')
             continue
         env = dict(os.environ, GRANDB200_LIB=path)
-        chk = subprocess.run([sys.executable, '-m', 'pytest', os.path.join(ROOT, 'tests', 'test_gpu_transformer.py'), '-q', '-x',
-                              '-m', 'gpu', '-k', 'fused_path or hub_segments or scaled_dot_forward'], env=env, cwd=ROOT,
-                             stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
-        ok = 'pass' if chk.returncode == 0 else 'FAIL'
-        if chk.returncode != 0:
-            with open(os.path.join(out_dir, f'sweep_{workload}_{tag}_pytest.log'), 'w') as fh:
-                fh.write(chk.stdout)
+        ok = 'not run'
+        if check:                                      # ~1 GPU-minute per variant: use it on the candidates worth keeping
+            chk = subprocess.run([sys.executable, '-m', 'pytest', os.path.join(ROOT, 'tests', 'test_gpu_transformer.py'), '-q',
+                                  '-x', '-m', 'gpu', '-k', 'fused_path or hub_segments or scaled_dot_forward'], env=env,
+                                 cwd=ROOT, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+            ok = 'pass' if chk.returncode == 0 else 'FAIL'
+            if chk.returncode != 0:
+                with open(os.path.join(out_dir, f'sweep_{workload}_{tag}_pytest.log'), 'w') as fh:
+                    fh.write(chk.stdout)
         cmd = [sys.executable, os.path.join(ROOT, 'bench.py'), '--workload', workload, '--steps', str(steps), '--warmup', '3',
                '--no-cpu-baseline', '--no-gpu-reference']
         if workload in ('c1', 'c2', 'c3'):
@@ -134,6 +136,7 @@ def main():
     ap.add_argument('--only', default='', help='comma-separated variant tags (default: all)')
     ap.add_argument('--workload', default='c4')
     ap.add_argument('--steps', type=int, default=3)
+    ap.add_argument('--check', action='store_true', help='run the parity spot check before each bench (about 1 GPU-minute each)')
     args = ap.parse_args()
     tags = [t for t in args.only.split(',') if t] or list(VARIANTS)
     for t in tags:
@@ -142,7 +145,7 @@ def main():
     if args.mode == 'build':
         build([t for t in tags if t != 'default'])
     else:
-        run(tags, args.workload, args.steps)
+        run(tags, args.workload, args.steps, args.check)
 
 
 if __name__ == '__main__':
