@@ -305,8 +305,10 @@ class ODEFuncTransformerAtt(ODEFunc):
         a, d = wq.shape
 
         def finish():
-            dx_share, grads = P.nl_local_vjp_cols(half)
-            dx = halo.reduce_scatter_rows(dx_share)
+            dx_share = P.nl_local_vjp_cols(half)
+            pending = halo.reduce_scatter_rows_async(dx_share)      # runs under the weight-gradient GEMM
+            grads = P.nl_local_vjp_weights(half)
+            dx = pending.wait()
             halo.all_reduce_(grads)
             dwq, dwk, dbq, dbk, dalpha, dbeta = P.unpack_nl_grads(grads, a, d)
             named = ((self.alpha_train, dalpha.reshape(self.alpha_train.shape)), (self.beta_train, dbeta.reshape(())),

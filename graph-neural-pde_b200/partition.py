@@ -104,6 +104,19 @@ class Halo:
         self.n_scatters += 1
         return out
 
+    def reduce_scatter_rows_async(self, full):
+        """start the reduce-scatter and return a pending handle (wait() -> this rank's [S, d] rows of the sum)"""
+        full = full.contiguous()
+        out = full.new_empty((self.part.slab,) + tuple(full.shape[1:]))
+        self.bytes_in += (self.part.world - 1) * out.numel() * out.element_size()
+        self.n_scatters += 1
+        if self.backend == 'gloo':                            # gloo has no reduce_scatter: all_reduce + slice on wait()
+            work = self.dist.all_reduce(full, group=self.group, async_op=True)
+            lo = self.part.rank * self.part.slab
+            return PendingScatter(full, work, lambda: out.copy_(full[lo:lo + self.part.slab]))
+        work = self.dist.reduce_scatter_tensor(out, full, group=self.group, async_op=True)
+        return PendingScatter(full, work, lambda: out)
+
     def all_reduce_(self, t):
         self.dist.all_reduce(t, group=self.group)
         return t
@@ -123,6 +136,21 @@ class PendingGather:
         return self._full
 
 
+class PendingScatter:
+    """a reduce-scatter in flight (Halo.reduce_scatter_rows_async); keeps the send buffer alive until wait()"""
+
+    def __init__(self, full, work, result):
+        self._full, self._work, self._result = full, work, result
+
+    def wait(self):
+        if self._work is not None:
+            self._work.wait()
+            self._work = None
+        out = self._result()
+        self._full = None
+        return out
+
+
 class LoopbackHalo:
     """world == 1 stand-in (no process group needed): the collectives are identities"""
 
@@ -140,6 +168,10 @@ class LoopbackHalo:
 
     def reduce_scatter_rows(self, full):
         return full.contiguous()
+
+    def reduce_scatter_rows_async(self, full):
+        c = full.contiguous()
+        return PendingScatter(c, None, lambda: c)
 
     def all_reduce_(self, t):
         return t
@@ -271,8 +303,9 @@ def _nl_adjoint_phase(lib, h, phase, workspace):
 
 
 def nl_local_vjp_cols(h):
-    """second half: column pass + the dense tail.  Returns (dx_share [N_pad, d], flat parameter-gradient share), the
-    same values nl_local_vjp returns."""
+    """second half, first part: column pass + dx += [dq|dk] [Wq;Wk].  Returns dx_share [N_pad, d] (what
+    nl_local_vjp returns as its second value) - ready for the reduce-scatter, which can then run while
+    nl_local_vjp_weights() forms the weight gradients."""
     from .ops import _nl_workspace
     lib = _lib.load()
     x_full = h.x_full
@@ -282,13 +315,23 @@ def nl_local_vjp_cols(h):
     w_cat = torch.cat([h.wq, h.wk], dim=0)
     _lib.check(lib.gb_linear_bwd_x(h.dqk.data_ptr(), 2 * a, n_pad, 2 * a, w_cat.data_ptr(), d, h.dx.data_ptr(), d, 1,
                                    _lib.stream()), 'gb_linear_bwd_x')
+    return h.dx
+
+
+def nl_local_vjp_weights(h):
+    """second half, second part: d[Wq;Wk] = [dq|dk]^T x, d[bq;bk] = column sums -> the flat parameter-gradient share
+    (third value of nl_local_vjp; its last two entries, dalpha / dbeta, were written by the column pass)"""
+    lib = _lib.load()
+    x_full = h.x_full
+    n_pad, d = x_full.shape
+    a = h.wq.shape[0]
     if h.want_w:
         ws = torch.empty(int(lib.gb_linear_bwd_w_workspace_bytes(n_pad, d, 2 * a)), dtype=torch.uint8,
                          device=x_full.device)
         _lib.check(lib.gb_linear_bwd_w(h.dqk.data_ptr(), 2 * a, x_full.data_ptr(), d, n_pad, d, 2 * a, h.grads.data_ptr(),
                                        h.grads.data_ptr() + 4 * 2 * a * d, ws.data_ptr(), ws.numel(), _lib.stream()),
                    'gb_linear_bwd_w')
-    return h.dx, h.grads
+    return h.grads
 
 
 def diffusion_local_forward(part, plan, vals, x_full, x0_slab, alpha_train, beta_train, alpha_sigmoid):
