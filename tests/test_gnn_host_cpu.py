@@ -122,3 +122,36 @@ def test_base_gnn_option_branches_build_and_run(host):
     assert out.shape == (n, classes)
     out.sum().backward()
     assert model.mx.weight.grad is not None and model.mp.weight.grad is not None and model.fc.weight.grad is not None
+
+
+@pytest.mark.parametrize('function,block', [('laplacian', 'constant'), ('transformer', 'attention'), ('laplacian', 'mixed')])
+def test_a_few_optimiser_steps_reduce_the_training_loss(host, function, block):
+    """the whole training step of run_GNN.py (model.train(); loss = CE(out[train_mask]); backward; Adam step,
+    src/graph_datasets/run_GNN.py:84-118) on a planted-partition graph: gradients have the right sign end to end"""
+    import grand_b200
+    n, classes, feats = 90, 3, 8
+    g = torch.Generator().manual_seed(0)
+    labels = torch.arange(n) % classes
+    same = labels[:, None] == labels[None, :]
+    prob = torch.where(same, torch.tensor(0.12), torch.tensor(0.01))
+    adj = torch.rand(n, n, generator=g) < prob
+    adj = (adj | adj.t()) & ~torch.eye(n, dtype=torch.bool)
+    ei = D(adj.nonzero().t().contiguous())
+    x = D(torch.randn(n, feats, generator=g) + 0.5 * F.one_hot(labels, feats).float())
+    labels = D(labels)
+    train_mask = D(torch.rand(n, generator=g) < 0.6)
+    torch.manual_seed(0)
+    opt = dict(OPT, function=function, block=block, adjoint=(block != 'mixed'), time=2.0, hidden_dim=16)
+    model = grand_b200.GNN(opt, classes, feats, helpers.device()).to(helpers.device())
+    optim = torch.optim.Adam(model.parameters(), lr=0.02)
+    losses = []
+    for _ in range(12):
+        model.train()
+        optim.zero_grad()
+        out = model(x, ei)
+        loss = F.cross_entropy(out[train_mask], labels[train_mask])
+        loss.backward()
+        optim.step()
+        model.resetNFE()
+        losses.append(float(loss.detach()))
+    assert all(np.isfinite(losses)) and losses[-1] < 0.8 * losses[0], losses
