@@ -505,7 +505,8 @@ def run_partitioned(args, cfg, device, rank, world):
     data.new_graph(ei, n)
     d = cfg['d']
     part = grand_b200.RowPartition(n, world, rank)
-    halo = grand_b200.Halo(part)
+    halo_kind = args.halo
+    halo = grand_b200.Halo(part) if halo_kind == 'dense' else grand_b200.SparseHalo(part)
     gen = torch.Generator(device=device).manual_seed(99 + rank)
     x_dev = torch.randn(part.slab, d, generator=gen, device=device)
     g_dev = torch.randn(part.slab, d, generator=gen, device=device)
@@ -514,6 +515,17 @@ def run_partitioned(args, cfg, device, rank, world):
     x_host = x_dev.cpu().pin_memory()
     block = build_block(cfg, device)
     block.set_partition(part, halo)
+    referenced = None
+    if halo_kind != 'dense':
+        train_pass(block, data, x_dev, g_dev)           # builds the per-peer index lists (SparseHalo.prepare)
+        frac = torch.tensor([halo.referenced_fraction], device=device)
+        dist.all_reduce(frac, op=dist.ReduceOp.MAX)
+        referenced = round(float(frac), 4)
+        if halo_kind == 'auto' and referenced > 0.7:   # dense halo (e.g. c4): whole slabs are cheaper than index lists
+            halo_kind, halo = 'dense', grand_b200.Halo(part)
+            block.set_partition(part, halo)
+        else:
+            halo_kind = 'sparse'
 
     for _ in range(max(args.warmup, 3)):
         evals, loss = train_pass(block, data, x_dev, g_dev)
@@ -605,7 +617,10 @@ def run_partitioned(args, cfg, device, rank, world):
                    'parallelism': f'1-D row partition over {world} GPUs ({part.slab} rows each), all-gather of the '
                                   f'state per evaluation + reduce-scatter of dL/dx per VJP (NCCL)',
                    'evals_per_step': evals, 'l2': 'inputs larger than L2 (no flush)',
-                   'overlapped_exchange': os.environ.get('GRANDB200_OVERLAP') == '1'},
+                   'overlapped_exchange': os.environ.get('GRANDB200_OVERLAP') == '1',
+                   'halo': halo_kind + (' (all_to_all_v of the referenced rows only)' if halo_kind == 'sparse' else
+                                        ' (all-gather / reduce-scatter of whole slabs)'),
+                   'remote_rows_referenced_max_over_ranks': referenced},
         'e2e': {'value': round(evals_e2e / (ms_e2e * 1e-3), 3), 'unit': 'evals/s',
                 'h2d_bytes_per_step': world * part.slab * d * 4, 'd2h_bytes_per_step': world * (part.slab * d * 4 + 4),
                 'ms_per_step': round(ms_e2e / args.steps, 3)},
@@ -643,9 +658,12 @@ def exchange_times(halo, part, d, device, n_gathers, n_scatters, step_ms):
         t = torch.tensor([a.elapsed_time(b) / 10], device=device)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         out[key] = round(float(t), 3)
-    recv = (part.world - 1) * part.slab * d * 4
-    out['all_gather_GBps_in'] = round(recv / (out['all_gather_ms'] * 1e-3) / 1e9, 1)
-    out['reduce_scatter_GBps_in'] = round(recv / (out['reduce_scatter_ms'] * 1e-3) / 1e9, 1)
+    recv_g = recv_s = (part.world - 1) * part.slab * d * 4
+    if hasattr(halo, 'recv_splits'):                     # SparseHalo: only the referenced rows travel
+        recv_g, recv_s = sum(halo.recv_splits) * d * 4, sum(halo.send_splits) * d * 4
+    out['all_gather_GBps_in'] = round(recv_g / (out['all_gather_ms'] * 1e-3) / 1e9, 1)
+    out['reduce_scatter_GBps_in'] = round(recv_s / (out['reduce_scatter_ms'] * 1e-3) / 1e9, 1)
+    out['bytes_in_per_all_gather'], out['bytes_in_per_reduce_scatter'] = recv_g, recv_s
     out['exchanges_per_step'] = {'all_gather': n_gathers, 'reduce_scatter': n_scatters}
     ex = n_gathers * out['all_gather_ms'] + n_scatters * out['reduce_scatter_ms']
     out['exchange_ms_per_step'] = round(ex, 2)
@@ -838,6 +856,9 @@ def main():
                     help='skip the torch-CUDA-ops comparator (N = 1 only)')
     ap.add_argument('--function', default='transformer', choices=['transformer', 'laplacian'],
                     help='transformer = GRAND-nl (BASELINE.json headline); laplacian = GRAND-l sweep of config 5')
+    ap.add_argument('--halo', default=os.environ.get('GRANDB200_HALO', 'dense'), choices=['dense', 'sparse', 'auto'],
+                    help='N > 1: exchange whole slabs (dense), only the rows the peers reference (sparse: R-MAT slabs '
+                         'reference ~25 %% of the others at 8 ranks), or decide from the measured fraction (auto)')
     ap.add_argument('--microbench', action='store_true',
                     help='isolated per-evaluation timing (SURVEY.md 8d): forward and adjoint evaluation alone, '
                          'L2 hot and L2 flushed, >= 100 iterations; 1 GPU')

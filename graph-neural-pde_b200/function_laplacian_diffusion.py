@@ -76,7 +76,9 @@ class LaplacianODEFunc(ODEFunc):
         return self._as_2d(x).shape[0] == self.partition[0].slab
 
     def prefetch_state(self, x):
-        pending = self.partition[1].all_gather_rows_async(self._as_2d(x).detach())
+        part, halo = self.partition
+        halo.prepare(self._plan(part.n_pad))
+        pending = halo.all_gather_rows_async(self._as_2d(x).detach())
         pending.src = x
         return pending
 
@@ -88,6 +90,7 @@ class LaplacianODEFunc(ODEFunc):
         part, halo = self.partition
         self._check_nfe()
         x2 = self._as_2d(x).detach().contiguous()
+        halo.prepare(self._plan(part.n_pad))
         if prefetched is not None and prefetched.src is x:
             x_full = prefetched.wait()
         else:

@@ -273,7 +273,8 @@ class ODEFuncTransformerAtt(ODEFunc):
 
     def prefetch_state(self, x):
         """start gathering the slabs of a state that a later eval_vjp_phased(…, prefetched=) call will evaluate"""
-        _part, halo = self.partition
+        part, halo = self.partition
+        halo.prepare(self._plan(part.n_pad))
         pending = halo.all_gather_rows_async(self._as_2d(x).detach())
         pending.src = x                                            # eval_vjp_phased checks identity against its `x`
         return pending
@@ -288,6 +289,7 @@ class ODEFuncTransformerAtt(ODEFunc):
         L = self.multihead_att_layer
         x2 = self._as_2d(x).detach().contiguous()
         self._check_nfe()
+        halo.prepare(self._plan(part.n_pad))
         if prefetched is not None and prefetched.src is x:
             x_full = prefetched.wait()
         else:

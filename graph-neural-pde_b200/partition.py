@@ -70,6 +70,9 @@ class Halo:
         self.bytes_in = 0                                     # bytes received so far (bench accounting)
         self.n_gathers = self.n_scatters = 0
 
+    def prepare(self, plan):
+        """hook for halos that need the graph (SparseHalo); the dense exchange needs nothing"""
+
     def all_gather_rows(self, slab):
         """[S, d] slab of every rank -> [N_pad, d] on every rank"""
         slab = slab.contiguous()
@@ -122,6 +125,147 @@ class Halo:
         return t
 
 
+class SparseHalo(Halo):
+    """Halo that exchanges only the REFERENCED rows (SURVEY.md 8e "refinement").
+
+    Rank p's kernels read x[j] only for the columns j its own edges point at, and its share of dL/dx is zero on every
+    other column it does not own.  On graphs whose slabs reference a small part of the other slabs (R-MAT: ~25 % at
+    P = 8, 38 % of the vertices are isolated) the all-gather / reduce-scatter of whole [N_pad, d] matrices moves
+    mostly rows nobody reads.  Here every pair of ranks exchanges index lists once per graph (`prepare`), and then
+
+        gather   send x_slab[rows peer q needs]  ->  all_to_all_v  ->  scatter into a zero [N_pad, d] matrix
+        scatter  send share[columns of peer q I touched]  ->  all_to_all_v  ->  out = share[own rows] + sum over peers,
+                 added peer after peer in rank order (indices unique per peer: deterministic, no float atomics)
+
+    Rows that are neither owned nor referenced stay exactly zero in the gathered matrix (the column pass and the
+    GEMMs run over all N_pad rows, but multiply them with zero coefficients)."""
+
+    def __init__(self, part, group=None):
+        super().__init__(part, group)
+        self._key = None
+
+    def prepare(self, plan):
+        """build the per-peer index lists for the graph of `plan` (this rank's edges, global column ids)"""
+        if self._key is plan:
+            return
+        part, dist, dev = self.part, self.dist, plan.colidx.device
+        cols = torch.unique(plan.colidx.long())                       # sorted
+        owner = torch.div(cols, part.slab, rounding_mode='floor')
+        remote = cols[owner != part.rank]
+        owner = owner[owner != part.rank]
+        need_counts = torch.bincount(owner, minlength=part.world)      # rows I need from each peer
+        give_counts = torch.empty_like(need_counts)
+        dist.all_to_all_single(give_counts, need_counts, group=self.group)
+        self.recv_splits = [int(v) for v in need_counts.tolist()]
+        self.send_splits = [int(v) for v in give_counts.tolist()]
+        wanted = torch.empty(sum(self.send_splits), dtype=torch.int64, device=dev)
+        dist.all_to_all_single(wanted, remote.contiguous(), self.send_splits, self.recv_splits, group=self.group)
+        self.recv_idx = remote.contiguous()                            # global positions of the rows I receive (peer order)
+        self.send_idx = (wanted - part.rank * part.slab).contiguous()  # my local rows each peer wants (peer order)
+        if self.send_idx.numel() and (int(self.send_idx.min()) < 0 or int(self.send_idx.max()) >= part.slab):
+            raise RuntimeError('SparseHalo: a peer asked for rows outside this slab')
+        self.referenced_fraction = float(remote.numel()) / max(1, part.n_pad - part.slab)
+        self.__dict__.pop('_ring', None)                              # other rows are referenced now: fresh zero buffers
+        self._key = plan
+
+    def _check(self):
+        if self._key is None:
+            raise RuntimeError('SparseHalo.prepare(plan) must run before the first exchange')
+
+    RING = 3       # gathered matrices alive at once under no_grad: the one in use, the prefetched one, one spare
+
+    def _gather_buffer(self, slab):
+        """[N_pad, d] matrix whose unreferenced rows are zero.  Under no_grad (forward integration, adjoint solve) the
+        result is consumed within the evaluation, so a small ring of persistent buffers is reused: only the owned and
+        referenced rows are rewritten, the rest was zeroed once (no 4 N d byte memset per exchange).  With autograd
+        recording, the gathered matrix is saved for backward and must not be overwritten: a fresh one each time."""
+        shape = (self.part.n_pad,) + tuple(slab.shape[1:])
+        if torch.is_grad_enabled():
+            return slab.new_zeros(shape)
+        key = (shape, slab.dtype, slab.device)
+        ring = self.__dict__.setdefault('_ring', {})
+        bufs, nxt = ring.get(key, ([], 0))
+        if len(bufs) < self.RING:
+            bufs.append(slab.new_zeros(shape))
+            buf = bufs[-1]
+        else:
+            buf = bufs[nxt % self.RING]
+        ring[key] = (bufs, nxt + 1)
+        return buf
+
+    def _finish_gather(self, slab, recv):
+        part = self.part
+        full = self._gather_buffer(slab)
+        full[part.rank * part.slab:(part.rank + 1) * part.slab] = slab
+        if recv.shape[0]:
+            full.index_copy_(0, self.recv_idx, recv)
+        return full
+
+    def _start_gather(self, slab, async_op):
+        self._check()
+        slab = slab.contiguous()
+        send = slab.index_select(0, self.send_idx)
+        recv = slab.new_empty((sum(self.recv_splits),) + tuple(slab.shape[1:]))
+        work = self.dist.all_to_all_single(recv, send, self.recv_splits, self.send_splits, group=self.group,
+                                           async_op=async_op)
+        self.bytes_in += recv.numel() * recv.element_size()
+        self.n_gathers += 1
+        return slab, send, recv, work
+
+    def all_gather_rows(self, slab):
+        slab, _send, recv, _ = self._start_gather(slab, False)
+        return self._finish_gather(slab, recv)
+
+    def all_gather_rows_async(self, slab):
+        slab_c, send, recv, work = self._start_gather(slab, True)
+        self.n_prefetched = getattr(self, 'n_prefetched', 0) + 1
+        return PendingExchange(slab, work, lambda: self._finish_gather(slab_c, recv), keep=(send,))
+
+    def _finish_scatter(self, full, recv):
+        part = self.part
+        out = full[part.rank * part.slab:(part.rank + 1) * part.slab].clone()
+        off = 0
+        for cnt in self.send_splits:                                   # peer after peer, rank order: a fixed order of adds
+            if cnt:
+                out.index_add_(0, self.send_idx[off:off + cnt], recv[off:off + cnt])
+            off += cnt
+        return out
+
+    def _start_scatter(self, full, async_op):
+        self._check()
+        full = full.contiguous()
+        send = full.index_select(0, self.recv_idx)                    # my share for the columns the peers own
+        recv = full.new_empty((sum(self.send_splits),) + tuple(full.shape[1:]))
+        work = self.dist.all_to_all_single(recv, send, self.send_splits, self.recv_splits, group=self.group,
+                                           async_op=async_op)
+        self.bytes_in += recv.numel() * recv.element_size()
+        self.n_scatters += 1
+        return full, send, recv, work
+
+    def reduce_scatter_rows(self, full):
+        full, _send, recv, _ = self._start_scatter(full, False)
+        return self._finish_scatter(full, recv)
+
+    def reduce_scatter_rows_async(self, full):
+        full, send, recv, work = self._start_scatter(full, True)
+        return PendingExchange(None, work, lambda: self._finish_scatter(full, recv), keep=(send,))
+
+
+class PendingExchange:
+    """an all_to_all_v in flight; wait() completes it and runs the local unpacking step"""
+
+    def __init__(self, src, work, finish, keep=()):
+        self.src, self._work, self._finish, self._keep = src, work, finish, keep
+
+    def wait(self):
+        if self._work is not None:
+            self._work.wait()
+            self._work = None
+        out = self._finish()
+        self._keep = ()
+        return out
+
+
 class PendingGather:
     """an all-gather in flight (Halo.all_gather_rows_async).  `src` is the tensor the caller asked to gather: the
     consumer checks identity before trusting the result."""
@@ -158,6 +302,9 @@ class LoopbackHalo:
         if part.world != 1:
             raise ValueError('LoopbackHalo is for a world of 1')
         self.part, self.bytes_in = part, 0
+
+    def prepare(self, plan):
+        pass
 
     def all_gather_rows(self, slab):
         return slab.contiguous()
@@ -375,6 +522,7 @@ class PartNlFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x_slab, wq, bq, wk, bk, alpha_train, beta_train, x0_slab, part, halo, plan, heads, alpha_sigmoid):
         x_slab = x_slab.contiguous()
+        halo.prepare(plan)
         x_full = halo.all_gather_rows(x_slab)
         out, q = nl_local_forward(part, plan, x_full, x_slab, wq.contiguous(), bq.contiguous(), wk.contiguous(),
                                   alpha_train, beta_train, x0_slab, heads, alpha_sigmoid)
@@ -409,6 +557,7 @@ class PartDiffusionFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x_slab, vals, alpha_train, beta_train, x0_slab, part, halo, plan, alpha_sigmoid):
+        halo.prepare(plan)
         x_full = halo.all_gather_rows(x_slab.contiguous())
         out = diffusion_local_forward(part, plan, vals, x_full, x0_slab, alpha_train, beta_train, alpha_sigmoid)
         ctx.save_for_backward(x_full, vals, alpha_train, beta_train, x0_slab)
@@ -434,6 +583,7 @@ def nl_eval_vjp_part(part, halo, plan, x_slab, g_slab, wq, bq, wk, alpha_train, 
                      alpha_sigmoid):
     """partitioned f and VJP in one fused pass (adjoint solver): (f_slab, dx_slab, flat parameter gradients)"""
     x_slab = x_slab.contiguous()
+    halo.prepare(plan)
     x_full = halo.all_gather_rows(x_slab)
     from .ops import _nl_q
     q = _nl_q(x_slab, wq, bq)

@@ -209,7 +209,7 @@ def _make_block(function='transformer'):
     return block
 
 
-def _gloo_worker(rank, world, port, n, d, ret, overlap=False, function='transformer'):
+def _gloo_worker(rank, world, port, n, d, ret, overlap=False, function='transformer', sparse=False):
     if overlap:
         os.environ['GRANDB200_OVERLAP'] = '1'
     sys.path.insert(0, ROOT)
@@ -226,7 +226,8 @@ def _gloo_worker(rank, world, port, n, d, ret, overlap=False, function='transfor
     os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
     dist.init_process_group('gloo', rank=rank, world_size=world)
     try:
-        ei = torch.tensor(og.shaped_graph(n, 6 * n // 2 * 2, 9))
+        # sparse halo: a graph thin enough that every slab references only part of the others
+        ei = torch.tensor(og.shaped_graph(n, (n if sparse else 6 * n) // 2 * 2, 9))
         gen = torch.Generator().manual_seed(0)
         x, gz = torch.randn(n, d, generator=gen), torch.randn(n, d, generator=gen)
         data = grand_b200.GraphData()
@@ -235,13 +236,17 @@ def _gloo_worker(rank, world, port, n, d, ret, overlap=False, function='transfor
         z_ref, g_ref, nfe_ref = _train_pass(_make_block(function), data, x, gz)
         # partitioned: this rank's slab in, this rank's slab out
         part = grand_b200.RowPartition(n, world, rank)
-        halo = grand_b200.Halo(part)
+        halo = grand_b200.SparseHalo(part) if sparse else grand_b200.Halo(part)
         block = _make_block(function)
         block.set_partition(part, halo)
         del emu.calls[:]
         z, grads, nfe = _train_pass(block, data, part.to_slab(x), part.to_slab(gz))
         assert nfe == nfe_ref == 16 and z.shape == (part.slab, d)
         assert halo.n_gathers == 16 and halo.n_scatters == 8          # one gather per evaluation, one scatter per VJP
+        if sparse:                                                    # only referenced rows travelled
+            assert 0 < halo.referenced_fraction < 0.9
+            dense_bytes = 24 * (world - 1) * part.slab * d * 4
+            assert halo.bytes_in < 0.9 * dense_bytes
         if overlap:
             # two-phase adjoint: 7 of the 8 adjoint evaluations find their state already gathered, and every row pass
             # is followed by the next gather BEFORE its own column pass is issued
@@ -294,6 +299,17 @@ def test_two_rank_laplacian_block_path(overlap):
     ret = mgr.dict()
     mp.spawn(_gloo_worker, args=(world, _free_port(), 157, 32, ret, overlap, 'laplacian'), nprocs=world, join=True)
     assert dict(ret) == {0: 'ok', 1: 'ok'}
+
+
+@pytest.mark.parametrize('world,overlap,function', [(2, False, 'transformer'), (3, True, 'transformer'),
+                                                     (3, False, 'laplacian'), (2, True, 'laplacian')])
+def test_sparse_halo_block_path(world, overlap, function):
+    """SparseHalo (only referenced rows exchanged, all_to_all_v) under the real block path: same numbers as the
+    single-process block, fewer bytes than the dense exchange; serial and overlapped, GRAND-nl and GRAND-l"""
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_gloo_worker, args=(world, _free_port(), 157, 32, ret, overlap, function, True), nprocs=world, join=True)
+    assert dict(ret) == {r: 'ok' for r in range(world)}
 
 
 def test_block_api_world_of_one_matches_unpartitioned(host):
