@@ -1,6 +1,10 @@
-"""Mirror of the reference's src/model_configurations.py:17-44: the string -> class registry behind
-the `--block` and `--function` flags (src/graph_datasets/run_GNN.py:318-319).  Blocks: constant, attention, mixed, hard_attention; functions: laplacian, transformer.  The others
-(rewire_attention, GAT) raise, naming the key."""
+"""The string -> class registry behind the `--block` and `--function` flags: same two entry points and the same two
+exception types as the reference's src/model_configurations.py:17-44 (callers: src/GNN.py:11-13,
+src/graph_datasets/run_GNN.py:318-319), kept as lookup tables.
+
+Blocks: constant, attention, mixed, hard_attention; functions: laplacian, transformer.  Keys the reference knows but
+this package does not accelerate raise NotImplementedError naming the key; unknown keys raise the reference's
+BlockNotDefined / FunctionNotDefined."""
 from .function_transformer_attention import ODEFuncTransformerAtt
 from .function_laplacian_diffusion import LaplacianODEFunc
 from .block_transformer_attention import AttODEblock
@@ -17,32 +21,27 @@ class FunctionNotDefined(Exception):
     pass
 
 
+BLOCKS = {'constant': ConstantODEblock, 'attention': AttODEblock, 'mixed': MixedODEblock,
+          'hard_attention': HardAttODEblock}
+FUNCTIONS = {'laplacian': LaplacianODEFunc, 'transformer': ODEFuncTransformerAtt}
+NOT_ACCELERATED = {
+    'rewire_attention': "block 'rewire_attention' (block_transformer_rewiring.py: kNN / GDC rewiring inside the block) "
+                        'is outside the accelerated path (SURVEY.md 2.1)',
+    'GAT': "function 'GAT' (function_GAT_attention.py) is outside the accelerated path",
+}
+
+
+def _lookup(table, key, missing):
+    if key in table:
+        return table[key]
+    if key in NOT_ACCELERATED:
+        raise NotImplementedError(NOT_ACCELERATED[key])
+    raise missing
+
+
 def set_block(opt):
-    ode_str = opt['block']
-    if ode_str == 'attention':
-        block = AttODEblock
-    elif ode_str == 'constant':
-        block = ConstantODEblock
-    elif ode_str == 'mixed':
-        block = MixedODEblock
-    elif ode_str == 'hard_attention':
-        block = HardAttODEblock
-    elif ode_str == 'rewire_attention':
-        raise NotImplementedError("block 'rewire_attention' (block_transformer_rewiring.py: kNN / GDC rewiring inside "
-                                  'the block) is outside the accelerated path (SURVEY.md 2.1)')
-    else:
-        raise BlockNotDefined
-    return block
+    return _lookup(BLOCKS, opt['block'], BlockNotDefined)
 
 
 def set_function(opt):
-    ode_str = opt['function']
-    if ode_str == 'laplacian':
-        f = LaplacianODEFunc
-    elif ode_str == 'transformer':
-        f = ODEFuncTransformerAtt
-    elif ode_str == 'GAT':
-        raise NotImplementedError("function 'GAT' (function_GAT_attention.py) is outside the accelerated path")
-    else:
-        raise FunctionNotDefined
-    return f
+    return _lookup(FUNCTIONS, opt['function'], FunctionNotDefined)
