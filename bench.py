@@ -506,7 +506,7 @@ def run_partitioned(args, cfg, device, rank, world):
     d = cfg['d']
     part = grand_b200.RowPartition(n, world, rank)
     halo_kind = args.halo
-    halo = grand_b200.Halo(part) if halo_kind == 'dense' else grand_b200.SparseHalo(part)
+    halo = {'dense': grand_b200.Halo, 'compact': grand_b200.CompactHalo}.get(halo_kind, grand_b200.SparseHalo)(part)
     gen = torch.Generator(device=device).manual_seed(99 + rank)
     x_dev = torch.randn(part.slab, d, generator=gen, device=device)
     g_dev = torch.randn(part.slab, d, generator=gen, device=device)
@@ -524,7 +524,7 @@ def run_partitioned(args, cfg, device, rank, world):
         if halo_kind == 'auto' and referenced > 0.7:   # dense halo (e.g. c4): whole slabs are cheaper than index lists
             halo_kind, halo = 'dense', grand_b200.Halo(part)
             block.set_partition(part, halo)
-        else:
+        elif halo_kind == 'auto':
             halo_kind = 'sparse'
 
     for _ in range(max(args.warmup, 3)):
@@ -618,8 +618,11 @@ def run_partitioned(args, cfg, device, rank, world):
                                   f'state per evaluation + reduce-scatter of dL/dx per VJP (NCCL)',
                    'evals_per_step': evals, 'l2': 'inputs larger than L2 (no flush)',
                    'overlapped_exchange': os.environ.get('GRANDB200_OVERLAP') == '1',
-                   'halo': halo_kind + (' (all_to_all_v of the referenced rows only)' if halo_kind == 'sparse' else
-                                        ' (all-gather / reduce-scatter of whole slabs)'),
+                   'halo': halo_kind + {'sparse': ' (all_to_all_v of the referenced rows only)',
+                                        'compact': ' (all_to_all_v of the referenced rows only; local graph relabelled to '
+                                                   '[own slab | referenced rows])'}.get(
+                                            halo_kind, ' (all-gather / reduce-scatter of whole slabs)'),
+                   'rows_of_the_local_problem_rank0': getattr(halo, 'view', part).n_pad,
                    'remote_rows_referenced_max_over_ranks': referenced},
         'e2e': {'value': round(evals_e2e / (ms_e2e * 1e-3), 3), 'unit': 'evals/s',
                 'h2d_bytes_per_step': world * part.slab * d * 4, 'd2h_bytes_per_step': world * (part.slab * d * 4 + 4),
@@ -641,7 +644,7 @@ def exchange_times(halo, part, d, device, n_gathers, n_scatters, step_ms):
     region: how much of a step is exchange, and the NVLink rate the exchanges themselves reach"""
     import torch.distributed as dist
     slab = torch.zeros(part.slab, d, device=device)
-    full = torch.zeros(part.n_pad, d, device=device)
+    full = torch.zeros(getattr(halo, 'view', part).n_pad, d, device=device)
     out = {}
     for key, fn in (('all_gather_ms', lambda: halo.all_gather_rows(slab)),
                     ('reduce_scatter_ms', lambda: halo.reduce_scatter_rows(full))):
@@ -856,9 +859,11 @@ def main():
                     help='skip the torch-CUDA-ops comparator (N = 1 only)')
     ap.add_argument('--function', default='transformer', choices=['transformer', 'laplacian'],
                     help='transformer = GRAND-nl (BASELINE.json headline); laplacian = GRAND-l sweep of config 5')
-    ap.add_argument('--halo', default=os.environ.get('GRANDB200_HALO', 'dense'), choices=['dense', 'sparse', 'auto'],
+    ap.add_argument('--halo', default=os.environ.get('GRANDB200_HALO', 'dense'), choices=['dense', 'sparse', 'compact', 'auto'],
                     help='N > 1: exchange whole slabs (dense), only the rows the peers reference (sparse: R-MAT slabs '
-                         'reference ~25 %% of the others at 8 ranks), or decide from the measured fraction (auto)')
+                         'reference ~25 %% of the others at 8 ranks), sparse exchange + the rank\'s graph relabelled to '
+                         '[own slab | referenced rows] so all per-rank work is O(N/P + halo) (compact), or dense / sparse '
+                         'decided from the measured fraction (auto)')
     ap.add_argument('--microbench', action='store_true',
                     help='isolated per-evaluation timing (SURVEY.md 8d): forward and adjoint evaluation alone, '
                          'L2 hot and L2 flushed, >= 100 iterations; 1 GPU')

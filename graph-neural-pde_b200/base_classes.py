@@ -155,7 +155,11 @@ class ODEblock(nn.Module):
                         edge_index, edge_weight, fill_value=self.opt['self_loop_weight'], num_nodes=data.num_nodes)
                 if self.partition is not None:               # keep the edges whose row this rank owns
                     batched = edge_index.dim() == 3
-                    edge_index, edge_weight = self.partition[0].local_edges(edge_index, edge_weight)
+                    part, halo = self.partition
+                    edge_index, edge_weight = part.local_edges(edge_index, edge_weight)
+                    if hasattr(halo, 'localize'):             # CompactHalo: local ids, [own slab | referenced rows]
+                        edge_index = halo.localize(edge_index)
+                        self.odefunc.partition = (halo.view, halo)
                     if batched:
                         edge_index, edge_weight = edge_index[None], edge_weight[None]
                 self._graph_cache = (key, ei, edge_index, edge_weight)

@@ -148,11 +148,17 @@ class SparseHalo(Halo):
         """build the per-peer index lists for the graph of `plan` (this rank's edges, global column ids)"""
         if self._key is plan:
             return
-        part, dist, dev = self.part, self.dist, plan.colidx.device
+        part = self.part
         cols = torch.unique(plan.colidx.long())                       # sorted
         owner = torch.div(cols, part.slab, rounding_mode='floor')
-        remote = cols[owner != part.rank]
-        owner = owner[owner != part.rank]
+        self._exchange_lists(cols[owner != part.rank], owner[owner != part.rank], plan.colidx.device)
+        self.__dict__.pop('_ring', None)                              # other rows are referenced now: fresh zero buffers
+        self._key = plan
+
+    def _exchange_lists(self, remote, owner, dev):
+        """remote: sorted global ids of the rows of other slabs this rank's edges reference, owner: their ranks.
+        Every pair of ranks swaps counts, then ids (two all_to_all calls, once per graph)."""
+        part, dist = self.part, self.dist
         need_counts = torch.bincount(owner, minlength=part.world)      # rows I need from each peer
         give_counts = torch.empty_like(need_counts)
         dist.all_to_all_single(give_counts, need_counts, group=self.group)
@@ -165,8 +171,6 @@ class SparseHalo(Halo):
         if self.send_idx.numel() and (int(self.send_idx.min()) < 0 or int(self.send_idx.max()) >= part.slab):
             raise RuntimeError('SparseHalo: a peer asked for rows outside this slab')
         self.referenced_fraction = float(remote.numel()) / max(1, part.n_pad - part.slab)
-        self.__dict__.pop('_ring', None)                              # other rows are referenced now: fresh zero buffers
-        self._key = plan
 
     def _check(self):
         if self._key is None:
@@ -249,6 +253,100 @@ class SparseHalo(Halo):
     def reduce_scatter_rows_async(self, full):
         full, send, recv, work = self._start_scatter(full, True)
         return PendingExchange(None, work, lambda: self._finish_scatter(full, recv), keep=(send,))
+
+
+class LocalRows:
+    """the partition as ONE rank's kernels see it under a CompactHalo: a graph of n_local = S + R nodes whose first S
+    ids are this rank's slab (rows [0, hi - lo) real, the rest padding) and whose last R ids are the remote rows its
+    edges reference, in (owner, global id) order.  Same attribute names as RowPartition, so the compute entry points
+    below take either."""
+
+    def __init__(self, part, n_local):
+        self.n, self.world, self.rank, self.slab = part.n, part.world, part.rank, part.slab
+        self.lo, self.hi = 0, part.hi - part.lo
+        self.n_pad = int(n_local)
+
+    def __repr__(self):
+        return f'LocalRows(rank={self.rank}, own={self.hi}, slab={self.slab}, n_local={self.n_pad})'
+
+
+class CompactHalo(SparseHalo):
+    """SparseHalo whose local problem is COMPACT: besides exchanging only the referenced rows, the rank's graph is
+    relabelled (`localize`) to [own slab | referenced remote rows], so every per-rank buffer and every kernel that
+    runs over "all columns" (column pass, [dq|dk] GEMMs, zero fill of the share) shrinks from N_pad rows to
+    S + R rows - per-rank work is O(N/P + halo + E/P) instead of O(N + E/P).  The exchanges become copy-free on the
+    receiving (gather) and sending (scatter) side: the all_to_all_v receives straight into the tail of the local
+    state matrix and sends straight from the tail of the local share.
+
+    Use: block.set_partition(part, CompactHalo(part)); ODEblock.reset_graph_data then relabels the rank's edges and
+    hands (halo.view, halo) to the ODE function."""
+
+    def __init__(self, part, group=None):
+        super().__init__(part, group)
+        self.view = None
+
+    def localize(self, edge_index):
+        """edges of this rank with GLOBAL ids [2, E_p] -> the same edges, same order, with LOCAL ids; builds the
+        per-peer index lists on the way (collective: every rank of the group must call it)"""
+        part = self.part
+        ei = edge_index[0] if edge_index.dim() == 3 else edge_index
+        rows, cols = ei[0].long(), ei[1].long()
+        if rows.numel() and (int(rows.min()) < part.lo or int(rows.max()) >= part.hi):
+            raise ValueError('CompactHalo.localize takes the edges whose row this rank owns (RowPartition.local_edges)')
+        uniq = torch.unique(cols)                                     # sorted: grouped by owner, ascending
+        owner = torch.div(uniq, part.slab, rounding_mode='floor')
+        remote = uniq[owner != part.rank].contiguous()
+        self._exchange_lists(remote, owner[owner != part.rank], ei.device)
+        mine = (cols >= part.rank * part.slab) & (cols < (part.rank + 1) * part.slab)
+        pos = torch.searchsorted(remote, cols)                        # only read where the column is remote
+        local_cols = torch.where(mine, cols - part.rank * part.slab, part.slab + pos)
+        self.view = LocalRows(part, part.slab + remote.numel())
+        self._key = self.view
+        return torch.stack([rows - part.lo, local_cols]).to(ei.dtype)
+
+    def prepare(self, plan):
+        if self.view is None:
+            raise RuntimeError('CompactHalo: localize(edge_index) must run before the first exchange '
+                               '(ODEblock.reset_graph_data does it)')
+        if plan.n != self.view.n_pad:
+            raise ValueError(f'CompactHalo: plan over {plan.n} nodes, local problem has {self.view.n_pad}')
+
+    def _start_gather(self, slab, async_op):
+        self._check()
+        slab = slab.contiguous()
+        s = self.part.slab
+        local = slab.new_empty((self.view.n_pad,) + tuple(slab.shape[1:]))
+        local[:s] = slab
+        send = slab.index_select(0, self.send_idx)
+        recv = local[s:]                                              # contiguous tail: received rows land in place
+        work = self.dist.all_to_all_single(recv, send, self.recv_splits, self.send_splits, group=self.group,
+                                           async_op=async_op)
+        self.bytes_in += recv.numel() * recv.element_size()
+        self.n_gathers += 1
+        return local, send, recv, work
+
+    def _finish_gather(self, local, recv):
+        return local
+
+    def _start_scatter(self, full, async_op):
+        self._check()
+        full = full.contiguous()
+        send = full[self.part.slab:]                                  # my share for the peers' rows, already in peer order
+        recv = full.new_empty((sum(self.send_splits),) + tuple(full.shape[1:]))
+        work = self.dist.all_to_all_single(recv, send, self.send_splits, self.recv_splits, group=self.group,
+                                           async_op=async_op)
+        self.bytes_in += recv.numel() * recv.element_size()
+        self.n_scatters += 1
+        return full, send, recv, work
+
+    def _finish_scatter(self, full, recv):
+        out = full[:self.part.slab].clone()
+        off = 0
+        for cnt in self.send_splits:                                   # peer after peer, rank order: a fixed order of adds
+            if cnt:
+                out.index_add_(0, self.send_idx[off:off + cnt], recv[off:off + cnt])
+            off += cnt
+        return out
 
 
 class PendingExchange:

@@ -236,7 +236,7 @@ def _gloo_worker(rank, world, port, n, d, ret, overlap=False, function='transfor
         z_ref, g_ref, nfe_ref = _train_pass(_make_block(function), data, x, gz)
         # partitioned: this rank's slab in, this rank's slab out
         part = grand_b200.RowPartition(n, world, rank)
-        halo = grand_b200.SparseHalo(part) if sparse else grand_b200.Halo(part)
+        halo = {False: grand_b200.Halo, True: grand_b200.SparseHalo, 'compact': grand_b200.CompactHalo}[sparse](part)
         block = _make_block(function)
         block.set_partition(part, halo)
         del emu.calls[:]
@@ -247,6 +247,21 @@ def _gloo_worker(rank, world, port, n, d, ret, overlap=False, function='transfor
             assert 0 < halo.referenced_fraction < 0.9
             dense_bytes = 24 * (world - 1) * part.slab * d * 4
             assert halo.bytes_in < 0.9 * dense_bytes
+        if sparse == 'compact':
+            # the rank's kernels ran on the compact problem: S own rows + the referenced remote rows, not N_pad
+            view = block.odefunc.partition[0]
+            assert view.n_pad == part.slab + sum(halo.recv_splits) < part.n_pad and (view.lo, view.hi) == (0, part.hi - part.lo)
+            ei_loc = block.odefunc.edge_index
+            assert int(ei_loc.max()) < view.n_pad and int(ei_loc[0].max()) < view.hi
+            # relabelling round trip: local ids map back to the global edges of this rank, in their original order
+            ref_block = _make_block(function)
+            ref_block.set_partition(part, grand_b200.Halo(part))
+            ref_block.reset_graph_data(data, torch.float32)
+            ei_glob = ref_block.odefunc.edge_index
+            cols = torch.where(ei_loc[1] < part.slab, ei_loc[1] + part.rank * part.slab,
+                               halo.recv_idx[(ei_loc[1] - part.slab).clamp(min=0)])
+            assert torch.equal(ei_loc[0] + part.lo, ei_glob[0]) and torch.equal(cols, ei_glob[1])
+            assert torch.equal(block.odefunc.edge_weight, ref_block.odefunc.edge_weight)
         if overlap:
             # two-phase adjoint: 7 of the 8 adjoint evaluations find their state already gathered, and every row pass
             # is followed by the next gather BEFORE its own column pass is issued
@@ -309,6 +324,18 @@ def test_sparse_halo_block_path(world, overlap, function):
     mgr = mp.Manager()
     ret = mgr.dict()
     mp.spawn(_gloo_worker, args=(world, _free_port(), 157, 32, ret, overlap, function, True), nprocs=world, join=True)
+    assert dict(ret) == {r: 'ok' for r in range(world)}
+
+
+@pytest.mark.parametrize('world,overlap,function', [(2, False, 'transformer'), (3, True, 'transformer'),
+                                                     (3, False, 'laplacian'), (2, True, 'laplacian')])
+def test_compact_halo_block_path(world, overlap, function):
+    """CompactHalo: the rank's graph relabelled to [own slab | referenced remote rows]; every buffer and kernel of the
+    rank runs over S + R rows instead of N_pad, the all_to_all_v lands in / leaves from the tail of the local matrices.
+    Same numbers as the single-process block."""
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_gloo_worker, args=(world, _free_port(), 157, 32, ret, overlap, function, 'compact'), nprocs=world, join=True)
     assert dict(ret) == {r: 'ok' for r in range(world)}
 
 
