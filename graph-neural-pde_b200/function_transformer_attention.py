@@ -96,9 +96,6 @@ class SpGraphTransAttentionLayer(nn.Module):
         att_type = self.opt.get('attention_type', 'scaled_dot')
         if att_type not in _lib.GB_ATT:
             raise NotImplementedError(f"attention_type '{att_type}'")
-        if self.beltrami_kernel:
-            raise NotImplementedError("beltrami + exp_kernel (split feature/positional kernels, "
-                                      'function_transformer_attention.py:164-216) is not implemented yet')
         if self.opt.get('square_plus', False):
             raise NotImplementedError("opt['square_plus']: the fork's call site is broken (2 args to a 3-arg "
                                       'function, function_transformer_attention.py:264); softmax only')
@@ -112,6 +109,8 @@ class SpGraphTransAttentionLayer(nn.Module):
         """evaluations of the other attention types that will be differentiated run as projection -> edge softmax
         -> SpMM (the fused forward kernels have no VJP for them): cosine_sim / pearson as scaled_dot of unit_heads,
         exp_kernel through ops.exp_kernel_score_vjp"""
+        if self.beltrami_kernel:
+            return True                                    # always the composite route (two projections, one kernel)
         if att_type == _lib.GB_ATT['scaled_dot'] or not torch.is_grad_enabled() or not _lib.unverified_enabled():
             return False
         params = [self.Q.weight, self.Q.bias, self.K.weight, self.K.bias]
@@ -133,13 +132,42 @@ class SpGraphTransAttentionLayer(nn.Module):
             self._wb_cache = hit
         return hit[1]
 
+    def _beltrami_qk(self, x2):
+        """beltrami + exp_kernel (function_transformer_attention.py:164-216): the score is the PRODUCT of an
+        exponential kernel on the feature columns and one on the positional columns,
+            sx^2 exp(-|qx - kx|^2 / 2 lx^2) * sp^2 exp(-|qp - kp|^2 / 2 lp^2)
+              = (sx sp)^2 exp(-|[qx/lx, qp/lp] - [kx/lx, kp/lp]|^2 / 2),
+        i.e. ONE exponential kernel with output_var sx*sp and lengthscale 1 on per-head vectors of width 2 d_k.
+        Returns ([q' | k'] [N, 4A], kparams [2]).  The fork slices `x[:, f:label]` on its batched layout (the node
+        axis); the feature axis is meant."""
+        f = int(self.opt['feat_hidden_dim'])
+        lab = f + int(self.opt['pos_enc_hidden_dim'])
+        n = x2.shape[0]
+        p = x2[:, f:lab].contiguous()
+        xf = torch.cat((x2[:, :f], x2[:, lab:]), dim=1)
+        qk_x = QKProjFn.apply(xf, self.Qx.weight, self.Qx.bias, self.Kx.weight, self.Kx.bias)
+        qk_p = QKProjFn.apply(p, self.Qp.weight, self.Qp.bias, self.Kp.weight, self.Kp.bias)
+        a, h, dk = self.attention_dim, self.h, self.d_k
+        halves = []
+        for lo in (0, a):                                  # q' then k'
+            hx = qk_x[:, lo:lo + a].reshape(n, h, dk) / self.lengthscale_x
+            hp = qk_p[:, lo:lo + a].reshape(n, h, dk) / self.lengthscale_p
+            halves.append(torch.cat((hx, hp), dim=2).reshape(n, 2 * a))
+        kparams = torch.cat([self.output_var_x * self.output_var_p, torch.ones_like(self.lengthscale_x)])
+        return torch.cat(halves, dim=1).contiguous(), kparams.to(torch.float32).contiguous()
+
     def attention_csr(self, x2, plan):
         """(att [E,H], abar [E], prods [E,H]) in CSR-slot order for an un-batched state x2 [N,d]"""
         att_type = self._check_supported()
-        qk = QKProjFn.apply(x2, self.Q.weight, self.Q.bias, self.K.weight, self.K.bias)
         edge_w = None
         if self.opt.get('reweight_attention', False) and self.edge_weights is not None:
             edge_w = _plan.cached_per_edge(plan, self.edge_weights, 'rw', lambda t: plan.to_csr_order(t.detach()))
+        if self.beltrami_kernel:
+            qk, kparams = self._beltrami_qk(x2)
+            if not _lib.unverified_enabled():              # the exp_kernel VJP has not run on hardware yet
+                kparams = kparams.detach()
+            return EdgeSoftmaxFn.apply(qk, plan, self.h, att_type, int(self.opt['attention_norm_idx']), edge_w, kparams)
+        qk = QKProjFn.apply(x2, self.Q.weight, self.Q.bias, self.K.weight, self.K.bias)
         kparams = None
         if att_type == _lib.GB_ATT['exp_kernel']:            # differentiable: EdgeSoftmaxFn returns d(output_var, lengthscale)
             kparams = torch.cat([self.output_var, self.lengthscale]).to(torch.float32).contiguous()

@@ -11,6 +11,10 @@ Follows:
   segment_softmax        src/utils.py:116-127
   attention_layer        src/function_transformer_attention.py:159-267 (line 249 replaced by the
                          per-edge dot product unless fork_literal=True)
+  beltrami_attention_layer  src/function_transformer_attention.py:164-216 (beltrami + exp_kernel: product of a
+                         feature kernel and a positional kernel).  PARITY UNPINNED for this branch: the fork
+                         slices `x[:, f:label]`, which on its batched [B,N,d] layout cuts the NODE axis; restated
+                         with the upstream intent (the feature axis), no reference golden exists.
   laplacian_f            src/function_laplacian_diffusion.py:39-77
   transformer_f          src/function_transformer_attention.py:20-59 (mix_features=False branch)
 """
@@ -78,6 +82,31 @@ def attention_layer(x, edge_index, wq, bq, wk, bk, heads, attention_type='scaled
     if square_plus:
         return squareplus(prods, grp, n), prods
     return segment_softmax(prods, grp, n), prods
+
+
+def beltrami_attention_layer(x, edge_index, w, heads, feat_dim, pos_dim, attention_norm_idx=0, edge_weight=None,
+                             reweight_attention=False):
+    """SpGraphTransAttentionLayer.forward, beltrami + exp_kernel branch (:164-216).  x = [features (feat_dim) |
+    positional encoding (pos_dim) | labels ...]; `w` maps 'Qx.weight', 'Qx.bias', 'Kx.*', 'Qp.*', 'Kp.*',
+    'output_var_x', 'lengthscale_x', 'output_var_p', 'lengthscale_p' to tensors.  Returns (attention, prods) [E,H]."""
+    n = x.shape[0]
+    lab = feat_dim + pos_dim
+    p = x[:, feat_dim:lab]
+    xf = torch.cat((x[:, :feat_dim], x[:, lab:]), dim=1)
+    row, col = edge_index[0], edge_index[1]
+
+    def heads_of(t):
+        return t.view(n, heads, t.shape[1] // heads)
+
+    src_x = heads_of(xf @ w['Qx.weight'].t() + w['Qx.bias'])[row]
+    dst_x = heads_of(xf @ w['Kx.weight'].t() + w['Kx.bias'])[col]
+    src_p = heads_of(p @ w['Qp.weight'].t() + w['Qp.bias'])[row]
+    dst_p = heads_of(p @ w['Kp.weight'].t() + w['Kp.bias'])[col]
+    prods = w['output_var_x'] ** 2 * torch.exp(-((src_x - dst_x) ** 2).sum(dim=2) / (2 * w['lengthscale_x'] ** 2)) \
+        * w['output_var_p'] ** 2 * torch.exp(-((src_p - dst_p) ** 2).sum(dim=2) / (2 * w['lengthscale_p'] ** 2))
+    if reweight_attention and edge_weight is not None:
+        prods = prods * edge_weight[:, None]
+    return segment_softmax(prods, edge_index[attention_norm_idx], n), prods
 
 
 def spmm(edge_index, values, x):

@@ -213,6 +213,54 @@ def test_exp_kernel_gradients_on_a_graph_with_hub_segments():
             assert_close(g.reshape(-1), r.reshape(-1), G_RTOL, f'{name} norm{norm_idx}')
 
 
+@pytest.mark.parametrize('norm_idx,labels', [(0, 0), (1, 4)])
+def test_beltrami_split_exp_kernel_matches_the_oracle(norm_idx, labels):
+    """beltrami + exp_kernel (function_transformer_attention.py:164-216): feature kernel x positional kernel, run as
+    ONE exp_kernel evaluation on per-head vectors [qx / lx, qp / lp] of width 2 d_k; attention, f and all gradients
+    (x, the four projections, both output variances and lengthscales) against the literal two-kernel product"""
+    import grand_b200
+    from helpers import rand_graph
+    n, feat, pos, heads, adim = 300, 16, 8, 2, 8
+    d = feat + pos + labels
+    ei = rand_graph(n, 2400, 33, hub=(3, 400))
+    rng = np.random.default_rng(8)
+    x, x0, gout = (0.5 * rng.standard_normal((n, d)).astype(np.float32) for _ in range(3))
+    opt = dict(BASE_OPT, attention_type='exp_kernel', beltrami=True, attention_norm_idx=norm_idx, hidden_dim=d,
+               feat_hidden_dim=feat, pos_enc_hidden_dim=pos, heads=heads, attention_dim=adim)
+    func = grand_b200.ODEFuncTransformerAtt(d, d, opt, device()).to(device())
+    L = func.multihead_att_layer
+    names = ['Qx.weight', 'Qx.bias', 'Kx.weight', 'Kx.bias', 'Qp.weight', 'Qp.bias', 'Kp.weight', 'Kp.bias',
+             'output_var_x', 'lengthscale_x', 'output_var_p', 'lengthscale_p']
+    params = dict(L.named_parameters())
+    with torch.no_grad():
+        for k in names[:8]:
+            params[k].copy_(dev((rng.standard_normal(tuple(params[k].shape)) / 3).astype(np.float32)))
+        for k, v in zip(names[8:], (1.2, 1.5, 0.8, 0.7)):
+            params[k].fill_(v)
+        func.alpha_train.fill_(0.3)
+        func.beta_train.fill_(0.1)
+    assert params['Qx.weight'].shape == (adim, d - pos) and params['Qp.weight'].shape == (adim, pos)
+    func.edge_index, func.x0 = dev(ei), dev(x0)
+    t64 = lambda a: torch.tensor(np.asarray(a), dtype=torch.float64)
+    w64 = {k: t64(params[k].detach().cpu().numpy()).requires_grad_(True) for k in names}
+    x64 = t64(x).requires_grad_(True)
+    ei_t = torch.tensor(ei)
+    att_ref, prods_ref = funcs.beltrami_attention_layer(x64, ei_t, w64, heads, feat, pos, attention_norm_idx=norm_idx)
+    with torch.no_grad():                                        # the layer alone, caller's edge order
+        att, (_v, prods) = L(dev(x), dev(ei))
+    assert_close(prods, prods_ref, F_RTOL, 'prods')
+    assert_close(att, att_ref, F_RTOL, 'attention')
+    xg = dev(x).requires_grad_(True)
+    out = func(0.0, xg)
+    grads = torch.autograd.grad(out, [xg, func.alpha_train, func.beta_train] + [params[k] for k in names], dev(gout))
+    a64, b64 = t64(0.3).requires_grad_(True), t64(0.1).requires_grad_(True)
+    ref = funcs.laplacian_f(x64, ei_t, att_ref.mean(dim=1), a64, b64, t64(x0))
+    rg = torch.autograd.grad(ref, [x64, a64, b64] + [w64[k] for k in names], t64(gout))
+    assert_close(out, ref, F_RTOL, 'f')
+    for g, r, name in zip(grads, rg, ['gx', 'galpha', 'gbeta'] + names):
+        assert_close(g.reshape(-1), r.reshape(-1), G_RTOL, name, floor=1e-4 * float(rg[0].abs().max()))
+
+
 # ---- MixedODEblock / HardAttODEblock (host compositions over the verified kernels) ----------------------------
 BLOCK_OPT = {'hidden_dim': 16, 'block': 'mixed', 'function': 'laplacian', 'max_nfe': 10000, 'no_alpha_sigmoid': False,
              'add_source': True, 'augment': False, 'adjoint': False, 'tol_scale': 1.0, 'tol_scale_adjoint': 1.0,

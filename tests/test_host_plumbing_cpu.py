@@ -264,6 +264,30 @@ def test_exp_kernel_gradients_with_hub_segments(unverified):
     zz.test_exp_kernel_gradients_on_a_graph_with_hub_segments()
 
 
+@pytest.mark.parametrize('norm_idx,labels', [(0, 0), (1, 4)])
+def test_beltrami_split_exp_kernel(unverified, norm_idx, labels):
+    zz.test_beltrami_split_exp_kernel_matches_the_oracle(norm_idx, labels)
+    assert unverified.calls.count('gb_edge_softmax_fwd') == 2 and 'gb_att_fwd_fused' not in unverified.calls
+
+
+def test_beltrami_split_exp_kernel_forward_is_on_by_default_training_is_not(host, monkeypatch):
+    """without GB_UNVERIFIED the forward (verified exp_kernel kernel) runs, differentiating it fails loudly"""
+    import grand_b200
+    monkeypatch.delenv('GB_UNVERIFIED', raising=False)
+    n, d = 40, 24
+    opt = dict(zz.BASE_OPT, attention_type='exp_kernel', beltrami=True, hidden_dim=d, feat_hidden_dim=16,
+               pos_enc_hidden_dim=8)
+    func = grand_b200.ODEFuncTransformerAtt(d, d, opt, CPU)
+    func.edge_index = torch.tensor(og.shaped_graph(n, 200, 3))
+    x = torch.randn(n, d, generator=torch.Generator().manual_seed(0))
+    func.x0 = x
+    with torch.no_grad():
+        assert torch.isfinite(func(0.0, x)).all()
+    out = func(0.0, x.clone().requires_grad_(True))
+    with pytest.raises(NotImplementedError):
+        out.sum().backward()
+
+
 def test_mixed_block(unverified):
     zz.test_mixed_block_state_and_gradients_incl_the_gate()
 
