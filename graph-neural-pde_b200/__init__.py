@@ -14,6 +14,7 @@ from .utils import MaxNFEException, get_rw_adj, gcn_norm_fill_val, add_remaining
 from .base_classes import ODEFunc, ODEblock, GraphData
 from .function_laplacian_diffusion import LaplacianODEFunc
 from .function_transformer_attention import ODEFuncTransformerAtt, SpGraphTransAttentionLayer
+from .function_GAT_attention import ODEFuncAtt, SpGraphAttentionLayer
 from .block_constant import ConstantODEblock
 from .block_transformer_attention import AttODEblock
 from .block_mixed import MixedODEblock
@@ -31,5 +32,5 @@ from .GNN_early import GNNEarly
 
 __all__ = ['GraphPlan', 'get_plan', 'MaxNFEException', 'get_rw_adj', 'gcn_norm_fill_val',
            'add_remaining_self_loops', 'Meter', 'ODEFunc', 'ODEblock', 'GraphData', 'LaplacianODEFunc',
-           'ODEFuncTransformerAtt', 'SpGraphTransAttentionLayer', 'ConstantODEblock', 'AttODEblock', 'MixedODEblock', 'HardAttODEblock',
+           'ODEFuncTransformerAtt', 'SpGraphTransAttentionLayer', 'ODEFuncAtt', 'SpGraphAttentionLayer', 'ConstantODEblock', 'AttODEblock', 'MixedODEblock', 'HardAttODEblock',
            'set_block', 'set_function', 'partition', 'GraphedPass', 'RowPartition', 'Halo', 'LoopbackHalo', 'SparseHalo', 'CompactHalo', 'odeint', 'odeint_adjoint', 'integrators', 'EarlyStopInt', 'BaseGNN', 'GNN', 'GNNEarly']

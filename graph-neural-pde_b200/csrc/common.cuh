@@ -58,6 +58,7 @@ enum KernelId {
   K_NL_FWD_LONG,
   K_NL_ADJ_ROWS,
   K_NL_ADJ_LONG,
+  K_GAT_SOFTMAX,
   K_NUM_KERNELS
 };
 

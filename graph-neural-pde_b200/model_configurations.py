@@ -2,11 +2,13 @@
 exception types as the reference's src/model_configurations.py:17-44 (callers: src/GNN.py:11-13,
 src/graph_datasets/run_GNN.py:318-319), kept as lookup tables.
 
-Blocks: constant, attention, mixed, hard_attention; functions: laplacian, transformer.  Keys the reference knows but
+Blocks: constant, attention, mixed, hard_attention; functions: laplacian, transformer, GAT (opt-in until its
+kernel has run on hardware, see function_GAT_attention.py).  Keys the reference knows but
 this package does not accelerate raise NotImplementedError naming the key; unknown keys raise the reference's
 BlockNotDefined / FunctionNotDefined."""
 from .function_transformer_attention import ODEFuncTransformerAtt
 from .function_laplacian_diffusion import LaplacianODEFunc
+from .function_GAT_attention import ODEFuncAtt
 from .block_transformer_attention import AttODEblock
 from .block_constant import ConstantODEblock
 from .block_mixed import MixedODEblock
@@ -23,11 +25,10 @@ class FunctionNotDefined(Exception):
 
 BLOCKS = {'constant': ConstantODEblock, 'attention': AttODEblock, 'mixed': MixedODEblock,
           'hard_attention': HardAttODEblock}
-FUNCTIONS = {'laplacian': LaplacianODEFunc, 'transformer': ODEFuncTransformerAtt}
+FUNCTIONS = {'laplacian': LaplacianODEFunc, 'transformer': ODEFuncTransformerAtt, 'GAT': ODEFuncAtt}
 NOT_ACCELERATED = {
     'rewire_attention': "block 'rewire_attention' (block_transformer_rewiring.py: kNN / GDC rewiring inside the block) "
                         'is outside the accelerated path (SURVEY.md 2.1)',
-    'GAT': "function 'GAT' (function_GAT_attention.py) is outside the accelerated path",
 }
 
 

@@ -176,6 +176,50 @@ class EdgeSoftmaxFn(torch.autograd.Function):
                 dkparams if ctx.needs_input_grad[6] else None)
 
 
+class GatSoftmaxFn(torch.autograd.Function):
+    """s [N,2H] = [s_src | s_dst] per-node score halves -> (att [E,H], abar [E], prods [E,H]) in CSR-slot order:
+    prods = leaky_relu(s_src[row] + s_dst[col]), att = segment softmax (function_GAT_attention.py:136-141).
+    Backward: softmax VJP kernel (gb_edge_softmax_bwd), leaky_relu' elementwise, then the two segment sums of the
+    [E,H] score gradients (prefix sums, deterministic) - per-node SCALARS, so there is no row gather to do."""
+
+    @staticmethod
+    def forward(ctx, s, plan, heads, slope, norm_idx):
+        lib = _lib.load()
+        _lib.require_cuda(s)
+        s = _f32c(s)
+        if s.shape[1] != 2 * heads:
+            raise ValueError(f'GatSoftmaxFn: s must be [N, {2 * heads}], got {tuple(s.shape)}')
+        att = torch.empty(plan.e, heads, dtype=torch.float32, device=s.device)
+        abar = torch.empty(plan.e, dtype=torch.float32, device=s.device)
+        prods = torch.empty(plan.e, heads, dtype=torch.float32, device=s.device)
+        _lib.check(lib.gb_gat_softmax_fwd(plan.c, norm_idx, s.data_ptr(), s.data_ptr() + 4 * heads, 2 * heads, heads,
+                                          float(slope), att.data_ptr(), abar.data_ptr(), prods.data_ptr(),
+                                          _lib.stream()), 'gb_gat_softmax_fwd')
+        ctx.save_for_backward(att, prods)
+        ctx.plan, ctx.heads, ctx.slope, ctx.norm_idx = plan, heads, float(slope), norm_idx
+        ctx.set_materialize_grads(False)
+        ctx.mark_non_differentiable(prods)
+        return att, abar, prods
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, datt, dabar, _dprods):
+        lib = _lib.load()
+        att, prods = ctx.saved_tensors
+        plan, heads = ctx.plan, ctx.heads
+        if datt is None and dabar is None:
+            return (None,) * 5
+        datt = None if datt is None else _f32c(datt)
+        dabar = None if dabar is None else _f32c(dabar)
+        ds = torch.empty(plan.e, heads, dtype=torch.float32, device=att.device)
+        _lib.check(lib.gb_edge_softmax_bwd(plan.c, ctx.norm_idx, att.data_ptr(), _lib.ptr(dabar), _lib.ptr(datt), heads,
+                                           None, ds.data_ptr(), _lib.stream()), 'gb_edge_softmax_bwd')
+        dz = torch.where(prods > 0, ds, ds * ctx.slope)
+        d_src = _segment_sums(dz, plan.rowptr)
+        d_dst = _segment_sums(dz[plan.tperm.long()], plan.colptr)
+        return torch.cat([d_src, d_dst], dim=1), None, None, None, None
+
+
 class DiffusionFn(torch.autograd.Function):
     """f = alpha (A x - x) + beta x0 with A given by `vals` [E] in CSR-slot order.
 

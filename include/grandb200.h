@@ -227,6 +227,17 @@ int gb_edge_score_bwd(const gb_graph* g, const float* ds, const float* q, int32_
                       const float* prods, float* dq, int32_t lddq, float* dk_out, int32_t lddk,
                       float* dkparams_partials, float* dkparams, void* stream);
 
+/* ---- GAT scores + segment softmax + head mean (function_GAT_attention.py:117-141 replaces the per-edge gather of
+ *      both endpoints' [dk,H] projections + `sum(a * edge_h)`; utils.py:116-127 the softmax).  The score factorises
+ *      into per-node scalars the caller projects once per evaluation (s_src[i,h] = <a[:dk], (xW)[i,h,:]>,
+ *      s_dst[j,h] = <a[dk:], (xW)[j,h,:]>, both [n, lds >= heads]):
+ *   prods[s,h] = leaky_relu(s_src[row_s,h] + s_dst[col_s,h], slope)
+ *   att[s,h]   = exp(prods - max_g) / (sum_g exp(prods - max_g) + 1e-16), groups = rows (norm_idx 0) / columns (1)
+ *   abar[s]    = mean_h att[s,h]
+ *   CSR-slot order; prods may be NULL; heads <= 8.  The backward of att is gb_edge_softmax_bwd. */
+int gb_gat_softmax_fwd(const gb_graph* g, int32_t norm_idx, const float* s_src, const float* s_dst, int32_t lds,
+                       int32_t heads, float slope, float* att, float* abar, float* prods, void* stream);
+
 /* ---- fused GRAND-nl evaluation (warp-per-row kernels, csrc/fused_att.cu) -------------------------
  * gb_att_fused_supported: 1 when the shapes/alignment fit the fused kernels (heads a power of two <= 8,
  * dk/4 a power of two, attention_dim <= 128, 16-byte aligned rows, d % 4 == 0, d <= 512; pass x == NULL to

@@ -15,6 +15,8 @@ Follows:
                          feature kernel and a positional kernel).  PARITY UNPINNED for this branch: the fork
                          slices `x[:, f:label]`, which on its batched [B,N,d] layout cuts the NODE axis; restated
                          with the upstream intent (the feature axis), no reference golden exists.
+  gat_attention_layer    src/function_GAT_attention.py:117-141 (literal: gather both endpoints' [H,dk] projections,
+                         a * edge_h summed over 2 dk, leaky relu, softmax);  gat_f  :53-69 (mix_features=False)
   laplacian_f            src/function_laplacian_diffusion.py:39-77
   transformer_f          src/function_transformer_attention.py:20-59 (mix_features=False branch)
 """
@@ -107,6 +109,26 @@ def beltrami_attention_layer(x, edge_index, w, heads, feat_dim, pos_dim, attenti
     if reweight_attention and edge_weight is not None:
         prods = prods * edge_weight[:, None]
     return segment_softmax(prods, edge_index[attention_norm_idx], n), prods
+
+
+def gat_attention_layer(x, edge_index, w, a, heads, slope, attention_norm_idx=0):
+    """SpGraphAttentionLayer.forward (function_GAT_attention.py:117-141): w [d, A], a [2 dk] (the reference keeps it
+    as [1, 2 dk, 1, 1]).  Returns (attention [E,H], raw scores after the leaky relu [E,H])."""
+    n = x.shape[0]
+    wx = x @ w
+    dk = wx.shape[1] // heads
+    h = wx.view(n, heads, dk)
+    edge_h = torch.cat((h[edge_index[0]], h[edge_index[1]]), dim=2)           # [E, H, 2 dk]
+    edge_e = torch.nn.functional.leaky_relu((a.reshape(1, 1, 2 * dk) * edge_h).sum(dim=2), slope)
+    return segment_softmax(edge_e, edge_index[attention_norm_idx], n), edge_e
+
+
+def gat_f(x, edge_index, w, a, heads, slope, alpha_train, beta_train, x0, add_source=True, no_alpha_sigmoid=False,
+          attention_norm_idx=0):
+    """ODEFuncAtt.forward (function_GAT_attention.py:53-69, mix_features=False): mean over heads of the attention
+    applied to x, same alpha / beta epilogue as the other functions."""
+    att, _ = gat_attention_layer(x, edge_index, w, a, heads, slope, attention_norm_idx)
+    return laplacian_f(x, edge_index, att.mean(dim=1), alpha_train, beta_train, x0, add_source, no_alpha_sigmoid)
 
 
 def spmm(edge_index, values, x):

@@ -271,6 +271,22 @@ class Emulator:
             f32(prods, G.e, heads)[:] = s.numpy()
         return 0
 
+    def gb_gat_softmax_fwd(self, g, norm_idx, s_src, s_dst, lds, heads, slope, att, abar, prods, stream):
+        self._note('gb_gat_softmax_fwd')
+        from oracle import funcs
+        G = Graph(g)
+        src = f32(s_src, G.n, heads, lds).astype(np.float64)
+        dst = f32(s_dst, G.n, heads, lds).astype(np.float64)
+        z = src[G.rows] + dst[G.colidx]
+        s = torch.tensor(np.where(z > 0, z, float(slope) * z))
+        grp = torch.tensor(G.rows if norm_idx == 0 else G.colidx)
+        p = funcs.segment_softmax(s, grp.long(), G.n)
+        f32(att, G.e, heads)[:] = p.numpy()
+        vec(abar, G.e)[:] = p.mean(dim=1).numpy()
+        if _p(prods):
+            f32(prods, G.e, heads)[:] = s.numpy()
+        return 0
+
     def gb_edge_softmax_bwd(self, g, norm_idx, att, dabar, datt, heads, edge_w, ds, stream):
         self._note('gb_edge_softmax_bwd')
         G = Graph(g)

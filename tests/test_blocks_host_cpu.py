@@ -16,8 +16,7 @@ def test_registry_maps_the_reference_keys():
     assert mc.set_function({'function': 'transformer'}) is grand_b200.ODEFuncTransformerAtt
     with pytest.raises(NotImplementedError):
         mc.set_block({'block': 'rewire_attention'})
-    with pytest.raises(NotImplementedError):
-        mc.set_function({'function': 'GAT'})
+    assert mc.set_function({'function': 'GAT'}) is grand_b200.ODEFuncAtt
     with pytest.raises(mc.BlockNotDefined):
         mc.set_block({'block': 'nope'})
     with pytest.raises(mc.FunctionNotDefined):

@@ -261,6 +261,86 @@ def test_beltrami_split_exp_kernel_matches_the_oracle(norm_idx, labels):
         assert_close(g.reshape(-1), r.reshape(-1), G_RTOL, name, floor=1e-4 * float(rg[0].abs().max()))
 
 
+@pytest.mark.parametrize('norm_idx,heads', [(0, 2), (1, 4), (0, 8), (1, 1)])
+def test_gat_function_matches_the_oracle(norm_idx, heads):
+    """ODEFuncAtt (function_GAT_attention.py): per-node score halves x (W_h a) -> gb_gat_softmax_fwd (leaky relu +
+    segment softmax + head mean over H gathered floats per edge) -> fused SpMM, against the literal restatement
+    (gather both endpoints' projections, a * edge_h); scores, attention, f and every gradient; hub row and column
+    longer than the plan's long-segment threshold"""
+    import grand_b200
+    from helpers import rand_graph
+    n, d, adim = 500, 24, 16
+    ei = rand_graph(n, 4000, 17, hub=(7, 600))
+    rng = np.random.default_rng(2)
+    x, x0, gout = (0.7 * rng.standard_normal((n, d)).astype(np.float32) for _ in range(3))
+    opt = dict(BASE_OPT, function='GAT', attention_norm_idx=norm_idx, hidden_dim=d, heads=heads, attention_dim=adim)
+    func = grand_b200.ODEFuncAtt(d, d, opt, device()).to(device())
+    L = func.multihead_att_layer
+    assert sorted(k for k, _ in L.named_parameters()) == ['W', 'Wout', 'a'] and L.a.shape == (1, 2 * adim // heads, 1, 1)
+    with torch.no_grad():
+        func.alpha_train.fill_(0.3)
+        func.beta_train.fill_(0.1)
+    func.edge_index, func.x0 = dev(ei), dev(x0)
+    t64 = lambda v: torch.tensor(np.asarray(v), dtype=torch.float64)
+    w64 = t64(L.W.detach().cpu().numpy()).requires_grad_(True)
+    a64 = t64(L.a.detach().cpu().numpy().reshape(-1)).requires_grad_(True)
+    x64 = t64(x).requires_grad_(True)
+    al64, be64 = t64(0.3).requires_grad_(True), t64(0.1).requires_grad_(True)
+    ei_t = torch.tensor(ei)
+    att_ref, prods_ref = funcs.gat_attention_layer(x64, ei_t, w64, a64, heads, 0.2, norm_idx)
+    with torch.no_grad():
+        att, wx = L(dev(x), dev(ei))
+    assert_close(att, att_ref, F_RTOL, 'attention')
+    assert_close(wx, x64 @ w64, F_RTOL, 'wx')
+    xg = dev(x).requires_grad_(True)
+    out = func(0.0, xg)
+    grads = torch.autograd.grad(out, [xg, func.alpha_train, func.beta_train, L.W, L.a], dev(gout))
+    ref = funcs.gat_f(x64, ei_t, w64, a64, heads, 0.2, al64, be64, t64(x0), attention_norm_idx=norm_idx)
+    rg = torch.autograd.grad(ref, [x64, al64, be64, w64, a64], t64(gout))
+    assert_close(out, ref, F_RTOL, 'f')
+    for g, r, name in zip(grads, rg, ('gx', 'galpha', 'gbeta', 'gW', 'ga')):
+        assert_close(g.reshape(-1), r.reshape(-1), G_RTOL, name)
+    assert func.nfe == 1
+
+
+def test_gat_function_under_the_constant_block_with_the_adjoint_solver():
+    """function 'GAT' through the registry and ConstantODEblock, rk4 + odeint_adjoint (autograd fallback of the
+    adjoint dynamics: no fused eval_vjp for this function) against the oracle integration"""
+    import grand_b200
+    from oracle import integrate as oint
+    n, e, d, heads, adim, T = 150, 900, 16, 4, 16, 2.0
+    opt = dict(BLOCK_OPT, function='GAT', block='constant', hidden_dim=d, heads=heads, attention_dim=adim, adjoint=True)
+    block = grand_b200.set_block(opt)(grand_b200.set_function(opt), [], opt, device(), t=torch.tensor([0., T])).to(device())
+    block.train()
+    ei = og.shaped_graph(n, e, 4)
+    data = grand_b200.GraphData()
+    data.new_graph(dev(ei), n)
+    func = block.odefunc
+    L = func.multihead_att_layer
+    with torch.no_grad():
+        func.alpha_train.fill_(-0.2)
+        func.beta_train.fill_(0.4)
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(n, d, generator=g)
+    gout = torch.randn(n, d, generator=g)
+    xg = dev(x.numpy()).requires_grad_(True)
+    block.set_x0(xg)
+    z = block(xg, data)
+    grads = torch.autograd.grad(z, [xg, func.alpha_train, func.beta_train, L.W, L.a], dev(gout.numpy()))
+    t64 = lambda v: torch.tensor(np.asarray(v), dtype=torch.float64)
+    ei_n, _ = og.reset_graph_data(ei, None, n, 'rw', 1.0)
+    leaves = [t64(x.numpy()), t64(-0.2), t64(0.4), t64(L.W.detach().cpu().numpy()),
+              t64(L.a.detach().cpu().numpy().reshape(-1))]
+    leaves = [v.requires_grad_(True) for v in leaves]
+    f = lambda t, y: funcs.gat_f(y, torch.tensor(ei_n), leaves[3], leaves[4], heads, 0.2, leaves[1], leaves[2],
+                                 t64(x.numpy()))
+    zo = oint.odeint_adjoint(f, leaves[0], [0., T], 'rk4', 1.0, adjoint_params=tuple(leaves[1:]))[1]
+    ro = torch.autograd.grad(zo, leaves, t64(gout.numpy()))
+    assert_close(z, zo, 1e-4, 'z(T)')
+    for got, r, name in zip(grads, ro, ('gx', 'galpha', 'gbeta', 'gW', 'ga')):
+        assert_close(got.reshape(-1), r.reshape(-1), 1e-4, name)
+
+
 # ---- MixedODEblock / HardAttODEblock (host compositions over the verified kernels) ----------------------------
 BLOCK_OPT = {'hidden_dim': 16, 'block': 'mixed', 'function': 'laplacian', 'max_nfe': 10000, 'no_alpha_sigmoid': False,
              'add_source': True, 'augment': False, 'adjoint': False, 'tol_scale': 1.0, 'tol_scale_adjoint': 1.0,

@@ -288,6 +288,28 @@ def test_beltrami_split_exp_kernel_forward_is_on_by_default_training_is_not(host
         out.sum().backward()
 
 
+@pytest.mark.parametrize('norm_idx,heads', [(0, 2), (1, 4), (0, 8), (1, 1)])
+def test_gat_function(unverified, norm_idx, heads):
+    zz.test_gat_function_matches_the_oracle(norm_idx, heads)
+    calls = unverified.calls
+    assert calls.count('gb_gat_softmax_fwd') == 2 and 'gb_edge_softmax_bwd' in calls and 'gb_spmm_fwd' in calls
+
+
+def test_gat_function_under_the_adjoint_block(unverified):
+    zz.test_gat_function_under_the_constant_block_with_the_adjoint_solver()
+
+
+def test_gat_function_is_opt_in(host, monkeypatch):
+    """the GAT kernel has not run on hardware: without GB_UNVERIFIED the function refuses loudly"""
+    import grand_b200
+    monkeypatch.delenv('GB_UNVERIFIED', raising=False)
+    opt = dict(zz.BASE_OPT, function='GAT', hidden_dim=8)
+    func = grand_b200.set_function(opt)(8, 8, opt, CPU)
+    func.edge_index = torch.tensor(og.shaped_graph(20, 60, 1))
+    with pytest.raises(NotImplementedError, match='GB_UNVERIFIED'):
+        func(0.0, torch.randn(20, 8))
+
+
 def test_mixed_block(unverified):
     zz.test_mixed_block_state_and_gradients_incl_the_gate()
 
