@@ -16,6 +16,12 @@ The fixtures pin `oracle/funcs.py` (and through it the CUDA path) to the referen
   ref_laplacian_*.npz        LaplacianODEFunc.forward + autograd grads   (function_laplacian_diffusion.py:39-77)
   ref_transformer_*.npz      ODEFuncTransformerAtt.forward + grads for cosine_sim / pearson /
                              exp_kernel (per-edge in the fork) and scaled_dot (fork-literal E x E sum)
+  ref_gat_n*.npz             SpGraphAttentionLayer.forward + ODEFuncAtt.forward (function_GAT_attention.py); FORWARD
+                             values only: the reference multiplies with `sparse_att.permute(0, 3, 1, 2).to_dense()`
+                             (:46-47) and torch 2.11's backward of a permuted sparse tensor does not un-permute the
+                             indices (dense-then-permute gives the finite-difference value, sparse-permute does not),
+                             so the reference's own gradients are wrong under this torch; the oracle's gradients are
+                             pinned by torch.autograd.gradcheck instead (tests/test_oracle_golden.py)
   ref_k3.npz                 the K3 / x=ones known answer: attention == 0.5 exactly
                              (test/test_transformer_attention.py:98-106)
 The GPU box has no /root/reference: tests only read the .npz files.
@@ -145,6 +151,34 @@ def gen_transformer(ref_att):
                      fork_literal=(att_type == 'scaled_dot'), **extra)
 
 
+def gen_gat():
+    """function_GAT_attention.py, imported unmodified like the other modules (load_reference() put the paths in place)"""
+    import function_GAT_attention as ref_gat                     # noqa: E402
+    dev = torch.device('cpu')
+    for norm_idx in (0, 1):
+        opt = dict(BASE_OPT, block='constant', function='GAT', attention_norm_idx=norm_idx, heads=2, attention_dim=8)
+        n, d = 11, opt['hidden_dim']
+        ei = toy_graph(n, 28, 15)
+        torch.manual_seed(21 + norm_idx)                          # xavier init of W, Wout, a
+        func = ref_gat.ODEFuncAtt(d, d, opt, dev)
+        layer = func.multihead_att_layer
+        g = torch.Generator().manual_seed(17)
+        with torch.no_grad():
+            func.alpha_train.fill_(0.25)
+            func.beta_train.fill_(-0.3)
+        x = torch.randn(1, n, d, generator=g).requires_grad_(True)
+        x0 = torch.randn(1, n, d, generator=g)
+        gout = torch.randn(1, n, d, generator=g)
+        func.edge_index, func.x0 = ei[None], x0
+        func.y = None
+        attention, wx = layer(x, ei[None])
+        f = func(torch.tensor(0.0), x)
+        np.savez(os.path.join(GOLD, f'ref_gat_n{norm_idx}.npz'),
+                 edge_index=np_(ei), x=np_(x[0]), x0=np_(x0[0]), gout=np_(gout[0]), heads=2, slope=opt['leaky_relu_slope'],
+                 w=np_(layer.W), a=np_(layer.a), alpha_train=0.25, beta_train=-0.3, attention_norm_idx=norm_idx,
+                 attention=np_(attention[0]), wx=np_(wx[0]), f=np_(f[0]), nfe=func.nfe)
+
+
 def gen_k3(ref_att):
     """test/test_transformer_attention.py:98-106 with the reference's default init."""
     opt = dict(BASE_OPT, heads=2, attention_dim=32, hidden_dim=6)
@@ -162,6 +196,10 @@ def gen_k3(ref_att):
 def main():
     os.makedirs(GOLD, exist_ok=True)
     ref_utils, ref_lap, ref_att = load_reference()
+    if sys.argv[1:] == ['gat']:                                  # only the GAT fixtures (leaves the others untouched)
+        gen_gat()
+        return
+    gen_gat()
     gen_softmax(ref_utils)
     gen_laplacian(ref_lap)
     gen_transformer(ref_att)

@@ -303,6 +303,33 @@ def test_gat_function_matches_the_oracle(norm_idx, heads):
     assert func.nfe == 1
 
 
+@pytest.mark.parametrize('path', sorted(glob.glob(os.path.join(GOLD, 'ref_gat_*.npz'))))
+def test_gat_function_matches_the_reference(path):
+    """ODEFuncAtt against the numbers the reference's own function_GAT_attention.py produced (tests/golden/ref_gat_*:
+    forward values; the gradients are checked against the gradcheck-pinned oracle in the test above)"""
+    import grand_b200
+    z = np.load(path)
+    n, d = z['x'].shape
+    opt = dict(BASE_OPT, function='GAT', attention_norm_idx=int(z['attention_norm_idx']), hidden_dim=d,
+               heads=int(z['heads']), attention_dim=int(z['w'].shape[1]), leaky_relu_slope=float(z['slope']))
+    func = grand_b200.ODEFuncAtt(d, d, opt, device()).to(device())
+    L = func.multihead_att_layer
+    with torch.no_grad():
+        L.W.copy_(dev(z['w']))
+        L.a.copy_(dev(z['a']))
+        func.alpha_train.fill_(float(z['alpha_train']))
+        func.beta_train.fill_(float(z['beta_train']))
+    func.edge_index, func.x0 = dev(z['edge_index']), dev(z['x0'])
+    with torch.no_grad():
+        att, wx = L(dev(z['x']), dev(z['edge_index']))
+    assert_close(att, z['attention'], F_RTOL, 'attention')
+    assert_close(wx, z['wx'], F_RTOL, 'wx')
+    with torch.no_grad():
+        out = func(0.0, dev(z['x']))
+    assert_close(out, z['f'], F_RTOL, 'f')
+    assert func.nfe == int(z['nfe'])
+
+
 def test_gat_function_under_the_constant_block_with_the_adjoint_solver():
     """function 'GAT' through the registry and ConstantODEblock, rk4 + odeint_adjoint (autograd fallback of the
     adjoint dynamics: no fused eval_vjp for this function) against the oracle integration"""

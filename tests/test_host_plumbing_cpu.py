@@ -295,6 +295,11 @@ def test_gat_function(unverified, norm_idx, heads):
     assert calls.count('gb_gat_softmax_fwd') == 2 and 'gb_edge_softmax_bwd' in calls and 'gb_spmm_fwd' in calls
 
 
+@pytest.mark.parametrize('path', _paths('ref_gat_*.npz'))
+def test_gat_function_vs_reference_goldens(unverified, path):
+    zz.test_gat_function_matches_the_reference(path)
+
+
 def test_gat_function_under_the_adjoint_block(unverified):
     zz.test_gat_function_under_the_constant_block_with_the_adjoint_solver()
 

@@ -67,6 +67,36 @@ def test_transformer_f_attention_and_grads(path):
             assert torch.allclose(got, ref, rtol=tol, atol=tol * max(float(ref.abs().max()), floor)), (key, att_type)
 
 
+@pytest.mark.parametrize('path', sorted(glob.glob(os.path.join(GOLD, 'ref_gat_*.npz'))))
+def test_gat_f_and_attention(path):
+    """oracle/funcs.gat_attention_layer / gat_f against what the reference's own function_GAT_attention.py produced
+    (oracle/make_golden.py::gen_gat).  Forward values only - see make_golden.py: the reference's gradients are wrong
+    under torch 2.11 (backward of a permuted sparse tensor); the oracle's are pinned by gradcheck below."""
+    z = np.load(path)
+    ei = torch.tensor(z['edge_index'])
+    heads, slope, norm_idx = int(z['heads']), float(z['slope']), int(z['attention_norm_idx'])
+    for dt, tol in ((torch.float32, 5e-6), (torch.float64, 5e-6)):
+        x, w, av = T(z['x'], dt), T(z['w'], dt), T(z['a'].reshape(-1), dt)
+        att, _ = funcs.gat_attention_layer(x, ei, w, av, heads, slope, norm_idx)
+        f = funcs.gat_f(x, ei, w, av, heads, slope, T(float(z['alpha_train']), dt), T(float(z['beta_train']), dt),
+                        T(z['x0'], dt), attention_norm_idx=norm_idx)
+        for got, key in ((att, 'attention'), (x @ w, 'wx'), (f, 'f')):
+            ref = T(z[key], dt).reshape(got.shape)
+            assert torch.allclose(got, ref, rtol=tol, atol=tol * float(ref.abs().max())), key
+
+
+@pytest.mark.parametrize('norm_idx', [0, 1])
+def test_gat_oracle_gradients_are_the_finite_difference_ones(norm_idx):
+    z = np.load(os.path.join(GOLD, f'ref_gat_n{norm_idx}.npz'))
+    ei = torch.tensor(z['edge_index'])
+    dt = torch.float64
+    leaves = [T(z['x'], dt), T(z['w'], dt), T(z['a'].reshape(-1), dt), T(0.25, dt), T(-0.3, dt)]
+    leaves = [v.requires_grad_(True) for v in leaves]
+    fn = lambda x, w, a, al, be: funcs.gat_f(x, ei, w, a, int(z['heads']), float(z['slope']), al, be, T(z['x0'], dt),
+                                             attention_norm_idx=norm_idx)
+    assert torch.autograd.gradcheck(fn, leaves, eps=1e-6, atol=1e-6, rtol=1e-5)
+
+
 def test_scaled_dot_per_edge_differs_from_fork_literal():
     """the fork's line 249 is NOT per-edge q.k; document the delta, keep upstream semantics."""
     z = np.load(os.path.join(GOLD, 'ref_transformer_scaled_dot_n0.npz'))
