@@ -209,7 +209,7 @@ def _make_block(function='transformer'):
     return block
 
 
-def _gloo_worker(rank, world, port, n, d, ret, overlap=False, function='transformer', sparse=False):
+def _gloo_worker(rank, world, port, n, d, ret, overlap=False, function='transformer', sparse=False, tiny=False):
     if overlap:
         os.environ['GRANDB200_OVERLAP'] = '1'
     sys.path.insert(0, ROOT)
@@ -243,7 +243,7 @@ def _gloo_worker(rank, world, port, n, d, ret, overlap=False, function='transfor
         z, grads, nfe = _train_pass(block, data, part.to_slab(x), part.to_slab(gz))
         assert nfe == nfe_ref == 16 and z.shape == (part.slab, d)
         assert halo.n_gathers == 16 and halo.n_scatters == 8          # one gather per evaluation, one scatter per VJP
-        if sparse:                                                    # only referenced rows travelled
+        if sparse and not tiny:                                       # only referenced rows travelled
             assert 0 < halo.referenced_fraction < 0.9
             dense_bytes = 24 * (world - 1) * part.slab * d * 4
             assert halo.bytes_in < 0.9 * dense_bytes
@@ -252,14 +252,15 @@ def _gloo_worker(rank, world, port, n, d, ret, overlap=False, function='transfor
             view = block.odefunc.partition[0]
             assert view.n_pad == part.slab + sum(halo.recv_splits) < part.n_pad and (view.lo, view.hi) == (0, part.hi - part.lo)
             ei_loc = block.odefunc.edge_index
-            assert int(ei_loc.max()) < view.n_pad and int(ei_loc[0].max()) < view.hi
+            assert ei_loc.numel() == 0 or (int(ei_loc.max()) < view.n_pad and int(ei_loc[0].max()) < view.hi)
             # relabelling round trip: local ids map back to the global edges of this rank, in their original order
             ref_block = _make_block(function)
             ref_block.set_partition(part, grand_b200.Halo(part))
             ref_block.reset_graph_data(data, torch.float32)
             ei_glob = ref_block.odefunc.edge_index
+            remote_ids = torch.cat([halo.recv_idx, halo.recv_idx.new_zeros(1)])     # never empty; the pad is not read
             cols = torch.where(ei_loc[1] < part.slab, ei_loc[1] + part.rank * part.slab,
-                               halo.recv_idx[(ei_loc[1] - part.slab).clamp(min=0)])
+                               remote_ids[(ei_loc[1] - part.slab).clamp(min=0)])
             assert torch.equal(ei_loc[0] + part.lo, ei_glob[0]) and torch.equal(cols, ei_glob[1])
             assert torch.equal(block.odefunc.edge_weight, ref_block.odefunc.edge_weight)
         if overlap:
@@ -336,6 +337,18 @@ def test_compact_halo_block_path(world, overlap, function):
     mgr = mp.Manager()
     ret = mgr.dict()
     mp.spawn(_gloo_worker, args=(world, _free_port(), 157, 32, ret, overlap, function, 'compact'), nprocs=world, join=True)
+    assert dict(ret) == {r: 'ok' for r in range(world)}
+
+
+@pytest.mark.parametrize('halo', [False, True, 'compact'])
+def test_rank_without_rows(halo):
+    """9 nodes over 4 ranks: slabs of 3, the last rank owns no row at all (and the thin graph leaves ranks that
+    reference nothing remote); dense, sparse and compact halos"""
+    world = 4
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_gloo_worker, args=(world, _free_port(), 9, 32, ret, False, 'transformer', halo, True), nprocs=world,
+             join=True)
     assert dict(ret) == {r: 'ok' for r in range(world)}
 
 
