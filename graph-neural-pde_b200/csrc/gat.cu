@@ -22,6 +22,7 @@ struct GatArgs {
   const int32_t* perm;     // nullptr or tperm (CSC slot -> CSR slot)
   const float* own;        // scalars indexed by the segment id: s_src (norm 0) / s_dst (norm 1)
   const float* oth;        // scalars gathered through idx
+  const float* scores;     // nullptr, or ready-made raw scores [E,H] in slot order (gb_segment_softmax_fwd)
   int32_t lds, n, heads, long_threshold;
   const int32_t* long_list;
   float slope;
@@ -65,7 +66,7 @@ __global__ void __launch_bounds__(kGatThreads) gat_softmax_kernel(const GatArgs 
   float own[kGatMaxHeads], m[kGatMaxHeads], sum[kGatMaxHeads];
 #pragma unroll
   for (int h = 0; h < kGatMaxHeads; ++h) {
-    own[h] = h < H ? __ldg(a.own + (size_t)seg * a.lds + h) : 0.f;
+    own[h] = (h < H && a.own) ? __ldg(a.own + (size_t)seg * a.lds + h) : 0.f;
     m[h] = -INFINITY;
     sum[h] = 0.f;
   }
@@ -102,13 +103,18 @@ __global__ void __launch_bounds__(kGatThreads) gat_softmax_kernel(const GatArgs 
 
   // ---- pass 1: raw scores (parked in att, kept in prods) and the segment maximum -----------------------------
   for (int p = first; p < end; p += step) {
-    const int other = ld_stream_i32(a.idx + p);
+    const int other = a.scores ? 0 : ld_stream_i32(a.idx + p);
     const int slot = a.perm ? ld_stream_i32(a.perm + p) : p;
 #pragma unroll
     for (int h = 0; h < kGatMaxHeads; ++h) {
       if (h >= H) break;
-      const float z = own[h] + __ldg(a.oth + (size_t)other * a.lds + h);
-      const float s = z > 0.f ? z : a.slope * z;
+      float s;
+      if (a.scores) {
+        s = ld_stream_f32(a.scores + (size_t)slot * H + h);
+      } else {
+        const float z = own[h] + __ldg(a.oth + (size_t)other * a.lds + h);
+        s = z > 0.f ? z : a.slope * z;
+      }
       a.att[(size_t)slot * H + h] = s;
       if (a.prods) a.prods[(size_t)slot * H + h] = s;
       m[h] = fmaxf(m[h], s);
@@ -141,7 +147,7 @@ __global__ void __launch_bounds__(kGatThreads) gat_softmax_kernel(const GatArgs 
       a.att[(size_t)slot * H + h] = v;
       mean += v;
     }
-    a.abar[slot] = mean * inv_h;
+    if (a.abar) a.abar[slot] = mean * inv_h;
   }
 }
 
@@ -180,6 +186,24 @@ int gb_gat_softmax_fwd(const gb_graph* g, int32_t norm_idx, const float* s_src, 
   gat_softmax_kernel<false><<<(unsigned)((g->n + warps - 1) / warps), kGatThreads, 0, stream>>>(a);
   if (n_long > 0) gat_softmax_kernel<true><<<(unsigned)n_long, kGatThreads, 0, stream>>>(a);
   return check_launch("gat_softmax");
+}
+
+
+int gb_segment_softmax_fwd(const int32_t* ptr, const int32_t* perm, int32_t n, int32_t heads, const float* scores,
+                           float* att, float* abar, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  GB_REQUIRE(ptr && scores && att && n > 0, "gb_segment_softmax_fwd: bad arguments");
+  if (heads < 1 || heads > kGatMaxHeads) {
+    set_error("gb_segment_softmax_fwd: 1 <= heads <= %d supported, got %d", kGatMaxHeads, heads);
+    return GB_ERR_UNSUPPORTED;
+  }
+  GatArgs a{};
+  a.ptr = ptr; a.perm = perm; a.scores = scores; a.n = n; a.heads = heads; a.slope = 1.f; a.att = att; a.abar = abar;
+  a.long_threshold = 0x7fffffff;                       // no hub lists for a bare index vector: every segment by a warp
+  const int warps = kGatThreads / 32;
+  LaunchScope ls(K_GAT_SOFTMAX, stream);
+  gat_softmax_kernel<false><<<(unsigned)((n + warps - 1) / warps), kGatThreads, 0, stream>>>(a);
+  return check_launch("segment_softmax");
 }
 
 }  // extern "C"

@@ -220,6 +220,33 @@ class GatSoftmaxFn(torch.autograd.Function):
         return torch.cat([d_src, d_dst], dim=1), None, None, None, None
 
 
+class SegmentSoftmaxFn(torch.autograd.Function):
+    """utils.softmax on ready-made scores: src [E,H], ptr [n+1] / perm [E] from the sorted group ids (utils.softmax
+    builds them) -> out [E,H].  Backward: ds = out * (dout - sum_g out * dout), the group sums as prefix sums in
+    sorted order (deterministic)."""
+
+    @staticmethod
+    def forward(ctx, src, ptr, perm, index):
+        lib = _lib.load()
+        _lib.require_cuda(src)
+        src = _f32c(src)
+        e, h = src.shape
+        out = torch.empty_like(src)
+        if e:
+            _lib.check(lib.gb_segment_softmax_fwd(ptr.data_ptr(), perm.data_ptr(), ptr.numel() - 1, h, src.data_ptr(),
+                                                  out.data_ptr(), None, _lib.stream()), 'gb_segment_softmax_fwd')
+        ctx.save_for_backward(out, ptr, perm, index)
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dout):
+        out, ptr, perm, index = ctx.saved_tensors
+        prod = out * dout
+        inner = _segment_sums(prod[perm.long()], ptr)
+        return out * (dout - inner[index]), None, None, None
+
+
 class DiffusionFn(torch.autograd.Function):
     """f = alpha (A x - x) + beta x0 with A given by `vals` [E] in CSR-slot order.
 

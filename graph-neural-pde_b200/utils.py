@@ -41,6 +41,31 @@ def maybe_num_nodes(edge_index, num_nodes=None):
     return num_nodes if num_nodes is not None else int(edge_index.max()) + 1
 
 
+def softmax(src, index, num_nodes=None):
+    """utils.py:116-127 (PyG 1.7 `softmax`): per head, out = exp(src - max_g) / (sum_g exp(src - max_g) + 1e-16) over the
+    groups g = index[e].  src [B,E,H] / index [B,E] (the fork's layout, B == 1) or [E,H] / [E].  The reference does
+    scatter_max / exp / scatter_add / divide with float atomics; here the group ids are sorted once (stable) and one
+    kernel makes the three passes per group (csrc/gat.cu, gb_segment_softmax_fwd).  The ODE functions do not call
+    this - their softmax is fused with the score kernels; it is the stand-alone entry for callers with their own
+    scores.  New device code, not yet run on hardware: opt-in (GB_UNVERIFIED=1)."""
+    from . import _lib
+    from .ops import SegmentSoftmaxFn
+    if not _lib.unverified_enabled():
+        raise NotImplementedError('utils.softmax runs on a kernel (gb_segment_softmax_fwd) that has not been verified on '
+                                  'hardware yet: set GB_UNVERIFIED=1 to enable it')
+    batched = src.dim() == 3
+    if batched and src.shape[0] != 1:
+        raise NotImplementedError('batched scores (B > 1) are normalised one graph at a time; pass B == 1')
+    s2 = src[0] if batched else src
+    idx = (index[0] if index.dim() == 2 else index).long()
+    n = maybe_num_nodes(idx, num_nodes)
+    order = torch.argsort(idx, stable=True)
+    ptr = torch.zeros(n + 1, dtype=torch.int32, device=idx.device)
+    ptr[1:] = torch.cumsum(torch.bincount(idx, minlength=n), 0).to(torch.int32)
+    out = SegmentSoftmaxFn.apply(s2, ptr, order.to(torch.int32).contiguous(), idx)
+    return out[None] if batched else out
+
+
 def add_remaining_self_loops(edge_index, edge_attr, fill_value, num_nodes):
     """PyG 1.7 semantics (what upstream called; the fork's src/utils.py:16-42 is broken): existing
     self-loops are moved to the end, every node without one gets (i,i) with weight `fill_value`."""

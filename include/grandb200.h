@@ -238,6 +238,13 @@ int gb_edge_score_bwd(const gb_graph* g, const float* ds, const float* q, int32_
 int gb_gat_softmax_fwd(const gb_graph* g, int32_t norm_idx, const float* s_src, const float* s_dst, int32_t lds,
                        int32_t heads, float slope, float* att, float* abar, float* prods, void* stream);
 
+/* ---- utils.softmax(src, index, num_nodes) on ready-made scores (utils.py:116-127), for callers that hold their own
+ *      [E,H] scores and a group id per edge rather than a graph plan: the host sorts the group ids once
+ *      (ptr [n+1] = segment boundaries, perm [E] = position in sorted order -> caller's slot, NULL if already sorted);
+ *   att[s,h] = exp(src[s,h] - max_g) / (sum_g exp(src[., h] - max_g) + 1e-16);  abar (head mean) may be NULL. heads <= 8 */
+int gb_segment_softmax_fwd(const int32_t* ptr, const int32_t* perm, int32_t n, int32_t heads, const float* scores,
+                           float* att, float* abar, void* stream);
+
 /* ---- fused GRAND-nl evaluation (warp-per-row kernels, csrc/fused_att.cu) -------------------------
  * gb_att_fused_supported: 1 when the shapes/alignment fit the fused kernels (heads a power of two <= 8,
  * dk/4 a power of two, attention_dim <= 128, 16-byte aligned rows, d % 4 == 0, d <= 512; pass x == NULL to

@@ -287,6 +287,20 @@ class Emulator:
             f32(prods, G.e, heads)[:] = s.numpy()
         return 0
 
+    def gb_segment_softmax_fwd(self, ptr, perm, n, heads, scores, att, abar, stream):
+        self._note('gb_segment_softmax_fwd')
+        from oracle import funcs
+        bounds = i32(ptr, n + 1)
+        e = int(bounds[-1])
+        order = i32(perm, e).astype(np.int64) if _p(perm) else np.arange(e)
+        grp = np.empty(e, dtype=np.int64)
+        grp[order] = np.repeat(np.arange(n), np.diff(bounds))
+        p = funcs.segment_softmax(torch.tensor(f32(scores, e, heads).astype(np.float64)), torch.tensor(grp), n)
+        f32(att, e, heads)[:] = p.numpy()
+        if _p(abar):
+            vec(abar, e)[:] = p.mean(dim=1).numpy()
+        return 0
+
     def gb_edge_softmax_bwd(self, g, norm_idx, att, dabar, datt, heads, edge_w, ds, stream):
         self._note('gb_edge_softmax_bwd')
         G = Graph(g)

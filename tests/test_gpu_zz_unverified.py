@@ -368,6 +368,40 @@ def test_gat_function_under_the_constant_block_with_the_adjoint_solver():
         assert_close(got.reshape(-1), r.reshape(-1), 1e-4, name)
 
 
+def test_utils_softmax_matches_the_reference_and_its_invariants():
+    """stand-alone utils.softmax (utils.py:116-127) on ready-made scores with an UNSORTED group vector: the golden the
+    reference itself produced (tests/golden/ref_softmax.npz), the reference tests' invariants (every group sums to
+    one, values in (0, 1]; test/test_transformer_attention.py:57-76), batched layout, empty groups, gradient vs the
+    oracle, run-to-run identity"""
+    from grand_b200 import utils
+    z = np.load(os.path.join(GOLD, 'ref_softmax.npz'))
+    out = utils.softmax(dev(z['src']), dev(z['index']), int(z['n']))
+    assert_close(out, z['out'], 1e-6, 'softmax vs reference golden')
+    out_b = utils.softmax(dev(z['src'])[None], dev(z['index'])[None], int(z['n']))
+    assert out_b.shape == (1,) + tuple(z['src'].shape) and torch.equal(out_b[0], out)
+    rng = np.random.default_rng(5)
+    n, e, h = 700, 9000, 4
+    index = rng.integers(0, n, e)
+    index[:3000] = 13                                                  # one long group
+    index[index == 200] = 201                                          # and an empty one
+    src = (3 * rng.standard_normal((e, h))).astype(np.float32)
+    sg = dev(src).requires_grad_(True)
+    att = utils.softmax(sg, dev(index), n)
+    sums = torch.zeros(n, h, device=att.device).index_add_(0, dev(index).long(), att.detach())
+    present = torch.zeros(n, dtype=torch.bool, device=att.device)
+    present[dev(index).long()] = True
+    assert torch.allclose(sums[present], torch.ones_like(sums[present]), atol=1e-5) and not bool(present[200])
+    assert float(att.detach().min()) > 0 and float(att.detach().max()) <= 1
+    gout = rng.standard_normal((e, h)).astype(np.float32)
+    g, = torch.autograd.grad(att, sg, dev(gout))
+    s64 = torch.tensor(src, dtype=torch.float64, requires_grad=True)
+    ref = funcs.segment_softmax(s64, torch.tensor(index), n)
+    rg, = torch.autograd.grad(ref, s64, torch.tensor(gout, dtype=torch.float64))
+    assert_close(att, ref, F_RTOL, 'softmax')
+    assert_close(g, rg, G_RTOL, 'd softmax', floor=1e-4 * float(rg.abs().max()))
+    assert torch.equal(utils.softmax(dev(src), dev(index), n), att.detach())
+
+
 # ---- MixedODEblock / HardAttODEblock (host compositions over the verified kernels) ----------------------------
 BLOCK_OPT = {'hidden_dim': 16, 'block': 'mixed', 'function': 'laplacian', 'max_nfe': 10000, 'no_alpha_sigmoid': False,
              'add_source': True, 'augment': False, 'adjoint': False, 'tol_scale': 1.0, 'tol_scale_adjoint': 1.0,

@@ -315,6 +315,18 @@ def test_gat_function_is_opt_in(host, monkeypatch):
         func(0.0, torch.randn(20, 8))
 
 
+def test_utils_softmax(unverified):
+    zz.test_utils_softmax_matches_the_reference_and_its_invariants()
+    assert 'gb_segment_softmax_fwd' in unverified.calls
+
+
+def test_utils_softmax_is_opt_in(host, monkeypatch):
+    from grand_b200 import utils
+    monkeypatch.delenv('GB_UNVERIFIED', raising=False)
+    with pytest.raises(NotImplementedError, match='GB_UNVERIFIED'):
+        utils.softmax(torch.randn(5, 2), torch.tensor([0, 1, 1, 0, 2]), 3)
+
+
 def test_mixed_block(unverified):
     zz.test_mixed_block_state_and_gradients_incl_the_gate()
 
