@@ -25,6 +25,23 @@ def _as_2xE(edge_index):
     return edge_index
 
 
+_ARRAYS = ('rowptr', 'colptr', 'colidx', 'eperm', 'rowidx', 'tperm', 'long_rows', 'long_cols')
+
+
+def fingerprint(edge_index, num_nodes):
+    """content key of (edge list IN ITS ORDER, node count) for the on-disk plan cache: E, n and three wrapping int64
+    sums, one of them position weighted (the plan's `eperm` depends on the caller's edge order).  Four reductions
+    over the edge list on its device, one host read."""
+    ei = _as_2xE(edge_index).to(torch.int64)
+    e = int(ei.shape[1])
+    if e == 0:
+        return (0, int(num_nodes), 0, 0, 0)
+    pos = torch.arange(1, e + 1, dtype=torch.int64, device=ei.device)
+    mixed = ei[0] * -7046029254386353131 + ei[1]                      # 0x9E3779B97F4A7C15 as int64; products wrap
+    sums = torch.stack([ei[0].sum(), ei[1].sum(), (mixed * pos).sum()]).tolist()
+    return (e, int(num_nodes)) + tuple(int(v) for v in sums)
+
+
 class GraphPlan:
     def __init__(self, edge_index, num_nodes, long_threshold=LONG_THRESHOLD, validate=True):
         lib = _lib.load()
@@ -56,6 +73,9 @@ class GraphPlan:
             self.long_rows = self._long_segments(lib, self.rowptr, ws)
             self.long_cols = self._long_segments(lib, self.colptr, ws)
         del ws
+        self._finish()
+
+    def _finish(self):
         self.identity_order = bool(self.e == 0 or torch.equal(
             self.eperm, torch.arange(self.e, dtype=torch.int32, device=self.device)))
         self._c = _lib.GbGraph(
@@ -82,6 +102,38 @@ class GraphPlan:
     def c(self):
         """ctypes pointer to the gb_graph struct"""
         return C.byref(self._c)
+
+    # ---- on-disk form (SURVEY.md 8f-4: the plan of a 10^8..10^9-edge graph outlives the process) -----------------
+    def save(self, path, key=None):
+        """the eight int32 arrays + sizes (+ the fingerprint of the edge list they were built from) as one torch file"""
+        blob = {name: getattr(self, name).cpu() for name in _ARRAYS}
+        blob.update(n=self.n, e=self.e, long_threshold=self.long_threshold, key=key, format=1)
+        tmp = f'{path}.tmp{id(self)}'
+        torch.save(blob, tmp)
+        import os
+        os.replace(tmp, path)                                          # readers never see a half-written file
+
+    @classmethod
+    def load(cls, path, device, key=None):
+        """plan from a file written by save(); no kernel runs.  `key`: refuse a file built from another edge list."""
+        blob = torch.load(path, map_location='cpu')
+        if blob.get('format') != 1:
+            raise ValueError(f'{path}: not a GraphPlan file of this version')
+        if key is not None and tuple(blob.get('key') or ()) != tuple(key):
+            raise ValueError(f'{path}: plan was built from a different edge list')
+        self = cls.__new__(cls)
+        self.device = torch.device(device)
+        self.n, self.e, self.long_threshold = int(blob['n']), int(blob['e']), int(blob['long_threshold'])
+        for name in _ARRAYS:
+            t = blob[name]
+            if t.dtype != torch.int32:
+                raise ValueError(f'{path}: {name} is {t.dtype}, expected int32')
+            setattr(self, name, t.to(self.device).contiguous())
+        if self.rowptr.numel() != self.n + 1 or self.colptr.numel() != self.n + 1 or \
+                any(getattr(self, k).numel() != self.e for k in ('colidx', 'eperm', 'rowidx', 'tperm')):
+            raise ValueError(f'{path}: array sizes do not match n = {self.n}, e = {self.e}')
+        self._finish()
+        return self
 
     # ---- per-edge reordering between the caller's COO order and CSR-slot order -----------------
     def to_csr_order(self, per_edge):
@@ -149,11 +201,31 @@ def get_plan(edge_index, num_nodes):
         ref, version, n, plan = hit
         if ref() is edge_index and version == edge_index._version and n == num_nodes:
             return plan
-    plan = GraphPlan(edge_index, num_nodes)
+    plan = _build_or_load(edge_index, num_nodes)
     if len(_PLAN_CACHE) >= _PLAN_CACHE_MAX:
         for k in [k for k, v in _PLAN_CACHE.items() if v[0]() is None] or list(_PLAN_CACHE)[:1]:
             _PLAN_CACHE.pop(k, None)
     _PLAN_CACHE[key] = (weakref.ref(edge_index), edge_index._version, num_nodes, plan)
+    return plan
+
+
+def _build_or_load(edge_index, num_nodes):
+    """GRANDB200_PLAN_CACHE=<dir>: plans are kept on disk under the fingerprint of their edge list and re-read by
+    later processes instead of being rebuilt (sort + two permutations over E edges)"""
+    import os
+    root = os.environ.get('GRANDB200_PLAN_CACHE')
+    if not root:
+        return GraphPlan(edge_index, num_nodes)
+    key = fingerprint(edge_index, num_nodes)
+    path = os.path.join(root, 'plan_' + '_'.join(f'{v & 0xffffffffffffffff:x}' for v in key) + '.pt')
+    if os.path.exists(path):
+        try:
+            return GraphPlan.load(path, _as_2xE(edge_index).device, key=key)
+        except Exception:                                              # unreadable, damaged or foreign file:
+            pass                                                       # rebuild and overwrite it
+    plan = GraphPlan(edge_index, num_nodes)
+    os.makedirs(root, exist_ok=True)
+    plan.save(path, key=key)
     return plan
 
 

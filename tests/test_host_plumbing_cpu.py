@@ -229,6 +229,49 @@ def test_attention_block_with_laplacian_function_trains_the_block_attention(host
         assert_close(got, r, 1e-4, name, floor=bias_scale if name in ('gbq', 'gbk') else 0.0)
 
 
+def test_plan_files_round_trip_and_the_disk_cache(host, tmp_path, monkeypatch):
+    """GraphPlan.save / load and GRANDB200_PLAN_CACHE: a second lookup of the same edge list (another tensor, e.g.
+    another process) reads the file instead of building; a permuted edge list or another node count is another key;
+    a foreign or damaged file is rebuilt"""
+    import grand_b200
+    from grand_b200 import plan as P
+    n = 60
+    ei = torch.tensor(og.shaped_graph(n, 400, 7))
+    built = P.GraphPlan(ei, n)
+    path = str(tmp_path / 'p.pt')
+    built.save(path, key=P.fingerprint(ei, n))
+    loaded = P.GraphPlan.load(path, CPU, key=P.fingerprint(ei, n))
+    for name in P._ARRAYS:
+        assert torch.equal(getattr(loaded, name), getattr(built, name)), name
+    assert (loaded.n, loaded.e, loaded.long_threshold, loaded.identity_order) == \
+        (built.n, built.e, built.long_threshold, built.identity_order)
+    with pytest.raises(ValueError):
+        P.GraphPlan.load(path, CPU, key=P.fingerprint(ei.flip(1), n))
+    assert P.fingerprint(ei, n) != P.fingerprint(ei.flip(1), n) and P.fingerprint(ei, n) != P.fingerprint(ei, n + 1)
+    assert P.fingerprint(ei[None], n) == P.fingerprint(ei.clone(), n)
+    # an evaluation through the loaded plan is the evaluation through the built one
+    x = torch.randn(n, 8, generator=torch.Generator().manual_seed(0))
+    vals = torch.rand(ei.shape[1], generator=torch.Generator().manual_seed(1))
+    from grand_b200.ops import DiffusionFn
+    a, b = torch.tensor(0.3), torch.tensor(0.1)
+    f1 = DiffusionFn.apply(x, built.to_csr_order(vals), a, b, x, built, True, None)
+    f2 = DiffusionFn.apply(x, loaded.to_csr_order(vals), a, b, x, loaded, True, None)
+    assert torch.equal(f1, f2)
+    # the cache directory
+    monkeypatch.setenv('GRANDB200_PLAN_CACHE', str(tmp_path / 'cache'))
+    del host.calls[:]
+    p1 = P.get_plan(ei.clone(), n)
+    assert host.calls.count('gb_plan_build') == 1 and len(list((tmp_path / 'cache').iterdir())) == 1
+    p2 = P.get_plan(ei.clone(), n)                                     # another tensor, same content: from disk
+    assert host.calls.count('gb_plan_build') == 1 and torch.equal(p2.tperm, p1.tperm)
+    P.get_plan(ei.flip(1).contiguous(), n)                             # another order: another plan
+    assert host.calls.count('gb_plan_build') == 2 and len(list((tmp_path / 'cache').iterdir())) == 2
+    for f in (tmp_path / 'cache').iterdir():
+        f.write_bytes(b'not a plan')
+    p3 = P.get_plan(ei.clone(), n)
+    assert host.calls.count('gb_plan_build') == 3 and torch.equal(p3.colidx, built.colidx)
+
+
 # ---- B. the not-yet-on-hardware GPU tests, host plumbing through the emulator -----------------------------------
 import test_gpu_zz_unverified as zz  # noqa: E402
 
