@@ -190,19 +190,24 @@ int gb_gat_softmax_fwd(const gb_graph* g, int32_t norm_idx, const float* s_src, 
 
 
 int gb_segment_softmax_fwd(const int32_t* ptr, const int32_t* perm, int32_t n, int32_t heads, const float* scores,
-                           float* att, float* abar, void* stream_) {
+                           float* att, float* abar, const int32_t* long_list, int32_t n_long, int32_t long_threshold,
+                           void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   GB_REQUIRE(ptr && scores && att && n > 0, "gb_segment_softmax_fwd: bad arguments");
+  GB_REQUIRE(n_long == 0 || (long_list && long_threshold > 0), "gb_segment_softmax_fwd: long-segment list without threshold");
   if (heads < 1 || heads > kGatMaxHeads) {
     set_error("gb_segment_softmax_fwd: 1 <= heads <= %d supported, got %d", kGatMaxHeads, heads);
     return GB_ERR_UNSUPPORTED;
   }
   GatArgs a{};
   a.ptr = ptr; a.perm = perm; a.scores = scores; a.n = n; a.heads = heads; a.slope = 1.f; a.att = att; a.abar = abar;
-  a.long_threshold = 0x7fffffff;                       // no hub lists for a bare index vector: every segment by a warp
+  // groups on `long_list` (more than long_threshold members) get a CTA each, everything else a warp
+  a.long_list = long_list;
+  a.long_threshold = n_long > 0 ? long_threshold : 0x7fffffff;
   const int warps = kGatThreads / 32;
   LaunchScope ls(K_GAT_SOFTMAX, stream);
   gat_softmax_kernel<false><<<(unsigned)((n + warps - 1) / warps), kGatThreads, 0, stream>>>(a);
+  if (n_long > 0) gat_softmax_kernel<true><<<(unsigned)n_long, kGatThreads, 0, stream>>>(a);
   return check_launch("segment_softmax");
 }
 

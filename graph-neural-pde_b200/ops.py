@@ -226,7 +226,7 @@ class SegmentSoftmaxFn(torch.autograd.Function):
     sorted order (deterministic)."""
 
     @staticmethod
-    def forward(ctx, src, ptr, perm, index):
+    def forward(ctx, src, ptr, perm, index, long_groups):
         lib = _lib.load()
         _lib.require_cuda(src)
         src = _f32c(src)
@@ -234,9 +234,13 @@ class SegmentSoftmaxFn(torch.autograd.Function):
         out = torch.empty_like(src)
         if e:
             _lib.check(lib.gb_segment_softmax_fwd(ptr.data_ptr(), perm.data_ptr(), ptr.numel() - 1, h, src.data_ptr(),
-                                                  out.data_ptr(), None, _lib.stream()), 'gb_segment_softmax_fwd')
+                                                  out.data_ptr(), None, _lib.ptr(long_groups) if long_groups.numel() else None,
+                                                  long_groups.numel(), SegmentSoftmaxFn.LONG, _lib.stream()),
+                       'gb_segment_softmax_fwd')
         ctx.save_for_backward(out, ptr, perm, index)
         return out
+
+    LONG = 256          # groups with more members get one CTA each
 
     @staticmethod
     @once_differentiable
@@ -244,7 +248,7 @@ class SegmentSoftmaxFn(torch.autograd.Function):
         out, ptr, perm, index = ctx.saved_tensors
         prod = out * dout
         inner = _segment_sums(prod[perm.long()], ptr)
-        return out * (dout - inner[index]), None, None, None
+        return out * (dout - inner[index]), None, None, None, None
 
 
 class DiffusionFn(torch.autograd.Function):

@@ -61,8 +61,10 @@ def softmax(src, index, num_nodes=None):
     n = maybe_num_nodes(idx, num_nodes)
     order = torch.argsort(idx, stable=True)
     ptr = torch.zeros(n + 1, dtype=torch.int32, device=idx.device)
-    ptr[1:] = torch.cumsum(torch.bincount(idx, minlength=n), 0).to(torch.int32)
-    out = SegmentSoftmaxFn.apply(s2, ptr, order.to(torch.int32).contiguous(), idx)
+    counts = torch.bincount(idx, minlength=n)
+    ptr[1:] = torch.cumsum(counts, 0).to(torch.int32)
+    long_groups = torch.nonzero(counts > SegmentSoftmaxFn.LONG).reshape(-1).to(torch.int32)
+    out = SegmentSoftmaxFn.apply(s2, ptr, order.to(torch.int32).contiguous(), idx, long_groups)
     return out[None] if batched else out
 
 

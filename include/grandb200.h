@@ -241,9 +241,12 @@ int gb_gat_softmax_fwd(const gb_graph* g, int32_t norm_idx, const float* s_src, 
 /* ---- utils.softmax(src, index, num_nodes) on ready-made scores (utils.py:116-127), for callers that hold their own
  *      [E,H] scores and a group id per edge rather than a graph plan: the host sorts the group ids once
  *      (ptr [n+1] = segment boundaries, perm [E] = position in sorted order -> caller's slot, NULL if already sorted);
- *   att[s,h] = exp(src[s,h] - max_g) / (sum_g exp(src[., h] - max_g) + 1e-16);  abar (head mean) may be NULL. heads <= 8 */
+ *   att[s,h] = exp(src[s,h] - max_g) / (sum_g exp(src[., h] - max_g) + 1e-16);  abar (head mean) may be NULL. heads <= 8
+ *   long_list [n_long]: the groups with more than long_threshold members (one CTA each instead of one warp); may be
+ *   NULL / 0 - then every group is taken by a warp whatever its size. */
 int gb_segment_softmax_fwd(const int32_t* ptr, const int32_t* perm, int32_t n, int32_t heads, const float* scores,
-                           float* att, float* abar, void* stream);
+                           float* att, float* abar, const int32_t* long_list, int32_t n_long, int32_t long_threshold,
+                           void* stream);
 
 /* ---- fused GRAND-nl evaluation (warp-per-row kernels, csrc/fused_att.cu) -------------------------
  * gb_att_fused_supported: 1 when the shapes/alignment fit the fused kernels (heads a power of two <= 8,

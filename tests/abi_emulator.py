@@ -287,8 +287,11 @@ class Emulator:
             f32(prods, G.e, heads)[:] = s.numpy()
         return 0
 
-    def gb_segment_softmax_fwd(self, ptr, perm, n, heads, scores, att, abar, stream):
+    def gb_segment_softmax_fwd(self, ptr, perm, n, heads, scores, att, abar, long_list, n_long, long_threshold, stream):
         self._note('gb_segment_softmax_fwd')
+        if n_long:                                   # the listed groups are exactly the ones above the threshold
+            sizes = np.diff(i32(ptr, n + 1))
+            assert sorted(i32(long_list, n_long).tolist()) == np.nonzero(sizes > long_threshold)[0].tolist()
         from oracle import funcs
         bounds = i32(ptr, n + 1)
         e = int(bounds[-1])
