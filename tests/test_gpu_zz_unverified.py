@@ -464,7 +464,7 @@ def test_mixed_block_state_and_gradients_incl_the_gate():
         assert_close(g.reshape(-1), r.reshape(-1), 1e-4, name)
 
 
-@pytest.mark.parametrize('function', ['laplacian', 'transformer'])
+@pytest.mark.parametrize('function', ['laplacian', 'transformer', 'GAT'])
 def test_hard_attention_block_samples_edges_while_training(function, capsys):
     from oracle import integrate as oint
     n, e, d, T = 300, 2400, 16, 2.0
@@ -478,7 +478,7 @@ def test_hard_attention_block_samples_edges_while_training(function, capsys):
     L = block.multihead_att_layer if function == 'laplacian' else block.odefunc.multihead_att_layer
     g = torch.Generator().manual_seed(2)
     with torch.no_grad():
-        for lin in (L.Q, L.K):
+        for lin in (() if function == 'GAT' else (L.Q, L.K)):             # GAT keeps its xavier init (W, a)
             lin.weight.copy_((torch.randn(lin.weight.shape, generator=g) / 4.0).to(device()))
         block.odefunc.alpha_train.fill_(0.4)
         block.odefunc.beta_train.fill_(0.2)
@@ -500,6 +500,8 @@ def test_hard_attention_block_samples_edges_while_training(function, capsys):
     x0 = _t64(x)
     if function == 'laplacian':
         f = lambda t, y: funcs.laplacian_f(y, eit, _t64(w), _t64(0.4), _t64(0.2), x0)
+    elif function == 'GAT':
+        f = lambda t, y: funcs.gat_f(y, eit, _t64(L.W), _t64(L.a).reshape(-1), 4, 0.2, _t64(0.4), _t64(0.2), x0)
     else:
         f = lambda t, y: funcs.transformer_f(y, eit, _t64(L.Q.weight), _t64(L.Q.bias), _t64(L.K.weight), _t64(L.K.bias), 4,
                                              _t64(0.4), _t64(0.2), x0)

@@ -374,7 +374,7 @@ def test_mixed_block(unverified):
     zz.test_mixed_block_state_and_gradients_incl_the_gate()
 
 
-@pytest.mark.parametrize('function', ['laplacian', 'transformer'])
+@pytest.mark.parametrize('function', ['laplacian', 'transformer', 'GAT'])
 def test_hard_attention_block(unverified, function, capsys):
     zz.test_hard_attention_block_samples_edges_while_training(function, capsys)
 
