@@ -69,12 +69,15 @@ def _combine_one(yi, terms):
     return acc
 
 
-def _combine(y, dt, ks, coeffs, signs=None):
+def _combine(y, dt, ks, coeffs, signs=None, skip=()):
     """y + dt * sum_j coeffs[j] * ks[j], per tuple component; signs[i] (+-1) multiplies component i's
     derivatives (reverse-time / adjoint sign conventions folded into the coefficients instead of
-    negating whole tensors)"""
+    negating whole tensors).  Components listed in `skip` are passed through unchanged."""
     out = []
     for i, yi in enumerate(y):
+        if i in skip:
+            out.append(yi)
+            continue
         sg = 1.0 if signs is None else signs[i]
         out.append(_combine_one(yi, [(k[i], dt * c * sg) for k, c in zip(ks, coeffs)]))
     return tuple(out)
@@ -106,6 +109,10 @@ class _Problem:
         self.dtype, self.device = ref.dtype, ref.device
         self._func = func
         self.comp_signs = None           # set by the adjoint driver: func returns raw VJPs (see _OdeintAdjoint)
+        # components the dynamics never READ (the adjoint's parameter / time integrals): their intermediate stage
+        # values are never formed, only the end-of-step combination (`passive`), or not even that (`dead`: the
+        # caller drops the component).  Same end-of-step numbers as forming everything, fewer tiny kernels.
+        self.passive, self.dead = (), ()
 
     def tensor_time(self, s):
         return torch.full((), self.sign * s, dtype=self.dtype, device=self.device)
@@ -139,17 +146,18 @@ def _fixed_grid(t0, t1, step_size):
 def _fixed_step(prob, method, t0, dt, t1, y):
     f = prob.f_raw                      # signs (reverse time, adjoint conventions) ride on the coefficients
     sg = prob.signs(len(y))
+    mid, end = tuple(prob.passive) + tuple(prob.dead), tuple(prob.dead)
     if method == 'euler':
-        return _combine(y, dt, [f(t0, y)], [1.0], sg)
+        return _combine(y, dt, [f(t0, y)], [1.0], sg, end)
     if method == 'midpoint':
         k1 = f(t0, y)
-        k2 = f(t0 + 0.5 * dt, _combine(y, dt, [k1], [0.5], sg))
-        return _combine(y, dt, [k2], [1.0], sg)
+        k2 = f(t0 + 0.5 * dt, _combine(y, dt, [k1], [0.5], sg, mid))
+        return _combine(y, dt, [k2], [1.0], sg, end)
     k1 = f(t0, y)
-    k2 = f(t0 + dt / 3, _combine(y, dt, [k1], [1 / 3], sg))
-    k3 = f(t0 + dt * 2 / 3, _combine(y, dt, [k1, k2], [-1 / 3, 1.0], sg))
-    k4 = f(t1, _combine(y, dt, [k1, k2, k3], [1.0, -1.0, 1.0], sg))
-    return _combine(y, dt, [k1, k2, k3, k4], [0.125, 0.375, 0.375, 0.125], sg)
+    k2 = f(t0 + dt / 3, _combine(y, dt, [k1], [1 / 3], sg, mid))
+    k3 = f(t0 + dt * 2 / 3, _combine(y, dt, [k1, k2], [-1 / 3, 1.0], sg, mid))
+    k4 = f(t1, _combine(y, dt, [k1, k2, k3], [1.0, -1.0, 1.0], sg, mid))
+    return _combine(y, dt, [k1, k2, k3, k4], [0.125, 0.375, 0.375, 0.125], sg, end)
 
 
 def _solve_fixed(prob, method, step_size, on_step=None):
@@ -264,7 +272,7 @@ def _solve_adaptive(prob, method, rtol, atol, max_num_steps=2 ** 31 - 1, on_step
 
 
 def odeint(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, event_fn=None, _comp_signs=None,
-           _on_step=None, _max_attempts=None):
+           _on_step=None, _max_attempts=None, _passive=(), _dead=()):
     if event_fn is not None:
         raise NotImplementedError('event handling is not part of the reference call sites')
     method = method or 'dopri5'
@@ -274,6 +282,10 @@ def odeint(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, even
         if method not in _FIXED:
             raise ValueError('_comp_signs is only meaningful for the fixed-grid solvers')
         prob.comp_signs = tuple(_comp_signs)
+    if _passive or _dead:
+        if method not in _FIXED:
+            raise ValueError('_passive / _dead components are only supported by the fixed-grid solvers')
+        prob.passive, prob.dead = tuple(_passive), tuple(_dead)
     if method in _FIXED:
         sols = _solve_fixed(prob, method, options.get('step_size'), on_step=_on_step)
     elif method in _ADAPTIVE:
@@ -333,6 +345,9 @@ def _adjoint_fixed_phased(func, params, state, t_hi, t_lo, method, step_size):
     return list(state)
 
 
+_PACK_PARAMS = True      # fixed-grid adjoint: one flat buffer for all parameter integrals (see _OdeintAdjoint.backward)
+
+
 class _OdeintAdjoint(torch.autograd.Function):
 
     @staticmethod
@@ -356,6 +371,24 @@ class _OdeintAdjoint(torch.autograd.Function):
         # Fixed-grid solves take the RAW products (cotangent +a_y) and carry the minus signs on the stage
         # coefficients (comp_signs) - no negated copies of [N,d] tensors; adaptive solves get signed values.
         comp_signs = (-1.0, 1.0, -1.0) + (-1.0,) * len(params)
+        # Fixed grid: the parameter integrals ride in ONE flat buffer (the VJPs of an evaluation are packed with one
+        # cat), are only combined at the end of a step (nothing reads their stage values) and the time integral is
+        # dropped altogether - the reference pays ~10 axpy kernels per parameter tensor per step for the same numbers.
+        packed = fixed and _PACK_PARAMS and len(params) > 0 and \
+            all(p.dtype == ys.dtype and p.device == ys.device for p in params)
+        sizes = [p.numel() for p in params]
+        zero_t = torch.zeros((), dtype=ys.dtype, device=ys.device)
+        zero_piece = {}
+
+        def pack(vps):
+            parts = []
+            for i, (g, p) in enumerate(zip(vps, params)):
+                if g is None:
+                    if i not in zero_piece:
+                        zero_piece[i] = torch.zeros(sizes[i], dtype=ys.dtype, device=ys.device)
+                    g = zero_piece[i]
+                parts.append(g.reshape(-1))
+            return torch.cat(parts)
 
         def aug_dynamics(tt, state):
             y, a_y = state[1], state[2]
@@ -366,6 +399,8 @@ class _OdeintAdjoint(torch.autograd.Function):
                 res = fused_vjp(tt, y, cot, params)
                 if res is not None:
                     f, vy, vps = res
+                    if packed:
+                        return (zero_t, f, vy, pack(vps))
                     vp = [g if g is not None else torch.zeros_like(p) for g, p in zip(vps, params)]
                     return (torch.zeros_like(tt), f, vy, *vp)
             with torch.enable_grad():
@@ -373,28 +408,41 @@ class _OdeintAdjoint(torch.autograd.Function):
                 y_ = y.detach().requires_grad_(True)
                 f = func(tt_, y_)
                 grads = torch.autograd.grad(f, (tt_, y_) + tuple(params), cot, allow_unused=True)
-            vt = grads[0] if grads[0] is not None else torch.zeros_like(tt)
             vy = grads[1] if grads[1] is not None else torch.zeros_like(y)
+            if packed:
+                return (zero_t, f.detach(), vy, pack(grads[2:]))
+            vt = grads[0] if grads[0] is not None else torch.zeros_like(tt)
             vp = [g if g is not None else torch.zeros_like(p) for g, p in zip(grads[2:], params)]
             return (vt, f.detach(), vy, *vp)
 
         with torch.no_grad():
-            state = [torch.zeros((), dtype=ys.dtype, device=ys.device), ys[-1], grad_ys[-1]] + \
-                    [torch.zeros_like(p) for p in params]
+            if packed:
+                state = [zero_t, ys[-1], grad_ys[-1], torch.zeros(sum(sizes), dtype=ys.dtype, device=ys.device)]
+                comp_signs = (-1.0, 1.0, -1.0, -1.0)
+            else:
+                state = [torch.zeros((), dtype=ys.dtype, device=ys.device), ys[-1], grad_ys[-1]] + \
+                        [torch.zeros_like(p) for p in params]
             phased = fixed and getattr(func, 'phased_ok', None) is not None and func.phased_ok(ys[-1])
             for i in range(len(times) - 1, 0, -1):
                 if phased:
+                    if packed:                                     # the phased solver keeps one tensor per parameter
+                        state = state[:3] + [v.reshape(p.shape) for v, p in zip(state[3].split(sizes), params)]
                     state = _adjoint_fixed_phased(func, params, state, times[i], times[i - 1], cfg['adjoint_method'],
                                                   cfg['adjoint_options'].get('step_size'))
+                    if packed:
+                        state = state[:3] + [torch.cat([v.reshape(-1) for v in state[3:]])]
                     state[1] = ys[i - 1]
                     state[2] = state[2] + grad_ys[i - 1]
                     continue
                 sol = odeint(aug_dynamics, tuple(state), [times[i], times[i - 1]], rtol=cfg['adjoint_rtol'],
                              atol=cfg['adjoint_atol'], method=cfg['adjoint_method'], options=cfg['adjoint_options'],
-                             _comp_signs=comp_signs if fixed else None)
+                             _comp_signs=comp_signs if fixed else None, _passive=(3,) if packed else (),
+                             _dead=(0,) if packed else ())
                 state = [s[1] for s in sol]
                 state[1] = ys[i - 1]
                 state[2] = state[2] + grad_ys[i - 1]
+            if packed:
+                state = state[:3] + [v.reshape(p.shape) for v, p in zip(state[3].split(sizes), params)]
         return (None, None, None, None, state[2]) + tuple(state[3:])
 
 

@@ -267,6 +267,40 @@ def test_eval_vjp_hook_gives_the_autograd_numbers(method):
             torch.testing.assert_close(u, v, rtol=1e-12, atol=1e-13)
 
 
+@pytest.mark.parametrize('method,step', [('rk4', 0.25), ('euler', 0.1), ('midpoint', 0.2)])
+@pytest.mark.parametrize('fused', [False, True])
+def test_packed_parameter_integrals_are_bit_identical_and_cheaper(method, step, fused, monkeypatch):
+    """fixed-grid adjoint: all parameter integrals in ONE flat buffer that is only combined at the end of a step (and
+    no time integral) - the same bits as one tensor per parameter with every stage value formed, a fraction of the
+    small-tensor operations"""
+    P = product()
+    from grand_b200 import integrators as I
+    y0 = torch.randn(30, 4, dtype=torch.float64)                 # >= 100 elements: only parameter-sized tensors are counted
+    t = torch.tensor([0.0, 0.5, 1.0], dtype=torch.float64)
+    solve = lambda f, y: P.odeint_adjoint(f, y, t, method=method, options=dict(step_size=step), adjoint_method=method,
+                                          adjoint_options=dict(step_size=step))
+    counts = {}
+    real = I._combine_one
+
+    def counting(yi, terms):
+        counts[key] = counts.get(key, 0) + (1 if yi.numel() < 100 and any(c != 0 for _, c in terms) else 0)
+        return real(yi, terms)
+
+    monkeypatch.setattr(I, '_combine_one', counting)
+    out = {}
+    for key in (True, False):
+        monkeypatch.setattr(I, '_PACK_PARAMS', key)
+        func = (FusedLinear if fused else Linear)(4, seed=3)
+        out[key] = _loss_and_grads(solve, func, y0)
+    assert out[True][0] == out[False][0] and torch.equal(out[True][1], out[False][1])
+    for a, b in zip(out[True][2], out[False][2]):
+        assert torch.equal(a, b) and a.shape == b.shape
+    n_stage = {'euler': 1, 'midpoint': 2, 'rk4': 4}[method]
+    steps = 2 * math.ceil(0.5 / step - 1e-9)                     # two output intervals, each on its own grid
+    assert counts[True] == steps                                 # one end-of-step combination of the flat buffer
+    assert counts[False] == steps * n_stage * 3                  # (time, A, b) x every stage and end-of-step combination
+
+
 def test_adjoint_params_subset_and_frozen_parameters():
     P = product()
     func = Linear(3, seed=4)
