@@ -83,6 +83,25 @@ def _combine(y, dt, ks, coeffs, signs=None, skip=()):
     return tuple(out)
 
 
+_TIME_CACHE = {}
+
+
+def _time_tensor(value, dtype, device):
+    """0-d tensor holding a time point.  A fixed grid asks for the same few values pass after pass and every
+    torch.full on a GPU is a kernel launch: the constants are kept (never written to; not while a CUDA graph is being
+    captured, whose allocations belong to the graph's pool)."""
+    key = (float(value), dtype, str(device))
+    hit = _TIME_CACHE.get(key)
+    if hit is not None:
+        return hit
+    t = torch.full((), float(value), dtype=dtype, device=device)
+    if device.type != 'cuda' or not torch.cuda.is_current_stream_capturing():
+        if len(_TIME_CACHE) >= 4096:
+            _TIME_CACHE.clear()
+        _TIME_CACHE[key] = t
+    return t
+
+
 def _rms(x):
     return x.pow(2).mean().sqrt()
 
@@ -115,7 +134,7 @@ class _Problem:
         self.passive, self.dead = (), ()
 
     def tensor_time(self, s):
-        return torch.full((), self.sign * s, dtype=self.dtype, device=self.device)
+        return _time_tensor(self.sign * s, self.dtype, self.device)
 
     def f_raw(self, s, state):
         """func at internal time s, as returned (no sign applied)"""
@@ -327,7 +346,7 @@ def _adjoint_fixed_phased(func, params, state, t_hi, t_lo, method, step_size):
         y_stage, a_stage = y, a_y
         for i in range(len(b)):
             s_i = g1 if (method == 'rk4' and i == 3) else g0 + c[i] * dt
-            tt = torch.full((), -s_i, dtype=ref.dtype, device=ref.device)
+            tt = _time_tensor(-s_i, ref.dtype, ref.device)
             f, finish = func.eval_vjp_phased(tt, y_stage, a_stage, params, prefetched=pre)
             fs = [k[1] for k in ks] + [f]
             coeffs = A[i] if i + 1 < len(b) else b
