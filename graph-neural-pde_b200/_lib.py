@@ -82,6 +82,8 @@ SIGNATURES = {
     'gb_att_bwd_fused': (C.c_int, [_G, _P, _I32, _P, _I32, _I32, _I32, _P, _P, _P, _I32, _P, _I32, _P, _I32, _P,
                                    _I32, _I32, _P, _P, _P, _I32, _P, _I32, _P, _I32, _P, _P, _P]),
     'gb_stage_combine': (C.c_int, [_P, C.POINTER(C.c_void_p), C.POINTER(C.c_float), _I32, _I64, _P, _P]),
+    'gb_stage_combine_multi': (C.c_int, [_P, C.POINTER(C.c_void_p), C.POINTER(C.c_float), _I32, _I64,
+                                         C.POINTER(C.c_void_p), _I32, _P]),
     'gb_nl_supported': (C.c_int, [_I32, _I32, _I32]),
     'gb_nl_workspace_bytes': (_SZ, []),
     'gb_nl_fwd': (C.c_int, [_G, _I32, _I32, _P, _I32, _P, _I32, _P, _I32, _I32, _I32, _I32, _P, _I32, _P, _I32, _P,

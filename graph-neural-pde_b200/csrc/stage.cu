@@ -35,6 +35,37 @@ __global__ void __launch_bounds__(256) stage_combine_kernel(const CombineArgs a)
   }
 }
 
+// The same combination written to up to 8 destinations: the caller's own buffer and the matching slab of the gathered
+// state matrix in every peer's memory (NVLink peer pointers / symmetric memory) - the all-gather of the NEXT stage's
+// state fused into the kernel that produces it (DESIGN.md "Multi-GPU", push-style exchange).  Loads are
+// read once from local HBM, every destination gets one 16-byte store per element group; remote stores are posted
+// writes, so the kernel runs at local-HBM speed while the copies drain over NVLink.
+struct CombineMultiArgs {
+  CombineArgs base;
+  float* outs[8];
+  int32_t n_out;
+};
+
+template <int NK>
+__global__ void __launch_bounds__(256) stage_combine_multi_kernel(const CombineMultiArgs m) {
+  const CombineArgs& a = m.base;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.count4; i += stride) {
+    float4 acc = ld_stream4(a.y + 4 * i);
+#pragma unroll
+    for (int j = 0; j < NK; ++j) fma4(acc, a.c[j], ld_stream4(a.k[j] + 4 * i));
+    for (int o = 0; o < m.n_out; ++o) st_stream4(m.outs[o] + 4 * i, acc);
+  }
+  const int64_t tail0 = a.count4 * 4;
+  const int64_t t = tail0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < a.count) {
+    float acc = a.y[t];
+#pragma unroll
+    for (int j = 0; j < NK; ++j) acc = fmaf(a.c[j], a.k[j][t], acc);
+    for (int o = 0; o < m.n_out; ++o) m.outs[o][t] = acc;
+  }
+}
+
 }  // namespace gb
 
 using namespace gb;
@@ -72,4 +103,47 @@ extern "C" int gb_stage_combine(const float* y, const float* const* k_host, cons
     default: stage_combine_kernel<7><<<(unsigned)blocks, 256, 0, stream>>>(a); break;
   }
   return check_launch("stage_combine");
+}
+
+extern "C" int gb_stage_combine_multi(const float* y, const float* const* k_host, const float* c_host, int32_t nk,
+                                      int64_t count, float* const* outs_host, int32_t n_out, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  GB_REQUIRE(y && outs_host && count >= 0 && nk >= 0 && nk <= 7 && n_out >= 1 && n_out <= 8,
+             "gb_stage_combine_multi: bad arguments (nk <= 7, 1 <= n_out <= 8)");
+  GB_REQUIRE(nk == 0 || (k_host && c_host), "gb_stage_combine_multi: null k / c");
+  if (count == 0) return GB_OK;
+  CombineMultiArgs m{};
+  CombineArgs& a = m.base;
+  a.y = y; a.out = nullptr; a.nk = nk; a.count = count;
+  m.n_out = n_out;
+  bool aligned = reinterpret_cast<uintptr_t>(y) % 16 == 0;
+  for (int o = 0; o < n_out; ++o) {
+    GB_REQUIRE(outs_host[o] != nullptr, "gb_stage_combine_multi: null destination %d", o);
+    m.outs[o] = outs_host[o];
+    aligned = aligned && reinterpret_cast<uintptr_t>(outs_host[o]) % 16 == 0;
+  }
+  for (int j = 0; j < nk; ++j) {
+    GB_REQUIRE(k_host[j] != nullptr, "gb_stage_combine_multi: null k[%d]", j);
+    a.k[j] = k_host[j];
+    a.c[j] = c_host[j];
+    aligned = aligned && reinterpret_cast<uintptr_t>(k_host[j]) % 16 == 0;
+  }
+  a.count4 = aligned ? count / 4 : 0;
+  const int64_t work = a.count4 > 0 ? a.count4 : count;
+  int64_t blocks = (work + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 16;
+  if (a.count4 > 0 && blocks > cap) blocks = cap;
+  if (a.count4 == 0) blocks = (count + 255) / 256;
+  LaunchScope ls(K_STAGE_AXPY, stream);
+  switch (nk) {
+    case 0: stage_combine_multi_kernel<0><<<(unsigned)blocks, 256, 0, stream>>>(m); break;
+    case 1: stage_combine_multi_kernel<1><<<(unsigned)blocks, 256, 0, stream>>>(m); break;
+    case 2: stage_combine_multi_kernel<2><<<(unsigned)blocks, 256, 0, stream>>>(m); break;
+    case 3: stage_combine_multi_kernel<3><<<(unsigned)blocks, 256, 0, stream>>>(m); break;
+    case 4: stage_combine_multi_kernel<4><<<(unsigned)blocks, 256, 0, stream>>>(m); break;
+    case 5: stage_combine_multi_kernel<5><<<(unsigned)blocks, 256, 0, stream>>>(m); break;
+    case 6: stage_combine_multi_kernel<6><<<(unsigned)blocks, 256, 0, stream>>>(m); break;
+    default: stage_combine_multi_kernel<7><<<(unsigned)blocks, 256, 0, stream>>>(m); break;
+  }
+  return check_launch("stage_combine_multi");
 }

@@ -286,6 +286,12 @@ int gb_att_bwd_fused(const gb_graph* g, const float* q, int32_t ldq, const float
  *   k_host: HOST array of nk device pointers; c_host: HOST array of nk coefficients (already times dt). */
 int gb_stage_combine(const float* y, const float* const* k_host, const float* c_host, int32_t nk, int64_t count,
                      float* out, void* stream);
+/* The same combination stored to n_out (1..8) destinations at once: the caller's buffer plus, on a row-partitioned
+ * graph, this rank's slab inside the gathered state matrix of every peer (peer pointers over NVLink: CUDA IPC or
+ * symmetric memory) - a push-style all-gather fused into the kernel that produces the next stage's state.  The
+ * caller orders the peers' reads after these writes (barrier / signal). */
+int gb_stage_combine_multi(const float* y, const float* const* k_host, const float* c_host, int32_t nk, int64_t count,
+                           float* const* outs_host, int32_t n_out, void* stream);
 
 /* ---- single-gather GRAND-nl evaluation and VJP (csrc/nl_kernels.cuh; scaled_dot, attention_norm_idx 0) ----
  * One row gather per edge: scores are formed as <Wk_h^T q_ih / sqrt(dk), x_j> (the per-(row, head) constant
