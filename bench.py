@@ -506,7 +506,8 @@ def run_partitioned(args, cfg, device, rank, world):
     d = cfg['d']
     part = grand_b200.RowPartition(n, world, rank)
     halo_kind = args.halo
-    halo = {'dense': grand_b200.Halo, 'compact': grand_b200.CompactHalo}.get(halo_kind, grand_b200.SparseHalo)(part)
+    halo = {'dense': grand_b200.Halo, 'compact': grand_b200.CompactHalo, 'push': grand_b200.PushHalo}.get(
+        halo_kind, grand_b200.SparseHalo)(part)
     gen = torch.Generator(device=device).manual_seed(99 + rank)
     x_dev = torch.randn(part.slab, d, generator=gen, device=device)
     g_dev = torch.randn(part.slab, d, generator=gen, device=device)
@@ -516,7 +517,7 @@ def run_partitioned(args, cfg, device, rank, world):
     block = build_block(cfg, device)
     block.set_partition(part, halo)
     referenced = None
-    if halo_kind != 'dense':
+    if halo_kind not in ('dense', 'push'):
         train_pass(block, data, x_dev, g_dev)           # builds the per-peer index lists (SparseHalo.prepare)
         frac = torch.tensor([halo.referenced_fraction], device=device)
         dist.all_reduce(frac, op=dist.ReduceOp.MAX)
@@ -620,7 +621,9 @@ def run_partitioned(args, cfg, device, rank, world):
                    'overlapped_exchange': os.environ.get('GRANDB200_OVERLAP') == '1',
                    'halo': halo_kind + {'sparse': ' (all_to_all_v of the referenced rows only)',
                                         'compact': ' (all_to_all_v of the referenced rows only; local graph relabelled to '
-                                                   '[own slab | referenced rows])'}.get(
+                                                   '[own slab | referenced rows])',
+                                        'push': ' (all-gather = one broadcast-store kernel into symmetric memory + barrier; '
+                                                'reduce-scatter over NCCL)'}.get(
                                             halo_kind, ' (all-gather / reduce-scatter of whole slabs)'),
                    'rows_of_the_local_problem_rank0': getattr(halo, 'view', part).n_pad,
                    'remote_rows_referenced_max_over_ranks': referenced},
@@ -639,6 +642,7 @@ def run_partitioned(args, cfg, device, rank, world):
     emit(line)
 
 
+@torch.no_grad()
 def exchange_times(halo, part, d, device, n_gathers, n_scatters, step_ms):
     """the two collectives of the partitioned path timed alone (CUDA events, max over ranks), outside the timed
     region: how much of a step is exchange, and the NVLink rate the exchanges themselves reach"""
@@ -859,11 +863,12 @@ def main():
                     help='skip the torch-CUDA-ops comparator (N = 1 only)')
     ap.add_argument('--function', default='transformer', choices=['transformer', 'laplacian'],
                     help='transformer = GRAND-nl (BASELINE.json headline); laplacian = GRAND-l sweep of config 5')
-    ap.add_argument('--halo', default=os.environ.get('GRANDB200_HALO', 'dense'), choices=['dense', 'sparse', 'compact', 'auto'],
+    ap.add_argument('--halo', default=os.environ.get('GRANDB200_HALO', 'dense'), choices=['dense', 'sparse', 'compact', 'push', 'auto'],
                     help='N > 1: exchange whole slabs (dense), only the rows the peers reference (sparse: R-MAT slabs '
                          'reference ~25 %% of the others at 8 ranks), sparse exchange + the rank\'s graph relabelled to '
                          '[own slab | referenced rows] so all per-rank work is O(N/P + halo) (compact), or dense / sparse '
-                         'decided from the measured fraction (auto)')
+                         'decided from the measured fraction (auto); push = whole slabs stored straight into the peers\' symmetric memory '
+                         'by one kernel instead of a NCCL all-gather')
     ap.add_argument('--microbench', action='store_true',
                     help='isolated per-evaluation timing (SURVEY.md 8d): forward and adjoint evaluation alone, '
                          'L2 hot and L2 flushed, >= 100 iterations; 1 GPU')

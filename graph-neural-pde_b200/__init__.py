@@ -23,7 +23,7 @@ from .model_configurations import set_block, set_function
 from . import integrators
 from . import partition
 from .graphed import GraphedPass
-from .partition import RowPartition, Halo, LoopbackHalo, SparseHalo, CompactHalo
+from .partition import RowPartition, Halo, LoopbackHalo, SparseHalo, CompactHalo, PushHalo
 from .integrators import odeint, odeint_adjoint
 from .early_stop_solver import EarlyStopInt
 from .base_classes import BaseGNN
@@ -33,4 +33,4 @@ from .GNN_early import GNNEarly
 __all__ = ['GraphPlan', 'get_plan', 'MaxNFEException', 'get_rw_adj', 'gcn_norm_fill_val',
            'add_remaining_self_loops', 'Meter', 'ODEFunc', 'ODEblock', 'GraphData', 'LaplacianODEFunc',
            'ODEFuncTransformerAtt', 'SpGraphTransAttentionLayer', 'ODEFuncAtt', 'SpGraphAttentionLayer', 'ConstantODEblock', 'AttODEblock', 'MixedODEblock', 'HardAttODEblock',
-           'set_block', 'set_function', 'partition', 'GraphedPass', 'RowPartition', 'Halo', 'LoopbackHalo', 'SparseHalo', 'CompactHalo', 'odeint', 'odeint_adjoint', 'integrators', 'EarlyStopInt', 'BaseGNN', 'GNN', 'GNNEarly']
+           'set_block', 'set_function', 'partition', 'GraphedPass', 'RowPartition', 'Halo', 'LoopbackHalo', 'SparseHalo', 'CompactHalo', 'PushHalo', 'odeint', 'odeint_adjoint', 'integrators', 'EarlyStopInt', 'BaseGNN', 'GNN', 'GNNEarly']

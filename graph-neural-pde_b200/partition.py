@@ -349,6 +349,67 @@ class CompactHalo(SparseHalo):
         return out
 
 
+class PushHalo(Halo):
+    """Halo whose all-gather is a PUSH over NVLink peer memory instead of a NCCL collective (DESIGN.md "Multi-GPU").
+
+    The gathered [N_pad, d] matrices live in symmetric memory (torch.distributed._symmetric_memory: every rank holds
+    a pointer to every peer's copy).  A gather is ONE kernel on the producing rank - gb_stage_combine_multi with no
+    stage terms = a P-way broadcast store of the rank's slab into its row range of every copy (posted writes: the
+    kernel runs at local HBM speed while the copies drain over NVLink) - followed by a symmetric-memory barrier that
+    orders every rank's reads after every rank's writes.  A ring of RING matrices per state width: a rank can only
+    start writing matrix b again after it has passed a later barrier, which every peer reaches only after its reads
+    of b were queued, so nobody overwrites what somebody still reads.  The reduce-scatter of dL/dx stays NCCL.
+
+    Not yet run on hardware (needs >= 2 GPUs): opt-in, `bench.py --halo push`."""
+
+    RING = 3
+
+    def __init__(self, part, group=None):
+        super().__init__(part, group)
+        self._rings = {}
+
+    def _symmetric(self, rows, width, dtype, device):
+        """(local tensor [rows, width], peer base pointers [world], barrier()) - one collective per allocation"""
+        import torch.distributed._symmetric_memory as symm
+        t = symm.empty(rows, width, dtype=dtype, device=device)
+        handle = symm.rendezvous(t, self.group if self.group is not None else self.dist.group.WORLD)
+        return t, [int(p) for p in handle.buffer_ptrs], handle.barrier
+
+    def _next(self, width, dtype, device):
+        key = (int(width), dtype, str(device))
+        ring = self._rings.get(key)
+        if ring is None:
+            ring = self._rings[key] = [[self._symmetric(self.part.n_pad, width, dtype, device)
+                                        for _ in range(self.RING)], 0]
+        entry = ring[0][ring[1] % self.RING]
+        ring[1] += 1
+        return entry
+
+    def all_gather_rows(self, slab):
+        import ctypes as C
+        slab = slab.contiguous()
+        if slab.dim() != 2 or slab.dtype != torch.float32:
+            raise TypeError('PushHalo exchanges fp32 [S, d] slabs')
+        part = self.part
+        full, ptrs, barrier = self._next(slab.shape[1], slab.dtype, slab.device)
+        offset = 4 * part.rank * part.slab * slab.shape[1]                 # my rows inside every copy
+        outs = (C.c_void_p * part.world)(*[p + offset for p in ptrs])
+        lib = _lib.load()
+        _lib.check(lib.gb_stage_combine_multi(slab.data_ptr(), None, None, 0, slab.numel(), outs, part.world,
+                                              _lib.stream()), 'gb_stage_combine_multi')
+        barrier()                                                          # all writes land before any rank reads
+        self.bytes_in += (part.world - 1) * slab.numel() * slab.element_size()
+        self.n_gathers += 1
+        # autograd keeps the gathered matrix for backward: hand out a private copy then, the ring buffer otherwise
+        return full.clone() if torch.is_grad_enabled() else full
+
+    def all_gather_rows_async(self, slab):
+        """the push is already asynchronous to the host and its stores are posted: issue it now, nothing to wait for"""
+        full = self.all_gather_rows(slab)
+        self.n_prefetched = getattr(self, 'n_prefetched', 0) + 1
+        return PendingGather(slab, slab, full, None)
+
+
 class PendingExchange:
     """an all_to_all_v in flight; wait() completes it and runs the local unpacking step"""
 

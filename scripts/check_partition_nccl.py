@@ -104,8 +104,10 @@ def main():
         for function in ('transformer', 'laplacian'):
             os.environ['GRANDB200_OVERLAP'] = '0'
             z_ref, g_ref = train_pass(make_block(function, device), data, x, gz)
-            for kind, cls in (('dense', grand_b200.Halo), ('sparse', grand_b200.SparseHalo),
-                              ('compact', grand_b200.CompactHalo)):
+            kinds = [('dense', grand_b200.Halo), ('sparse', grand_b200.SparseHalo), ('compact', grand_b200.CompactHalo)]
+            if not args.emulate:                                   # symmetric memory needs real GPUs
+                kinds.append(('push', grand_b200.PushHalo))
+            for kind, cls in kinds:
                 for overlap in ('0', '1'):
                     os.environ['GRANDB200_OVERLAP'] = overlap
                     halo = cls(part)

@@ -304,6 +304,15 @@ class Emulator:
             vec(abar, e)[:] = p.mean(dim=1).numpy()
         return 0
 
+    def gb_stage_combine_multi(self, y, ks, cs, nk, count, outs, n_out, stream):
+        self._note('gb_stage_combine_multi')
+        acc = vec(y, count).astype(np.float64)
+        for j in range(nk):
+            acc = acc + float(cs[j]) * vec(ks[j], count)
+        for o in range(n_out):
+            vec(outs[o], count)[:] = acc
+        return 0
+
     def gb_edge_softmax_bwd(self, g, norm_idx, att, dabar, datt, heads, edge_w, ds, stream):
         self._note('gb_edge_softmax_bwd')
         G = Graph(g)

@@ -352,6 +352,49 @@ def test_rank_without_rows(halo):
     assert dict(ret) == {r: 'ok' for r in range(world)}
 
 
+def test_push_halo_world_of_one(host, monkeypatch, tmp_path):
+    """PushHalo's host logic on a 1-rank gloo group with local memory standing in for the symmetric allocation: the
+    gather is one gb_stage_combine_multi call (no stage terms, one destination per rank) + a barrier, buffers come
+    from a ring of 3, autograd gets private copies; the block path equals the un-partitioned block"""
+    import torch.distributed as dist
+    import grand_b200
+    n, d = 150, 32
+    ei = torch.tensor(og.shaped_graph(n, 900, 9))
+    gen = torch.Generator().manual_seed(0)
+    x, gz = torch.randn(n, d, generator=gen), torch.randn(n, d, generator=gen)
+    data = grand_b200.GraphData()
+    data.new_graph(ei, n)
+    base = _train_pass(_make_block(), data, x, gz)
+    dist.init_process_group('gloo', init_method=f'file://{tmp_path}/rdzv', rank=0, world_size=1)
+    try:
+        part = grand_b200.RowPartition(n, 1, 0)
+        halo = grand_b200.PushHalo(part)
+        allocs, barriers = [], []
+
+        def fake_symmetric(rows, width, dtype, device):
+            t = torch.full((rows, width), float('nan'), dtype=dtype)
+            allocs.append(t)
+            return t, [t.data_ptr()], lambda: barriers.append(len(allocs))
+
+        monkeypatch.setattr(halo, '_symmetric', fake_symmetric)
+        block = _make_block()
+        block.set_partition(part, halo)
+        del host.calls[:]
+        other = _train_pass(block, data, x, gz)
+        assert host.calls.count('gb_stage_combine_multi') == halo.n_gathers == len(barriers) == 16
+        assert len(allocs) == 3                                        # the ring, allocated once
+        assert_close(other[0], base[0], 2e-5, 'z')
+        for a, b in zip(other[1], base[1]):
+            assert_close(a, b, 2e-5, 'grad', floor=1e-3)
+        with torch.no_grad():                                          # no autograd: the ring buffer itself is handed out
+            full = halo.all_gather_rows(x)
+        assert any(full is t for t in allocs) and torch.equal(full, x)
+        with torch.enable_grad():
+            assert not any(halo.all_gather_rows(x) is t for t in allocs)
+    finally:
+        dist.destroy_process_group()
+
+
 def test_block_api_world_of_one_matches_unpartitioned(host):
     """port of tests/test_gpu_partition.py::test_block_api_world_of_one_matches_unpartitioned"""
     import grand_b200
