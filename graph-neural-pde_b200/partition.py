@@ -404,10 +404,37 @@ class PushHalo(Halo):
         return full.clone() if torch.is_grad_enabled() else full
 
     def all_gather_rows_async(self, slab):
-        """the push is already asynchronous to the host and its stores are posted: issue it now, nothing to wait for"""
-        full = self.all_gather_rows(slab)
+        """the push and its barrier issued on a side stream (ordered after the work already queued on the current
+        one), so that kernels launched before wait() overlap the barrier's wait for the slowest peer"""
+        if not slab.is_cuda:
+            full = self.all_gather_rows(slab)
+            self.n_prefetched = getattr(self, 'n_prefetched', 0) + 1
+            return PendingGather(slab, slab, full, None)
+        side = self.__dict__.get('_side')
+        if side is None:
+            side = self._side = torch.cuda.Stream(device=slab.device)
+        main = torch.cuda.current_stream(slab.device)
+        side.wait_stream(main)
+        slab_c = slab.contiguous()
+        with torch.cuda.stream(side):
+            full = self.all_gather_rows(slab_c)
+        slab_c.record_stream(side)
+        full.record_stream(side)
         self.n_prefetched = getattr(self, 'n_prefetched', 0) + 1
-        return PendingGather(slab, slab, full, None)
+        return _StreamPending(slab, full, side)
+
+
+class _StreamPending:
+    """work queued on a side stream; wait() makes the current stream wait for it (no host block)"""
+
+    def __init__(self, src, result, stream):
+        self.src, self._result, self._stream = src, result, stream
+
+    def wait(self):
+        if self._stream is not None:
+            torch.cuda.current_stream(self._result.device).wait_stream(self._stream)
+            self._stream = None
+        return self._result
 
 
 class PendingExchange:
