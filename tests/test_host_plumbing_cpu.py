@@ -331,7 +331,7 @@ def test_beltrami_split_exp_kernel_forward_is_on_by_default_training_is_not(host
         out.sum().backward()
 
 
-@pytest.mark.parametrize('norm_idx,heads', [(0, 2), (1, 4), (0, 8), (1, 1)])
+@pytest.mark.parametrize('norm_idx,heads', [(0, 2), (1, 4), (0, 8), (1, 1), (0, 3)])
 def test_gat_function(unverified, norm_idx, heads):
     zz.test_gat_function_matches_the_oracle(norm_idx, heads)
     calls = unverified.calls
