@@ -623,7 +623,7 @@ def run_partitioned(args, cfg, device, rank, world):
                                         'compact': ' (all_to_all_v of the referenced rows only; local graph relabelled to '
                                                    '[own slab | referenced rows])',
                                         'push': ' (all-gather = one broadcast-store kernel into symmetric memory + barrier; '
-                                                'reduce-scatter over NCCL)'}.get(
+                                                'reduce-scatter = barrier + one kernel pulling the peers\' shares)'}.get(
                                             halo_kind, ' (all-gather / reduce-scatter of whole slabs)'),
                    'rows_of_the_local_problem_rank0': getattr(halo, 'view', part).n_pad,
                    'remote_rows_referenced_max_over_ranks': referenced},

@@ -107,7 +107,8 @@ class LaplacianODEFunc(ODEFunc):
         g_slab = self._as_2d(cot).detach().contiguous()
 
         def finish():
-            dx_share, dparams = P.diffusion_local_vjp(part, plan, vals, x_full, x0, alpha, sig, g_slab)
+            dx_share, dparams = P.diffusion_local_vjp(part, plan, vals, x_full, x0, alpha, sig, g_slab,
+                                                      dx_out=P.share_buffer(halo, x_full))
             dx = halo.reduce_scatter_rows(dx_share)
             halo.all_reduce_(dparams)
             named = ((self.alpha_train, dparams[0].reshape(self.alpha_train.shape)),

@@ -331,7 +331,8 @@ class ODEFuncTransformerAtt(ODEFunc):
         q = _nl_q(x2, wq, bq)
         half = P.nl_local_vjp_rows(part, plan, x_full, q, wq, wk, self.alpha_train.detach(),
                                    self.beta_train.detach() if x0 is not None else None, x0, L.h,
-                                   not self.opt['no_alpha_sigmoid'], self._as_2d(cot).detach().contiguous(), True)
+                                   not self.opt['no_alpha_sigmoid'], self._as_2d(cot).detach().contiguous(), True,
+                                   dx_out=P.share_buffer(halo, x_full))
         a, d = wq.shape
 
         def finish():

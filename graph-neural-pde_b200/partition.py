@@ -358,7 +358,13 @@ class PushHalo(Halo):
     kernel runs at local HBM speed while the copies drain over NVLink) - followed by a symmetric-memory barrier that
     orders every rank's reads after every rank's writes.  A ring of RING matrices per state width: a rank can only
     start writing matrix b again after it has passed a later barrier, which every peer reaches only after its reads
-    of b were queued, so nobody overwrites what somebody still reads.  The reduce-scatter of dL/dx stays NCCL.
+    of b were queued, so nobody overwrites what somebody still reads.
+
+    The reduce-scatter of dL/dx is a PULL over the same mechanism: every rank forms its share for all columns in a
+    symmetric buffer (`share_buffer`, handed to the VJP kernels as their output), a barrier, then ONE
+    gb_stage_combine launch per rank sums its own slab rows of the P shares - own share first, then the peers' in
+    rank order, read straight from their memory: deterministic, no NCCL on the data path.  Parameter gradients
+    (a few KB) still go through all_reduce.
 
     Not yet run on hardware (needs >= 2 GPUs): opt-in, `bench.py --halo push`."""
 
@@ -422,6 +428,45 @@ class PushHalo(Halo):
         full.record_stream(side)
         self.n_prefetched = getattr(self, 'n_prefetched', 0) + 1
         return _StreamPending(slab, full, side)
+
+    def share_buffer(self, rows, width, device):
+        """next [rows, width] fp32 matrix of the ring the peers can read (nl_local_vjp & co. write dL/dx into it)"""
+        key = ('share', int(rows), int(width), str(device))
+        ring = self._rings.get(key)
+        if ring is None:
+            ring = self._rings[key] = [[self._symmetric(rows, width, torch.float32, device)
+                                        for _ in range(self.RING)], 0]
+        entry = ring[0][ring[1] % self.RING]
+        ring[1] += 1
+        self.__dict__.setdefault('_shares', {})[id(entry[0])] = entry
+        return entry[0]
+
+    def reduce_scatter_rows(self, full):
+        import ctypes as C
+        entry = self.__dict__.get('_shares', {}).get(id(full))
+        if entry is None or entry[0] is not full:                          # not formed in a share buffer: NCCL
+            return super().reduce_scatter_rows(full)
+        part = self.part
+        _t, ptrs, barrier = entry
+        width = full.shape[1]
+        if full.shape[0] != part.n_pad:
+            raise ValueError('PushHalo.reduce_scatter_rows: share must cover all N_pad rows')
+        barrier()                                                          # every rank's share is complete
+        offset = 4 * part.rank * part.slab * width
+        peers = [ptrs[p] + offset for p in range(part.world) if p != part.rank]
+        out = full.new_empty((part.slab, width))
+        ks = (C.c_void_p * max(1, len(peers)))(*peers)
+        cs = (C.c_float * max(1, len(peers)))(*([1.0] * len(peers)))
+        lib = _lib.load()
+        _lib.check(lib.gb_stage_combine(ptrs[part.rank] + offset, ks, cs, len(peers), part.slab * width,
+                                        out.data_ptr(), _lib.stream()), 'gb_stage_combine')
+        self.bytes_in += (part.world - 1) * out.numel() * out.element_size()
+        self.n_scatters += 1
+        return out
+
+    def reduce_scatter_rows_async(self, full):
+        out = self.reduce_scatter_rows(full)
+        return PendingScatter(full, None, lambda: out)
 
 
 class _StreamPending:
@@ -534,8 +579,15 @@ def nl_local_forward(part, plan, x_full, x_slab, wq, bq, wk, alpha_train, beta_t
     return out, q
 
 
+def share_buffer(halo, like):
+    """where a rank's share of dL/dx for all columns is formed: a buffer the halo can exchange in place (PushHalo:
+    symmetric memory the peers pull from) or None (an ordinary allocation)"""
+    make = getattr(halo, 'share_buffer', None)
+    return None if make is None else make(like.shape[0], like.shape[1], like.device)
+
+
 def nl_local_vjp(part, plan, x_full, q, wq, wk, alpha_train, beta_train, x0_slab, heads, alpha_sigmoid, g_slab,
-                 want_f, want_w):
+                 want_f, want_w, dx_out=None):
     """this rank's share of the VJP.  Returns (f_slab|None, dx_share [N_pad,d] (to be reduce-scattered; already
     holds dq Wq for the owned rows and dk Wk for every column), grads: flat share of
     (dWq, dWk, dbq, dbk, dalpha, dbeta) [2A(d+1) + 2], or of (dalpha, dbeta) [2] when want_w is False) -
@@ -555,7 +607,7 @@ def nl_local_vjp(part, plan, x_full, q, wq, wk, alpha_train, beta_train, x0_slab
     dqk = torch.empty(n_pad, 2 * a, **f32)
     dqk[:part.lo, :a].zero_()
     dqk[part.hi:, :a].zero_()
-    dx = torch.empty(n_pad, d, **f32)
+    dx = torch.empty(n_pad, d, **f32) if dx_out is None else dx_out
     out = None
     if want_f:
         out = torch.zeros(s, d, **f32) if part.hi - part.lo < s else torch.empty(s, d, **f32)
@@ -589,7 +641,7 @@ class _NlVjpHalf:
 
 
 def nl_local_vjp_rows(part, plan, x_full, q, wq, wk, alpha_train, beta_train, x0_slab, heads, alpha_sigmoid, g_slab,
-                      want_w):
+                      want_w, dx_out=None):
     """first half of nl_local_vjp: the row pass only (gb_nl_adjoint_phase, GB_NL_PHASE_ROWS).  On return (i.e. once
     the launch is queued) `.f` holds f for the owned rows - all the solver needs to form the NEXT stage's state, whose
     all-gather can then run while nl_local_vjp_cols() works."""
@@ -610,7 +662,7 @@ def nl_local_vjp_rows(part, plan, x_full, q, wq, wk, alpha_train, beta_train, x0
     h.dqk = torch.empty(n_pad, 2 * a, **f32)
     h.dqk[:part.lo, :a].zero_()
     h.dqk[part.hi:, :a].zero_()
-    h.dx = torch.empty(n_pad, d, **f32)
+    h.dx = torch.empty(n_pad, d, **f32) if dx_out is None else dx_out
     h.f = torch.zeros(s, d, **f32) if part.hi - part.lo < s else torch.empty(s, d, **f32)
     h.partials = torch.empty(int(lib.gb_att_bwd_fused_partials(plan.c)), **f32)
     h.grads = torch.empty(2 * a * d + 2 * a + 2 if want_w else 2, **f32)
@@ -682,12 +734,12 @@ def diffusion_local_forward(part, plan, vals, x_full, x0_slab, alpha_train, beta
     return out
 
 
-def diffusion_local_vjp(part, plan, vals, x_full, x0_slab, alpha_train, alpha_sigmoid, g_slab):
+def diffusion_local_vjp(part, plan, vals, x_full, x0_slab, alpha_train, alpha_sigmoid, g_slab, dx_out=None):
     """this rank's share of dx for all columns [N_pad, d] and of (dalpha_train, dbeta_train) [2]"""
     lib = _lib.load()
     n_pad, d = x_full.shape
     dev = x_full.device
-    dx = torch.empty(n_pad, d, dtype=torch.float32, device=dev)
+    dx = torch.empty(n_pad, d, dtype=torch.float32, device=dev) if dx_out is None else dx_out
     partials = torch.empty(int(lib.gb_spmm_bwd_partials(plan.c, d)), dtype=torch.float32, device=dev)
     dparams = torch.empty(2, dtype=torch.float32, device=dev)
     own_hi = part.hi if part.hi > 0 else -1                  # (0, 0) means "own everything" to the library
@@ -723,7 +775,7 @@ class PartNlFn(torch.autograd.Function):
         a, d = wq.shape
         _, dx_share, grads = nl_local_vjp(ctx.part, ctx.plan, x_full, q, wq.contiguous(), wk.contiguous(), alpha_train,
                                           beta_train, x0_slab, ctx.heads, ctx.alpha_sigmoid, g_slab.contiguous(),
-                                          False, True)
+                                          False, True, dx_out=share_buffer(ctx.halo, x_full))
         dx = ctx.halo.reduce_scatter_rows(dx_share)
         ctx.halo.all_reduce_(grads)
         dwq, dwk, dbq, dbk, dalpha, dbeta = unpack_nl_grads(grads, a, d)
@@ -758,7 +810,8 @@ class PartDiffusionFn(torch.autograd.Function):
             raise NotImplementedError('gradients w.r.t. edge values are not available on the partitioned path')
         dx_share, dparams = diffusion_local_vjp(ctx.part, ctx.plan, vals, x_full,
                                                 x0_slab if beta_train is not None else None, alpha_train,
-                                                ctx.alpha_sigmoid, g_slab.contiguous())
+                                                ctx.alpha_sigmoid, g_slab.contiguous(),
+                                                dx_out=share_buffer(ctx.halo, x_full))
         dx = ctx.halo.reduce_scatter_rows(dx_share)
         ctx.halo.all_reduce_(dparams)
         return (dx, None, dparams[0].reshape(alpha_train.shape),
@@ -774,6 +827,6 @@ def nl_eval_vjp_part(part, halo, plan, x_slab, g_slab, wq, bq, wk, alpha_train, 
     from .ops import _nl_q
     q = _nl_q(x_slab, wq, bq)
     f, dx_share, grads = nl_local_vjp(part, plan, x_full, q, wq, wk, alpha_train, beta_train, x0_slab, heads,
-                                      alpha_sigmoid, g_slab.contiguous(), True, True)
+                                      alpha_sigmoid, g_slab.contiguous(), True, True, dx_out=share_buffer(halo, x_full))
     dx = halo.reduce_scatter_rows(dx_share)
     return f, dx, grads

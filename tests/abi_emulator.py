@@ -304,6 +304,14 @@ class Emulator:
             vec(abar, e)[:] = p.mean(dim=1).numpy()
         return 0
 
+    def gb_stage_combine(self, y, ks, cs, nk, count, out, stream):
+        self._note('gb_stage_combine')
+        acc = vec(y, count).astype(np.float64)
+        for j in range(nk):
+            acc = acc + float(cs[j]) * vec(ks[j], count)
+        vec(out, count)[:] = acc
+        return 0
+
     def gb_stage_combine_multi(self, y, ks, cs, nk, count, outs, n_out, stream):
         self._note('gb_stage_combine_multi')
         acc = vec(y, count).astype(np.float64)

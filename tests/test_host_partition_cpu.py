@@ -381,8 +381,10 @@ def test_push_halo_world_of_one(host, monkeypatch, tmp_path):
         block.set_partition(part, halo)
         del host.calls[:]
         other = _train_pass(block, data, x, gz)
-        assert host.calls.count('gb_stage_combine_multi') == halo.n_gathers == len(barriers) == 16
-        assert len(allocs) == 3                                        # the ring, allocated once
+        assert host.calls.count('gb_stage_combine_multi') == halo.n_gathers == 16
+        # the 8 VJPs formed their dL/dx share in symmetric buffers and were reduced by a pull (no collective)
+        assert host.calls.count('gb_stage_combine') == halo.n_scatters == 8 and len(barriers) == 24
+        assert len(allocs) == 6                                        # two rings (gathered state, dL/dx share) of 3
         assert_close(other[0], base[0], 2e-5, 'z')
         for a, b in zip(other[1], base[1]):
             assert_close(a, b, 2e-5, 'grad', floor=1e-3)
