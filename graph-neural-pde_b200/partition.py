@@ -376,9 +376,18 @@ class PushHalo(Halo):
 
     def _symmetric(self, rows, width, dtype, device):
         """(local tensor [rows, width], peer base pointers [world], barrier()) - one collective per allocation"""
+        import warnings
         import torch.distributed._symmetric_memory as symm
+        group = self.group if self.group is not None else self.dist.group.WORLD
+        try:                                                   # older torch wants the group registered first
+            with warnings.catch_warnings():
+                warnings.simplefilter('ignore')
+                if not symm.is_symm_mem_enabled_for_group(group.group_name):
+                    symm.enable_symm_mem_for_group(group.group_name)
+        except (AttributeError, RuntimeError):
+            pass
         t = symm.empty(rows, width, dtype=dtype, device=device)
-        handle = symm.rendezvous(t, self.group if self.group is not None else self.dist.group.WORLD)
+        handle = symm.rendezvous(t, group)
         return t, [int(p) for p in handle.buffer_ptrs], handle.barrier
 
     def _next(self, width, dtype, device):
