@@ -73,8 +73,9 @@ class Halo:
     def prepare(self, plan):
         """hook for halos that need the graph (SparseHalo); the dense exchange needs nothing"""
 
-    def all_gather_rows(self, slab):
-        """[S, d] slab of every rank -> [N_pad, d] on every rank"""
+    def all_gather_rows(self, slab, keep=False):
+        """[S, d] slab of every rank -> [N_pad, d] on every rank.  keep=True: the caller will hold on to the result
+        (saved for a backward pass) - halos that recycle their gather buffers hand out a private one then."""
         slab = slab.contiguous()
         full = slab.new_empty((self.part.n_pad,) + tuple(slab.shape[1:]))
         self.dist.all_gather_into_tensor(full, slab, group=self.group)
@@ -178,13 +179,13 @@ class SparseHalo(Halo):
 
     RING = 3       # gathered matrices alive at once under no_grad: the one in use, the prefetched one, one spare
 
-    def _gather_buffer(self, slab):
+    def _gather_buffer(self, slab, keep=False):
         """[N_pad, d] matrix whose unreferenced rows are zero.  Under no_grad (forward integration, adjoint solve) the
         result is consumed within the evaluation, so a small ring of persistent buffers is reused: only the owned and
         referenced rows are rewritten, the rest was zeroed once (no 4 N d byte memset per exchange).  With autograd
         recording, the gathered matrix is saved for backward and must not be overwritten: a fresh one each time."""
         shape = (self.part.n_pad,) + tuple(slab.shape[1:])
-        if torch.is_grad_enabled():
+        if keep or torch.is_grad_enabled():
             return slab.new_zeros(shape)
         key = (shape, slab.dtype, slab.device)
         ring = self.__dict__.setdefault('_ring', {})
@@ -197,9 +198,9 @@ class SparseHalo(Halo):
         ring[key] = (bufs, nxt + 1)
         return buf
 
-    def _finish_gather(self, slab, recv):
+    def _finish_gather(self, slab, recv, keep=False):
         part = self.part
-        full = self._gather_buffer(slab)
+        full = self._gather_buffer(slab, keep)
         full[part.rank * part.slab:(part.rank + 1) * part.slab] = slab
         if recv.shape[0]:
             full.index_copy_(0, self.recv_idx, recv)
@@ -216,9 +217,9 @@ class SparseHalo(Halo):
         self.n_gathers += 1
         return slab, send, recv, work
 
-    def all_gather_rows(self, slab):
+    def all_gather_rows(self, slab, keep=False):
         slab, _send, recv, _ = self._start_gather(slab, False)
-        return self._finish_gather(slab, recv)
+        return self._finish_gather(slab, recv, keep)
 
     def all_gather_rows_async(self, slab):
         slab_c, send, recv, work = self._start_gather(slab, True)
@@ -325,8 +326,8 @@ class CompactHalo(SparseHalo):
         self.n_gathers += 1
         return local, send, recv, work
 
-    def _finish_gather(self, local, recv):
-        return local
+    def _finish_gather(self, local, recv, keep=False):
+        return local                                                   # a fresh matrix every time: nothing is recycled
 
     def _start_scatter(self, full, async_op):
         self._check()
@@ -400,7 +401,7 @@ class PushHalo(Halo):
         ring[1] += 1
         return entry
 
-    def all_gather_rows(self, slab):
+    def all_gather_rows(self, slab, keep=False):
         import ctypes as C
         slab = slab.contiguous()
         if slab.dim() != 2 or slab.dtype != torch.float32:
@@ -415,8 +416,8 @@ class PushHalo(Halo):
         barrier()                                                          # all writes land before any rank reads
         self.bytes_in += (part.world - 1) * slab.numel() * slab.element_size()
         self.n_gathers += 1
-        # autograd keeps the gathered matrix for backward: hand out a private copy then, the ring buffer otherwise
-        return full.clone() if torch.is_grad_enabled() else full
+        # a caller that keeps the gathered matrix (saved for backward) gets a private copy, else the ring buffer
+        return full.clone() if (keep or torch.is_grad_enabled()) else full
 
     def all_gather_rows_async(self, slab):
         """the push and its barrier issued on a side stream (ordered after the work already queued on the current
@@ -546,7 +547,7 @@ class LoopbackHalo:
     def prepare(self, plan):
         pass
 
-    def all_gather_rows(self, slab):
+    def all_gather_rows(self, slab, keep=False):
         return slab.contiguous()
 
     def all_gather_rows_async(self, slab):
@@ -770,7 +771,8 @@ class PartNlFn(torch.autograd.Function):
     def forward(ctx, x_slab, wq, bq, wk, bk, alpha_train, beta_train, x0_slab, part, halo, plan, heads, alpha_sigmoid):
         x_slab = x_slab.contiguous()
         halo.prepare(plan)
-        x_full = halo.all_gather_rows(x_slab)
+        # Function.forward runs with grad mode off: tell the halo itself whether this state is saved for a backward
+        x_full = halo.all_gather_rows(x_slab, keep=any(ctx.needs_input_grad))
         out, q = nl_local_forward(part, plan, x_full, x_slab, wq.contiguous(), bq.contiguous(), wk.contiguous(),
                                   alpha_train, beta_train, x0_slab, heads, alpha_sigmoid)
         ctx.save_for_backward(x_full, q, wq, wk, alpha_train, beta_train, x0_slab)
@@ -805,7 +807,7 @@ class PartDiffusionFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x_slab, vals, alpha_train, beta_train, x0_slab, part, halo, plan, alpha_sigmoid):
         halo.prepare(plan)
-        x_full = halo.all_gather_rows(x_slab.contiguous())
+        x_full = halo.all_gather_rows(x_slab.contiguous(), keep=any(ctx.needs_input_grad))
         out = diffusion_local_forward(part, plan, vals, x_full, x0_slab, alpha_train, beta_train, alpha_sigmoid)
         ctx.save_for_backward(x_full, vals, alpha_train, beta_train, x0_slab)
         ctx.part, ctx.halo, ctx.plan, ctx.alpha_sigmoid = part, halo, plan, alpha_sigmoid

@@ -193,9 +193,9 @@ def _train_pass(block, data, x, g):
     return z.detach(), grads, block.odefunc.nfe
 
 
-def _make_block(function='transformer'):
+def _make_block(function='transformer', adjoint=True):
     import grand_b200
-    opt = dict(OPT, function=function, block='attention' if function == 'transformer' else 'constant')
+    opt = dict(OPT, function=function, block='attention' if function == 'transformer' else 'constant', adjoint=adjoint)
     block = grand_b200.set_block(opt)(grand_b200.set_function(opt), [], opt, CPU, t=torch.tensor([0., 2.]))
     block.train()
     g = torch.Generator().manual_seed(5)
@@ -209,7 +209,8 @@ def _make_block(function='transformer'):
     return block
 
 
-def _gloo_worker(rank, world, port, n, d, ret, overlap=False, function='transformer', sparse=False, tiny=False):
+def _gloo_worker(rank, world, port, n, d, ret, overlap=False, function='transformer', sparse=False, tiny=False,
+                 adjoint=True):
     if overlap:
         os.environ['GRANDB200_OVERLAP'] = '1'
     sys.path.insert(0, ROOT)
@@ -233,16 +234,16 @@ def _gloo_worker(rank, world, port, n, d, ret, overlap=False, function='transfor
         data = grand_b200.GraphData()
         data.new_graph(ei, n)
         # single-process truth (same emulated ABI, un-partitioned block)
-        z_ref, g_ref, nfe_ref = _train_pass(_make_block(function), data, x, gz)
+        z_ref, g_ref, nfe_ref = _train_pass(_make_block(function, adjoint), data, x, gz)
         # partitioned: this rank's slab in, this rank's slab out
         part = grand_b200.RowPartition(n, world, rank)
         halo = {False: grand_b200.Halo, True: grand_b200.SparseHalo, 'compact': grand_b200.CompactHalo}[sparse](part)
-        block = _make_block(function)
+        block = _make_block(function, adjoint)
         block.set_partition(part, halo)
         del emu.calls[:]
         z, grads, nfe = _train_pass(block, data, part.to_slab(x), part.to_slab(gz))
-        assert nfe == nfe_ref == 16 and z.shape == (part.slab, d)
-        assert halo.n_gathers == 16 and halo.n_scatters == 8          # one gather per evaluation, one scatter per VJP
+        assert nfe == nfe_ref == (16 if adjoint else 8) and z.shape == (part.slab, d)
+        assert halo.n_gathers == nfe and halo.n_scatters == 8         # one gather per evaluation, one scatter per VJP
         if sparse and not tiny:                                       # only referenced rows travelled
             assert 0 < halo.referenced_fraction < 0.9
             dense_bytes = 24 * (world - 1) * part.slab * d * 4
@@ -388,6 +389,14 @@ def test_push_halo_world_of_one(host, monkeypatch, tmp_path):
         assert_close(other[0], base[0], 2e-5, 'z')
         for a, b in zip(other[1], base[1]):
             assert_close(a, b, 2e-5, 'grad', floor=1e-3)
+        # backprop through the solver: 8 evaluations each keep their gathered state, more than the ring holds
+        base_bp = _train_pass(_make_block(adjoint=False), data, x, gz)
+        block_bp = _make_block(adjoint=False)
+        block_bp.set_partition(part, halo)
+        other_bp = _train_pass(block_bp, data, x, gz)
+        assert_close(other_bp[0], base_bp[0], 2e-5, 'z (backprop)')
+        for a, b in zip(other_bp[1], base_bp[1]):
+            assert_close(a, b, 2e-5, 'grad (backprop)', floor=1e-3)
         with torch.no_grad():                                          # no autograd: the ring buffer itself is handed out
             full = halo.all_gather_rows(x)
         assert any(full is t for t in allocs) and torch.equal(full, x)
@@ -395,6 +404,19 @@ def test_push_halo_world_of_one(host, monkeypatch, tmp_path):
             assert not any(halo.all_gather_rows(x) is t for t in allocs)
     finally:
         dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('halo,function', [(False, 'transformer'), (True, 'transformer'), ('compact', 'transformer'),
+                                           (True, 'laplacian')])
+def test_backprop_through_the_solver_keeps_every_gathered_state(halo, function):
+    """adjoint=False: autograd runs back through all 8 evaluations, each of which saved ITS gathered state - a halo that
+    recycles gather buffers must not hand a recycled one to an evaluation that will be differentiated"""
+    world = 2
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_gloo_worker, args=(world, _free_port(), 157, 32, ret, False, function, halo, False, False), nprocs=world,
+             join=True)
+    assert dict(ret) == {r: 'ok' for r in range(world)}
 
 
 def test_block_api_world_of_one_matches_unpartitioned(host):
