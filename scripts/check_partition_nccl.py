@@ -31,8 +31,8 @@ OPT = {'hidden_dim': 64, 'max_nfe': 10 ** 6, 'no_alpha_sigmoid': False, 'add_sou
        'directional_penalty': None}
 
 
-def make_block(function, device):
-    opt = dict(OPT, function=function, block='attention' if function == 'transformer' else 'constant')
+def make_block(function, device, adjoint=True):
+    opt = dict(OPT, function=function, block='attention' if function == 'transformer' else 'constant', adjoint=adjoint)
     block = grand_b200.set_block(opt)(grand_b200.set_function(opt), [], opt, device, t=torch.tensor([0., 2.])).to(device)
     block.train()
     g = torch.Generator().manual_seed(5)
@@ -101,17 +101,17 @@ def main():
         gen = torch.Generator(device=device).manual_seed(3)               # same seed on every rank: same tensors
         x, gz = torch.randn(n, d, generator=gen, device=device), torch.randn(n, d, generator=gen, device=device)
         part = grand_b200.RowPartition(n, world, rank)
-        for function in ('transformer', 'laplacian'):
+        for function, adjoint in (('transformer', True), ('laplacian', True), ('transformer', False)):
             os.environ['GRANDB200_OVERLAP'] = '0'
-            z_ref, g_ref = train_pass(make_block(function, device), data, x, gz)
+            z_ref, g_ref = train_pass(make_block(function, device, adjoint), data, x, gz)
             kinds = [('dense', grand_b200.Halo), ('sparse', grand_b200.SparseHalo), ('compact', grand_b200.CompactHalo)]
             if not args.emulate:                                   # symmetric memory needs real GPUs
                 kinds.append(('push', grand_b200.PushHalo))
             for kind, cls in kinds:
-                for overlap in ('0', '1'):
+                for overlap in (('0', '1') if adjoint else ('0',)):
                     os.environ['GRANDB200_OVERLAP'] = overlap
                     halo = cls(part)
-                    block = make_block(function, device)
+                    block = make_block(function, device, adjoint)
                     block.set_partition(part, halo)
                     z, grads = train_pass(block, data, part.to_slab(x), part.to_slab(gz))
                     errs = [rel(z, part.to_slab(z_ref)), rel(grads[0], part.to_slab(g_ref[0]), float(g_ref[0].abs().max()))]
@@ -123,7 +123,7 @@ def main():
                     bad += 0 if ok else 1
                     if rank == 0:
                         frac = getattr(halo, 'referenced_fraction', None)
-                        print(f"{gname:8s} {function:11s} halo={kind:7s} overlap={overlap} world={world} "
+                        print(f"{gname:8s} {function:11s} {'adjoint ' if adjoint else 'backprop'} halo={kind:7s} overlap={overlap} world={world} "
                               f"max rel err {float(worst):.2e} referenced={frac if frac is None else round(frac, 3)} "
                               f"{'ok' if ok else 'MISMATCH'}", flush=True)
     dist.barrier()
