@@ -107,7 +107,11 @@ def _rms(x):
 
 
 def _mixed_norm(state):
-    return max(float(_rms(s)) for s in state if s.numel() > 0)
+    """max over the components of their RMS (torchdiffeq's mixed norm) - ONE device read for all of them"""
+    vals = [_rms(s.detach()) for s in state if s.numel() > 0]
+    if len(vals) == 1 or len({(v.device, v.dtype) for v in vals}) > 1:
+        return max(float(v) for v in vals)
+    return float(torch.stack(vals).max())
 
 
 class _Problem:
