@@ -124,6 +124,18 @@ class LaplacianODEFunc(ODEFunc):
 
         return f.view_as(x), finish
 
+    def eval_vjp(self, t, x, cot, params):
+        """f(t, x) and cot^T df/d(x, params) without an autograd graph - offered on a row-partitioned graph with
+        fixed edge weights (the two local kernels + the two exchanges, same numbers as forward() + autograd.grad);
+        None elsewhere: the solver then differentiates forward()."""
+        if self.partition is None or self.opt['block'] != 'constant':
+            return None
+        if self._as_2d(x).shape[0] != self.partition[0].slab:
+            return None
+        f, finish = self.eval_vjp_phased(t, x, cot, params)
+        vy, vps = finish()
+        return f, vy, vps
+
     def forward(self, t, x):  # the t param is needed by the ODE solver.
         self._check_nfe()
         x2 = self._as_2d(x)
