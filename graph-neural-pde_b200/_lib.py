@@ -172,12 +172,3 @@ class Profiler:
                 out[lib.gb_prof_name(i).decode()] = {'ms': ms.value, 'launches': cnt.value,
                                                      'overlapped': int(lib.gb_prof_overlapped(i))}
         return out
-
-
-def unverified_enabled():
-    """GB_UNVERIFIED=1 switches on the code paths written after the round-1 GPU budget was spent (they are
-    checked on the CPU against the oracle / the reference's golden gradients, but have not run on a B200 yet):
-    the training path of attention_type cosine_sim / pearson / exp_kernel.  Off: those backward passes raise
-    NotImplementedError, exactly as in the hardware-verified build.  The switch disappears once
-    tests/test_gpu_zz_unverified.py has passed on hardware."""
-    return os.environ.get('GB_UNVERIFIED') == '1'

@@ -11,9 +11,7 @@ The score is a SUM of a row term and a column term, so it factorises into per-no
 one [N,d] x [d,2H] projection per evaluation (csrc/linear.cu), then ONE kernel (csrc/gat.cu) that gathers H floats
 per edge, applies the leaky relu and the segment softmax and writes the head mean, then the fused SpMM + epilogue
 of the Laplacian function.  Parameter names (`multihead_att_layer.W`, `.Wout`, `.a`) and shapes are the
-reference's (there `nn.Parameter(...).to(device)` silently un-registers them on a GPU; here they are registered).
-
-The kernel behind `gb_gat_softmax_fwd` has not run on hardware yet: the function is opt-in (GB_UNVERIFIED=1)."""
+reference's (there `nn.Parameter(...).to(device)` silently un-registers them on a GPU; here they are registered)."""
 import torch
 from torch import nn
 
@@ -21,12 +19,6 @@ from . import _lib
 from . import plan as _plan
 from .base_classes import ODEFunc
 from .ops import QKProjFn, GatSoftmaxFn, DiffusionFn, ToCooOrderFn
-
-
-def _require_opt_in():
-    if not _lib.unverified_enabled():
-        raise NotImplementedError("function 'GAT' runs on a kernel (gb_gat_softmax_fwd) that has not been verified on "
-                                  'hardware yet: set GB_UNVERIFIED=1 to enable it')
 
 
 class SpGraphAttentionLayer(nn.Module):
@@ -65,7 +57,6 @@ class SpGraphAttentionLayer(nn.Module):
 
     def attention_csr(self, x2, plan):
         """(att [E,H], abar [E], prods [E,H]) in CSR-slot order for an un-batched state x2 [N,d]"""
-        _require_opt_in()
         m = self.score_weights()
         zero = torch.zeros(self.h, dtype=m.dtype, device=m.device)
         s = QKProjFn.apply(x2, m[:self.h], zero, m[self.h:], zero)            # [N, 2H] = [s_src | s_dst]

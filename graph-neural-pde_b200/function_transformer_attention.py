@@ -111,7 +111,7 @@ class SpGraphTransAttentionLayer(nn.Module):
         exp_kernel through ops.exp_kernel_score_vjp"""
         if self.beltrami_kernel:
             return True                                    # always the composite route (two projections, one kernel)
-        if att_type == _lib.GB_ATT['scaled_dot'] or not torch.is_grad_enabled() or not _lib.unverified_enabled():
+        if att_type == _lib.GB_ATT['scaled_dot'] or not torch.is_grad_enabled():
             return False
         params = [self.Q.weight, self.Q.bias, self.K.weight, self.K.bias]
         if att_type == _lib.GB_ATT['exp_kernel']:
@@ -164,16 +164,12 @@ class SpGraphTransAttentionLayer(nn.Module):
             edge_w = _plan.cached_per_edge(plan, self.edge_weights, 'rw', lambda t: plan.to_csr_order(t.detach()))
         if self.beltrami_kernel:
             qk, kparams = self._beltrami_qk(x2)
-            if not _lib.unverified_enabled():              # the exp_kernel VJP has not run on hardware yet
-                kparams = kparams.detach()
             return EdgeSoftmaxFn.apply(qk, plan, self.h, att_type, int(self.opt['attention_norm_idx']), edge_w, kparams)
         qk = QKProjFn.apply(x2, self.Q.weight, self.Q.bias, self.K.weight, self.K.bias)
         kparams = None
         if att_type == _lib.GB_ATT['exp_kernel']:            # differentiable: EdgeSoftmaxFn returns d(output_var, lengthscale)
             kparams = torch.cat([self.output_var, self.lengthscale]).to(torch.float32).contiguous()
-            if not _lib.unverified_enabled():
-                kparams = kparams.detach()
-        if att_type in self._UNIT_TYPES and torch.is_grad_enabled() and qk.requires_grad and _lib.unverified_enabled():
+        if att_type in self._UNIT_TYPES and torch.is_grad_enabled() and qk.requires_grad:
             # training: the VJP kernels implement scaled_dot; cosine_sim / pearson are scaled_dot of unit vectors
             qk = unit_heads(qk, self.h, centre=att_type == _lib.GB_ATT['pearson'])
             att_type = _lib.GB_ATT['scaled_dot']

@@ -145,9 +145,6 @@ class EdgeSoftmaxFn(torch.autograd.Function):
         if ctx.att_type not in (_lib.GB_ATT['scaled_dot'], _lib.GB_ATT['exp_kernel']):
             raise NotImplementedError('cosine_sim / pearson are differentiated as scaled_dot of unit vectors '
                                       '(function_transformer_attention.unit_heads); call through the layer')
-        if ctx.att_type == _lib.GB_ATT['exp_kernel'] and not _lib.unverified_enabled():
-            raise NotImplementedError('backward of attention_type exp_kernel has not run on hardware yet: '
-                                      'set GB_UNVERIFIED=1 to enable it (see _lib.unverified_enabled)')
         if ctx.att_type == _lib.GB_ATT['exp_kernel'] and ctx.edge_w is not None:
             raise NotImplementedError('backward of exp_kernel with reweight_attention is not implemented')
         datt = None if datt is None else _f32c(datt)

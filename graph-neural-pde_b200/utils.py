@@ -47,12 +47,8 @@ def softmax(src, index, num_nodes=None):
     scatter_max / exp / scatter_add / divide with float atomics; here the group ids are sorted once (stable) and one
     kernel makes the three passes per group (csrc/gat.cu, gb_segment_softmax_fwd).  The ODE functions do not call
     this - their softmax is fused with the score kernels; it is the stand-alone entry for callers with their own
-    scores.  New device code, not yet run on hardware: opt-in (GB_UNVERIFIED=1)."""
-    from . import _lib
+    scores."""
     from .ops import SegmentSoftmaxFn
-    if not _lib.unverified_enabled():
-        raise NotImplementedError('utils.softmax runs on a kernel (gb_segment_softmax_fwd) that has not been verified on '
-                                  'hardware yet: set GB_UNVERIFIED=1 to enable it')
     batched = src.dim() == 3
     if batched and src.shape[0] != 1:
         raise NotImplementedError('batched scores (B > 1) are normalised one graph at a time; pass B == 1')

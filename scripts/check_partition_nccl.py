@@ -55,8 +55,9 @@ def train_pass(block, data, x, g):
     L = getattr(block.odefunc, 'multihead_att_layer', None)
     if L is not None:
         params = [L.Q.weight, L.Q.bias, L.K.weight, L.K.bias] + params
-    grads = torch.autograd.grad((z * g).sum(), [xg] + params)
-    return z.detach(), [t.detach() for t in grads]
+    # plain backprop leaves K.bias out of the graph (a per-row constant of the scores: the row softmax cancels it)
+    grads = torch.autograd.grad((z * g).sum(), [xg] + params, allow_unused=True)
+    return z.detach(), [torch.zeros_like(p) if t is None else t.detach() for t, p in zip(grads, [xg] + params)]
 
 
 def rel(a, b, floor=0.0):

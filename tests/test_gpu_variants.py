@@ -1,7 +1,7 @@
-"""GPU tests written in the CPU-only tail of round 1 (the round's GPU budget was spent): they have NOT run on
-hardware yet, so they are opt-in - `GB_UNVERIFIED=1 python -m pytest tests/test_gpu_zz_unverified.py -m gpu` is
-the first GPU command of round 2; each test moves into its topical file once it has passed on a B200.
-Everything here composes kernels that the verified suite already covers (no new device code)."""
+"""GPU parity of the widened rows of SURVEY.md 8f: training paths of attention_type cosine_sim / pearson / exp_kernel
+(incl. the beltrami split kernel), the GAT function, utils.softmax, MixedODEblock / HardAttODEblock, the two-phase
+adjoint, the 2^16-node R-MAT parity gate and the GNN / GNNEarly mirrors.  First run on a B200 in round 2
+(profiles/r02a_pytest_all.log: all green); part of the plain `pytest -m gpu` run."""
 import glob
 import os
 
@@ -12,9 +12,7 @@ import torch
 from oracle import funcs, graph as og
 from helpers import assert_close, dev, device
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get('GB_UNVERIFIED') != '1',
-                                 reason='not yet run on hardware (set GB_UNVERIFIED=1); see module docstring')]
+pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(__file__), 'golden')
 F_RTOL, G_RTOL = 1e-5, 1e-4
 

@@ -439,8 +439,8 @@ def test_block_api_world_of_one_matches_unpartitioned(host):
 
 
 def test_two_phase_adjoint_equals_the_single_call(host, monkeypatch):
-    """host plumbing of tests/test_gpu_zz_unverified.py::test_two_phase_adjoint_is_bit_identical_to_the_single_call"""
-    import test_gpu_zz_unverified as zz
+    """host plumbing of tests/test_gpu_variants.py::test_two_phase_adjoint_is_bit_identical_to_the_single_call"""
+    import test_gpu_variants as zz
     zz.test_two_phase_adjoint_is_bit_identical_to_the_single_call(monkeypatch)
     calls = [c for c in host.calls if c.startswith('gb_nl_adjoint')]
     assert calls == ['gb_nl_adjoint'] * 8 + ['gb_nl_adjoint_rows', 'gb_nl_adjoint_cols'] * 8

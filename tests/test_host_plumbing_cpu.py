@@ -3,7 +3,7 @@
 Part A pins the emulator: flows that ARE verified on the B200 (graph normalisation bit-exact, reference goldens,
 scaled_dot forward + every gradient for both softmax groupings, blocks under odeint / odeint_adjoint) must come
 out right through it, exactly as they do through libgrandb200.so in tests/test_gpu_*.py.
-Part B runs the GPU tests that have not been on hardware yet (tests/test_gpu_zz_unverified.py - cosine_sim /
+Part B runs the GPU tests of tests/test_gpu_variants.py ( - cosine_sim /
 pearson / exp_kernel training, MixedODEblock, HardAttODEblock) through the same emulator: their host plumbing
 (routing, layouts, autograd wiring, permutations, solver glue) is exercised here; what is left for the B200 is the
 device arithmetic of kernels the verified suite already covers.
@@ -272,13 +272,12 @@ def test_plan_files_round_trip_and_the_disk_cache(host, tmp_path, monkeypatch):
     assert host.calls.count('gb_plan_build') == 3 and torch.equal(p3.colidx, built.colidx)
 
 
-# ---- B. the not-yet-on-hardware GPU tests, host plumbing through the emulator -----------------------------------
-import test_gpu_zz_unverified as zz  # noqa: E402
+# ---- B. the GPU tests of tests/test_gpu_variants.py, host plumbing through the emulator -----------------------------------
+import test_gpu_variants as zz  # noqa: E402
 
 
 @pytest.fixture
-def unverified(host, monkeypatch):
-    monkeypatch.setenv('GB_UNVERIFIED', '1')
+def variants(host):
     return host
 
 
@@ -287,109 +286,60 @@ def _paths(pattern):
 
 
 @pytest.mark.parametrize('path', _paths('ref_transformer_cosine_sim_*.npz') + _paths('ref_transformer_pearson_*.npz'))
-def test_cosine_and_pearson_gradients(unverified, path):
+def test_cosine_and_pearson_gradients(variants, path):
     zz.test_cosine_and_pearson_gradients_match_the_reference(path)
-    calls = unverified.calls
+    calls = variants.calls
     assert 'gb_edge_score_bwd' in calls and 'gb_edge_softmax_bwd' in calls       # the scaled_dot VJP kernels did the edge work
 
 
 @pytest.mark.parametrize('att_type', ['cosine_sim', 'pearson'])
-def test_cosine_and_pearson_under_the_adjoint_solver(unverified, att_type):
+def test_cosine_and_pearson_under_the_adjoint_solver(variants, att_type):
     zz.test_cosine_and_pearson_train_under_the_adjoint_block(att_type)
 
 
 @pytest.mark.parametrize('path', _paths('ref_transformer_exp_kernel_*.npz'))
-def test_exp_kernel_gradients(unverified, path):
+def test_exp_kernel_gradients(variants, path):
     zz.test_exp_kernel_gradients_match_the_reference(path)
 
 
-def test_exp_kernel_gradients_with_hub_segments(unverified):
+def test_exp_kernel_gradients_with_hub_segments(variants):
     zz.test_exp_kernel_gradients_on_a_graph_with_hub_segments()
 
 
 @pytest.mark.parametrize('norm_idx,labels', [(0, 0), (1, 4)])
-def test_beltrami_split_exp_kernel(unverified, norm_idx, labels):
+def test_beltrami_split_exp_kernel(variants, norm_idx, labels):
     zz.test_beltrami_split_exp_kernel_matches_the_oracle(norm_idx, labels)
-    assert unverified.calls.count('gb_edge_softmax_fwd') == 2 and 'gb_att_fwd_fused' not in unverified.calls
+    assert variants.calls.count('gb_edge_softmax_fwd') == 2 and 'gb_att_fwd_fused' not in variants.calls
 
-
-def test_beltrami_split_exp_kernel_forward_is_on_by_default_training_is_not(host, monkeypatch):
-    """without GB_UNVERIFIED the forward (verified exp_kernel kernel) runs, differentiating it fails loudly"""
-    import grand_b200
-    monkeypatch.delenv('GB_UNVERIFIED', raising=False)
-    n, d = 40, 24
-    opt = dict(zz.BASE_OPT, attention_type='exp_kernel', beltrami=True, hidden_dim=d, feat_hidden_dim=16,
-               pos_enc_hidden_dim=8)
-    func = grand_b200.ODEFuncTransformerAtt(d, d, opt, CPU)
-    func.edge_index = torch.tensor(og.shaped_graph(n, 200, 3))
-    x = torch.randn(n, d, generator=torch.Generator().manual_seed(0))
-    func.x0 = x
-    with torch.no_grad():
-        assert torch.isfinite(func(0.0, x)).all()
-    out = func(0.0, x.clone().requires_grad_(True))
-    with pytest.raises(NotImplementedError):
-        out.sum().backward()
 
 
 @pytest.mark.parametrize('norm_idx,heads', [(0, 2), (1, 4), (0, 8), (1, 1), (0, 3)])
-def test_gat_function(unverified, norm_idx, heads):
+def test_gat_function(variants, norm_idx, heads):
     zz.test_gat_function_matches_the_oracle(norm_idx, heads)
-    calls = unverified.calls
+    calls = variants.calls
     assert calls.count('gb_gat_softmax_fwd') == 2 and 'gb_edge_softmax_bwd' in calls and 'gb_spmm_fwd' in calls
 
 
 @pytest.mark.parametrize('path', _paths('ref_gat_*.npz'))
-def test_gat_function_vs_reference_goldens(unverified, path):
+def test_gat_function_vs_reference_goldens(variants, path):
     zz.test_gat_function_matches_the_reference(path)
 
 
-def test_gat_function_under_the_adjoint_block(unverified):
+def test_gat_function_under_the_adjoint_block(variants):
     zz.test_gat_function_under_the_constant_block_with_the_adjoint_solver()
 
 
-def test_gat_function_is_opt_in(host, monkeypatch):
-    """the GAT kernel has not run on hardware: without GB_UNVERIFIED the function refuses loudly"""
-    import grand_b200
-    monkeypatch.delenv('GB_UNVERIFIED', raising=False)
-    opt = dict(zz.BASE_OPT, function='GAT', hidden_dim=8)
-    func = grand_b200.set_function(opt)(8, 8, opt, CPU)
-    func.edge_index = torch.tensor(og.shaped_graph(20, 60, 1))
-    with pytest.raises(NotImplementedError, match='GB_UNVERIFIED'):
-        func(0.0, torch.randn(20, 8))
 
-
-def test_utils_softmax(unverified):
+def test_utils_softmax(variants):
     zz.test_utils_softmax_matches_the_reference_and_its_invariants()
-    assert 'gb_segment_softmax_fwd' in unverified.calls
+    assert 'gb_segment_softmax_fwd' in variants.calls
 
 
-def test_utils_softmax_is_opt_in(host, monkeypatch):
-    from grand_b200 import utils
-    monkeypatch.delenv('GB_UNVERIFIED', raising=False)
-    with pytest.raises(NotImplementedError, match='GB_UNVERIFIED'):
-        utils.softmax(torch.randn(5, 2), torch.tensor([0, 1, 1, 0, 2]), 3)
 
-
-def test_mixed_block(unverified):
+def test_mixed_block(variants):
     zz.test_mixed_block_state_and_gradients_incl_the_gate()
 
 
 @pytest.mark.parametrize('function', ['laplacian', 'transformer', 'GAT'])
-def test_hard_attention_block(unverified, function, capsys):
+def test_hard_attention_block(variants, function, capsys):
     zz.test_hard_attention_block_samples_edges_while_training(function, capsys)
-
-
-def test_without_the_switch_the_other_attention_types_still_refuse_to_train(host, monkeypatch):
-    """GB_UNVERIFIED unset = the hardware-verified behaviour: forward works, backward raises"""
-    import grand_b200
-    monkeypatch.delenv('GB_UNVERIFIED', raising=False)
-    z = np.load(_paths('ref_transformer_cosine_sim_*.npz')[0])
-    n, d = z['x'].shape
-    opt = dict(OPT, block='attention', function='transformer', attention_type='cosine_sim', heads=int(z['heads']),
-               attention_dim=int(z['wq'].shape[0]), hidden_dim=d)
-    func = grand_b200.ODEFuncTransformerAtt(d, d, opt, CPU)
-    func.edge_index, func.x0 = torch.tensor(z['edge_index']), T32(z['x0'])
-    xg = T32(z['x']).requires_grad_(True)
-    out = func(0.0, xg)
-    with pytest.raises((NotImplementedError, RuntimeError)):
-        torch.autograd.grad(out, xg, T32(z['gout']))
