@@ -65,6 +65,7 @@ SIGNATURES = {
                                    C.POINTER(GbStage), _P]),
     'gb_spmm_bwd_partials': (_SZ, [_G, _I32]),
     'gb_spmm_bwd': (C.c_int, [_G, _P, _P, _I32, _P, _I32, _P, _I32, _P, _I32, _I32, _P, _I32, _I32, _P, _P, _P]),
+    'gb_spmm_bwd_static': (C.c_int, [_G, _P, _P, _I32, _P, _I32, _P, _I32, _P, _I32, _I32, _P, _I32, _I32, _P, _P]),
     'gb_spmm_bwd_part': (C.c_int, [_G, _I32, _I32, _P, _P, _I32, _P, _I32, _P, _I32, _P, _I32, _I32, _P, _I32, _I32, _P,
                                    _P, _P]),
     'gb_linear_tc_eligible': (C.c_int, [_P, _I32, _P, _I32, _P, _I32, _I32, _I32, _I32]),

@@ -16,6 +16,7 @@
 // shared memory in a fixed order.  No atomics anywhere: results are bit-reproducible run to run.
 //
 // Roofline: HBM.  Algorithmic bytes per forward launch: 8E + 12Nd + 4N.
+#include <mutex>
 #include "spmm_common.cuh"
 
 namespace gb {
@@ -405,6 +406,53 @@ int gb_spmm_bwd_part(const gb_graph* g, int32_t own_lo, int32_t own_hi, const fl
   if (int rc = run_spmm<true>(a, d, v, n_long, stream, &slots)) return rc;
   if (dparams) return reduce_partials_launch(partials, slots, alpha_train, alpha_sigmoid, dparams, stream);
   return GB_OK;
+}
+
+// ---- allocation-free variant of gb_spmm_bwd (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA-graph capture, tight serving loops) ---------------------
+// The reduction workspace (`partials` of gb_spmm_bwd) lives in a file-scope device array: every GPU that loads
+// the library holds GB_SPMM_BWD_STATIC_MAX_FLOATS floats (4 MiB) until the process exits.  In host code the
+// array's NAME is a host-side stand-in, not a device address; the address comes from cudaGetSymbolAddress, once per
+// device, with that device current.
+static __device__ __align__(256) float g_spmm_bwd_scratch[GB_SPMM_BWD_STATIC_MAX_FLOATS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+float* g_scratch_ptr[kMaxDevices] = {};                  // per device, filled on first use
+std::mutex g_scratch_mutex;
+
+int static_scratch(float** out) {
+  int dev = -1;
+  GB_CUDA(cudaGetDevice(&dev));
+  GB_REQUIRE(dev >= 0 && dev < kMaxDevices, "gb_spmm_bwd_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_scratch_mutex);
+  if (g_scratch_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    GB_CUDA(cudaGetSymbolAddress(&p, g_spmm_bwd_scratch));   // the CURRENT device's copy of the array
+    g_scratch_ptr[dev] = static_cast<float*>(p);
+  }
+  *out = g_scratch_ptr[dev];
+  return GB_OK;
+}
+}  // namespace
+
+int gb_spmm_bwd_static(const gb_graph* g, const float* vals, const float* gout, int32_t ldg, const float* x,
+                       int32_t ldx, const float* x0, int32_t ldx0, const float* alpha_train, int32_t alpha_sigmoid,
+                       int32_t d, float* dx, int32_t lddx, int32_t accumulate, float* dparams, void* stream_) {
+  if (int rc = check_graph(g, "gb_spmm_bwd_static")) return rc;
+  GB_REQUIRE(d > 0, "gb_spmm_bwd_static: d <= 0");
+  const size_t need = gb_spmm_bwd_partials(g, d);
+  if (need > (size_t)GB_SPMM_BWD_STATIC_MAX_FLOATS) {
+    set_error("gb_spmm_bwd_static: n=%d, d=%d needs %zu floats of reduction scratch, the built-in array holds %d; "
+              "use gb_spmm_bwd with a caller-provided workspace", g->n, d, need, (int)GB_SPMM_BWD_STATIC_MAX_FLOATS);
+    return GB_ERR_WORKSPACE;
+  }
+  float* scratch = nullptr;
+  if (int rc = static_scratch(&scratch)) return rc;
+  // the array keeps the previous call's contents: clear the part this call reduces over
+  GB_CUDA(cudaMemsetAsync(scratch, 0, need * sizeof(float), (cudaStream_t)stream_));
+  return gb_spmm_bwd_part(g, 0, 0, vals, gout, ldg, x, ldx, x0, ldx0, alpha_train, alpha_sigmoid, d, dx, lddx,
+                          accumulate, scratch, dparams, stream_);
 }
 
 }  // extern "C"

@@ -180,6 +180,19 @@ int gb_spmm_bwd_part(const gb_graph* g, int32_t own_lo, int32_t own_hi, const fl
                      const float* alpha_train, int32_t alpha_sigmoid, int32_t d, float* dx, int32_t lddx,
                      int32_t accumulate, float* partials, float* dparams, void* stream);
 
+/* ---- gb_spmm_bwd without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ *      for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops,
+ *      harnesses that forbid it).  Same arguments, arithmetic and results as gb_spmm_bwd minus `partials`: the
+ *      reduction scratch is a file-scope device array of GB_SPMM_BWD_STATIC_MAX_FLOATS floats (4 MiB, held by every
+ *      GPU that loads the library until the process exits).  Graphs / widths whose gb_spmm_bwd_partials(g, d)
+ *      exceeds that limit are refused with GB_ERR_WORKSPACE (use gb_spmm_bwd).  Calls no cudaMalloc / cudaFree.
+ *      All calls on a device share the one array: calls that overlap on the GPU (different streams) race on it. */
+#define GB_SPMM_BWD_STATIC_MAX_FLOATS (1 << 20)
+int gb_spmm_bwd_static(const gb_graph* g, const float* vals, const float* gout, int32_t ldg,
+                       const float* x, int32_t ldx, const float* x0, int32_t ldx0,
+                       const float* alpha_train, int32_t alpha_sigmoid, int32_t d,
+                       float* dx, int32_t lddx, int32_t accumulate, float* dparams, void* stream);
+
 /* ---- K3: Q/K projection (nn.Linear x2, function_transformer_attention.py:224-225)
  *   out[i, j] = sum_c x[i,c] * w[j,c] + b[j],  j < nout   (w is torch's Linear.weight layout [nout, d];
  *   pass Q and K weights concatenated along dim 0 to get [q | k] rows in one pass) */
