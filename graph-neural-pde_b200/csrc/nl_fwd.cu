@@ -1,8 +1,24 @@
 // nl_fwd.cu - forward instantiations of the single-gather GRAND-nl kernels (see nl_kernels.cuh) and gb_nl_fwd.
-#include "nl_kernels.cuh"
+#include <stdlib.h>
+#include "nl2_kernels.cuh"
 
 namespace gb {
+// GRANDB200_NL_IMPL=1 selects the first-generation row kernels (register-resident gathers, nl_kernels.cuh) for A/B
+// timing; default: the shared-memory-staged second generation (nl2_kernels.cuh) wherever it covers the shape.
+int nl_impl() {
+  static int impl = 0;
+  if (impl == 0) {
+    const char* s = getenv("GRANDB200_NL_IMPL");
+    impl = (s != nullptr && s[0] == '1') ? 1 : 2;
+  }
+  return impl;
+}
+
 int nl_dispatch_fwd(const NlArgs& a, int heads, int n_long, cudaStream_t stream) {
+  if (nl_impl() == 2) {
+    const int rc = nl2_dispatch<false>(a, heads, n_long, stream);
+    if (rc != GB_ERR_UNSUPPORTED) return rc;
+  }
   return nl_dispatch<false>(a, heads, n_long, stream);
 }
 
