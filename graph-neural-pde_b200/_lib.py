@@ -94,6 +94,12 @@ SIGNATURES = {
     'gb_nl_adjoint_phase': (C.c_int, [_G, _I32, _I32, _P, _I32, _P, _I32, _P, _I32, _I32, _I32, _I32, _P, _I32, _P,
                                       _I32, _P, _P, _I32, _P, _I32, _P, _P, _P, _P, _I32, _P, _I32, _P, _I32, _P, _P, _P,
                                       _I32, _P]),
+    'gb_nlk_supported': (C.c_int, [_I32, _I32, _I32]),
+    'gb_nlk_fwd': (C.c_int, [_G, _I32, _I32, _P, _I32, _P, _I32, _P, _I32, _I32, _I32, _I32, _P, _I32, _P, _I32, _P,
+                             _P, _I32, C.POINTER(GbStage), _P, _P]),
+    'gb_nlk_adjoint_phase': (C.c_int, [_G, _I32, _I32, _P, _I32, _P, _I32, _P, _I32, _I32, _I32, _I32, _P, _I32, _P,
+                                       _I32, _P, _P, _I32, _P, _I32, _P, _P, _P, _P, _I32, _P, _I32, _P, _I32, _P, _P,
+                                       _P, _I32, _P]),
     'gb_edge_score_bwd': (C.c_int, [_G, _P, _P, _I32, _P, _I32, _I32, _I32, _I32, _P, _P, _P, _I32, _P, _I32, _P, _P, _P]),
     'gb_gat_softmax_fwd': (C.c_int, [_G, _I32, _P, _P, _I32, _I32, C.c_float, _P, _P, _P, _P]),
     'gb_segment_softmax_fwd': (C.c_int, [_P, _P, _I32, _I32, _P, _P, _P, _P, _I32, _I32, _P]),

@@ -676,6 +676,62 @@ int gb_att_bwd_fused(const gb_graph* g, const float* q, int32_t ldq, const float
   return GB_OK;
 }
 
+}  // extern "C"
+
+namespace gb {
+// Column pass of the GRAND-nl VJP, shared by gb_nl_adjoint_phase (single gather) and gb_nlk_adjoint_phase (k gather):
+// transpose SpMM (dx, dalpha / dbeta partial sums) + dk over the edges this rank holds, from the ds [E,H] / abar [E]
+// the row pass left behind.
+int nl_cols_pass(const gb_graph* g, int32_t row_lo, int32_t row_hi, const float* x, int32_t ldx, const float* q,
+                 int32_t ldq, int32_t heads, int32_t dk, int32_t d, const float* x0, int32_t ldx0,
+                 const float* alpha_train, int32_t alpha_sigmoid, const float* beta_train, const float* gout,
+                 int32_t ldg, float* ds, float* abar, float* dq, int32_t lddq, float* dk_out, int32_t lddk, float* dx,
+                 int32_t lddx, float* partials, float* dparams, cudaStream_t stream) {
+  const bool use_long = g->long_threshold > 0;
+  // columns: transpose SpMM (dx, dalpha / dbeta partial sums) + dk over the edges this rank holds
+  const bool part = !(row_lo == 0 && row_hi == g->n);
+  FusedBwdArgs b{};
+  b.rowptr = g->rowptr; b.colidx = g->colidx; b.colptr = g->colptr; b.rowidx = g->rowidx; b.tperm = g->tperm;
+  b.n = g->n; b.heads = heads; b.dk = dk; b.lh = dk / 4;
+  b.q = q; b.ldq = ldq; b.k = nullptr; b.ldk = 0; b.att = nullptr; b.abar = abar;
+  b.g = gout; b.ldg = ldg; b.x = x; b.ldx = ldx; b.xdv = d / 4;
+  b.ds = ds; b.dq = dq; b.lddq = lddq; b.dk_out = dk_out; b.lddk = lddk; b.col_cap = kColCap;
+  SpmmArgs& sp = b.sp;
+  sp.ptr = g->colptr; sp.idx = g->rowidx; sp.perm = g->tperm; sp.vals = abar; sp.n = g->n; sp.dv = d / 4;
+  sp.long_threshold = kFusedCap; sp.src = gout; sp.lds = ldg; sp.alpha_train = alpha_train;
+  sp.alpha_sigmoid = alpha_sigmoid; sp.x0 = (dparams && beta_train) ? x0 : nullptr; sp.ldx0 = ldx0;
+  sp.x = dparams ? x : nullptr; sp.ldx = ldx; sp.out = dx; sp.ldo = lddx; sp.accumulate = 0;
+  sp.partials = partials + kMidFloats; sp.partial_base = 0; sp.long_list = g->long_cols;
+  if (part) { sp.part_lo = row_lo; sp.part_hi = row_hi; }
+  const char* why = "";
+  if (!fused_supported(q, ldq, q, ldq, heads, dk, &why)) {
+    set_error("gb_nl_adjoint: column pass does not support this shape (%s)", why);
+    return GB_ERR_UNSUPPORTED;
+  }
+  int slots = (g->n + kFusedWarps - 1) / kFusedWarps;
+  const int nlc = use_long ? g->n_long_cols : 0;
+  const cudaStream_t side = nlc > 0 ? side_fork(stream) : stream;   // hub columns next to the main column pass
+  if (nlc > 0) {
+    SpmmArgs lsp = sp;
+    lsp.partial_base = slots;
+    lsp.long_threshold = kColCap;                         // shorter listed columns are done by the main kernel
+    if (int rc = spmm_long_only(lsp, 4, true, nlc, side)) return rc;
+    slots += nlc;
+    MhArgs mh{};
+    mh.ptr = g->colptr; mh.idx = g->rowidx; mh.perm = g->tperm; mh.ds = ds; mh.src = q; mh.lds = ldq;
+    mh.out = dk_out; mh.ldo = lddk; mh.n = g->n; mh.heads = heads; mh.dk = dk; mh.long_threshold = kColCap;
+    mh.scale = 1.0f / sqrtf((float)dk); mh.long_list = g->long_cols;
+    if (int rc = mh_spmm_long(mh, 4, nlc, K_EDGE_SCORE_BWD_K, side)) return rc;
+  }
+  if (int rc = dispatch_bwd(b, stream, true)) return rc;
+  if (int rc = side_join(stream, side)) return rc;
+  if (dparams) return reduce_partials_launch(partials, slots, alpha_train, alpha_sigmoid, dparams, stream);
+  return GB_OK;
+}
+}  // namespace gb
+
+extern "C" {
+
 int gb_nl_adjoint(const gb_graph* g, int32_t row_lo, int32_t row_hi, const float* x, int32_t ldx, const float* q,
                   int32_t ldq, const float* wk, int32_t ldwk, int32_t heads, int32_t dk, int32_t d, const float* x0,
                   int32_t ldx0, const float* alpha_train, int32_t alpha_sigmoid, const float* beta_train,
@@ -720,45 +776,8 @@ int gb_nl_adjoint_phase(const gb_graph* g, int32_t row_lo, int32_t row_hi, const
   }
   if (phase == GB_NL_PHASE_ROWS) return GB_OK;
 
-  // columns: transpose SpMM (dx, dalpha / dbeta partial sums) + dk over the edges this rank holds
-  const bool part = !(row_lo == 0 && row_hi == g->n);
-  FusedBwdArgs b{};
-  b.rowptr = g->rowptr; b.colidx = g->colidx; b.colptr = g->colptr; b.rowidx = g->rowidx; b.tperm = g->tperm;
-  b.n = g->n; b.heads = heads; b.dk = dk; b.lh = dk / 4;
-  b.q = q; b.ldq = ldq; b.k = nullptr; b.ldk = 0; b.att = nullptr; b.abar = abar;
-  b.g = gout; b.ldg = ldg; b.x = x; b.ldx = ldx; b.xdv = d / 4;
-  b.ds = ds; b.dq = dq; b.lddq = lddq; b.dk_out = dk_out; b.lddk = lddk; b.col_cap = kColCap;
-  SpmmArgs& sp = b.sp;
-  sp.ptr = g->colptr; sp.idx = g->rowidx; sp.perm = g->tperm; sp.vals = abar; sp.n = g->n; sp.dv = d / 4;
-  sp.long_threshold = kFusedCap; sp.src = gout; sp.lds = ldg; sp.alpha_train = alpha_train;
-  sp.alpha_sigmoid = alpha_sigmoid; sp.x0 = (dparams && beta_train) ? x0 : nullptr; sp.ldx0 = ldx0;
-  sp.x = dparams ? x : nullptr; sp.ldx = ldx; sp.out = dx; sp.ldo = lddx; sp.accumulate = 0;
-  sp.partials = partials + kMidFloats; sp.partial_base = 0; sp.long_list = g->long_cols;
-  if (part) { sp.part_lo = row_lo; sp.part_hi = row_hi; }
-  const char* why = "";
-  if (!fused_supported(q, ldq, q, ldq, heads, dk, &why)) {
-    set_error("gb_nl_adjoint: column pass does not support this shape (%s)", why);
-    return GB_ERR_UNSUPPORTED;
-  }
-  int slots = (g->n + kFusedWarps - 1) / kFusedWarps;
-  const int nlc = use_long ? g->n_long_cols : 0;
-  const cudaStream_t side = nlc > 0 ? side_fork(stream) : stream;   // hub columns next to the main column pass
-  if (nlc > 0) {
-    SpmmArgs lsp = sp;
-    lsp.partial_base = slots;
-    lsp.long_threshold = kColCap;                         // shorter listed columns are done by the main kernel
-    if (int rc = spmm_long_only(lsp, 4, true, nlc, side)) return rc;
-    slots += nlc;
-    MhArgs mh{};
-    mh.ptr = g->colptr; mh.idx = g->rowidx; mh.perm = g->tperm; mh.ds = ds; mh.src = q; mh.lds = ldq;
-    mh.out = dk_out; mh.ldo = lddk; mh.n = g->n; mh.heads = heads; mh.dk = dk; mh.long_threshold = kColCap;
-    mh.scale = 1.0f / sqrtf((float)dk); mh.long_list = g->long_cols;
-    if (int rc = mh_spmm_long(mh, 4, nlc, K_EDGE_SCORE_BWD_K, side)) return rc;
-  }
-  if (int rc = dispatch_bwd(b, stream, true)) return rc;
-  if (int rc = side_join(stream, side)) return rc;
-  if (dparams) return reduce_partials_launch(partials, slots, alpha_train, alpha_sigmoid, dparams, stream);
-  return GB_OK;
+  return nl_cols_pass(g, row_lo, row_hi, x, ldx, q, ldq, heads, dk, d, x0, ldx0, alpha_train, alpha_sigmoid, beta_train,
+                      gout, ldg, ds, abar, dq, lddq, dk_out, lddk, dx, lddx, partials, dparams, stream);
 }
 
 }  // extern "C"

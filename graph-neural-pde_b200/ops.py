@@ -9,6 +9,8 @@ its dense restatement, and `odeint_adjoint` calls autograd.grad on the same forw
 backward (`create_graph=True`, used only by regularized_ODE_function.py:39-75) is not supported and
 raises.  Every tensor must live on a CUDA device: there is no CPU path.
 """
+import os
+
 import torch
 from torch.autograd.function import once_differentiable
 
@@ -458,8 +460,29 @@ def nl_supported(plan, x, heads, adim, att_type, norm_idx, edge_w):
     return bool(_lib.load().gb_nl_supported(heads, adim // heads, x.shape[1]))
 
 
+def nlk_eligible(heads, adim, d):
+    """k-gather row kernels (csrc/nlk_kernels.cuh) instead of the single-gather ones: they fetch k[col] next to x[col]
+    (4A more bytes per edge) and drop the per-row Wk work; measured faster whenever d > attention_dim
+    (profiles/r02*).  GRANDB200_NL_IMPL=1|2 keeps the single-gather generations for A/B timing."""
+    if os.environ.get('GRANDB200_NL_IMPL', '3') != '3' or d <= adim:
+        return False
+    return bool(_lib.load().gb_nlk_supported(heads, adim // heads, d))
+
+
+def _nl_qk(x, wq, bq, wk, bk):
+    """[q | k] = x [Wq; Wk]^T + [bq; bk] in one projection pass ([N, 2A])"""
+    lib = _lib.load()
+    n, d = x.shape
+    a2 = 2 * wq.shape[0]
+    w_cat, b_cat = torch.cat([wq, wk], dim=0), torch.cat([bq, bk], dim=0)
+    qk = torch.empty(n, a2, dtype=torch.float32, device=x.device)
+    _lib.check(lib.gb_linear_fwd(x.data_ptr(), d, n, d, w_cat.data_ptr(), b_cat.data_ptr(), a2, qk.data_ptr(), a2,
+                                 _lib.stream()), 'gb_linear_fwd')
+    return qk
+
+
 def _nl_vjp(plan, rows, x, q, wq, wk, x0, alpha_train, beta_train, alpha_sigmoid, heads, gout, want_f, want_params,
-            x_row_offset=0):
+            x_row_offset=0, kgather=False):
     """shared by NlTransformerFn.backward and nl_eval_vjp.  Returns (f|None, dx_direct [Ncols,d], dqk [Nrows?,2A],
     dparams|None).  All row-indexed tensors are full-height here (one GPU)."""
     lib = _lib.load()
@@ -476,6 +499,15 @@ def _nl_vjp(plan, rows, x, q, wq, wk, x0, alpha_train, beta_train, alpha_sigmoid
     partials = torch.empty(int(lib.gb_att_bwd_fused_partials(plan.c)), dtype=torch.float32, device=dev)
     dparams = torch.empty(2, dtype=torch.float32, device=dev) if want_params else None
     source = beta_train is not None and x0 is not None
+    if kgather:                                              # q is [q | k] ([N, 2A]) here
+        _lib.check(lib.gb_nlk_adjoint_phase(
+            plan.c, rows[0], rows[1], x.data_ptr(), d, q.data_ptr(), 2 * a, q.data_ptr() + 4 * a, 2 * a, heads, dk, d,
+            _lib.ptr(x0) if source else None, d, alpha_train.data_ptr(), int(alpha_sigmoid),
+            beta_train.data_ptr() if source else None, gout.data_ptr(), d, _lib.ptr(out), d, ds.data_ptr(),
+            dabar.data_ptr(), abar.data_ptr(), dqk.data_ptr(), 2 * a, dqk.data_ptr() + 4 * a, 2 * a, dx.data_ptr(), d,
+            partials.data_ptr(), _lib.ptr(dparams), _nl_workspace(dev).data_ptr(), 0, _lib.stream()),
+            'gb_nlk_adjoint_phase')
+        return out, dx, dqk, dparams
     _lib.check(lib.gb_nl_adjoint(plan.c, rows[0], rows[1], x.data_ptr(), d, q.data_ptr(), a, wk.data_ptr(), d, heads, dk,
                                  d, _lib.ptr(x0) if source else None, d, alpha_train.data_ptr(), int(alpha_sigmoid),
                                  beta_train.data_ptr() if source else None, gout.data_ptr(), d, _lib.ptr(out), d,
@@ -528,12 +560,21 @@ class NlTransformerFn(torch.autograd.Function):
         source = beta_train is not None and x0 is not None
         if source:
             x0 = _f32c(x0)
-        q = _nl_q(x, wq, bq)
         out = torch.empty_like(x)
-        _lib.check(lib.gb_nl_fwd(plan.c, 0, n, x.data_ptr(), d, q.data_ptr(), a, wk.data_ptr(), d, heads, a // heads, d,
-                                 _lib.ptr(x0) if source else None, d, alpha_train.data_ptr(), int(alpha_sigmoid),
-                                 beta_train.data_ptr() if source else None, out.data_ptr(), d, stage,
-                                 _nl_workspace(x.device).data_ptr(), _lib.stream()), 'gb_nl_fwd')
+        ctx.kgather = nlk_eligible(heads, a, d)
+        if ctx.kgather:
+            q = _nl_qk(x, wq, bq, wk, _f32c(bk))           # [q | k]
+            _lib.check(lib.gb_nlk_fwd(plan.c, 0, n, x.data_ptr(), d, q.data_ptr(), 2 * a, q.data_ptr() + 4 * a, 2 * a,
+                                      heads, a // heads, d, _lib.ptr(x0) if source else None, d,
+                                      alpha_train.data_ptr(), int(alpha_sigmoid),
+                                      beta_train.data_ptr() if source else None, out.data_ptr(), d, stage,
+                                      _nl_workspace(x.device).data_ptr(), _lib.stream()), 'gb_nlk_fwd')
+        else:
+            q = _nl_q(x, wq, bq)
+            _lib.check(lib.gb_nl_fwd(plan.c, 0, n, x.data_ptr(), d, q.data_ptr(), a, wk.data_ptr(), d, heads, a // heads,
+                                     d, _lib.ptr(x0) if source else None, d, alpha_train.data_ptr(), int(alpha_sigmoid),
+                                     beta_train.data_ptr() if source else None, out.data_ptr(), d, stage,
+                                     _nl_workspace(x.device).data_ptr(), _lib.stream()), 'gb_nl_fwd')
         ctx.save_for_backward(x, wq, wk, q, alpha_train, beta_train if source else None, x0 if source else None)
         ctx.plan, ctx.heads, ctx.alpha_sigmoid = plan, heads, int(alpha_sigmoid)
         return out
@@ -547,7 +588,7 @@ class NlTransformerFn(torch.autograd.Function):
         gout = _f32c(gout)
         want_params = ctx.needs_input_grad[5] or ctx.needs_input_grad[6]
         _, dx, dqk, dparams = _nl_vjp(ctx.plan, (0, n), x, q, wq, wk, x0, alpha_train, beta_train, ctx.alpha_sigmoid,
-                                      ctx.heads, gout, False, want_params)
+                                      ctx.heads, gout, False, want_params, kgather=ctx.kgather)
         w_cat = torch.cat([wq, wk], dim=0)
         dw, db = _nl_dense_tail(x, dqk, w_cat, dx, any(ctx.needs_input_grad[1:5]))
         dwq = dbq = dwk = dbk = None
@@ -567,9 +608,11 @@ def nl_eval_vjp(x, gout, wq, bq, wk, bk, alpha_train, beta_train, x0, plan, head
     n = x.shape[0]
     a = wq_.shape[0]
     source = beta_train is not None and x0 is not None
-    q = _nl_q(x, wq_, bq_)
+    kgather = nlk_eligible(heads, a, x.shape[1])
+    q = _nl_qk(x, wq_, bq_, wk_, _f32c(bk.detach())) if kgather else _nl_q(x, wq_, bq_)
     f, dx, dqk, dparams = _nl_vjp(plan, (0, n), x, q, wq_, wk_, _f32c(x0) if source else None, alpha_train.detach(),
-                                  beta_train.detach() if source else None, int(alpha_sigmoid), heads, gout, True, True)
+                                  beta_train.detach() if source else None, int(alpha_sigmoid), heads, gout, True, True,
+                                  kgather=kgather)
     dw, db = _nl_dense_tail(x, dqk, torch.cat([wq_, wk_], dim=0), dx, want_w)
     grads = {'alpha_train': dparams[0].reshape(alpha_train.shape), 'beta_train': dparams[1].reshape(()) if source else None}
     if dw is not None:

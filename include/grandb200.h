@@ -351,6 +351,24 @@ int gb_nl_adjoint_phase(const gb_graph* g, int32_t row_lo, int32_t row_hi, const
                         float* dk_out, int32_t lddk, float* dx, int32_t lddx, float* partials, float* dparams,
                         void* workspace, int32_t phase, void* stream);
 
+/* ---- K-gather form of the fused GRAND-nl kernels (csrc/nlk_kernels.cuh): same function, results and buffers as
+ *      gb_nl_fwd / gb_nl_adjoint_phase (ODEFuncTransformerAtt.forward, function_transformer_attention.py:44-59, and
+ *      its VJP), but the caller projects k = x Wk^T + bk as well (one GEMM for [q | k]) and passes it instead of Wk:
+ *      the kernels gather x[col] AND k[col] per edge and do no per-row Wk work.  Faster whenever d > attention_dim
+ *      (measured, profiles/r02*); one GPU / un-partitioned rows or any row range whose columns have k rows. */
+int gb_nlk_supported(int32_t heads, int32_t dk, int32_t d);
+int gb_nlk_fwd(const gb_graph* g, int32_t row_lo, int32_t row_hi, const float* x, int32_t ldx, const float* q,
+               int32_t ldq, const float* k, int32_t ldk, int32_t heads, int32_t dk, int32_t d, const float* x0,
+               int32_t ldx0, const float* alpha_train, int32_t alpha_sigmoid, const float* beta_train, float* out,
+               int32_t ldo, const gb_stage* stage, void* workspace, void* stream);
+int gb_nlk_adjoint_phase(const gb_graph* g, int32_t row_lo, int32_t row_hi, const float* x, int32_t ldx,
+                         const float* q, int32_t ldq, const float* k, int32_t ldk, int32_t heads, int32_t dk,
+                         int32_t d, const float* x0, int32_t ldx0, const float* alpha_train, int32_t alpha_sigmoid,
+                         const float* beta_train, const float* gout, int32_t ldg, float* out, int32_t ldo, float* ds,
+                         float* dabar_scratch, float* abar, float* dq, int32_t lddq, float* dk_out, int32_t lddk,
+                         float* dx, int32_t lddx, float* partials, float* dparams, void* workspace, int32_t phase,
+                         void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -92,7 +92,11 @@ class Emulator:
         self.error = b''
         self.calls = []                       # names of the entry points called, in order (tests assert on routes)
 
+    _quiet = False                 # set while an entry point is emulated through another one (one call = one note)
+
     def _note(self, name):
+        if self._quiet:
+            return
         self.calls.append(name)
         self.launches += 1
 
@@ -411,7 +415,10 @@ class Emulator:
         X = f32(x, G.n, d, ldx).astype(np.float64)
         Q = np.zeros((G.n, a))
         Q[lo:hi] = self._rows(q, lo, hi, a, ldq)
-        K = X @ f32(wk, a, d, ldwk).astype(np.float64).T
+        if isinstance(wk, tuple):                      # ('k', pointer): the k-gather entry points pass k itself
+            K = f32(wk[1], G.n, a, ldwk).astype(np.float64)
+        else:
+            K = X @ f32(wk, a, d, ldwk).astype(np.float64).T
         s = (Q.reshape(G.n, heads, dk)[G.rows] * K.reshape(G.n, heads, dk)[G.colidx]).sum(axis=2) / math.sqrt(dk)
         m = np.full((G.n, heads), -np.inf)
         np.maximum.at(m, G.rows, s)
@@ -434,6 +441,33 @@ class Emulator:
             f = f + scalar(beta_train) * self._rows(x0, lo, hi, d, ldx0)
         self._rows(out, lo, hi, d, ldo)[:] = f
         return 0
+
+    # k-gather entry points (csrc/nlk_kernels.cuh): same functions with k = x Wk^T + bk given instead of Wk
+    def gb_nlk_supported(self, heads, dk, d):
+        return int(self.gb_nl_supported(heads, dk, d) and heads * dk <= 128)
+
+    def gb_nlk_fwd(self, g, lo, hi, x, ldx, q, ldq, k, ldk, heads, dk, d, x0, ldx0, alpha_train, alpha_sigmoid,
+                   beta_train, out, ldo, stage, workspace, stream):
+        self._note('gb_nlk_fwd')
+        self._quiet = True
+        try:
+            return self.gb_nl_fwd(g, lo, hi, x, ldx, q, ldq, ('k', k), ldk, heads, dk, d, x0, ldx0, alpha_train,
+                                  alpha_sigmoid, beta_train, out, ldo, stage, workspace, stream)
+        finally:
+            self._quiet = False
+
+    def gb_nlk_adjoint_phase(self, g, lo, hi, x, ldx, q, ldq, k, ldk, heads, dk, d, x0, ldx0, alpha_train,
+                             alpha_sigmoid, beta_train, gout, ldg, out, ldo, ds, dabar, abar, dq, lddq, dk_out, lddk,
+                             dx, lddx, partials, dparams, workspace, phase, stream):
+        self._note({0: 'gb_nlk_adjoint', 1: 'gb_nlk_adjoint_rows', 2: 'gb_nlk_adjoint_cols'}[phase])
+        self._quiet = True
+        try:
+            return self.gb_nl_adjoint_phase(g, lo, hi, x, ldx, q, ldq, ('k', k), ldk, heads, dk, d, x0, ldx0,
+                                            alpha_train, alpha_sigmoid, beta_train, gout, ldg, out, ldo, ds, dabar,
+                                            abar, dq, lddq, dk_out, lddk, dx, lddx, partials, dparams, workspace,
+                                            phase, stream)
+        finally:
+            self._quiet = False
 
     def gb_nl_adjoint(self, g, lo, hi, x, ldx, q, ldq, wk, ldwk, heads, dk, d, x0, ldx0, alpha_train, alpha_sigmoid,
                       beta_train, gout, ldg, out, ldo, ds, dabar, abar, dq, lddq, dk_out, lddk, dx, lddx, partials,

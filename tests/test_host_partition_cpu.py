@@ -64,7 +64,10 @@ def make_func(d, heads, adim, seed=1):
     return func
 
 
-def test_single_gather_route_forward_gradients_and_fused_vjp(host):
+@pytest.mark.parametrize('impl', ['2', '3'])
+def test_single_gather_route_forward_gradients_and_fused_vjp(host, monkeypatch, impl):
+    """impl 2: single-gather entry points (gb_nl_*); 3 (default): k-gather entry points (gb_nlk_*), d > attention_dim"""
+    monkeypatch.setenv('GRANDB200_NL_IMPL', impl)
     n, e, d, heads, adim = 300, 2400, 32, 4, 16
     ei = rand_graph(n, e, 12, hub=(7, 300))
     rng = np.random.default_rng(5)
@@ -76,7 +79,9 @@ def test_single_gather_route_forward_gradients_and_fused_vjp(host):
     xg = T32(x).requires_grad_(True)
     out = func(0.0, xg)
     grads = torch.autograd.grad(out, [xg] + params, T32(gout))
-    assert 'gb_nl_fwd' in host.calls and 'gb_nl_adjoint' in host.calls and 'gb_edge_softmax_fwd' not in host.calls
+    fwd, adj = ('gb_nl_fwd', 'gb_nl_adjoint') if impl == '2' else ('gb_nlk_fwd', 'gb_nlk_adjoint')
+    assert fwd in host.calls and adj in host.calls and 'gb_edge_softmax_fwd' not in host.calls
+    assert not ({'gb_nl_fwd', 'gb_nl_adjoint', 'gb_nlk_fwd', 'gb_nlk_adjoint'} - {fwd, adj}) & set(host.calls)
     leaves = [T64(v).requires_grad_(True) for v in [x] + params]
     ref = funcs.transformer_f(leaves[0], torch.tensor(ei), leaves[1], leaves[2], leaves[3], leaves[4], heads, leaves[5],
                               leaves[6], T64(x0))
@@ -388,7 +393,7 @@ def test_push_halo_world_of_one(host, monkeypatch, tmp_path):
         assert len(allocs) == 6                                        # two rings (gathered state, dL/dx share) of 3
         assert_close(other[0], base[0], 2e-5, 'z')
         for a, b in zip(other[1], base[1]):
-            assert_close(a, b, 2e-5, 'grad', floor=1e-3)
+            assert_close(a, b, 2e-5, 'grad', floor=4e-3)   # bias gradients are rounding noise (sum of ds = 0); the un-partitioned base takes the k-gather route
         # backprop through the solver: 8 evaluations each keep their gathered state, more than the ring holds
         base_bp = _train_pass(_make_block(adjoint=False), data, x, gz)
         block_bp = _make_block(adjoint=False)
@@ -396,7 +401,7 @@ def test_push_halo_world_of_one(host, monkeypatch, tmp_path):
         other_bp = _train_pass(block_bp, data, x, gz)
         assert_close(other_bp[0], base_bp[0], 2e-5, 'z (backprop)')
         for a, b in zip(other_bp[1], base_bp[1]):
-            assert_close(a, b, 2e-5, 'grad (backprop)', floor=1e-3)
+            assert_close(a, b, 2e-5, 'grad (backprop)', floor=4e-3)
         with torch.no_grad():                                          # no autograd: the ring buffer itself is handed out
             full = halo.all_gather_rows(x)
         assert any(full is t for t in allocs) and torch.equal(full, x)
@@ -435,7 +440,7 @@ def test_block_api_world_of_one_matches_unpartitioned(host):
     other = _train_pass(block, data, x, gz)
     assert_close(other[0], base[0], 2e-5, 'z')
     for a, b in zip(other[1], base[1]):
-        assert_close(a, b, 2e-5, 'grad', floor=1e-3)
+        assert_close(a, b, 2e-5, 'grad', floor=4e-3)   # bias gradients are rounding noise (sum of ds = 0); the un-partitioned base takes the k-gather route
 
 
 def test_two_phase_adjoint_equals_the_single_call(host, monkeypatch):
