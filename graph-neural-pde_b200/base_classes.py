@@ -64,6 +64,70 @@ class ODEFunc(nn.Module):
         # state is then this rank's [S, d] slab and edge_index holds the edges whose row it owns
         self.partition = None
 
+    # `attention_weights` is a plain attribute for every caller (the blocks assign it, LaplacianODEFunc and users read
+    # it); a block may also park a zero-argument callable with `defer_attention_weights`, evaluated on the first read.
+    # AttODEblock does that when opt['function'] == 'transformer': the reference computes the block-level attention
+    # there too (block_transformer_attention.py:24-32) but nothing on the path reads it.
+    @property
+    def attention_weights(self):
+        thunk = self.__dict__.get('_attention_thunk')
+        if thunk is not None:
+            self.__dict__['_attention_thunk'] = None
+            self.__dict__['_attention_weights'] = thunk()
+        return self.__dict__.get('_attention_weights')
+
+    @attention_weights.setter
+    def attention_weights(self, value):
+        self.__dict__['_attention_thunk'] = None
+        self.__dict__['_attention_weights'] = value
+
+    def defer_attention_weights(self, thunk):
+        self.__dict__['_attention_weights'] = None
+        self.__dict__['_attention_thunk'] = thunk
+
+    # ---- Runge-Kutta stage fusion (north_star (a)) ----------------------------------------------
+    # The fixed-grid solvers (integrators._fixed_step) form the next stage's state  y + sum_j c_j k_j + c f(t, x)  in
+    # the epilogue of the kernel that produces f instead of a separate pass over the state: they call forward_stage,
+    # which parks a `gb_stage` descriptor, runs forward() and reports whether the route taken consumed it.  Only
+    # without autograd (inference, and the forward solve of odeint_adjoint, which runs under no_grad).
+    _pending_stage = None
+
+    def forward_stage(self, t, x, y, prev, coeffs, c_self):
+        """(f(t, x), y + sum_j coeffs[j] * prev[j] + c_self * f(t, x)); the second value is None when the evaluation
+        could not fuse the combination (the caller then forms it itself)."""
+        import ctypes as C
+        from . import _lib
+        ok = (not torch.is_grad_enabled() and self.partition is None and x.is_cuda and x.dtype == torch.float32
+              and x.is_contiguous() and len(prev) <= 6 and x.dim() in (2, 3)
+              and all(v.shape == x.shape and v.dtype == x.dtype and v.is_contiguous() for v in [y] + list(prev)))
+        if not ok:
+            return self.forward(t, x), None
+        ynext = torch.empty_like(x)
+        st = _lib.GbStage()
+        st.y = y.data_ptr()
+        for j, (k, c) in enumerate(zip(prev, coeffs)):
+            st.k[j] = k.data_ptr()
+            st.c[j] = float(c)
+        st.c[len(prev)] = float(c_self)
+        st.n_prev, st.write_f, st.ynext, st.ld = len(prev), 1, ynext.data_ptr(), x.shape[-1]
+        self._pending_stage = st
+        try:
+            f = self.forward(t, x)
+            fused = self._pending_stage is None
+        finally:
+            self._pending_stage = None
+        return f, (ynext if fused else None)
+
+    def _take_stage(self):
+        """the parked stage descriptor (as the ctypes argument of the kernel entry points), at most once"""
+        st = self._pending_stage
+        if st is None:
+            return None
+        import ctypes as C
+        self._pending_stage = None
+        self._stage_keepalive = st               # the launch reads the struct by value; keep it until the next one
+        return C.pointer(st)
+
     # ---- helpers shared by the two ODE functions ------------------------------------------------
     @staticmethod
     def _as_2d(x):

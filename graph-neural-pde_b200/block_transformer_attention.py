@@ -1,8 +1,9 @@
 """`AttODEblock` - mirror of the reference's src/block_transformer_attention.py:6-69: owns a second
 SpGraphTransAttentionLayer, computes attention ONCE at t = 0 from the block input and parks it on
 `odefunc.attention_weights` (read by LaplacianODEFunc when opt['block'] == 'attention'), then
-integrates.  With opt['function'] == 'transformer' that block-level attention is computed but never
-read, exactly as in the reference."""
+integrates.  With opt['function'] == 'transformer' that block-level attention is never read on the path
+(the reference computes and discards it); here it is evaluated lazily, on the first read of
+`odefunc.attention_weights` (ODEFunc.defer_attention_weights)."""
 import torch
 
 from .base_classes import ODEblock, _integrators
@@ -31,5 +32,12 @@ class AttODEblock(ODEblock):
                 raise NotImplementedError("block 'attention' with a row-partitioned graph needs function 'transformer'")
             self.odefunc.attention_weights = None
             return self._integrate(x)
-        self.odefunc.attention_weights = self.get_attention_weights(x)
+        if self.opt['function'] == 'transformer' and hasattr(self.odefunc, 'defer_attention_weights'):
+            # ODEFuncTransformerAtt recomputes its own attention at every evaluation and never reads this one: it is
+            # evaluated on the first read of `odefunc.attention_weights` instead (same values: same layer, same
+            # block input, the graph of this forward), not once per block forward
+            xin, edge_index = x.detach(), self.odefunc.edge_index
+            self.odefunc.defer_attention_weights(lambda: self.multihead_att_layer(xin, edge_index)[0])
+        else:
+            self.odefunc.attention_weights = self.get_attention_weights(x)
         return self._integrate(x)

@@ -146,5 +146,5 @@ class LaplacianODEFunc(ODEFunc):
         source = bool(self.opt['add_source'])
         x0 = self._as_2d(self.x0) if (source and self.x0 is not None) else None
         f = DiffusionFn.apply(x2, vals, self.alpha_train, self.beta_train if x0 is not None else None, x0, plan,
-                              not self.opt['no_alpha_sigmoid'], None)
+                              not self.opt['no_alpha_sigmoid'], self._take_stage())
         return f.view_as(x)

@@ -221,7 +221,7 @@ class ODEFuncTransformerAtt(ODEFunc):
         if nl_supported(plan, x2, L.h, L.attention_dim, att_type, int(self.opt['attention_norm_idx']), edge_w):
             f = NlTransformerFn.apply(x2, L.Q.weight, L.Q.bias, L.K.weight, L.K.bias, self.alpha_train,
                                       self.beta_train if x0 is not None else None, x0, plan, L.h,
-                                      not self.opt['no_alpha_sigmoid'], None)
+                                      not self.opt['no_alpha_sigmoid'], self._take_stage())
         elif not L.needs_composite_backward(att_type, x2) and fused_transformer_supported(
                 plan, x2, L.h, L.attention_dim, att_type, int(self.opt['attention_norm_idx']), edge_w):
             kparams = None
@@ -229,11 +229,11 @@ class ODEFuncTransformerAtt(ODEFunc):
                 kparams = torch.cat([L.output_var.detach(), L.lengthscale.detach()]).to(torch.float32).contiguous()
             f = FusedTransformerFn.apply(x2, L.Q.weight, L.Q.bias, L.K.weight, L.K.bias, self.alpha_train,
                                          self.beta_train if x0 is not None else None, x0, plan, L.h, att_type,
-                                         not self.opt['no_alpha_sigmoid'], kparams, L.qk_weights(), None)
+                                         not self.opt['no_alpha_sigmoid'], kparams, L.qk_weights(), self._take_stage())
         else:
             _att, abar, _prods = L.attention_csr(x2, plan)
             f = DiffusionFn.apply(x2, abar, self.alpha_train, self.beta_train if x0 is not None else None, x0, plan,
-                                  not self.opt['no_alpha_sigmoid'], None)
+                                  not self.opt['no_alpha_sigmoid'], self._take_stage())
         return f.view_as(x)
 
     def _partitioned(self, x, x2, vjp):

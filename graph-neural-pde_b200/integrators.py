@@ -45,6 +45,7 @@ _AH = dict(alpha=[1.], beta=[[1.]], c_sol=[0.5, 0.5], c_err=[0.5, -0.5], c_mid=N
 
 
 _FUSE_MIN = 1 << 14        # below this many elements the launch overhead of either form is the same
+_FUSE_STAGES = True        # stage combinations in the epilogue of the function's kernel (tests switch it off to compare)
 
 
 def _combine_one(yi, terms):
@@ -166,7 +167,35 @@ def _fixed_grid(t0, t1, step_size):
     return grid
 
 
+def _fused_stages_ok(prob, y):
+    """can the function form the next stage's state in the epilogue of its own kernel? (ODEFunc.forward_stage:
+    plain tensor state, no autograd - inference and the forward solve of odeint_adjoint)"""
+    return (_FUSE_STAGES and not prob.is_tuple and len(y) == 1 and not torch.is_grad_enabled()
+            and getattr(prob._func, 'forward_stage', None) is not None and y[0].numel() >= _FUSE_MIN)
+
+
+def _fixed_step_fused(prob, method, t0, dt, t1, y):
+    """_fixed_step for a single-tensor state with every stage combination written by the kernel that produces the
+    stage's f (same operations in the same order as gb_stage_combine: bit-identical states)."""
+    fs, sg, y0 = prob._func.forward_stage, prob.signs(1)[0], y[0]
+    A, b, c = _TABLEAU[method]
+    rows = list(A) + [b]                                  # combination that FOLLOWS stage i: rows[i] (last: the step)
+    ks, x = [], y0
+    for i, row in enumerate(rows):
+        s = t1 if c[i] == 1.0 else t0 + c[i] * dt
+        coeffs = [dt * cf * sg for cf in row]
+        prev = [(k, cf) for k, cf in zip(ks, coeffs[:-1]) if cf != 0]
+        f, xn = fs(prob.tensor_time(s), x, y0, [k for k, _ in prev], [cf for _, cf in prev], coeffs[-1])
+        ks.append(f)
+        if xn is None:                                    # the route taken could not fuse: one separate pass
+            xn = _combine_one(y0, list(zip(ks, coeffs)))
+        x = xn
+    return (x,)
+
+
 def _fixed_step(prob, method, t0, dt, t1, y):
+    if _fused_stages_ok(prob, y):
+        return _fixed_step_fused(prob, method, t0, dt, t1, y)
     f = prob.f_raw                      # signs (reverse time, adjoint conventions) ride on the coefficients
     sg = prob.signs(len(y))
     mid, end = tuple(prob.passive) + tuple(prob.dead), tuple(prob.dead)

@@ -114,6 +114,63 @@ def test_attention_block_transformer_function(adjoint):
         assert_close(g, r, 1e-4, name, floor=bias_scale if name in ('gbq', 'gbk') else 0.0)
 
 
+def test_attention_block_transformer_function_evaluates_the_block_attention_lazily():
+    """block_transformer_attention.py:24-32 computes attention_weights at t = 0 although function 'transformer'
+    never reads it; here the same values appear on the first read, and the block forward launches no edge softmax"""
+    import grand_b200
+    n, e, d, T = 300, 2000, 16, 2.0
+    opt = dict(OPT, block='attention', function='transformer', adjoint=False)
+    block, data, ei = build(opt, n, e, T, seed=2)
+    rand_qk(block.odefunc.multihead_att_layer, 1)
+    rand_qk(block.multihead_att_layer, 2)
+    x = torch.randn(n, d, device='cuda')
+    block.set_x0(x)
+    with grand_b200._lib.Profiler() as prof:
+        with torch.no_grad():
+            block(x, data)
+        kernels = prof.results()
+        assert 'nl_fwd' in kernels and 'edge_softmax_fwd' not in kernels, sorted(kernels)
+        lazy = block.odefunc.attention_weights                       # first read: evaluated now
+        assert 'edge_softmax_fwd' in prof.results()
+    with torch.no_grad():
+        eager = block.get_attention_weights(x)
+    assert lazy is block.odefunc.attention_weights                   # evaluated once
+    assert torch.equal(lazy, eager) and lazy.shape[-1] == 4
+    block.odefunc.attention_weights = None                           # plain assignment still works
+    assert block.odefunc.attention_weights is None
+
+
+@pytest.mark.parametrize('function,blockname,method', [('transformer', 'attention', 'rk4'), ('laplacian', 'constant', 'rk4'),
+                                                       ('transformer', 'attention', 'midpoint'), ('laplacian', 'constant', 'euler')])
+def test_stage_combinations_fused_into_the_kernel_epilogues_are_bit_identical(function, blockname, method):
+    """north_star (a): y + h sum c_j k_j of the next Runge-Kutta stage is written by the kernel that produces f
+    (gb_stage epilogue) - no stage_axpy launches in a no-grad solve, and the same bits as the separate pass"""
+    import grand_b200
+    from grand_b200 import integrators
+    n, e, d, T = 3000, 24000, 64, 2.0
+    opt = dict(OPT, block=blockname, function=function, adjoint=False, hidden_dim=d, attention_dim=32, method=method)
+    block, data, ei = build(opt, n, e, T, seed=4)
+    if function == 'transformer':
+        rand_qk(block.odefunc.multihead_att_layer, 1)
+    with torch.no_grad():
+        block.odefunc.alpha_train.fill_(0.4)
+        block.odefunc.beta_train.fill_(0.2)
+    x = torch.randn(n, d, device='cuda')
+    block.set_x0(x)
+    out = {}
+    for fuse in (True, False):
+        integrators._FUSE_STAGES = fuse
+        try:
+            with grand_b200._lib.Profiler() as prof, torch.no_grad():
+                out[fuse] = block(x, data)
+                kernels = prof.results()
+        finally:
+            integrators._FUSE_STAGES = True
+        stages = {'rk4': 4, 'midpoint': 2, 'euler': 1}[method]
+        assert kernels.get('stage_axpy', {'launches': 0})['launches'] == (0 if fuse else 2 * stages), kernels
+    assert torch.equal(out[True], out[False])
+
+
 def test_attention_block_laplacian_function_trains_block_attention_without_adjoint():
     """GRAND-nl as configured by best_params (block=attention, function=laplacian): attention computed
     once from the block input; without adjoint its Q/K receive gradients."""
