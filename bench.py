@@ -26,8 +26,19 @@ if ROOT not in sys.path:
 
 import torch  # noqa: E402
 
-T_END = 2.0            # integration time -> 2 rk4 steps forward, 2 backward
+T_END = 2.0            # integration time -> 2 rk4 steps forward, 2 backward (--t-end / the workload's preset)
 STEP_SIZE = 1.0
+# BASELINE.json's configs as the reference names them; flags override single fields
+PRESETS = {
+    'c1': dict(function='laplacian', block='constant', method='rk4', t_end=10.0),     # GRAND-l, Cora shape, T = 10
+    'c2': dict(function='transformer', block='attention', method='dopri5', t_end=2.0),  # GRAND-nl, PubMed shape
+    'c3': dict(function='laplacian', block='attention', method='rk4', t_end=2.0),     # BLEND primary, ogbn-arxiv shape
+    'c4': dict(function='transformer', block='attention', method='rk4', t_end=2.0),   # GRAND-nl + adjoint (headline)
+    'c5': dict(function='transformer', block='attention', method='rk4', t_end=2.0),   # R-MAT scale 24 sweep
+}
+BLOCK = 'attention'
+METHOD = 'rk4'
+TOL_SCALE = 1.0
 
 
 def read_peaks():
@@ -40,10 +51,10 @@ def read_peaks():
 
 
 def make_opt(cfg, adjoint=True, function='transformer'):
-    return {'hidden_dim': cfg['d'], 'block': 'attention' if function == 'transformer' else 'constant', 'function': function, 'max_nfe': 10 ** 9,
-            'no_alpha_sigmoid': False, 'add_source': True, 'augment': False, 'adjoint': adjoint, 'tol_scale': 1.0,
-            'tol_scale_adjoint': 1.0, 'data_norm': 'rw', 'self_loop_weight': 1.0, 'method': 'rk4',
-            'step_size': STEP_SIZE, 'max_iters': 100, 'adjoint_method': 'rk4', 'adjoint_step_size': STEP_SIZE,
+    return {'hidden_dim': cfg['d'], 'block': BLOCK, 'function': function, 'max_nfe': 10 ** 9,
+            'no_alpha_sigmoid': False, 'add_source': True, 'augment': False, 'adjoint': adjoint, 'tol_scale': TOL_SCALE,
+            'tol_scale_adjoint': TOL_SCALE, 'data_norm': 'rw', 'self_loop_weight': 1.0, 'method': METHOD,
+            'step_size': STEP_SIZE, 'max_iters': 100, 'adjoint_method': METHOD, 'adjoint_step_size': STEP_SIZE,
             'leaky_relu_slope': 0.2, 'heads': cfg['heads'], 'attention_dim': cfg['adim'], 'attention_norm_idx': 0,
             'reweight_attention': False, 'beltrami': False, 'attention_type': 'scaled_dot', 'square_plus': False,
             'mix_features': False, 'multi_modal': False, 'kinetic_energy': None, 'jacobian_norm2': None,
@@ -52,7 +63,7 @@ def make_opt(cfg, adjoint=True, function='transformer'):
 
 # ---- algorithmic bytes per launch of each kernel (fp32 = 4 B, int32 index = 4 B; every matrix read
 # ---- once per kernel that needs it, perfect reuse of gathered rows) - DESIGN.md "Kernels" ---------
-def algorithmic_bytes(n, e, d, a, h):
+def algorithmic_bytes(n, e, d, a, h, kgather=False):
     return {
         'spmm_fwd': 8 * e + 12 * n * d + 4 * n,
         'spmm_bwd': 12 * e + 16 * n * d + 4 * n,
@@ -69,17 +80,19 @@ def algorithmic_bytes(n, e, d, a, h):
         'fused_att_spmm_fwd': 8 * n * a + 4 * n + 4 * e + 12 * n * d,
         'fused_att_bwd_row': 8 * n * d + 8 * n * a + 4 * e + 8 * e * h + 4 * n,
         'fused_att_bwd_col': 16 * n * d + 8 * n * a + 12 * e + 4 * e * h + 4 * n,
-        # single-gather kernels (csrc/nl_kernels.cuh)
-        'nl_fwd': 4 * e + 4 * n + 4 * n * a + 12 * n * d,
-        'nl_adj_rows': 4 * e + 4 * n + 8 * n * a + 16 * n * d + 4 * e * h + 4 * e,
+        # single-gather kernels (csrc/nl_kernels.cuh, nl2_kernels.cuh); k-gather kernels (csrc/nlk_kernels.cuh): + 4NA (k)
+        'nl_fwd': 4 * e + 4 * n + 4 * n * a + 12 * n * d + (4 * n * a if kgather else 0),
+        'nl_adj_rows': 4 * e + 4 * n + 8 * n * a + 16 * n * d + 4 * e * h + 4 * e + (4 * n * a if kgather else 0),
+        'edge_softmax_fwd_long': 0, 'stage_axpy': 0,
     }
 
 
-def gather_bytes(n, e, d, a, h):
+def gather_bytes(n, e, d, a, h, kgather=False):
     """no-reuse gather model: every edge fetches its endpoint's rows from HBM.  Added to the
     algorithmic bytes minus the one compulsory read of those matrices."""
     extra = 4 * (e - n) * (a + d)
-    return {'nl_fwd': 4 * (e - n) * d, 'nl_adj_rows': 4 * (e - n) * d, 'fused_att_spmm_fwd': extra, 'fused_att_bwd_row': extra, 'fused_att_bwd_col': extra,
+    row = 4 * (e - n) * (d + a) if kgather else 4 * (e - n) * d
+    return {'nl_fwd': row, 'nl_adj_rows': row, 'fused_att_spmm_fwd': extra, 'fused_att_bwd_row': extra, 'fused_att_bwd_col': extra,
             'spmm_fwd': 4 * (e - n) * d, 'spmm_bwd': 4 * (e - n) * d}
 
 
@@ -153,8 +166,9 @@ def build_block(cfg, device):
     block.train()
     g = torch.Generator().manual_seed(7)
     with torch.no_grad():                       # random-init weights of the named architecture (N(0, 1/d))
-        if FUNCTION == 'transformer':
-            for layer in (block.odefunc.multihead_att_layer, block.multihead_att_layer):
+        layers = [getattr(block.odefunc, 'multihead_att_layer', None), getattr(block, 'multihead_att_layer', None)]
+        if True:
+            for layer in [l for l in layers if l is not None]:
                 for lin in (layer.Q, layer.K):
                     lin.weight.copy_((torch.randn(lin.weight.shape, generator=g) / cfg['d'] ** 0.5).to(device))
         block.odefunc.alpha_train.fill_(0.3)
@@ -163,11 +177,20 @@ def build_block(cfg, device):
 
 
 def model_name():
-    return 'GRAND-nl' if FUNCTION == 'transformer' else 'GRAND-l'
+    if FUNCTION == 'transformer':
+        return 'GRAND-nl'
+    return 'GRAND-l' if BLOCK == 'constant' else 'BLEND-style GRAND-l (block-level attention, laplacian function)'
 
 
 def block_name():
-    return 'AttODEblock + ODEFuncTransformerAtt' if FUNCTION == 'transformer' else 'ConstantODEblock + LaplacianODEFunc'
+    blk = {'constant': 'ConstantODEblock', 'attention': 'AttODEblock'}[BLOCK]
+    return blk + (' + ODEFuncTransformerAtt' if FUNCTION == 'transformer' else ' + LaplacianODEFunc')
+
+
+def solver_name():
+    tol = '' if METHOD in ('rk4', 'euler', 'midpoint') else f', atol {1e-7 * TOL_SCALE:g} rtol {1e-9 * TOL_SCALE:g}'
+    step = f' step {STEP_SIZE}' if METHOD in ('rk4', 'euler', 'midpoint') else ''
+    return f'{METHOD}{step} T={T_END}{tol}, odeint_adjoint ({METHOD})'
 
 
 def main_kernels(kernels):
@@ -328,9 +351,13 @@ def run_ours(args):
 
     # ---- roofline of the dominant kernel ---------------------------------------------------------
     peak, peak_src = read_peaks()
-    alg = algorithmic_bytes(n, e_prime, d, cfg['adim'], cfg['heads'])
-    gat = gather_bytes(n, e_prime, d, cfg['adim'], cfg['heads'])
-    top = max(main_kernels(kernels).items(), key=lambda kv: kv[1]['ms'])
+    from grand_b200 import ops as _ops
+    kgather = FUNCTION == 'transformer' and _ops.nlk_eligible(cfg['heads'], cfg['adim'], d)
+    alg = algorithmic_bytes(n, e_prime, d, cfg['adim'], cfg['heads'], kgather)
+    gat = gather_bytes(n, e_prime, d, cfg['adim'], cfg['heads'], kgather)
+    # the dominant kernel AMONG THOSE WITH A BYTE MODEL (a kernel without one is listed but never chosen)
+    modelled = {k: v for k, v in main_kernels(kernels).items() if alg.get(k)}
+    top = max((modelled or main_kernels(kernels)).items(), key=lambda kv: kv[1]['ms'])
     kname, kstat = top
     per_launch_ms = kstat['ms'] / kstat['launches']
     achieved = alg.get(kname, 0) / (per_launch_ms * 1e-3) / 1e9 if per_launch_ms > 0 else 0.0
@@ -342,7 +369,7 @@ def run_ours(args):
                 'kernels': {k: {'ms_per_launch': round(v['ms'] / v['launches'], 4), 'launches': v['launches'],
                                 'share': None if v.get('overlapped') else round(v['ms'] / ksum, 4),
                                 'overlapped_with_main_kernel': bool(v.get('overlapped')),
-                                'alg_GBps': round(alg[k] / (v['ms'] / v['launches'] * 1e-3) / 1e9, 1) if k in alg else None,
+                                'alg_GBps': round(alg[k] / (v['ms'] / v['launches'] * 1e-3) / 1e9, 1) if alg.get(k) else None,
                                 'gather_model_GBps': round((alg[k] + gat[k]) / (v['ms'] / v['launches'] * 1e-3) / 1e9, 1)
                                 if k in alg and k in gat else None}
                             for k, v in sorted(kernels.items(), key=lambda kv: -kv[1]['ms'])}}
@@ -353,8 +380,8 @@ def run_ours(args):
         'ms_per_step': round(ms / args.steps, 3), 'higher_is_better': True, 'scaling': 'strong',
         'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
         'config': {'workload': f"{name}: {model_name()} ({cfg['desc']}), N={n}, E'={e_prime}, d={d}, heads={cfg['heads']}, "
-                               f"attention_dim={cfg['adim']}, {block_name()}, rk4 step {STEP_SIZE} "
-                               f"T={T_END}, odeint_adjoint (rk4)",
+                               f"attention_dim={cfg['adim']}, {block_name()}, {solver_name()}",
+                   'row_kernels': 'k-gather (nlk)' if kgather else 'single-gather (nl2)' if FUNCTION == 'transformer' else 'spmm',
                    'evals_per_step': evals, 'cuda_graph': bool(args.cuda_graph), 'l2': 'inputs larger than L2 (no flush)' if name in ('c4', 'c5')
                    else 'working set partly L2-resident; no flush (state reused across evaluations as in the solver)'},
         'e2e': {'value': round(evals_e2e / (ms_e2e * 1e-3), 3), 'unit': 'evals/s',
@@ -363,14 +390,22 @@ def run_ours(args):
                 'copies': 'every step uploads its input from pinned host memory and downloads loss + dL/dx; '
                           'copy stream, overlapped with the neighbouring steps (first upload / last download exposed)'
                           if graphed is None else 'in line on the compute stream (CUDA-graph replay)'},
-        'gpu_launches': int(launches), 'clocks': clocks.summary(), 'roofline': roofline,
+        'gpu_launches': int(launches), 'loss_checksum': float(loss.detach().double()), 'clocks': clocks.summary(), 'roofline': roofline,
     }
     if args.gpu_reference:
-        try:
-            line['gpu_reference'] = gpu_reference(name, cfg, device)
-            line['gpu_reference']['speedup_of_value'] = round(line['value'] / line['gpu_reference']['value'], 1)
-        except torch.cuda.OutOfMemoryError as exc:                       # the comparator's temporaries, not ours
-            line['gpu_reference'] = {'unavailable': f'out of memory in the torch-ops comparator: {str(exc)[:80]}'}
+        del block, x_dev, g_dev, graphed
+        import gc
+        gc.collect()
+        torch.cuda.empty_cache()
+        line['gpu_reference'] = {'unavailable': 'out of memory in the torch-ops comparator at every sample size'}
+        for div in [dv for dv in (1, 2, 4, 8, 16, 32) if dv <= GPU_REF_SCALE[name]]:   # full size first; its [E,d] temporaries may not fit
+            try:
+                line['gpu_reference'] = gpu_reference(name, cfg, device, div)
+                line['gpu_reference']['speedup_of_value'] = round(line['value'] / line['gpu_reference']['value'], 1)
+                break
+            except torch.cuda.OutOfMemoryError:                              # the comparator's temporaries, not ours
+                gc.collect()
+                torch.cuda.empty_cache()
     if args.cpu_baseline:
         line['cpu_baseline'] = cpu_baseline(name, cfg, steps=2, warmup=1)
     emit(line)
@@ -508,11 +543,11 @@ def run_partitioned(args, cfg, device, rank, world):
     halo_kind = args.halo
     halo = {'dense': grand_b200.Halo, 'compact': grand_b200.CompactHalo, 'push': grand_b200.PushHalo}.get(
         halo_kind, grand_b200.SparseHalo)(part)
-    gen = torch.Generator(device=device).manual_seed(99 + rank)
-    x_dev = torch.randn(part.slab, d, generator=gen, device=device)
-    g_dev = torch.randn(part.slab, d, generator=gen, device=device)
-    x_dev[part.hi - part.lo:] = 0                       # zero padding rows of the last slab
-    g_dev[part.hi - part.lo:] = 0
+    # the SAME global state and cotangent as the 1-GPU run (seed 99), sliced to this rank's slab: the loss checksum of
+    # the JSON line is comparable across N
+    gen = torch.Generator(device=device).manual_seed(99)
+    x_dev = part.to_slab(torch.randn(n, d, generator=gen, device=device)).contiguous()
+    g_dev = part.to_slab(torch.randn(n, d, generator=gen, device=device)).contiguous()
     x_host = x_dev.cpu().pin_memory()
     block = build_block(cfg, device)
     block.set_partition(part, halo)
@@ -552,10 +587,12 @@ def run_partitioned(args, cfg, device, rank, world):
     launches0 = _lib.launch_count()
     halo.bytes_in = halo.n_gathers = halo.n_scatters = halo.n_prefetched = 0
 
+    last_loss = [None]
+
     def loop():
         tot = 0
         for _ in range(args.steps):
-            ev, _ = train_pass(block, data, x_dev, g_dev)
+            ev, last_loss[0] = train_pass(block, data, x_dev, g_dev)
             tot += ev
         return tot
 
@@ -567,33 +604,56 @@ def run_partitioned(args, cfg, device, rank, world):
     n_gathers, n_scatters = halo.n_gathers // args.steps, halo.n_scatters // args.steps
 
     gx_host = torch.empty(part.slab, d).pin_memory()
+    copy_s = torch.cuda.Stream()
+    x_bufs = [torch.empty_like(x_dev) for _ in range(2)]
 
     def loop_e2e():
         tot = 0
-        for _ in range(args.steps):
-            xin = x_host.to(device, non_blocking=True)
+        # as in the 1-GPU arm: uploads / downloads on a copy stream, overlapped with the neighbouring steps
+        main_s = torch.cuda.current_stream()
+        copy_s.wait_stream(main_s)
+        uploaded = [torch.cuda.Event(), torch.cuda.Event()]
+
+        def upload(i):
+            with torch.cuda.stream(copy_s):
+                x_bufs[i % 2].copy_(x_host, non_blocking=True)
+                uploaded[i % 2].record(copy_s)
+        upload(0)
+        for i in range(args.steps):
+            main_s.wait_event(uploaded[i % 2])
+            if i + 1 < args.steps:
+                upload(i + 1)
             func = block.odefunc
             func.nfe = 0
-            xg = xin.requires_grad_(True)
+            xg = x_bufs[i % 2].detach().requires_grad_(True)
             block.set_x0(xg)
             z = block(xg, data)
             loss = (z * g_dev).sum()
             gx, = torch.autograd.grad(loss, xg)
-            gx_host.copy_(gx, non_blocking=True)
+            done = torch.cuda.Event()
+            done.record(main_s)
+            with torch.cuda.stream(copy_s):
+                copy_s.wait_event(done)
+                gx_host.copy_(gx, non_blocking=True)
+                gx.record_stream(copy_s)
             float(loss.detach())
             tot += func.nfe
+        main_s.wait_stream(copy_s)
         return tot
 
     ms_e2e, evals_e2e = timed(loop_e2e)
     # collective: EVERY rank takes part (before the rank-0-only reporting below)
     exchange = exchange_times(halo, part, d, device, n_gathers, n_scatters, ms / args.steps)
+    loss_sum = last_loss[0].detach().double().reshape(1).clone()
+    dist.all_reduce(loss_sum)                           # = the 1-GPU loss: same graph, weights, state and cotangent
     if rank != 0:
         return
     peak, peak_src = read_peaks()
     rows = part.hi - part.lo
     alg = algorithmic_bytes(rows, e_local, d, cfg['adim'], cfg['heads'])
     gat = gather_bytes(rows, e_local, d, cfg['adim'], cfg['heads'])
-    kname, kstat = max(main_kernels(kernels).items(), key=lambda kv: kv[1]['ms'])
+    modelled = {k: v for k, v in main_kernels(kernels).items() if alg.get(k)}
+    kname, kstat = max((modelled or main_kernels(kernels)).items(), key=lambda kv: kv[1]['ms'])
     per_launch_ms = kstat['ms'] / kstat['launches']
     achieved = alg.get(kname, 0) / (per_launch_ms * 1e-3) / 1e9 if per_launch_ms > 0 else 0.0
     ksum = sum(v['ms'] for v in main_kernels(kernels).values())
@@ -613,8 +673,7 @@ def run_partitioned(args, cfg, device, rank, world):
         'ms_per_step': round(ms / args.steps, 3), 'higher_is_better': True, 'scaling': 'strong',
         'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
         'config': {'workload': f"{name}: {model_name()} ({cfg['desc']}), N={n}, E'={int(e_total)}, d={d}, heads={cfg['heads']}, "
-                               f"attention_dim={cfg['adim']}, {block_name()}, rk4 step {STEP_SIZE} "
-                               f"T={T_END}, odeint_adjoint (rk4)",
+                               f"attention_dim={cfg['adim']}, {block_name()}, {solver_name()}",
                    'parallelism': f'1-D row partition over {world} GPUs ({part.slab} rows each), all-gather of the '
                                   f'state per evaluation + reduce-scatter of dL/dx per VJP (NCCL)',
                    'evals_per_step': evals, 'l2': 'inputs larger than L2 (no flush)',
@@ -630,7 +689,7 @@ def run_partitioned(args, cfg, device, rank, world):
         'e2e': {'value': round(evals_e2e / (ms_e2e * 1e-3), 3), 'unit': 'evals/s',
                 'h2d_bytes_per_step': world * part.slab * d * 4, 'd2h_bytes_per_step': world * (part.slab * d * 4 + 4),
                 'ms_per_step': round(ms_e2e / args.steps, 3)},
-        'gpu_launches': int(launches), 'clocks': clocks.summary(), 'roofline': roofline,
+        'gpu_launches': int(launches), 'loss_checksum': float(loss_sum), 'clocks': clocks.summary(), 'roofline': roofline,
         'nvlink': {'bytes_in_per_rank_per_step': halo_bytes // args.steps,
                    'GBps_in_per_rank_if_serial': round(halo_bytes / (ms * 1e-3) / 1e9, 1), 'peak_GBps': 770.0,
                    'prefetched_gathers_per_step': getattr(halo, 'n_prefetched', 0) // args.steps,
@@ -682,7 +741,7 @@ def exchange_times(halo, part, d, device, n_gathers, n_scatters, step_ms):
 GPU_REF_SCALE = {'c1': 1, 'c2': 1, 'c3': 1, 'c4': 8, 'c5': 32}
 
 
-def gpu_reference(name, cfg, device):
+def gpu_reference(name, cfg, device, div_override=None):
     """SURVEY.md 8d comparator (3): what the reference's GPU path does when its sparse dependencies are present -
     index_select gathers, [E,d] temporaries, scatter_add / scatter_max (float atomics), autograd backward -
     written with plain torch CUDA ops (torch_sparse / torch_scatter / PyG are not installable here; they
@@ -690,7 +749,7 @@ def gpu_reference(name, cfg, device):
     not fit otherwise), 1 forward evaluation + 1 adjoint evaluation, extrapolated linearly.  None of our kernels."""
     import math
     from grand_b200 import synth
-    div = GPU_REF_SCALE[name]
+    div = div_override or GPU_REF_SCALE[name]
     ei, n = synth.make_graph(name, device, seed=77, scale_div=div)
     loops = torch.arange(n, device=device)
     ei = torch.cat([ei[:, ei[0] != ei[1]], torch.stack([loops, loops])], dim=1)
@@ -738,9 +797,10 @@ def gpu_reference(name, cfg, device):
     ms = start.elapsed_time(stop) / reps
     del x, x0, gout, ei
     torch.cuda.empty_cache()
-    return {'value': round(2 / (ms * 1e-3) / div, 3), 'unit': 'evals/s', 'kind': 'torch CUDA ops (index_select, [E,d] '
+    return {'value': round(2 / (ms * 1e-3) / div, 3), 'unit': 'evals/s', 'extrapolated': div > 1, 'kind': 'torch CUDA ops (index_select, [E,d] '
             'temporaries, scatter_add / scatter_reduce atomics, autograd) = what torch_sparse.spmm + PyG softmax lower to',
-            'sample': f'{name} shape scaled 1/{div} (N={n}, E\'={row.numel()}), 1 forward + 1 adjoint evaluation, '
+            'sample': (f'EXTRAPOLATED from a 1/{div}-scale sample: ' if div > 1 else 'full size: ') +
+                      f'{name} shape scaled 1/{div} (N={n}, E\'={row.numel()}), 1 forward + 1 adjoint evaluation, '
                       f'{ms:.2f} ms per pair, evals/s divided by {div}'}
 
 
@@ -808,7 +868,8 @@ def cpu_baseline(name, cfg, steps=1, warmup=1):
         evals += cpu_pass(st)
     dt = time.perf_counter() - t0
     return {'value': round(evals / dt / div, 4), 'unit': 'evals/s', 'cores': cores, 'kind': 'port',
-            'sample': f'oracle port (torch CPU fp32, upstream-semantics sparse restatement, {model_name()}) on the {name} shape scaled '
+            'extrapolated': div > 1,
+            'sample': ('EXTRAPOLATED from a 1/%d-scale sample: ' % div if div > 1 else '') + f'oracle port (torch CPU fp32, upstream-semantics sparse restatement, {model_name()}) on the {name} shape scaled '
                       f'1/{div} (N={st.n}, E\'={st.e}); {steps} x (1 forward eval + 1 adjoint eval); evals/s divided '
                       f'by {div} (linear-cost extrapolation to the full shape)',
             'seconds': round(dt, 2)}
@@ -826,8 +887,8 @@ def run_reference(args):
             'ms_per_step': round(base['seconds'] / max(1, args.steps) * 1e3, 3), 'higher_is_better': True,
             'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
             'config': {'workload': f"{args.workload}: {model_name()} ({cfg['desc']}), N={cfg['n']}, E'={cfg['e'] + cfg['n']}, "
-                                   f"d={cfg['d']}, heads={cfg['heads']}, attention_dim={cfg['adim']}, {block_name()}, rk4 step "
-                                   f"{STEP_SIZE} T={T_END}, odeint_adjoint (rk4)",
+                                   f"d={cfg['d']}, heads={cfg['heads']}, attention_dim={cfg['adim']}, {block_name()}, "
+                                   f"{solver_name()}",
                        'arm': 'reference path on the host cores (oracle port of the upstream-semantics sparse path; the '
                               'reference itself needs dense [N,N] memory and uninstallable sparse packages), bounded sample, '
                               'see cpu_baseline.sample'},
@@ -861,7 +922,7 @@ def main():
     ap.add_argument('--no-cpu-baseline', dest='cpu_baseline', action='store_false')
     ap.add_argument('--no-gpu-reference', dest='gpu_reference', action='store_false',
                     help='skip the torch-CUDA-ops comparator (N = 1 only)')
-    ap.add_argument('--function', default='transformer', choices=['transformer', 'laplacian'],
+    ap.add_argument('--function', default=None, choices=['transformer', 'laplacian'],
                     help='transformer = GRAND-nl (BASELINE.json headline); laplacian = GRAND-l sweep of config 5')
     ap.add_argument('--halo', default=os.environ.get('GRANDB200_HALO', 'dense'), choices=['dense', 'sparse', 'compact', 'push', 'auto'],
                     help='N > 1: exchange whole slabs (dense), only the rows the peers reference (sparse: R-MAT slabs '
@@ -875,9 +936,24 @@ def main():
     ap.add_argument('--watchdog', type=int, default=1500,
                     help='seconds after which a still-running bench process kills itself (a rank stuck in a '
                          'collective must not hold the GPUs)')
+    ap.add_argument('--block', default=None, choices=['constant', 'attention'], help='default: the workload preset')
+    ap.add_argument('--method', default=None, choices=['rk4', 'euler', 'midpoint', 'dopri5', 'adaptive_heun'],
+                    help='solver of the forward and of the adjoint solve; default: the workload preset')
+    ap.add_argument('--t-end', type=float, default=None, help='integration time; default: the workload preset')
+    ap.add_argument('--tol-scale', type=float, default=None,
+                    help='tol_scale / tol_scale_adjoint of the adaptive solvers (atol 1e-7, rtol 1e-9 times this); '
+                         'default 1e3 for fp32 states')
     args = ap.parse_args()
-    global FUNCTION
-    FUNCTION = args.function
+    global FUNCTION, BLOCK, METHOD, T_END, TOL_SCALE
+    preset = PRESETS[args.workload]
+    FUNCTION = args.function or preset['function']
+    BLOCK = args.block or (preset['block'] if FUNCTION == preset['function'] else
+                           ('attention' if FUNCTION == 'transformer' else 'constant'))
+    METHOD = args.method or preset['method']
+    T_END = args.t_end if args.t_end is not None else preset['t_end']
+    TOL_SCALE = args.tol_scale if args.tol_scale is not None else (1.0 if METHOD in ('rk4', 'euler', 'midpoint') else 1e3)
+    if int(os.environ.get('WORLD_SIZE', '1')) > 1 and args.function is None and args.workload in ('c1', 'c2', 'c3'):
+        pass                                           # the small shapes stay on one GPU; a partitioned run is by request
     if args.watchdog > 0:
         import threading
 
