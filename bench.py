@@ -215,6 +215,18 @@ def train_pass(block, data, x_dev, g_dev):
     return func.nfe, loss
 
 
+def loss_checksum(block, data, x_dev, g_dev):
+    """sum(z(T) * g) of one extra no-grad solve, accumulated in fp64 (the fp32 loss of the timed passes carries
+    ~1e-7 * sum|z g| of summation noise, which hides real differences between runs at different N)"""
+    with torch.no_grad():
+        block.set_x0(x_dev)
+        z = block(x_dev, data)
+        tot = torch.zeros((), dtype=torch.float64, device=x_dev.device)
+        for lo in range(0, z.shape[0], 1 << 18):
+            tot += (z[lo:lo + (1 << 18)].double() * g_dev[lo:lo + (1 << 18)].double()).sum()
+    return tot
+
+
 def run_ours(args):
     import grand_b200
     from grand_b200 import synth, _lib
@@ -228,7 +240,12 @@ def run_ours(args):
     if world > 1:
         import torch.distributed as dist
         import datetime
-        dist.init_process_group('nccl', device_id=device, timeout=datetime.timedelta(seconds=600))
+        pg_opts = None
+        if os.environ.get('GRANDB200_NCCL_PRIORITY', '1') == '1':
+            # NCCL's kernels on high-priority streams: a collective issued next to our kernels (overlapped exchange)
+            # gets SMs as soon as thread blocks retire instead of after the queued grid has drained
+            pg_opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)
+        dist.init_process_group('nccl', device_id=device, timeout=datetime.timedelta(seconds=600), pg_options=pg_opts)
         try:
             return run_partitioned(args, cfg, device, rank, world)
         finally:
@@ -390,7 +407,7 @@ def run_ours(args):
                 'copies': 'every step uploads its input from pinned host memory and downloads loss + dL/dx; '
                           'copy stream, overlapped with the neighbouring steps (first upload / last download exposed)'
                           if graphed is None else 'in line on the compute stream (CUDA-graph replay)'},
-        'gpu_launches': int(launches), 'loss_checksum': float(loss.detach().double()), 'clocks': clocks.summary(), 'roofline': roofline,
+        'gpu_launches': int(launches), 'loss_checksum': round(float(loss_checksum(block, data, x_dev, g_dev)), 6), 'clocks': clocks.summary(), 'roofline': roofline,
     }
     if args.gpu_reference:
         del block, x_dev, g_dev, graphed
@@ -644,8 +661,8 @@ def run_partitioned(args, cfg, device, rank, world):
     ms_e2e, evals_e2e = timed(loop_e2e)
     # collective: EVERY rank takes part (before the rank-0-only reporting below)
     exchange = exchange_times(halo, part, d, device, n_gathers, n_scatters, ms / args.steps)
-    loss_sum = last_loss[0].detach().double().reshape(1).clone()
-    dist.all_reduce(loss_sum)                           # = the 1-GPU loss: same graph, weights, state and cotangent
+    loss_sum = loss_checksum(block, data, x_dev, g_dev).reshape(1)
+    dist.all_reduce(loss_sum)                           # = the 1-GPU checksum: same graph, weights, state and cotangent
     if rank != 0:
         return
     peak, peak_src = read_peaks()
@@ -689,7 +706,7 @@ def run_partitioned(args, cfg, device, rank, world):
         'e2e': {'value': round(evals_e2e / (ms_e2e * 1e-3), 3), 'unit': 'evals/s',
                 'h2d_bytes_per_step': world * part.slab * d * 4, 'd2h_bytes_per_step': world * (part.slab * d * 4 + 4),
                 'ms_per_step': round(ms_e2e / args.steps, 3)},
-        'gpu_launches': int(launches), 'loss_checksum': float(loss_sum), 'clocks': clocks.summary(), 'roofline': roofline,
+        'gpu_launches': int(launches), 'loss_checksum': round(float(loss_sum), 6), 'clocks': clocks.summary(), 'roofline': roofline,
         'nvlink': {'bytes_in_per_rank_per_step': halo_bytes // args.steps,
                    'GBps_in_per_rank_if_serial': round(halo_bytes / (ms * 1e-3) / 1e9, 1), 'peak_GBps': 770.0,
                    'prefetched_gathers_per_step': getattr(halo, 'n_prefetched', 0) // args.steps,

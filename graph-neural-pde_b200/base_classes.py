@@ -165,7 +165,11 @@ class ODEblock(nn.Module):
         self.aug_dim = 2 if opt['augment'] else 1
         self.odefunc = odefunc(self.aug_dim * opt['hidden_dim'], self.aug_dim * opt['hidden_dim'], opt, device)
         self.nreg = len(regularization_fns)
-        self.reg_odefunc = _RegShim(self.odefunc)
+        # the reference builds the function twice: `reg_odefunc` keeps the FIRST instance (base_classes.py:40-43) and
+        # every concrete block then replaces `self.odefunc` with a second one (e.g. block_constant.py:11), so its
+        # state_dict carries `reg_odefunc.odefunc.*` next to `odefunc.*`; same keys, same parameter count here
+        self.reg_odefunc = RegularizedODEfunc(odefunc(self.aug_dim * opt['hidden_dim'], self.aug_dim * opt['hidden_dim'],
+                                                      opt, device), regularization_fns)
         self.train_integrator = _integrators(opt['adjoint'])
         self.test_integrator = None
         self.set_tol()
@@ -181,6 +185,7 @@ class ODEblock(nn.Module):
 
     def set_x0(self, x0):
         self.odefunc.x0 = x0.clone().detach()
+        self.reg_odefunc.odefunc.x0 = self.odefunc.x0          # base_classes.py:53-55 (the reference clones twice)
 
     def set_tol(self):
         self.atol = self.opt['tol_scale'] * 1e-7
@@ -270,12 +275,25 @@ class ODEblock(nn.Module):
             + ")"
 
 
-class _RegShim(object):
-    """stands where the reference keeps `reg_odefunc` (base_classes.py:43): callers read
-    `block.reg_odefunc.odefunc.nfe` (base_classes.py:174-179)."""
+class RegularizedODEfunc(nn.Module):
+    """regularized_ODE_function.py:8-35: holds its own instance of the ODE function (parameters registered under
+    `reg_odefunc.odefunc.*`, as in the reference's checkpoints) and the regularisation functions.  Integrating through
+    it needs create_graph=True through the function (double backward), which the B200 operators do not offer: the
+    blocks refuse non-empty regularisation lists (`_no_regularisers`), so forward() is never reached on a valid
+    configuration."""
 
-    def __init__(self, odefunc):
+    def __init__(self, odefunc, regularization_fns):
+        super(RegularizedODEfunc, self).__init__()
         self.odefunc = odefunc
+        self.regularization_fns = regularization_fns
+
+    def forward(self, t, state):
+        raise NotImplementedError('RNODE regularisers need double backward through the ODE function; the B200 '
+                                  'operators implement first-order VJPs only')
+
+    @property
+    def _num_evals(self):
+        return self.odefunc._num_evals
 
 
 class GraphData(object):

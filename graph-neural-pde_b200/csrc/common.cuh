@@ -75,6 +75,9 @@ struct LaunchScope {
 int check_launch(const char* name);   // cudaGetLastError -> gb_status
 
 int sm_count();
+// SMs the persistent row kernels occupy: sm_count() minus GRANDB200_SM_RESERVE (default 0).  A row-partitioned run
+// that overlaps NCCL collectives with these kernels leaves a few SMs to NCCL's kernels this way.
+int persistent_sms();
 
 // fork / join of the per-device side stream (runtime.cu); side_fork returns `main` when unavailable
 cudaStream_t side_fork(cudaStream_t main);

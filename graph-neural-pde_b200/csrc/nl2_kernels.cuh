@@ -614,11 +614,11 @@ int nl2_launch(NlArgs a, int n_long, cudaStream_t stream) {
   a.n_long = n_long;
   GB_CUDA(cudaMemsetAsync(a.counter, 0, sizeof(int32_t), stream));
   // rows per scheduler grab: up to kNl2ChunkRows, fewer on small graphs so that every warp of the machine gets work
-  const int warps = W * sm_count();
+  const int warps = W * persistent_sms();
   int chunk = nrows / (4 * warps);
   chunk = chunk < 1 ? 1 : (chunk > kNl2ChunkRows ? kNl2ChunkRows : chunk);
   const int want = (nrows + W * chunk - 1) / (W * chunk);
-  const int blocks = min_int(want, sm_count());
+  const int blocks = min_int(want, persistent_sms());
   {
     LaunchScope ls(ADJ ? K_NL_ADJ_ROWS : K_NL_FWD, stream);
     nl2_rows_kernel<XL, H, ADJ, W><<<blocks, W * 32, geo.total, stream>>>(a, chunk);

@@ -68,6 +68,17 @@ int sm_count() {
   return cached;
 }
 
+int persistent_sms() {
+  static int reserve = -1;
+  if (reserve < 0) {
+    const char* e = getenv("GRANDB200_SM_RESERVE");
+    reserve = e != nullptr ? atoi(e) : 0;
+    if (reserve < 0) reserve = 0;
+  }
+  const int n = sm_count() - reserve;
+  return n < 1 ? 1 : n;
+}
+
 // ---- side stream: the CTA-per-long-segment kernels run next to the main kernel of the same pass ------------
 // A handful of hub rows / columns (one CTA each, up to ~1 ms for a 20 000-edge hub) would otherwise run alone
 // on a few SMs after the main kernel.  They touch disjoint output rows, so they are launched FIRST on a side

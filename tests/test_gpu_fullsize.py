@@ -65,6 +65,39 @@ def test_sampled_rows_match_the_oracle(c4):
     assert_close(f[rows], ref[loc_rows.cpu()], 1e-5, 'sampled rows of f')
 
 
+def test_sampled_columns_of_the_vjp_match_the_oracle(c4):
+    """dL/dx_j depends on the rows with an edge into j (their whole softmax rows) and on row j itself: the oracle's
+    autograd on the sub-problem "all out-edges of S and of every in-neighbour of S" reproduces dx[S] of the full-size
+    fused VJP exactly (as a formula) - 48 random columns plus the column with the most in-edges among 2000 candidates"""
+    func, ei, n = c4['func'], c4['ei'], c4['n']
+    _, dx, _ = func.eval_vjp(0.0, c4['x'], c4['g'], _params(func))
+    cand = torch.randperm(n, generator=torch.Generator().manual_seed(5))[:2000].cuda()
+    indeg = torch.bincount(ei[1], minlength=n)
+    cols = torch.cat([cand[:48], cand[indeg[cand].argmax()][None]])
+    in_s = torch.zeros(n, dtype=torch.bool, device='cuda')
+    in_s[cols] = True
+    rows = torch.unique(torch.cat([cols, ei[0, in_s[ei[1]]]]))          # S and every row with an edge into S
+    in_r = torch.zeros(n, dtype=torch.bool, device='cuda')
+    in_r[rows] = True
+    sub = ei[:, in_r[ei[0]]]                                            # every out-edge of those rows
+    nodes, inv = torch.unique(torch.cat([cols, rows, sub.reshape(-1)]), return_inverse=True)
+    loc_cols = inv[:cols.numel()].cpu()
+    loc_rows = inv[cols.numel():cols.numel() + rows.numel()].cpu()
+    loc_ei = inv[cols.numel() + rows.numel():].reshape(2, -1).cpu()
+    assert loc_ei.shape[1] < 3_000_000, loc_ei.shape                    # stays a seconds-sized oracle problem
+    L = func.multihead_att_layer
+    c = lambda t: t.detach().double().cpu()
+    xs = c(c4['x'][nodes]).requires_grad_(True)
+    ref = funcs.transformer_f(xs, loc_ei, c(L.Q.weight), c(L.Q.bias), c(L.K.weight), c(L.K.bias), HEADS,
+                              c(func.alpha_train), c(func.beta_train), c(c4['x0'][nodes]))
+    gsub = torch.zeros_like(ref)
+    gsub[loc_rows] = c(c4['g'][rows])                                   # rows outside R do not reach x[S]
+    rdx, = torch.autograd.grad(ref, xs, gsub)
+    assert_close(dx[cols], rdx[loc_cols], 1e-4, 'sampled columns of dL/dx')
+    from helpers import assert_rows_close
+    assert_rows_close(dx[cols], rdx[loc_cols], 1e-4, 'sampled columns of dL/dx (per row)')
+
+
 def test_constant_state_is_a_fixed_point_of_the_attention_diffusion(c4):
     """row softmax is row-stochastic: x_j = v for every node  =>  A(x) x = x  =>  f = beta * x0"""
     func, n = c4['func'], c4['n']
