@@ -219,16 +219,22 @@ template <int V, int LPR, int CPL, bool BWD>
 int launch_shape(const SpmmArgs& a, int n_long, cudaStream_t stream) {
   constexpr int RPT = kSpmmThreads / LPR;
   const int blocks = (a.n - a.row0 + RPT * kRowTiles - 1) / (RPT * kRowTiles);
+  // hub rows (> a.long_threshold edges, one CTA each) FIRST and on the forked high-priority side stream: their few
+  // CTAs are placed before the main kernel's fill every SM and run next to it (profiles/r01q: as a second serial
+  // launch they cost more than the main kernel on R-MAT graphs)
+  cudaStream_t side = stream;
+  if (n_long > 0) {
+    side = side_fork(stream);
+    SpmmArgs b = a;
+    b.partial_base = a.partial_base + blocks;
+    LaunchScope ls(BWD ? K_SPMM_BWD_LONG : K_SPMM_FWD_LONG, side);
+    spmm_long<V, LPR, CPL, BWD><<<n_long, kSpmmThreads, 0, side>>>(b);
+  }
   if (blocks > 0) {
     LaunchScope ls(BWD ? K_SPMM_BWD : K_SPMM_FWD, stream);
     spmm_rows<V, LPR, CPL, BWD><<<blocks, kSpmmThreads, 0, stream>>>(a);
   }
-  if (n_long > 0) {
-    SpmmArgs b = a;
-    b.partial_base = a.partial_base + blocks;
-    LaunchScope ls(BWD ? K_SPMM_BWD_LONG : K_SPMM_FWD_LONG, stream);
-    spmm_long<V, LPR, CPL, BWD><<<n_long, kSpmmThreads, 0, stream>>>(b);
-  }
+  if (side != stream) side_join(stream, side);
   return blocks + n_long;
 }
 
@@ -277,6 +283,14 @@ int run_spmm(SpmmArgs a, int d, int v, int n_long, cudaStream_t stream, int* slo
   }
   if (slots_used) *slots_used = slot;
   return check_launch(BWD ? "spmm_bwd" : "spmm_fwd");
+}
+
+// Rows up to kSpmmLongRow edges stay with the sub-warp groups of spmm_rows (the plan lists rows > 256; a CTA per row
+// only pays beyond a few thousand edges - below that its launch, shared-memory combine and barrier dominate)
+constexpr int kSpmmLongRow = 2048;
+int spmm_long_threshold(const gb_graph* g) {
+  if (g->long_threshold <= 0) return 0x7fffffff;
+  return g->long_threshold > kSpmmLongRow ? g->long_threshold : kSpmmLongRow;
 }
 
 int check_graph(const gb_graph* g, const char* who) {
@@ -338,7 +352,7 @@ int gb_spmm_fwd_part(const gb_graph* g, int32_t row_lo, int32_t row_hi, const fl
   GB_REQUIRE(ldx >= d && ldo >= d, "gb_spmm_fwd: leading dimension smaller than d");
   SpmmArgs a{};
   a.ptr = g->rowptr; a.idx = g->colidx; a.perm = nullptr; a.vals = vals;
-  a.n = row_hi; a.row0 = row_lo; a.long_threshold = g->long_threshold > 0 ? g->long_threshold : 0x7fffffff;
+  a.n = row_hi; a.row0 = row_lo; a.long_threshold = spmm_long_threshold(g);
   a.src = x; a.lds = ldx; a.alpha_train = alpha_train; a.alpha_sigmoid = alpha_sigmoid;
   const bool source = (x0 != nullptr && beta_train != nullptr);
   a.x0 = source ? x0 : nullptr; a.ldx0 = ldx0; a.beta_train = source ? beta_train : nullptr;
@@ -386,7 +400,7 @@ int gb_spmm_bwd_part(const gb_graph* g, int32_t own_lo, int32_t own_hi, const fl
   GB_REQUIRE(dparams == nullptr || partials != nullptr, "gb_spmm_bwd: dparams requested without partials workspace");
   SpmmArgs a{};
   a.ptr = g->colptr; a.idx = g->rowidx; a.perm = g->tperm; a.vals = vals;
-  a.n = g->n; a.long_threshold = g->long_threshold > 0 ? g->long_threshold : 0x7fffffff;
+  a.n = g->n; a.long_threshold = spmm_long_threshold(g);
   a.src = gout; a.lds = ldg; a.alpha_train = alpha_train; a.alpha_sigmoid = alpha_sigmoid;
   a.x0 = dparams ? x0 : nullptr; a.ldx0 = ldx0;
   a.x = dparams ? x : nullptr; a.ldx = ldx;
