@@ -17,7 +17,9 @@
 //
 // Roofline: HBM.  Algorithmic bytes per forward launch: 8E + 12Nd + 4N.
 #include <mutex>
+#include <stdlib.h>
 #include "spmm_common.cuh"
+#include "spmm2_kernels.cuh"
 
 namespace gb {
 
@@ -257,8 +259,56 @@ inline int slice_blocks(int n, int n_long) {
 }
 
 // splits the d columns into slices of at most 128 vector chunks and launches each
+// ---- large graphs: the dynamically scheduled kernels of spmm2_kernels.cuh ------------------------------------------
+// Scheduler counters live in a file-scope device array (no workspace argument in gb_spmm_*): a ring of 64, one per
+// launch in turn, zeroed on the launching stream before the kernel; launches that overlap on the GPU use different
+// counters unless more than 64 are in flight.
+static __device__ int32_t g_spmm2_counters[64];
+constexpr int kSpmm2MinRows = 262144;     // below this the statically tiled kernels keep every SM busy with less set-up
+
+// GRANDB200_SPMM_IMPL=1 keeps the statically tiled kernels; GRANDB200_SPMM2_MIN_ROWS overrides the size threshold
+// (tests run the dynamic kernels on small graphs with it).  Read per call: a getenv is nothing next to a launch.
+bool spmm2_enabled() {
+  const char* e = getenv("GRANDB200_SPMM_IMPL");
+  return !(e != nullptr && e[0] == '1');
+}
+int spmm2_min_rows() {
+  const char* e = getenv("GRANDB200_SPMM2_MIN_ROWS");
+  return e != nullptr && e[0] ? atoi(e) : kSpmm2MinRows;
+}
+
+int spmm2_counter(int32_t** out) {
+  static int32_t* base[64] = {};
+  static std::mutex mu;
+  static unsigned next = 0;
+  int dev = -1;
+  GB_CUDA(cudaGetDevice(&dev));
+  GB_REQUIRE(dev >= 0 && dev < 64, "spmm2: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (base[dev] == nullptr) {
+    void* p = nullptr;
+    GB_CUDA(cudaGetSymbolAddress(&p, g_spmm2_counters));
+    base[dev] = static_cast<int32_t*>(p);
+  }
+  *out = base[dev] + (next++ % 64);
+  return GB_OK;
+}
+
+template <bool BWD>
+int run_spmm2(const SpmmArgs& a, int n_long, cudaStream_t stream, int* slots_used) {
+  int32_t* counter = nullptr;
+  if (int rc = spmm2_counter(&counter)) return rc;
+  if (a.dv <= 16) return spmm2_launch<16, BWD, 24>(a, n_long, counter, stream, slots_used);
+  return spmm2_launch<32, BWD, 24>(a, n_long, counter, stream, slots_used);
+}
+
 template <bool BWD>
 int run_spmm(SpmmArgs a, int d, int v, int n_long, cudaStream_t stream, int* slots_used) {
+  if (v == 4 && d <= 128 && a.n - a.row0 >= spmm2_min_rows() && spmm2_enabled()) {
+    a.dv = d / 4;
+    a.partial_base = 0;
+    return run_spmm2<BWD>(a, n_long, stream, slots_used);
+  }
   const int max_cols = 128 * v;
   int slot = 0;
   for (int c0 = 0; c0 < d; c0 += max_cols) {
@@ -285,13 +335,10 @@ int run_spmm(SpmmArgs a, int d, int v, int n_long, cudaStream_t stream, int* slo
   return check_launch(BWD ? "spmm_bwd" : "spmm_fwd");
 }
 
-// Rows up to kSpmmLongRow edges stay with the sub-warp groups of spmm_rows (the plan lists rows > 256; a CTA per row
-// only pays beyond a few thousand edges - below that its launch, shared-memory combine and barrier dominate)
-constexpr int kSpmmLongRow = 2048;
-int spmm_long_threshold(const gb_graph* g) {
-  if (g->long_threshold <= 0) return 0x7fffffff;
-  return g->long_threshold > kSpmmLongRow ? g->long_threshold : kSpmmLongRow;
-}
+// rows longer than the plan's list threshold (256) go to spmm_long.  Raising this to 2048 for the statically tiled
+// spmm_rows was measured and rejected (profiles/r02p: C5 GRAND-l 644 -> 718 ms/step, C3 BLEND 8.9 -> 16.2 ms: a 16-lane
+// group walking 2000 edges stalls its whole CTA); large graphs take the dynamically scheduled spmm2 kernels instead
+int spmm_long_threshold(const gb_graph* g) { return g->long_threshold > 0 ? g->long_threshold : 0x7fffffff; }
 
 int check_graph(const gb_graph* g, const char* who) {
   GB_REQUIRE(g != nullptr, "%s: null graph", who);
@@ -377,7 +424,9 @@ int gb_spmm_fwd_part(const gb_graph* g, int32_t row_lo, int32_t row_hi, const fl
 size_t gb_spmm_bwd_partials(const gb_graph* g, int32_t d) {
   if (!g || g->n <= 0 || d <= 0) return 0;
   const int slices = (d + 127) / 128;                       // worst case: scalar path, 128 columns per slice
-  const size_t slots = (size_t)slices * (size_t)slice_blocks(g->n, g->n_long_cols);
+  size_t per_slice = (size_t)slice_blocks(g->n, g->n_long_cols);
+  if ((size_t)spmm2_slots(g->n, g->n_long_cols) > per_slice) per_slice = (size_t)spmm2_slots(g->n, g->n_long_cols);
+  const size_t slots = (size_t)slices * per_slice;
   return slots * 2 + kMidFloats + 64;                       // in floats
 }
 

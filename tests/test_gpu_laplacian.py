@@ -101,6 +101,41 @@ def test_hub_rows_and_duplicates_long_path():
         assert_close(g, r, G_RTOL, name)
 
 
+@pytest.mark.parametrize('n,e,d,hub', [(3000, 24000, 128, None), (2500, 20000, 64, (17, 5000)), (1500, 9000, 96, (3, 2500)),
+                                       (1200, 7000, 40, None), (900, 6000, 16, (5, 3000))])
+def test_dynamically_scheduled_spmm_vs_oracle_and_vs_the_static_kernels(n, e, d, hub, monkeypatch):
+    """csrc/spmm2_kernels.cuh (the large-graph path: persistent CTAs, TMA-staged gathers, CTA-wide rows > 2048 edges)
+    forced onto small graphs: f and all gradients vs the fp64 oracle, run-to-run identical, and within rounding of the
+    statically tiled kernels"""
+    import grand_b200
+    ei = rand_graph(n, e, n + d, hub=hub)
+    ei = np.concatenate([ei, np.array([[7, 7, 7], [9, 9, 9]])], axis=1)           # duplicate edges add
+    w = (np.random.default_rng(2).random(ei.shape[1]).astype(np.float32) + 0.1) / 40
+    rng = np.random.default_rng(d)
+    x, x0, gout = (rng.standard_normal((n, d)).astype(np.float32) for _ in range(3))
+    x[11] = 0                                                                     # and an isolated-looking row
+    res = {}
+    for impl in ('dynamic', 'dynamic-again', 'static'):
+        monkeypatch.setenv('GRANDB200_SPMM2_MIN_ROWS', '1')
+        monkeypatch.setenv('GRANDB200_SPMM_IMPL', '1' if impl == 'static' else '2')
+        f = make_func(d, alpha=0.3, beta=0.1)
+        f.edge_index, f.edge_weight, f.x0 = dev(ei), dev(w), dev(x0)
+        xg = dev(x).requires_grad_(True)
+        with grand_b200._lib.Profiler() as prof:
+            out = f(0.0, xg)
+            grads = torch.autograd.grad(out, (xg, f.alpha_train, f.beta_train), dev(gout))
+            kernels = prof.results()
+        assert ('spmm_fwd_long' in kernels) == (impl == 'static' and hub is not None), sorted(kernels)
+        res[impl] = (out.detach(),) + tuple(g.detach() for g in grads)
+    ref, rg = oracle_eval(ei, w, x, x0, gout, 0.3, 0.1, True, False)
+    for got, want, name in zip(res['dynamic'], (ref,) + tuple(rg), ('f', 'gx', 'galpha', 'gbeta')):
+        assert_close(got, want, F_RTOL if name == 'f' else G_RTOL, name)
+    for a_, b_ in zip(res['dynamic'], res['dynamic-again']):
+        assert torch.equal(a_, b_)
+    for a_, b_, name in zip(res['dynamic'], res['static'], ('f', 'gx', 'galpha', 'gbeta')):
+        assert_close(a_, b_, 2e-6 if name in ('f', 'gx') else 1e-5, name + ' vs the static kernels')
+
+
 def test_isolated_nodes_and_empty_graph():
     n, d = 40, 8
     f = make_func(d, alpha=0.2, beta=0.0, add_source=False)
