@@ -464,7 +464,7 @@ def nlk_eligible(heads, adim, d):
     """k-gather row kernels (csrc/nlk_kernels.cuh) instead of the single-gather ones: they fetch k[col] next to x[col]
     (4A more bytes per edge) and drop the per-row Wk work; measured faster whenever d > attention_dim
     (profiles/r02*).  GRANDB200_NL_IMPL=1|2 keeps the single-gather generations for A/B timing."""
-    if os.environ.get('GRANDB200_NL_IMPL', '3') != '3' or d <= adim:
+    if os.environ.get('GRANDB200_NL_IMPL', '3') != '3' or d < adim:
         return False
     return bool(_lib.load().gb_nlk_supported(heads, adim // heads, d))
 
