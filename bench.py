@@ -160,6 +160,7 @@ FUNCTION = 'transformer'      # --function: transformer = GRAND-nl (headline), l
 
 def build_block(cfg, device):
     import grand_b200
+    torch.manual_seed(1234)                     # every parameter not set below (V, Wout, ...) is seeded as well
     opt = make_opt(cfg, function=FUNCTION)
     block = grand_b200.set_block(opt)(grand_b200.set_function(opt), [], opt, device,
                                       t=torch.tensor([0., T_END])).to(device)
@@ -171,6 +172,8 @@ def build_block(cfg, device):
             for layer in [l for l in layers if l is not None]:
                 for lin in (layer.Q, layer.K):
                     lin.weight.copy_((torch.randn(lin.weight.shape, generator=g) / cfg['d'] ** 0.5).to(device))
+                    lin.bias.copy_((0.1 * torch.randn(lin.bias.shape, generator=g)).to(device))   # seeded too: the
+                    # default init draws from the global generator and made every process a different model
         block.odefunc.alpha_train.fill_(0.3)
         block.odefunc.beta_train.fill_(0.1)
     return block
@@ -213,6 +216,13 @@ def train_pass(block, data, x_dev, g_dev):
         p.grad = None
     loss.backward()
     return func.nfe, loss
+
+
+def input_checksums(ei, x_dev, g_dev):
+    """order-independent fingerprints of the synthetic inputs (so that two JSON lines can be compared at all)"""
+    e = ei.reshape(2, -1)
+    return {'graph': int(((e[0] * 1000003 + e[1]) % 2147483647).sum()), 'edges': int(e.shape[1]),
+            'x': round(float(x_dev.double().sum()), 6), 'g': round(float(g_dev.double().sum()), 6)}
 
 
 def loss_checksum(block, data, x_dev, g_dev):
@@ -407,7 +417,8 @@ def run_ours(args):
                 'copies': 'every step uploads its input from pinned host memory and downloads loss + dL/dx; '
                           'copy stream, overlapped with the neighbouring steps (first upload / last download exposed)'
                           if graphed is None else 'in line on the compute stream (CUDA-graph replay)'},
-        'gpu_launches': int(launches), 'loss_checksum': round(float(loss_checksum(block, data, x_dev, g_dev)), 6), 'clocks': clocks.summary(), 'roofline': roofline,
+        'gpu_launches': int(launches), 'loss_checksum': round(float(loss_checksum(block, data, x_dev, g_dev)), 6),
+        'input_checksums': input_checksums(ei, x_dev, g_dev), 'clocks': clocks.summary(), 'roofline': roofline,
     }
     if args.gpu_reference:
         del block, x_dev, g_dev, graphed
@@ -583,6 +594,8 @@ def run_partitioned(args, cfg, device, rank, world):
     for _ in range(max(args.warmup, 3)):
         evals, loss = train_pass(block, data, x_dev, g_dev)
     torch.cuda.synchronize()
+    gen2 = torch.Generator(device=device).manual_seed(99)
+    in_sums = input_checksums(ei, torch.randn(n, d, generator=gen2, device=device), torch.randn(n, d, generator=gen2, device=device))
     del ei
     e_local = int(block.odefunc.edge_index.shape[-1])
     e_total = torch.tensor([e_local], device=device)
@@ -694,7 +707,7 @@ def run_partitioned(args, cfg, device, rank, world):
                    'parallelism': f'1-D row partition over {world} GPUs ({part.slab} rows each), all-gather of the '
                                   f'state per evaluation + reduce-scatter of dL/dx per VJP (NCCL)',
                    'evals_per_step': evals, 'l2': 'inputs larger than L2 (no flush)',
-                   'overlapped_exchange': os.environ.get('GRANDB200_OVERLAP') == '1',
+                   'overlapped_exchange': os.environ.get('GRANDB200_OVERLAP', '1') == '1',
                    'halo': halo_kind + {'sparse': ' (all_to_all_v of the referenced rows only)',
                                         'compact': ' (all_to_all_v of the referenced rows only; local graph relabelled to '
                                                    '[own slab | referenced rows])',
@@ -706,7 +719,7 @@ def run_partitioned(args, cfg, device, rank, world):
         'e2e': {'value': round(evals_e2e / (ms_e2e * 1e-3), 3), 'unit': 'evals/s',
                 'h2d_bytes_per_step': world * part.slab * d * 4, 'd2h_bytes_per_step': world * (part.slab * d * 4 + 4),
                 'ms_per_step': round(ms_e2e / args.steps, 3)},
-        'gpu_launches': int(launches), 'loss_checksum': round(float(loss_sum), 6), 'clocks': clocks.summary(), 'roofline': roofline,
+        'gpu_launches': int(launches), 'loss_checksum': round(float(loss_sum), 6), 'input_checksums': in_sums, 'clocks': clocks.summary(), 'roofline': roofline,
         'nvlink': {'bytes_in_per_rank_per_step': halo_bytes // args.steps,
                    'GBps_in_per_rank_if_serial': round(halo_bytes / (ms * 1e-3) / 1e9, 1), 'peak_GBps': 770.0,
                    'prefetched_gathers_per_step': getattr(halo, 'n_prefetched', 0) // args.steps,

@@ -71,7 +71,7 @@ class LaplacianODEFunc(ODEFunc):
     # ---- two-phase evaluation + VJP for the row-partitioned adjoint solve (see ODEFuncTransformerAtt.phased_ok) ---
     def phased_ok(self, x):
         import os
-        if self.partition is None or os.environ.get('GRANDB200_OVERLAP') != '1' or self.opt['block'] != 'constant':
+        if self.partition is None or os.environ.get('GRANDB200_OVERLAP', '1') != '1' or self.opt['block'] != 'constant':
             return False
         return self._as_2d(x).shape[0] == self.partition[0].slab
 

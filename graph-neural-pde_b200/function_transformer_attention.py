@@ -282,10 +282,10 @@ class ODEFuncTransformerAtt(ODEFunc):
     # run while the column pass, the dense tail and the reduce-scatter of this evaluation are still at work
     # (DESIGN.md "Multi-GPU").  integrators._adjoint_fixed_phased drives this protocol when phased_ok() says so.
     def phased_ok(self, x):
-        """two-phase protocol available?  Row-partitioned, single-gather kernels, and switched on: the overlap has
-        not run on hardware yet, so it is opt-in (GRANDB200_OVERLAP=1)"""
+        """two-phase protocol available?  Row-partitioned, single-gather kernels, and not switched off: the overlap is
+        verified over NCCL (profiles/r02_partition_nccl_n2.log) and on by default (GRANDB200_OVERLAP=0 turns it off)"""
         import os
-        if self.partition is None or os.environ.get('GRANDB200_OVERLAP') != '1' or self.opt.get('mix_features', False):
+        if self.partition is None or os.environ.get('GRANDB200_OVERLAP', '1') != '1' or self.opt.get('mix_features', False):
             return False
         part, _halo = self.partition
         L = self.multihead_att_layer
