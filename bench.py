@@ -98,7 +98,7 @@ def gather_bytes(n, e, d, a, h, kgather=False):
 
 def measured_traffic(workload, kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` on `workload`, from the committed
-    `ncu --set full` summary (profiles/traffic.json, written by hand from the .ncu-rep); None if not captured"""
+    `ncu --set full` summaries (profiles/traffic.json, generated by scripts/make_traffic.py); None if not captured"""
     path = os.path.join(ROOT, 'profiles', 'traffic.json')
     try:
         with open(path) as fh:
@@ -390,7 +390,8 @@ def run_ours(args):
     achieved = alg.get(kname, 0) / (per_launch_ms * 1e-3) / 1e9 if per_launch_ms > 0 else 0.0
     ksum = sum(v['ms'] for v in main_kernels(kernels).values())
     roofline = {'bound': 'hbm', 'kernel': kname, 'achieved': round(achieved, 1), 'peak': peak, 'unit': 'GB/s',
-                'frac': round(achieved / peak, 4), 'traffic': measured_traffic(name, kname), 'peak_source': peak_src,
+                'frac': round(achieved / peak, 4), 'peak_source': peak_src,
+                'traffic': measured_traffic(name, kname + ('@single-gather' if kname in ('nl_fwd', 'nl_adj_rows') and not kgather else '')),
                 'algorithmic_bytes_per_launch': alg.get(kname, 0), 'avg_launch_ms': round(per_launch_ms, 4),
                 'share_of_kernel_time': round(kstat['ms'] / ksum, 4) if ksum else None,
                 'kernels': {k: {'ms_per_launch': round(v['ms'] / v['launches'], 4), 'launches': v['launches'],

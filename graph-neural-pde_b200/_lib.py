@@ -179,3 +179,24 @@ class Profiler:
                 out[lib.gb_prof_name(i).decode()] = {'ms': ms.value, 'launches': cnt.value,
                                                      'overlapped': int(lib.gb_prof_overlapped(i))}
         return out
+
+
+class nvtx_range:
+    """NVTX range around a phase of the solve (forward integration, adjoint solve, halo exchanges) when
+    GRANDB200_NVTX=1; a no-op otherwise (no nsys on the build box: the ranges are for timelines taken elsewhere)."""
+    _on = os.environ.get('GRANDB200_NVTX') == '1'
+
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        if self._on:
+            import torch
+            torch.cuda.nvtx.range_push(self.name)
+        return self
+
+    def __exit__(self, *exc):
+        if self._on:
+            import torch
+            torch.cuda.nvtx.range_pop()
+

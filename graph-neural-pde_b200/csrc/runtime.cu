@@ -4,6 +4,7 @@
 #include <atomic>
 #include <mutex>
 #include <vector>
+#include <nvtx3/nvToolsExt.h>
 #include "common.cuh"
 
 namespace gb {
@@ -144,8 +145,18 @@ int side_join(cudaStream_t main, cudaStream_t side) {
   return GB_OK;
 }
 
+// GRANDB200_NVTX=1: every launch sits in an NVTX range named after its kernel id (nsys / ncu --nvtx timelines)
+static bool nvtx_on() {
+  static const bool on = [] {
+    const char* e = getenv("GRANDB200_NVTX");
+    return e != nullptr && e[0] == '1';
+  }();
+  return on;
+}
+
 LaunchScope::LaunchScope(int kernel_id, cudaStream_t s) : id(kernel_id), stream(s), rec(nullptr) {
   g_launches.fetch_add(1, std::memory_order_relaxed);
+  if (nvtx_on()) nvtxRangePushA(kernel_id >= 0 && kernel_id < K_NUM_KERNELS ? kNames[kernel_id] : "gb_kernel");
   if (!g_prof_on.load(std::memory_order_relaxed)) return;
   EventRec* r = nullptr;
   {
@@ -169,6 +180,7 @@ LaunchScope::LaunchScope(int kernel_id, cudaStream_t s) : id(kernel_id), stream(
 }
 
 LaunchScope::~LaunchScope() {
+  if (nvtx_on()) nvtxRangePop();
   if (!rec) return;
   EventRec* r = static_cast<EventRec*>(rec);
   cudaEventRecord(r->stop, stream);

@@ -323,8 +323,15 @@ def _solve_adaptive(prob, method, rtol, atol, max_num_steps=2 ** 31 - 1, on_step
     return sols
 
 
-def odeint(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, event_fn=None, _comp_signs=None,
-           _on_step=None, _max_attempts=None, _passive=(), _dead=()):
+def odeint(func, y0, t, **kwargs):
+    """torchdiffeq.odeint(func, y0, t, rtol=, atol=, method=, options=) - see _odeint_impl"""
+    from . import _lib
+    with _lib.nvtx_range('grand_b200.odeint' if '_comp_signs' not in kwargs else 'grand_b200.adjoint_solve'):
+        return _odeint_impl(func, y0, t, **kwargs)
+
+
+def _odeint_impl(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, event_fn=None, _comp_signs=None,
+                 _on_step=None, _max_attempts=None, _passive=(), _dead=()):
     if event_fn is not None:
         raise NotImplementedError('event handling is not part of the reference call sites')
     method = method or 'dopri5'

@@ -22,6 +22,19 @@ import torch
 from . import _lib
 
 
+def _nvtx(name):
+    """NVTX range around a halo exchange (GRANDB200_NVTX=1)"""
+    def deco(fn):
+        import functools
+
+        @functools.wraps(fn)
+        def wrapped(*a, **k):
+            with _lib.nvtx_range(name):
+                return fn(*a, **k)
+        return wrapped
+    return deco
+
+
 class RowPartition:
     """contiguous equal-height row slabs of an n-node graph over `world` ranks"""
 
@@ -73,6 +86,7 @@ class Halo:
     def prepare(self, plan):
         """hook for halos that need the graph (SparseHalo); the dense exchange needs nothing"""
 
+    @_nvtx('halo.all_gather')
     def all_gather_rows(self, slab, keep=False):
         """[S, d] slab of every rank -> [N_pad, d] on every rank.  keep=True: the caller will hold on to the result
         (saved for a backward pass) - halos that recycle their gather buffers hand out a private one then."""
@@ -95,6 +109,7 @@ class Halo:
         self.n_prefetched = getattr(self, 'n_prefetched', 0) + 1
         return PendingGather(slab, slab_c, full, work)
 
+    @_nvtx('halo.reduce_scatter')
     def reduce_scatter_rows(self, full):
         """sum over ranks of [N_pad, d], rank p keeps rows [p*S, (p+1)*S)"""
         full = full.contiguous()
@@ -217,6 +232,7 @@ class SparseHalo(Halo):
         self.n_gathers += 1
         return slab, send, recv, work
 
+    @_nvtx('halo.all_gather')
     def all_gather_rows(self, slab, keep=False):
         slab, _send, recv, _ = self._start_gather(slab, False)
         return self._finish_gather(slab, recv, keep)
@@ -247,6 +263,7 @@ class SparseHalo(Halo):
         self.n_scatters += 1
         return full, send, recv, work
 
+    @_nvtx('halo.reduce_scatter')
     def reduce_scatter_rows(self, full):
         full, _send, recv, _ = self._start_scatter(full, False)
         return self._finish_scatter(full, recv)
@@ -401,6 +418,7 @@ class PushHalo(Halo):
         ring[1] += 1
         return entry
 
+    @_nvtx('halo.all_gather')
     def all_gather_rows(self, slab, keep=False):
         import ctypes as C
         slab = slab.contiguous()
@@ -451,6 +469,7 @@ class PushHalo(Halo):
         self.__dict__.setdefault('_shares', {})[id(entry[0])] = entry
         return entry[0]
 
+    @_nvtx('halo.reduce_scatter')
     def reduce_scatter_rows(self, full):
         import ctypes as C
         entry = self.__dict__.get('_shares', {}).get(id(full))
@@ -547,6 +566,7 @@ class LoopbackHalo:
     def prepare(self, plan):
         pass
 
+    @_nvtx('halo.all_gather')
     def all_gather_rows(self, slab, keep=False):
         return slab.contiguous()
 
@@ -554,6 +574,7 @@ class LoopbackHalo:
         c = slab.contiguous()
         return PendingGather(slab, c, c, None)
 
+    @_nvtx('halo.reduce_scatter')
     def reduce_scatter_rows(self, full):
         return full.contiguous()
 
