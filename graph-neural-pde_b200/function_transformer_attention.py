@@ -20,7 +20,7 @@ from torch import nn
 from .base_classes import ODEFunc
 from . import _lib
 from . import plan as _plan
-from .ops import (QKProjFn, EdgeSoftmaxFn, DiffusionFn, ToCooOrderFn, FusedTransformerFn, fused_transformer_supported,
+from .ops import (QKProjFn, EdgeSoftmaxFn, EdgeScoreFn, squareplus_csr, DiffusionFn, ToCooOrderFn, FusedTransformerFn, fused_transformer_supported,
                   NlTransformerFn, nl_supported, nl_eval_vjp)
 
 
@@ -96,10 +96,15 @@ class SpGraphTransAttentionLayer(nn.Module):
         att_type = self.opt.get('attention_type', 'scaled_dot')
         if att_type not in _lib.GB_ATT:
             raise NotImplementedError(f"attention_type '{att_type}'")
-        if self.opt.get('square_plus', False):
-            raise NotImplementedError("opt['square_plus']: the fork's call site is broken (2 args to a 3-arg "
-                                      'function, function_transformer_attention.py:264); softmax only')
         return _lib.GB_ATT[att_type]
+
+    @property
+    def square_plus(self):
+        """opt['square_plus']: utils.squareplus instead of the segment softmax (utils.py:129-140).  The fork's call
+        site (function_transformer_attention.py:264) passes two arguments to that three-argument function and
+        cannot run; the function itself is well defined (pinned by tests/golden/ref_squareplus.npz) and is applied
+        with the group ids the softmax would use."""
+        return bool(self.opt.get('square_plus', False))
 
     @property
     def _UNIT_TYPES(self):
@@ -109,7 +114,7 @@ class SpGraphTransAttentionLayer(nn.Module):
         """evaluations of the other attention types that will be differentiated run as projection -> edge softmax
         -> SpMM (the fused forward kernels have no VJP for them): cosine_sim / pearson as scaled_dot of unit_heads,
         exp_kernel through ops.exp_kernel_score_vjp"""
-        if self.beltrami_kernel:
+        if self.beltrami_kernel or self.square_plus:
             return True                                    # always the composite route (two projections, one kernel)
         if att_type == _lib.GB_ATT['scaled_dot'] or not torch.is_grad_enabled():
             return False
@@ -164,6 +169,8 @@ class SpGraphTransAttentionLayer(nn.Module):
             edge_w = _plan.cached_per_edge(plan, self.edge_weights, 'rw', lambda t: plan.to_csr_order(t.detach()))
         if self.beltrami_kernel:
             qk, kparams = self._beltrami_qk(x2)
+            if self.square_plus:
+                return self._squareplus(qk, plan, att_type, edge_w, kparams)
             return EdgeSoftmaxFn.apply(qk, plan, self.h, att_type, int(self.opt['attention_norm_idx']), edge_w, kparams)
         qk = QKProjFn.apply(x2, self.Q.weight, self.Q.bias, self.K.weight, self.K.bias)
         kparams = None
@@ -173,7 +180,15 @@ class SpGraphTransAttentionLayer(nn.Module):
             # training: the VJP kernels implement scaled_dot; cosine_sim / pearson are scaled_dot of unit vectors
             qk = unit_heads(qk, self.h, centre=att_type == _lib.GB_ATT['pearson'])
             att_type = _lib.GB_ATT['scaled_dot']
+        if self.square_plus:
+            return self._squareplus(qk, plan, att_type, edge_w, kparams)
         return EdgeSoftmaxFn.apply(qk, plan, self.h, att_type, int(self.opt['attention_norm_idx']), edge_w, kparams)
+
+    def _squareplus(self, qk, plan, att_type, edge_w, kparams):
+        """scores from the edge kernel (EdgeScoreFn, differentiable), squareplus normalisation as [E,H] torch glue"""
+        prods = EdgeScoreFn.apply(qk, plan, self.h, att_type, edge_w, kparams)
+        att, abar = squareplus_csr(prods, plan, int(self.opt['attention_norm_idx']))
+        return att, abar, prods.detach()
 
     def forward(self, x, edge, y=None):
         """returns (attention [B,E,H] in the caller's edge order, (v, prods)); v is None because the
@@ -218,7 +233,7 @@ class ODEFuncTransformerAtt(ODEFunc):
         L = self.multihead_att_layer
         att_type = L._check_supported()
         edge_w = L.edge_weights if self.opt.get('reweight_attention', False) else None
-        if nl_supported(plan, x2, L.h, L.attention_dim, att_type, int(self.opt['attention_norm_idx']), edge_w):
+        if (not L.square_plus and nl_supported(plan, x2, L.h, L.attention_dim, att_type, int(self.opt['attention_norm_idx']), edge_w)):
             f = NlTransformerFn.apply(x2, L.Q.weight, L.Q.bias, L.K.weight, L.K.bias, self.alpha_train,
                                       self.beta_train if x0 is not None else None, x0, plan, L.h,
                                       not self.opt['no_alpha_sigmoid'], self._take_stage())
@@ -247,7 +262,7 @@ class ODEFuncTransformerAtt(ODEFunc):
         if x2.shape[0] != part.slab:
             raise ValueError(f'partitioned state must be the [{part.slab}, d] slab of this rank, got {tuple(x2.shape)}')
         plan = self._plan(part.n_pad)
-        if not nl_supported(plan, x2, L.h, L.attention_dim, att_type, int(self.opt['attention_norm_idx']), edge_w):
+        if not (not L.square_plus and nl_supported(plan, x2, L.h, L.attention_dim, att_type, int(self.opt['attention_norm_idx']), edge_w)):
             raise NotImplementedError('the row-partitioned path supports scaled_dot attention with attention_norm_idx 0, '
                                       'heads in {1,2,4,8}, d <= 128 (single-gather kernels)')
         source = bool(self.opt['add_source'])
@@ -292,7 +307,7 @@ class ODEFuncTransformerAtt(ODEFunc):
         x2 = self._as_2d(x)
         edge_w = L.edge_weights if self.opt.get('reweight_attention', False) else None
         plan = self._plan(part.n_pad)
-        return x2.shape[0] == part.slab and nl_supported(plan, x2, L.h, L.attention_dim, L._check_supported(),
+        return x2.shape[0] == part.slab and not L.square_plus and nl_supported(plan, x2, L.h, L.attention_dim, L._check_supported(),
                                                          int(self.opt['attention_norm_idx']), edge_w)
 
     def prefetch_state(self, x):
@@ -366,7 +381,7 @@ class ODEFuncTransformerAtt(ODEFunc):
         L = self.multihead_att_layer
         att_type = L._check_supported()
         edge_w = L.edge_weights if self.opt.get('reweight_attention', False) else None
-        if not nl_supported(plan, x2, L.h, L.attention_dim, att_type, int(self.opt['attention_norm_idx']), edge_w):
+        if not (not L.square_plus and nl_supported(plan, x2, L.h, L.attention_dim, att_type, int(self.opt['attention_norm_idx']), edge_w)):
             return None
         self._check_nfe()
         source = bool(self.opt['add_source'])

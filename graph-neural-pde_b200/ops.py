@@ -68,8 +68,12 @@ class QKProjFn(torch.autograd.Function):
 def _segment_sums(vals, ptr):
     """[E,H] values laid out segment after segment, ptr [n+1] -> [n,H] sums.  Prefix sums in fp64 (deterministic on
     every backend; a difference of two prefixes loses ~1e-16 * E relative to the running total)"""
-    cs = torch.zeros(vals.shape[0] + 1, vals.shape[1], dtype=torch.float64, device=vals.device)
-    torch.cumsum(vals.double(), dim=0, out=cs[1:])
+    if vals.requires_grad:                       # autograd path (opt['square_plus']): no out= argument
+        cs = torch.cat([torch.zeros(1, vals.shape[1], dtype=torch.float64, device=vals.device),
+                        torch.cumsum(vals.double(), dim=0)], dim=0)
+    else:
+        cs = torch.zeros(vals.shape[0] + 1, vals.shape[1], dtype=torch.float64, device=vals.device)
+        torch.cumsum(vals.double(), dim=0, out=cs[1:])
     ptr = ptr.long()
     return (cs[ptr[1:]] - cs[ptr[:-1]]).to(vals.dtype)
 
@@ -100,6 +104,91 @@ def exp_kernel_score_vjp(ds, prods, q, k, kparams, rowptr, colptr, tperm, heads,
     d_ov = w.double().sum() * 2.0 / ov.double()
     d_ls = (w.double() * (-2.0 * logt.double())).sum() / ls.double()
     return dq.reshape(n, a), dkk.reshape(n, a), torch.stack([d_ov, d_ls]).to(ds.dtype)
+
+
+def _score_vjp(plan, qk, heads, dk, att_type, ds, prods, kparams, edge_w, want_kparams):
+    """VJP of the per-edge scores w.r.t. [q | k] (and the exp_kernel parameters) given ds = dL/d(raw score) [E,H] in
+    CSR-slot order.  `prods` are the scores as the forward kernel stored them, i.e. AFTER the optional
+    reweight_attention factor `edge_w`; the exp_kernel VJP needs the raw ones (prods / edge_w)."""
+    lib = _lib.load()
+    n, a2 = qk.shape
+    a = a2 // 2
+    if att_type not in (_lib.GB_ATT['scaled_dot'], _lib.GB_ATT['exp_kernel']):
+        raise NotImplementedError('cosine_sim / pearson are differentiated as scaled_dot of unit vectors '
+                                  '(function_transformer_attention.unit_heads); call through the layer')
+    dqk = torch.empty_like(qk)
+
+    def mh(c, scale=1.0):
+        """sum_{e in row i} c_eh k[col_e,h] -> dqk[:, :A], sum_{e in col j} c_eh q[row_e,h] -> dqk[:, A:]; the
+        kernels multiply by 1/sqrt(dk) (scaled_dot VJP), `scale` undoes it where the caller needs plain sums"""
+        c = _f32c(c * scale if scale != 1.0 else c)
+        _lib.check(lib.gb_edge_score_bwd(plan.c, c.data_ptr(), qk.data_ptr(), a2, qk.data_ptr() + 4 * a, a2, heads,
+                                         dk, _lib.GB_ATT['scaled_dot'], None, None, dqk.data_ptr(), a2,
+                                         dqk.data_ptr() + 4 * a, a2, None, None, _lib.stream()),
+                   'gb_edge_score_bwd')
+        return dqk[:, :a], dqk[:, a:]
+
+    if att_type == _lib.GB_ATT['scaled_dot']:
+        mh(ds)
+        return dqk, None
+    raw = prods
+    if edge_w is not None:                       # s_raw = prods / w; w == 0 -> ds == 0 there, any finite value does
+        w = edge_w.reshape(-1, 1)
+        raw = torch.where(w != 0, prods / torch.where(w != 0, w, torch.ones_like(w)), torch.zeros_like(prods))
+    dq, dkk, dkparams = exp_kernel_score_vjp(ds, raw, qk[:, :a], qk[:, a:], kparams, plan.rowptr, plan.colptr,
+                                             plan.tperm, heads, lambda c: mh(c, float(dk) ** 0.5))
+    return torch.cat([dq, dkk], dim=1), (dkparams if want_kparams else None)
+
+
+class EdgeScoreFn(torch.autograd.Function):
+    """qk [N,2A] -> prods [E,H] (CSR-slot order): the per-edge scores alone, differentiable - for normalisations
+    other than the fused segment softmax (opt['square_plus'], utils.squareplus)."""
+
+    @staticmethod
+    def forward(ctx, qk, plan, heads, att_type, edge_w, kparams):
+        lib = _lib.load()
+        _lib.require_cuda(qk)
+        qk = _f32c(qk)
+        n, a2 = qk.shape
+        a = a2 // 2
+        dk = a // heads
+        f32 = dict(dtype=torch.float32, device=qk.device)
+        att, abar, prods = torch.empty(plan.e, heads, **f32), torch.empty(plan.e, **f32), torch.empty(plan.e, heads, **f32)
+        _lib.check(lib.gb_edge_softmax_fwd(plan.c, 0, qk.data_ptr(), a2, qk.data_ptr() + 4 * a, a2, heads, dk, att_type,
+                                           _lib.ptr(edge_w), _lib.ptr(kparams), att.data_ptr(), abar.data_ptr(),
+                                           prods.data_ptr(), _lib.stream()), 'gb_edge_softmax_fwd')
+        exp_kernel = att_type == _lib.GB_ATT['exp_kernel']
+        ctx.save_for_backward(qk, prods if exp_kernel else None, kparams if exp_kernel else None)
+        ctx.plan, ctx.heads, ctx.dk, ctx.att_type, ctx.edge_w = plan, heads, dk, att_type, edge_w
+        return prods
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dprods):
+        qk, prods, kparams = ctx.saved_tensors
+        ds = _f32c(dprods)
+        if ctx.edge_w is not None:
+            ds = ds * ctx.edge_w.reshape(-1, 1)
+        dqk, dkparams = _score_vjp(ctx.plan, qk, ctx.heads, ctx.dk, ctx.att_type, ds, prods, kparams, ctx.edge_w,
+                                   ctx.needs_input_grad[5])
+        return dqk, None, None, None, None, dkparams
+
+
+def squareplus_csr(prods, plan, norm_idx):
+    """utils.squareplus (utils.py:129-140; upstream semantics - the fork's call site at
+    function_transformer_attention.py:264 passes two arguments to this three-argument function):
+    out = s - max(s over ALL edges and heads); sp = (out + sqrt(out^2 + 4)) / 2; attention = sp / (group sum + 1e-16),
+    groups = rows (norm_idx 0) or columns (1) per head.  prods in CSR-slot order -> (att [E,H], abar [E]).
+    [E,H]-sized torch glue (autograd-friendly; group sums are fp64 prefix sums: deterministic)."""
+    out = prods - prods.amax()                   # differentiated through, as the src.amax of utils.py:132 is
+    sp = (out + torch.sqrt(out * out + 4.0)) * 0.5
+    counts = (plan.rowptr[1:] - plan.rowptr[:-1]).long()
+    if norm_idx == 0:
+        den = torch.repeat_interleave(_segment_sums(sp, plan.rowptr), counts, dim=0)
+    else:
+        den = _segment_sums(sp[plan.tperm.long()], plan.colptr)[plan.colidx.long()]
+    att = sp / (den + 1e-16)
+    return att, att.mean(dim=1)
 
 
 class EdgeSoftmaxFn(torch.autograd.Function):
@@ -144,35 +233,14 @@ class EdgeSoftmaxFn(torch.autograd.Function):
         a = a2 // 2
         if datt is None and dabar is None:
             return (None,) * 7
-        if ctx.att_type not in (_lib.GB_ATT['scaled_dot'], _lib.GB_ATT['exp_kernel']):
-            raise NotImplementedError('cosine_sim / pearson are differentiated as scaled_dot of unit vectors '
-                                      '(function_transformer_attention.unit_heads); call through the layer')
-        if ctx.att_type == _lib.GB_ATT['exp_kernel'] and ctx.edge_w is not None:
-            raise NotImplementedError('backward of exp_kernel with reweight_attention is not implemented')
         datt = None if datt is None else _f32c(datt)
         dabar = None if dabar is None else _f32c(dabar)
         ds = torch.empty(plan.e, heads, dtype=torch.float32, device=qk.device)
         _lib.check(lib.gb_edge_softmax_bwd(plan.c, ctx.norm_idx, att.data_ptr(), _lib.ptr(dabar), _lib.ptr(datt), heads,
                                            _lib.ptr(ctx.edge_w), ds.data_ptr(), _lib.stream()), 'gb_edge_softmax_bwd')
-        dqk = torch.empty_like(qk)
-
-        def mh(c, scale=1.0):
-            """sum_{e in row i} c_eh k[col_e,h] -> dqk[:, :A], sum_{e in col j} c_eh q[row_e,h] -> dqk[:, A:]; the
-            kernels multiply by 1/sqrt(dk) (scaled_dot VJP), `scale` undoes it where the caller needs plain sums"""
-            c = _f32c(c * scale if scale != 1.0 else c)
-            _lib.check(lib.gb_edge_score_bwd(plan.c, c.data_ptr(), qk.data_ptr(), a2, qk.data_ptr() + 4 * a, a2, heads,
-                                             dk, _lib.GB_ATT['scaled_dot'], None, None, dqk.data_ptr(), a2,
-                                             dqk.data_ptr() + 4 * a, a2, None, None, _lib.stream()),
-                       'gb_edge_score_bwd')
-            return dqk[:, :a], dqk[:, a:]
-
-        if ctx.att_type == _lib.GB_ATT['scaled_dot']:
-            mh(ds)
-            return dqk, None, None, None, None, None, None
-        dq, dkk, dkparams = exp_kernel_score_vjp(ds, prods, qk[:, :a], qk[:, a:], kparams, plan.rowptr, plan.colptr,
-                                                 plan.tperm, heads, lambda c: mh(c, float(dk) ** 0.5))
-        return (torch.cat([dq, dkk], dim=1), None, None, None, None, None,
-                dkparams if ctx.needs_input_grad[6] else None)
+        dqk, dkparams = _score_vjp(plan, qk, heads, dk, ctx.att_type, ds, prods, kparams, ctx.edge_w,
+                                   ctx.needs_input_grad[6])
+        return dqk, None, None, None, None, None, dkparams
 
 
 class GatSoftmaxFn(torch.autograd.Function):

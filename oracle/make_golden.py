@@ -13,6 +13,7 @@ batched layout with B=1 ([1,N,d], [1,2,E], [1,E], [1,E,H]) and are stored un-bat
 
 The fixtures pin `oracle/funcs.py` (and through it the CUDA path) to the reference:
   ref_softmax.npz            utils.softmax                               (utils.py:116-127)
+  ref_squareplus.npz         utils.squareplus                            (utils.py:129-140)
   ref_laplacian_*.npz        LaplacianODEFunc.forward + autograd grads   (function_laplacian_diffusion.py:39-77)
   ref_transformer_*.npz      ODEFuncTransformerAtt.forward + grads for cosine_sim / pearson /
                              exp_kernel (per-edge in the fork) and scaled_dot (fork-literal E x E sum)
@@ -78,6 +79,17 @@ def gen_softmax(ref_utils):
     index = torch.randint(0, n, (1, e), generator=g)
     out = ref_utils.softmax(src, index, n)
     np.savez(os.path.join(GOLD, 'ref_softmax.npz'), src=np_(src[0]), index=np_(index[0]), n=n, out=np_(out[0]))
+
+
+def gen_squareplus(ref_utils):
+    """utils.squareplus itself (utils.py:129-140) on the fork's batched layout; its only call site
+    (function_transformer_attention.py:264) passes two arguments and cannot run, the function can"""
+    g = torch.Generator().manual_seed(12)
+    n, e, h = 9, 40, 3
+    src = torch.randn(1, e, h, generator=g) * 3
+    index = torch.randint(0, n, (1, e), generator=g)
+    out = ref_utils.squareplus(src, index, n)
+    np.savez(os.path.join(GOLD, 'ref_squareplus.npz'), src=np_(src[0]), index=np_(index[0]), n=n, out=np_(out[0]))
 
 
 def gen_laplacian(ref_lap):
@@ -201,6 +213,7 @@ def main():
         return
     gen_gat()
     gen_softmax(ref_utils)
+    gen_squareplus(ref_utils)
     gen_laplacian(ref_lap)
     gen_transformer(ref_att)
     gen_k3(ref_att)

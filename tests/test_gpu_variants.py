@@ -177,6 +177,64 @@ def test_exp_kernel_gradients_match_the_reference(path):
         assert_close(g.reshape(-1), np.asarray(z[key]).reshape(-1), G_RTOL, key)
 
 
+@pytest.mark.parametrize('att_type,norm_idx,reweight', [('scaled_dot', 0, False), ('scaled_dot', 1, True),
+                                                         ('exp_kernel', 0, True), ('cosine_sim', 1, False)])
+def test_square_plus_and_reweighted_exp_kernel_train(att_type, norm_idx, reweight):
+    """opt['square_plus'] (utils.squareplus instead of the segment softmax) and the exp_kernel backward under
+    reweight_attention: f and every gradient against the fp64 oracle on a graph with hub segments"""
+    import grand_b200
+    from helpers import rand_graph
+    n, d, heads, adim = 500, 32, 4, 32
+    ei = rand_graph(n, 4000, 31, hub=(9, 600))
+    rng = np.random.default_rng(6)
+    x, x0, gout = (0.5 * rng.standard_normal((n, d)).astype(np.float32) for _ in range(3))
+    ew = (0.5 + rng.random(ei.shape[1])).astype(np.float32)
+    z = dict(wq=rng.standard_normal((adim, d)).astype(np.float32) / np.sqrt(d), bq=0.1 * rng.standard_normal(adim).astype(np.float32),
+             wk=rng.standard_normal((adim, d)).astype(np.float32) / np.sqrt(d), bk=0.1 * rng.standard_normal(adim).astype(np.float32),
+             alpha_train=0.3, beta_train=0.1)
+    t64 = lambda a: torch.tensor(np.asarray(a), dtype=torch.float64)
+    for square_plus in (True, False):
+        if not square_plus and not (att_type == 'exp_kernel' and reweight):
+            continue                                               # the plain softmax cases are covered elsewhere
+        opt = dict(BASE_OPT, attention_type=att_type, attention_norm_idx=norm_idx, hidden_dim=d, heads=heads,
+                   attention_dim=adim, square_plus=square_plus, reweight_attention=reweight)
+        import grand_b200
+        func = grand_b200.ODEFuncTransformerAtt(d, d, opt, device()).to(device())
+        L = func.multihead_att_layer
+        L.edge_weights = dev(ew) if reweight else None            # per edge, in the caller's edge order
+        with torch.no_grad():
+            for lin, w, b in ((L.Q, 'wq', 'bq'), (L.K, 'wk', 'bk')):
+                lin.weight.copy_(dev(z[w]))
+                lin.bias.copy_(dev(z[b]))
+            func.alpha_train.fill_(0.3)
+            func.beta_train.fill_(0.1)
+            if att_type == 'exp_kernel':
+                L.output_var.fill_(1.2)
+                L.lengthscale.fill_(1.5)
+        func.edge_index, func.x0 = dev(ei), dev(x0)
+        xg = dev(x).requires_grad_(True)
+        params = [xg, L.Q.weight, L.Q.bias, L.K.weight, L.K.bias] + ([L.output_var, L.lengthscale] if att_type == 'exp_kernel' else [])
+        out = func(0.0, xg)
+        grads = torch.autograd.grad(out, params, dev(gout))
+        leaves = [t64(v).requires_grad_(True) for v in (x, z['wq'], z['bq'], z['wk'], z['bk'])]
+        kw = dict(attention_type=att_type, attention_norm_idx=norm_idx, square_plus=square_plus,
+                  edge_weight=t64(ew) if reweight else None, reweight_attention=reweight)
+        extra = []
+        if att_type == 'exp_kernel':
+            extra = [t64(1.2).requires_grad_(True), t64(1.5).requires_grad_(True)]
+            kw.update(output_var=extra[0], lengthscale=extra[1])
+        ref = funcs.transformer_f(leaves[0], torch.tensor(ei), leaves[1], leaves[2], leaves[3], leaves[4], heads,
+                                  t64(0.3), t64(0.1), t64(x0), **kw)
+        rg = torch.autograd.grad(ref, leaves + extra, t64(gout))
+        tag = f'{att_type} norm{norm_idx} sq{int(square_plus)}'
+        assert_close(out, ref, F_RTOL, 'f ' + tag)
+        scale = max(float(r.abs().max()) for r in rg[1:5])
+        for g, r, name in zip(grads, rg, ('gx', 'gwq', 'gbq', 'gwk', 'gbk', 'gov', 'gls')):
+            assert_close(g.reshape(-1), r.reshape(-1), G_RTOL, f'{name} {tag}', floor=scale if name in ('gbq', 'gbk') else 0.0)
+        with torch.no_grad():
+            assert_close(func(0.0, dev(x)), ref, F_RTOL, 'f (no grad) ' + tag)
+
+
 def test_exp_kernel_gradients_on_a_graph_with_hub_segments():
     import grand_b200
     from helpers import rand_graph

@@ -336,6 +336,12 @@ def test_utils_softmax(variants):
 
 
 
+@pytest.mark.parametrize('att_type,norm_idx,reweight', [('scaled_dot', 0, False), ('scaled_dot', 1, True),
+                                                         ('exp_kernel', 0, True), ('cosine_sim', 1, False)])
+def test_square_plus_and_reweighted_exp_kernel(variants, att_type, norm_idx, reweight):
+    zz.test_square_plus_and_reweighted_exp_kernel_train(att_type, norm_idx, reweight)
+
+
 def test_mixed_block(variants):
     zz.test_mixed_block_state_and_gradients_incl_the_gate()
 

@@ -21,6 +21,17 @@ def test_softmax_matches_reference_bitwise():
     assert torch.equal(out, T(z['out']))                      # same op order in fp32 -> same bits
 
 
+def test_squareplus_matches_the_reference_function():
+    """utils.squareplus (utils.py:129-140), run by the reference itself on its batched layout; its call site in the
+    attention layer is broken in the fork, the function is what opt['square_plus'] means"""
+    z = np.load(os.path.join(GOLD, 'ref_squareplus.npz'))
+    out = funcs.squareplus(T(z['src']), torch.tensor(z['index']), int(z['n']))
+    assert torch.allclose(out, T(z['out']), rtol=1e-6, atol=1e-7)
+    sums = torch.zeros(int(z['n']), out.shape[1]).index_add_(0, torch.tensor(z['index']), out)
+    present = torch.zeros(int(z['n'])).index_add_(0, torch.tensor(z['index']), torch.ones(out.shape[0])) > 0
+    assert torch.allclose(sums[present], torch.ones_like(sums[present]), atol=1e-5) and bool((out > 0).all())
+
+
 @pytest.mark.parametrize('path', sorted(glob.glob(os.path.join(GOLD, 'ref_laplacian_*.npz'))))
 def test_laplacian_f_and_grads(path):
     z = np.load(path)
