@@ -15,7 +15,7 @@ Differences, all deliberate:
 import torch
 from torch import nn
 
-from . import plan as _plan
+from . import ops, plan as _plan
 from .utils import get_rw_adj, gcn_norm_fill_val, add_remaining_self_loops, Meter
 
 
@@ -318,7 +318,8 @@ class BaseGNN(nn.Module):
     """base_classes.py:137-186 - encoder / decoder around the ODE block: `m1` (or `mx` + `mp` with opt['beltrami']),
     optional `m11` / `m12` MLP, `fc`, batch norms and the decoder `m2`.  Same parameter names and the same in-place
     edits of `opt['hidden_dim']` (beltrami, use_labels) as the reference, so its checkpoints load.  These are dense
-    [N, F] x [F, d] layers executed once per step: torch.nn.Linear (library GEMMs), outside the per-evaluation path."""
+    [N, F] x [F, d] layers executed once per step: `ops.Linear` (nn.Linear's parameters, the library's own GEMM kernels -
+    K-sliced tcgen05 3xTF32 for the encoder, exact-fp32 tiles for the decoder)"""
 
     def __init__(self, opt, num_classes, num_features, device=torch.device('cpu')):
         super(BaseGNN, self).__init__()
@@ -331,20 +332,20 @@ class BaseGNN(nn.Module):
         self.fm = Meter()
         self.bm = Meter()
         if opt.get('beltrami', False):
-            self.mx = nn.Linear(self.num_features, opt['feat_hidden_dim'])
-            self.mp = nn.Linear(opt['pos_enc_dim'], opt['pos_enc_hidden_dim'])
+            self.mx = ops.Linear(self.num_features, opt['feat_hidden_dim'])
+            self.mp = ops.Linear(opt['pos_enc_dim'], opt['pos_enc_hidden_dim'])
             opt['hidden_dim'] = opt['feat_hidden_dim'] + opt['pos_enc_hidden_dim']
         else:
-            self.m1 = nn.Linear(self.num_features, opt['hidden_dim'])
+            self.m1 = ops.Linear(self.num_features, opt['hidden_dim'])
         if opt.get('use_mlp', False):
-            self.m11 = nn.Linear(opt['hidden_dim'], opt['hidden_dim'])
-            self.m12 = nn.Linear(opt['hidden_dim'], opt['hidden_dim'])
+            self.m11 = ops.Linear(opt['hidden_dim'], opt['hidden_dim'])
+            self.m12 = ops.Linear(opt['hidden_dim'], opt['hidden_dim'])
         if opt.get('use_labels', False):
             opt['hidden_dim'] = opt['hidden_dim'] + num_classes
         self.hidden_dim = opt['hidden_dim']
         if opt.get('fc_out', False):
-            self.fc = nn.Linear(opt['hidden_dim'], opt['hidden_dim'])
-        self.m2 = nn.Linear(opt['hidden_dim'], num_classes)
+            self.fc = ops.Linear(opt['hidden_dim'], opt['hidden_dim'])
+        self.m2 = ops.Linear(opt['hidden_dim'], num_classes)
         if opt.get('batch_norm', False):
             self.bn_in = torch.nn.BatchNorm1d(opt['hidden_dim'])
             self.bn_out = torch.nn.BatchNorm1d(opt['hidden_dim'])

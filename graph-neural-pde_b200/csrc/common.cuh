@@ -59,6 +59,7 @@ enum KernelId {
   K_NL_ADJ_ROWS,
   K_NL_ADJ_LONG,
   K_GAT_SOFTMAX,
+  K_DECODE_EVAL,
   K_NUM_KERNELS
 };
 

@@ -154,8 +154,11 @@ static int choose_splits(int n, int nout, int d) {
 namespace gb {
 struct TcArgs {
   const float* a; int64_t lda; const float* w; int64_t ldw; const float* bias; float* out; int64_t ldo;
-  int32_t rows, no, k; int32_t trans_w, accumulate, stages;
+  int32_t rows, no, k; int32_t trans_w, accumulate, stages; int32_t k_valid, a_vec, w_vec;
 };
+bool tc_gemm_sliced_supported(const void* out, int64_t ldo, int no);
+int tc_gemm_sliced_launch(const float* x, int64_t ldx, int rows, int k, const float* w, int64_t ldw, const float* bias,
+                          int no, float* out, int64_t ldo, int kernel_id, cudaStream_t stream);
 bool tc_gemm_supported(const void* a, int64_t lda, const void* w, int64_t ldw, const void* out, int64_t ldo, int no,
                        int k, int trans_w);
 int tc_gemm_launch(const TcArgs& a, int kernel_id, cudaStream_t stream);
@@ -183,6 +186,9 @@ int gb_linear_fwd(const float* x, int32_t ldx, int32_t n, int32_t d, const float
     TcArgs t{x, ldx, w, d, b, out, ldo, n, nout, d, 0, 0, 0};
     return tc_gemm_launch(t, K_LINEAR_FWD, stream);
   }
+  // wide / unaligned reductions (the encoder, src/GNN.py:30-38: [N, 1433] x [1433, d]): K slices on the same kernel
+  if (d >= 32 && n >= 128 && tc_gemm_sliced_supported(out, ldo, nout))
+    return tc_gemm_sliced_launch(x, ldx, n, d, w, d, b, nout, out, ldo, K_LINEAR_FWD, stream);
   dim3 grid((n + BM - 1) / BM, (nout + BN - 1) / BN);
   LaunchScope ls(K_LINEAR_FWD, stream);
   sgemm_rowA<<<grid, GT, 0, stream>>>(x, ldx, n, d, w, 1, d, nout, b, out, ldo, 0);

@@ -40,6 +40,10 @@ struct TcArgs {
   int64_t ldo;
   int32_t rows, no, k;   // NO % 16 == 0, NO <= 128, K % 32 == 0, K <= 128
   int32_t trans_w, accumulate, stages;
+  // K slices of a wider reduction (gb_linear_fwd on the encoder, src/GNN.py:30-38: F = 1433 input features):
+  // the slice holds k_valid <= k real columns (the rest of the last K-block is zero-filled), and operands whose
+  // rows are not 16-byte aligned are loaded element-wise.  k_valid == 0: k_valid = k, both operands vectorised.
+  int32_t k_valid, a_vec, w_vec;
 };
 
 // ---- PTX wrappers ---------------------------------------------------------------------------------
@@ -125,6 +129,17 @@ __device__ __forceinline__ void split_tf32(const float4& v, float4& hi, float4& 
   lo.w = rna_tf32(v.w - hi.w);
 }
 
+// four consecutive K elements starting at column kcol of a row; columns >= kv read as zero
+__device__ __forceinline__ float4 tc_load4(const float* p, int kcol, int kv, bool vec, bool stream) {
+  if (vec && kcol + 4 <= kv) return stream ? ld_stream4(p) : __ldg(reinterpret_cast<const float4*>(p));
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (kcol < kv) v.x = __ldg(p);
+  if (kcol + 1 < kv) v.y = __ldg(p + 1);
+  if (kcol + 2 < kv) v.z = __ldg(p + 2);
+  if (kcol + 3 < kv) v.w = __ldg(p + 3);
+  return v;
+}
+
 // byte offset of (row, 16-byte chunk c) inside a [rows x 128 B] K-block tile in the SWIZZLE_128B layout
 __device__ __forceinline__ uint32_t sw128(int row, int c) { return (uint32_t)row * 128u + (uint32_t)((c ^ (row & 7)) << 4); }
 
@@ -190,7 +205,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_gemm_rows_kernel(const TcArg
       if (!a.trans_w) {
         kc = idx % (a.k / 4);
         n = idx / (a.k / 4);
-        v = __ldg(reinterpret_cast<const float4*>(a.w + (int64_t)n * a.ldw + 4 * kc));
+        v = tc_load4(a.w + (int64_t)n * a.ldw + 4 * kc, 4 * kc, a.k_valid, a.w_vec != 0, false);
       } else {
         n = idx % a.no;
         kc = idx / a.no;
@@ -228,7 +243,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_gemm_rows_kernel(const TcArg
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           const int row = tile * kTcTileM + r0 + 16 * i;
-          v[i] = row < a.rows ? ld_stream4(a.a + (int64_t)row * a.lda + kb * kTcKBlock + 4 * c)
+          const int kcol = kb * kTcKBlock + 4 * c;
+          v[i] = row < a.rows ? tc_load4(a.a + (int64_t)row * a.lda + kcol, kcol, a.k_valid, a.a_vec != 0, true)
                               : make_float4(0.f, 0.f, 0.f, 0.f);
         }
         mbar_wait(base + L.empty + 8 * s, ph ^ 1u);
@@ -557,8 +573,36 @@ bool tc_gemm_supported(const void* a, int64_t lda, const void* w, int64_t ldw, c
   return true;
 }
 
+// out[rows, no] = a[rows, k] . w[no, k]^T + bias for ANY k (and unaligned a / w rows): slices of <= 128 columns
+bool tc_gemm_sliced_supported(const void* out, int64_t ldo, int no) {
+  static const bool disabled = getenv("GRANDB200_NO_TC") != nullptr;
+  if (disabled) return false;
+  return no % 16 == 0 && no >= 16 && no <= 128 && reinterpret_cast<uintptr_t>(out) % 16 == 0 && ldo % 4 == 0;
+}
+
+int tc_gemm_launch(const TcArgs& a_in, int kernel_id, cudaStream_t stream);
+
+int tc_gemm_sliced_launch(const float* x, int64_t ldx, int rows, int k, const float* w, int64_t ldw, const float* bias,
+                          int no, float* out, int64_t ldo, int kernel_id, cudaStream_t stream) {
+  auto al = [](const void* p) { return reinterpret_cast<uintptr_t>(p) % 16 == 0; };
+  for (int k0 = 0; k0 < k; k0 += 128) {
+    const int kv = min(128, k - k0);
+    TcArgs t{};
+    t.a = x + k0; t.lda = ldx; t.w = w + k0; t.ldw = ldw; t.bias = k0 == 0 ? bias : nullptr;
+    t.out = out; t.ldo = ldo; t.rows = rows; t.no = no;
+    t.k = (kv + kTcKBlock - 1) / kTcKBlock * kTcKBlock;
+    t.k_valid = kv;
+    t.a_vec = al(t.a) && ldx % 4 == 0;
+    t.w_vec = al(t.w) && ldw % 4 == 0;
+    t.accumulate = k0 != 0;
+    if (int rc = tc_gemm_launch(t, kernel_id, stream)) return rc;
+  }
+  return GB_OK;
+}
+
 int tc_gemm_launch(const TcArgs& a_in, int kernel_id, cudaStream_t stream) {
   TcArgs a = a_in;
+  if (a.k_valid == 0) { a.k_valid = a.k; a.a_vec = 1; a.w_vec = 1; }
   // shared memory: weights (2 x K x NO x 4 B) + stages x 32 KB; keep at least 2 stages
   a.stages = kTcMaxStages;
   while (a.stages > 2 && tc_smem_layout(a.no, a.k, a.stages).total + 1024 > 220 * 1024) --a.stages;

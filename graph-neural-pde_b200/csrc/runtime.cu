@@ -31,7 +31,7 @@ static const char* kNames[K_NUM_KERNELS] = {
     "edge_softmax_fwd_long", "sddmm",          "edge_softmax_bwd",  "edge_score_bwd_q",  "edge_score_bwd_k",
     "plan",               "edge_util",         "fused_att_spmm_fwd", "fused_att_bwd_row", "fused_att_bwd_col",
     "linear_tc",          "stage_axpy",        "nl_fwd",            "nl_fwd_long",       "nl_adj_rows",
-    "nl_adj_long",        "gat_softmax"};
+    "nl_adj_long",        "gat_softmax",       "decode_eval"};
 
 void set_error(const char* fmt, ...) {
   char buf[1024];

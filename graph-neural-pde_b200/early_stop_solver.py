@@ -5,14 +5,13 @@ drives, :30-234): the TEST-time integrator of GNNEarly.  It integrates the ODE f
 validation accuracy (`solver.best_val / best_test / best_train / best_time`).
 
 The reference subclasses torchdiffeq's private solver classes; here the restated solvers of integrators.py take a
-per-step callback instead, so the ODE function (the CUDA hot path) is driven exactly as in training.  The decode is a
-[N, d] x [d, C] GEMM plus masked arg-max comparisons per accepted step: plain torch ops (library GEMM), not part of
-the per-evaluation hot path.
+per-step callback instead, so the ODE function (the CUDA hot path) is driven exactly as in training.  The decode
+(relu -> [N, d] x [d, C] -> masked arg-max -> counts) is ONE kernel launch and one 24-byte read-back
+per accepted step (`ops.decode_eval`, csrc/decode.cu) where the reference runs ~20 kernels and six `.item()` syncs.
 """
 import torch
-import torch.nn.functional as F
 
-from . import integrators
+from . import integrators, ops
 
 
 def _masks(data):
@@ -47,12 +46,13 @@ class EarlyStopSolverState:
 
     @torch.no_grad()
     def evaluate(self, z, t0, t1):
-        width = self.m2_weight.shape[-1]
-        if z.shape[-1] != width:                       # augmented system: the first half is the state
-            z = torch.split(z, width, dim=-1)[0]
-        z = F.linear(F.relu(z), self.m2_weight, self.m2_bias)
+        """relu -> m2 -> per-mask accuracy.  An augmented state (wider than m2) contributes its first
+        m2_weight.shape[-1] columns (early_stop_solver.py:113-114): the kernel simply does not read the rest."""
+        masks = [m for _, m in _masks(self.data)]
+        counts, _, _ = ops.decode_eval(z, self.m2_weight, self.m2_bias, self.data.y, masks)
+        c = counts.tolist()                            # the one host synchronisation of the step
         self.n_evaluations += 1
-        return self.test(z)
+        return [c[i] / c[3 + i] for i in range(3)]
 
     def on_step(self, t0, t1, y1):
         y = y1[0] if isinstance(y1, (tuple, list)) else y1

@@ -65,6 +65,98 @@ class QKProjFn(torch.autograd.Function):
         return dx, None, None, None, None
 
 
+class LinearFn(torch.autograd.Function):
+    """y = x w^T + b for x [..., d], w [nout, d] (torch's Linear.weight layout), b [nout] or None: the encoder /
+    decoder layers of GNN.forward (src/GNN.py:30-38, :66-74; src/base_classes.py:149-160) on the library's own GEMMs -
+    tcgen05 3xTF32 where the shape qualifies (K slices for the [N, 1433] x [1433, d] encoder), exact-fp32 CUDA-core
+    tiles otherwise (the [d] -> [classes] decoder)."""
+
+    @staticmethod
+    def forward(ctx, x, w, b):
+        lib = _lib.load()
+        _lib.require_cuda(x, w, b)
+        shape = x.shape
+        x2 = _f32c(x.reshape(-1, shape[-1]))
+        w = _f32c(w)
+        n, d = x2.shape
+        nout = w.shape[0]
+        out = torch.empty(n, nout, dtype=torch.float32, device=x.device)
+        if n > 0:
+            _lib.check(lib.gb_linear_fwd(x2.data_ptr(), d, n, d, w.data_ptr(), _lib.ptr(None if b is None else _f32c(b)),
+                                         nout, out.data_ptr(), nout, _lib.stream()), 'gb_linear_fwd')
+        ctx.save_for_backward(x2, w)
+        ctx.shape, ctx.has_bias = shape, b is not None
+        return out.reshape(*shape[:-1], nout)
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        lib = _lib.load()
+        x2, w = ctx.saved_tensors
+        n, d = x2.shape
+        nout = w.shape[0]
+        dy = _f32c(dy.reshape(-1, nout))
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x2)
+            if n > 0:
+                _lib.check(lib.gb_linear_bwd_x(dy.data_ptr(), nout, n, nout, w.data_ptr(), d, dx.data_ptr(), d, 0,
+                                               _lib.stream()), 'gb_linear_bwd_x')
+            dx = dx.reshape(ctx.shape)
+        if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
+            dw = torch.zeros(nout, d, dtype=torch.float32, device=x2.device)
+            db = torch.zeros(nout, dtype=torch.float32, device=x2.device)
+            if n > 0:
+                ws = torch.empty(int(lib.gb_linear_bwd_w_workspace_bytes(n, d, nout)), dtype=torch.uint8, device=x2.device)
+                _lib.check(lib.gb_linear_bwd_w(dy.data_ptr(), nout, x2.data_ptr(), d, n, d, nout, dw.data_ptr(),
+                                               db.data_ptr(), ws.data_ptr(), ws.numel(), _lib.stream()), 'gb_linear_bwd_w')
+            if not ctx.has_bias:
+                db = None
+        return dx, dw, db
+
+
+class Linear(torch.nn.Linear):
+    """torch.nn.Linear with the same parameters (`weight`, `bias`: reference checkpoints load unchanged) whose forward
+    and backward run on the library's GEMM kernels instead of cuBLAS"""
+
+    def forward(self, x):
+        return LinearFn.apply(x, self.weight, self.bias)
+
+
+def decode_eval(z, w2, b2, y, masks, want_logits=False, want_pred=False):
+    """EarlyStopInt's per-step evaluation (src/early_stop_solver.py:108-128 + :88-98) in one kernel: z [N, >= d] (or
+    the fork's [1, N, .]) state, w2 [C, d], b2 [C]; y [N] int64; masks = (train, val, test) bool [N] (entries may be
+    None).  Returns (counts int32[6] ON THE DEVICE: correct x3, total x3, logits or None, pred or None)."""
+    lib = _lib.load()
+    _lib.require_cuda(z, w2, b2, y, *masks)
+    z2 = _f32c(z.reshape(-1, z.shape[-1]))
+    w2 = _f32c(w2.reshape(-1, w2.shape[-1]))
+    n, ldz = z2.shape
+    classes, d = w2.shape
+    if d > ldz:
+        raise ValueError(f'decoder expects {d} features, the state has {ldz}')
+    y = y.reshape(-1)
+    if y.dtype != torch.int64 or y.numel() != n:
+        raise TypeError(f'labels must be int64 [N={n}]; got {y.dtype} {tuple(y.shape)}')
+    y = y.contiguous()
+    ms = []
+    for m in masks:
+        if m is not None:
+            m = m.reshape(-1)
+            if m.dtype != torch.bool or m.numel() != n:
+                raise TypeError(f'masks must be bool [N={n}]; got {m.dtype} {tuple(m.shape)}')
+            m = m.contiguous().view(torch.uint8)
+        ms.append(m)
+    counts = torch.empty(6, dtype=torch.int32, device=z.device)
+    logits = torch.empty(n, classes, dtype=torch.float32, device=z.device) if want_logits else None
+    pred = torch.empty(n, dtype=torch.int64, device=z.device) if want_pred else None
+    _lib.check(lib.gb_decode_eval(z2.data_ptr(), ldz, n, d, w2.data_ptr(), d, _lib.ptr(None if b2 is None else _f32c(b2)),
+                                  classes, y.data_ptr(), _lib.ptr(ms[0]), _lib.ptr(ms[1]), _lib.ptr(ms[2]),
+                                  counts.data_ptr(), _lib.ptr(logits), classes, _lib.ptr(pred), _lib.stream()),
+               'gb_decode_eval')
+    return counts, logits, pred
+
+
 def _segment_sums(vals, ptr):
     """[E,H] values laid out segment after segment, ptr [n+1] -> [n,H] sums.  Prefix sums in fp64 (deterministic on
     every backend; a difference of two prefixes loses ~1e-16 * E relative to the running total)"""

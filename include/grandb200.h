@@ -199,7 +199,10 @@ int gb_spmm_bwd_static(const gb_graph* g, const float* vals, const float* gout, 
 /* Tensor-core path (csrc/linear_tc.cu): tcgen05.mma kind::tf32 with a 3-term hi/lo split (fp32-accurate), TMEM
  * accumulators, persistent warp-specialised CTAs.  Taken by gb_linear_fwd / gb_linear_bwd_x when the reduction
  * length is a multiple of 32 and <= 128, the output width a multiple of 16 and <= 128, rows 16-byte aligned
- * (every GRAND-nl configuration of BASELINE.json); other shapes run the CUDA-core SGEMM.  Returns 1 / 0. */
+ * (every GRAND-nl configuration of BASELINE.json).  gb_linear_fwd also takes it for ANY reduction length >= 32 when
+ * n >= 128 and the output qualifies (the encoder m1 / mx / mp of src/GNN.py:30-38, e.g. [N, 1433] x [1433, 64]):
+ * slices of 128 input columns accumulate into `out`, a ragged last slice is zero-filled, rows that are not 16-byte
+ * aligned are loaded element-wise.  Other shapes run the CUDA-core SGEMM.  Returns 1 / 0 (the un-sliced form). */
 int gb_linear_tc_eligible(const float* a, int32_t lda, const float* w, int32_t ldw, const float* out, int32_t ldo,
                           int32_t nout, int32_t k, int32_t trans_w);
 int gb_linear_fwd(const float* x, int32_t ldx, int32_t n, int32_t d, const float* w, const float* b,
@@ -260,6 +263,21 @@ int gb_gat_softmax_fwd(const gb_graph* g, int32_t norm_idx, const float* s_src, 
 int gb_segment_softmax_fwd(const int32_t* ptr, const int32_t* perm, int32_t n, int32_t heads, const float* scores,
                            float* att, float* abar, const int32_t* long_list, int32_t n_long, int32_t long_threshold,
                            void* stream);
+
+/* ---- per-step evaluation of the early-stopping integrator in one launch (csrc/decode.cu).  Replaces
+ *      EarlyStopDopri5/EarlyStopRK4.evaluate + ode_test (src/early_stop_solver.py:108-128, :88-98 and :210-226):
+ *          logits = relu(z[:, :d]) w2^T + b2;   pred = argmax(logits, -1)     (first maximum; NaN counts as largest)
+ *          counts[m]     = #{i : mask_m[i] and pred[i] == y[i]},  counts[3 + m] = #{i : mask_m[i]},  m = train, val, test
+ *      z [n, ldz >= d] device fp32 (columns >= d - the augmented half - are not read); w2 [classes, ldw] = m2.weight,
+ *      b2 [classes] = m2.bias (may be NULL); y [n] int64 labels; masks: one byte per node (torch.bool), each may be NULL;
+ *      counts [6] int32 on the device, zeroed by the call (NULL: no counting); logits [n, ldl] and pred [n] int64 are
+ *      optional outputs (NULL to skip).  classes <= gb_decode_eval_max_classes() (64), else GB_ERR_UNSUPPORTED.
+ *      The accuracies are counts[m] / counts[3 + m] - divided by the caller after ONE 24-byte read-back (the
+ *      reference synchronises six times per step with .item()). */
+int gb_decode_eval_max_classes(void);
+int gb_decode_eval(const float* z, int32_t ldz, int32_t n, int32_t d, const float* w2, int32_t ldw, const float* b2,
+                   int32_t classes, const int64_t* y, const uint8_t* train_mask, const uint8_t* val_mask,
+                   const uint8_t* test_mask, int32_t* counts, float* logits, int32_t ldl, int64_t* pred, void* stream);
 
 /* ---- fused GRAND-nl evaluation (warp-per-row kernels, csrc/fused_att.cu) -------------------------
  * gb_att_fused_supported: 1 when the shapes/alignment fit the fused kernels (heads a power of two <= 8,

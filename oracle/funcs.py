@@ -19,6 +19,7 @@ Follows:
                          a * edge_h summed over 2 dk, leaky relu, softmax);  gat_f  :53-69 (mix_features=False)
   laplacian_f            src/function_laplacian_diffusion.py:39-77
   transformer_f          src/function_transformer_attention.py:20-59 (mix_features=False branch)
+  decode_eval            src/early_stop_solver.py:108-128 (evaluate) + :88-98 (test): relu, m2, masked arg-max counts
 """
 import math
 import torch
@@ -162,3 +163,25 @@ def transformer_f(x, edge_index, wq, bq, wk, bk, heads, alpha_train, beta_train,
     if add_source:
         f = f + beta_train * x0
     return f
+
+
+def decode_eval(z, w2, b2, y, masks):
+    """EarlyStopDopri5.evaluate + test (src/early_stop_solver.py:108-128, :88-98; same in EarlyStopRK4 :210-226):
+    z [N, >= d] state after a solver step (an augmented state keeps only the first d = w2.shape[1] columns, :113-114),
+    logits = relu(z) w2^T + b2, and for each mask (train, val, test): pred = logits[mask].max(-1)[1],
+    correct = pred.eq(y[mask]).sum(), total = mask.sum().  Returns (logits, pred [N], [(correct, total)] per mask);
+    the reference's accuracy is correct / total.  Un-batched restatement of the fork's [1, N, d] layout."""
+    d = w2.shape[1]
+    zz = torch.relu(z[:, :d])
+    logits = zz @ w2.t()
+    if b2 is not None:
+        logits = logits + b2
+    pred = logits.max(dim=-1)[1]
+    counts = []
+    for m in masks:
+        if m is None:
+            counts.append((0, 0))
+            continue
+        m = m.bool()
+        counts.append((int(pred[m].eq(y[m]).sum().item()), int(m.sum().item())))
+    return logits, pred, counts

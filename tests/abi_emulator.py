@@ -275,6 +275,28 @@ class Emulator:
             f32(prods, G.e, heads)[:] = s.numpy()
         return 0
 
+    def gb_decode_eval_max_classes(self):
+        return 64
+
+    def gb_decode_eval(self, z, ldz, n, d, w2, ldw, b2, classes, y, train_mask, val_mask, test_mask, counts, logits,
+                       ldl, pred, stream):
+        self._note('gb_decode_eval')
+        if classes > 64:
+            return 3
+        from oracle import funcs
+        masks = [torch.tensor(_arr(_p(m), C.c_uint8, n).copy()) if _p(m) else None for m in (train_mask, val_mask, test_mask)]
+        yv = torch.tensor(i64(y, n).copy()) if _p(y) else torch.zeros(n, dtype=torch.long)
+        lg, pr, cnt = funcs.decode_eval(torch.tensor(f32(z, n, d, ldz).astype(np.float64)),
+                                        torch.tensor(f32(w2, classes, d, ldw).astype(np.float64)),
+                                        torch.tensor(vec(b2, classes).astype(np.float64)) if _p(b2) else None, yv, masks)
+        if _p(counts):
+            i32(counts, 6)[:] = [c for c, _ in cnt] + [t for _, t in cnt]
+        if _p(logits):
+            f32(logits, n, classes, ldl)[:] = lg.numpy()
+        if _p(pred):
+            i64(pred, n)[:] = pr.numpy()
+        return 0
+
     def gb_gat_softmax_fwd(self, g, norm_idx, s_src, s_dst, lds, heads, slope, att, abar, prods, stream):
         self._note('gb_gat_softmax_fwd')
         from oracle import funcs

@@ -1,4 +1,4 @@
-"""CPU: EarlyStopInt (mirror of the reference's src/early_stop_solver.py) over the restated solvers: the per-step
+"""CPU (C ABI emulated): EarlyStopInt (mirror of the reference's src/early_stop_solver.py) over the restated solvers: the per-step
 decode + best-validation bookkeeping against a hand-rolled loop, the returned solution against plain odeint, the
 attempt budget of the adaptive solver."""
 import types
@@ -10,11 +10,11 @@ import torch.nn.functional as F
 
 def setup(n=60, d=6, classes=3, seed=0):
     g = torch.Generator().manual_seed(seed)
-    A = 0.8 * torch.randn(d, d, generator=g, dtype=torch.float64)
+    A = 0.8 * torch.randn(d, d, generator=g, dtype=torch.float32)
     func = lambda t, y: y @ A.T
-    y0 = torch.randn(n, d, generator=g, dtype=torch.float64)
-    w = torch.randn(classes, d, generator=g, dtype=torch.float64)
-    b = torch.randn(classes, generator=g, dtype=torch.float64)
+    y0 = torch.randn(n, d, generator=g, dtype=torch.float32)
+    w = torch.randn(classes, d, generator=g, dtype=torch.float32)
+    b = torch.randn(classes, generator=g, dtype=torch.float32)
     labels = torch.randint(0, classes, (n,), generator=g)
     idx = torch.randperm(n, generator=g)
     masks = [torch.zeros(n, dtype=torch.bool) for _ in range(3)]
@@ -36,7 +36,7 @@ def make(opt_over, T=2.0):
     return EarlyStopInt(T, opt, device=torch.device('cpu')), opt
 
 
-def test_rk4_tracks_the_best_validation_step_and_returns_the_plain_solution():
+def test_rk4_tracks_the_best_validation_step_and_returns_the_plain_solution(emulated_abi):
     from grand_b200 import integrators
     func, y0, w, b, data = setup()
     es, opt = make({})
@@ -56,7 +56,7 @@ def test_rk4_tracks_the_best_validation_step_and_returns_the_plain_solution():
     assert (s.best_train, s.best_val, s.best_test) == pytest.approx(best[:3]) and s.best_time == pytest.approx(best[3])
 
 
-def test_batched_fork_layout_and_augmented_state():
+def test_batched_fork_layout_and_augmented_state(emulated_abi):
     func, y0, w, b, data = setup()
     es, _ = make({})
     es.data, es.m2_weight, es.m2_bias = data, w, b
@@ -69,7 +69,7 @@ def test_batched_fork_layout_and_augmented_state():
     assert (s1.best_val, s1.best_test, s1.best_time) == (es.solver.best_val, es.solver.best_test, es.solver.best_time)
 
 
-def test_dopri5_evaluates_every_attempt_and_honours_the_attempt_budget():
+def test_dopri5_evaluates_every_attempt_and_honours_the_attempt_budget(emulated_abi):
     from grand_b200 import integrators
     func, y0, w, b, data = setup(seed=3)
     es, _ = make(dict(method='dopri5', earlystopxT=1.0))
@@ -86,7 +86,7 @@ def test_dopri5_evaluates_every_attempt_and_honours_the_attempt_budget():
     assert es2.solver.best_time < 2.0
 
 
-def test_requires_data_and_only_rk4_or_dopri5():
+def test_requires_data_and_only_rk4_or_dopri5(emulated_abi):
     func, y0, w, b, data = setup()
     es, _ = make({})
     with pytest.raises(RuntimeError):
