@@ -4,7 +4,8 @@ directory name `graph-neural-pde_b200` is not a Python identifier.
 
 Module names mirror the reference's `src/` files so a maintainer can swap imports one for one:
   base_classes, function_laplacian_diffusion, function_transformer_attention, block_constant,
-  block_transformer_attention, block_mixed, block_transformer_hard_attention, model_configurations, utils  (+ integrators: torchdiffeq-compatible
+  block_transformer_attention, block_mixed, block_transformer_hard_attention, model_configurations, utils, GNN, GNN_early,
+  early_stop_solver, CGNN (model classes), graph_rewiring (positional-encoding files only)  (+ integrators: torchdiffeq-compatible
   odeint / odeint_adjoint used when torchdiffeq is not installed).
 All device work goes through libgrandb200.so (csrc/, C ABI in include/grandb200.h).
 """
@@ -29,6 +30,7 @@ from .early_stop_solver import EarlyStopInt
 from .base_classes import BaseGNN
 from .GNN import GNN
 from .GNN_early import GNNEarly
+from . import CGNN, graph_rewiring, ops
 
 __all__ = ['GraphPlan', 'get_plan', 'MaxNFEException', 'get_rw_adj', 'gcn_norm_fill_val',
            'add_remaining_self_loops', 'Meter', 'ODEFunc', 'ODEblock', 'GraphData', 'LaplacianODEFunc',

@@ -19,6 +19,7 @@ Follows:
                          a * edge_h summed over 2 dk, leaky relu, softmax);  gat_f  :53-69 (mix_features=False)
   laplacian_f            src/function_laplacian_diffusion.py:39-77
   transformer_f          src/function_transformer_attention.py:20-59 (mix_features=False branch)
+  cgnn_f                 src/CGNN.py:85-91 (per-node alpha, fixed adjacency, source x0 with unit weight)
   decode_eval            src/early_stop_solver.py:108-128 (evaluate) + :88-98 (test): relu, m2, masked arg-max counts
 """
 import math
@@ -185,3 +186,10 @@ def decode_eval(z, w2, b2, y, masks):
         m = m.bool()
         counts.append((int(pred[m].eq(y[m]).sum().item()), int(m.sum().item())))
     return logits, pred, counts
+
+
+def cgnn_f(x, edge_index, values, alpha_train, x0):
+    """CGNN's ODEFunc.forward (src/CGNN.py:85-91): sigmoid(alpha_train)[:, None] * 0.5 * (A x - x) + x0 with
+    alpha_train [N] (one per node) and A = the fixed normalised adjacency (torch.spmm(adj, x), :89)"""
+    alph = torch.sigmoid(alpha_train).unsqueeze(dim=1)
+    return alph * 0.5 * (spmm(edge_index, values, x) - x) + x0

@@ -23,6 +23,9 @@ The fixtures pin `oracle/funcs.py` (and through it the CUDA path) to the referen
                              indices (dense-then-permute gives the finite-difference value, sparse-permute does not),
                              so the reference's own gradients are wrong under this torch; the oracle's gradients are
                              pinned by torch.autograd.gradcheck instead (tests/test_oracle_golden.py)
+  ref_cgnn.npz               CGNN.ODEFunc.forward (torch.spmm on coo2tensor's sparse tensor, per-node alpha) + autograd
+                             grads w.r.t. x and alpha_train           (CGNN.py:68-91, :269-277); needs the import-only
+                             stubs ray / torchdiffeq / data (the fork ships no src/data.py) / torch_geometric.utils.convert
   ref_k3.npz                 the K3 / x=ones known answer: attention == 0.5 exactly
                              (test/test_transformer_attention.py:98-106)
 The GPU box has no /root/reference: tests only read the .npz files.
@@ -205,9 +208,34 @@ def gen_k3(ref_att):
              attention=np_(attention[0]), heads=2)
 
 
+def gen_cgnn():
+    import scipy.sparse
+    import CGNN as ref_cgnn                                      # noqa: E402  (the reference's src/CGNN.py, unmodified)
+    n, e, h = 23, 90, 4
+    ei = toy_graph(n, e, 31)                                     # duplicates + self loops
+    g = torch.Generator().manual_seed(32)
+    w = torch.rand(ei.shape[1], generator=g) * 0.3
+    coo = scipy.sparse.coo_matrix((np_(w), (np_(ei[0]), np_(ei[1]))), shape=(n, n))
+    adj = ref_cgnn.coo2tensor(coo, torch.device('cpu'))
+    opt = {'alpha': 0.9, 'hidden_dim': h}
+    func = ref_cgnn.ODEFunc(2 * h, 2 * h, opt, adj)
+    with torch.no_grad():
+        func.alpha_train.copy_(torch.randn(n, generator=g))
+    x = torch.randn(n, 2 * h, generator=g, requires_grad=True)
+    func.x0 = torch.randn(n, 2 * h, generator=g)
+    f = func(0.0, x)
+    cot = torch.randn(n, 2 * h, generator=g)
+    dx, dalpha = torch.autograd.grad(f, [x, func.alpha_train], cot)
+    np.savez(os.path.join(GOLD, 'ref_cgnn.npz'), edge_index=np_(ei), w=np_(w), n=n, hidden=h, alpha_train=np_(func.alpha_train),
+             x=np_(x), x0=np_(func.x0), f=np_(f), cot=np_(cot), dx=np_(dx), dalpha=np_(dalpha))
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     ref_utils, ref_lap, ref_att = load_reference()
+    if sys.argv[1:] == ['cgnn']:                                 # only this fixture
+        gen_cgnn()
+        return
     if sys.argv[1:] == ['gat']:                                  # only the GAT fixtures (leaves the others untouched)
         gen_gat()
         return
@@ -217,6 +245,7 @@ def main():
     gen_laplacian(ref_lap)
     gen_transformer(ref_att)
     gen_k3(ref_att)
+    gen_cgnn()
     print('wrote', sorted(os.listdir(GOLD)))
 
 

@@ -156,3 +156,35 @@ def test_a_few_optimiser_steps_reduce_the_training_loss(host, function, block):
         model.resetNFE()
         losses.append(float(loss.detach()))
     assert all(np.isfinite(losses)) and losses[-1] < 0.8 * losses[0], losses
+
+
+def test_positional_encoding_files_round_trip(tmp_path):
+    """graph_rewiring.apply_beltrami (src/graph_rewiring.py:277-313): same file name and pickle payloads as the
+    reference - a plain tensor for GDC, {'data': ...} for the DW* types - plus the optional CSV side file"""
+    import os
+    import pickle
+    import types
+    import numpy as np
+    from grand_b200 import graph_rewiring as gr
+    data = types.SimpleNamespace(num_nodes=7)
+    p = torch.randn(7, 5)
+    opt = {'dataset': 'Cora', 'pos_enc_type': 'GDC', 'pos_enc_csv': True}
+    with pytest.raises(NotImplementedError, match='Cora_GDC.pkl'):
+        gr.apply_beltrami(data, opt, str(tmp_path))
+    fname = gr.save_pos_encoding(p, opt, str(tmp_path))
+    assert fname == str(tmp_path / 'pos_encodings' / 'Cora_GDC.pkl')
+    with open(fname, 'rb') as f:
+        assert torch.equal(pickle.load(f), p)                                 # what the reference's reader expects
+    assert torch.equal(gr.apply_beltrami(data, opt, str(tmp_path)), p)
+    table = np.loadtxt(str(tmp_path / 'pos_encodings' / 'Cora_GDC.csv'), delimiter=',')
+    assert table.shape == (35, 3) and np.allclose(table[:, 2], p.reshape(-1).numpy(), atol=1e-6)
+    opt = {'dataset': 'Photo', 'pos_enc_type': 'DW128'}
+    with pytest.raises(FileNotFoundError):
+        gr.apply_beltrami(data, opt, str(tmp_path))
+    os.makedirs(tmp_path / 'pos_encodings', exist_ok=True)
+    with open(tmp_path / 'pos_encodings' / 'Photo_DW128.pkl', 'wb') as f:     # as the reference's DeepWalk files are laid out
+        pickle.dump({'data': p.double().numpy()}, f)
+    got = gr.apply_beltrami(data, opt, str(tmp_path))
+    assert got.dtype == torch.float32 and torch.allclose(got, p)
+    with pytest.raises(ValueError, match='7 rows'):
+        gr.apply_beltrami(types.SimpleNamespace(num_nodes=8), opt, str(tmp_path))

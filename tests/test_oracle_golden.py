@@ -32,6 +32,18 @@ def test_squareplus_matches_the_reference_function():
     assert torch.allclose(sums[present], torch.ones_like(sums[present]), atol=1e-5) and bool((out > 0).all())
 
 
+def test_cgnn_f_and_grads_match_the_reference_class():
+    """CGNN.ODEFunc.forward run by the reference itself (torch.spmm on its sparse COO adjacency, CGNN.py:85-91)"""
+    z = np.load(os.path.join(GOLD, 'ref_cgnn.npz'))
+    for dt in (torch.float32, torch.float64):
+        x = T(z['x'], dt).requires_grad_(True)
+        a = T(z['alpha_train'], dt).requires_grad_(True)
+        f = funcs.cgnn_f(x, torch.tensor(z['edge_index']), T(z['w'], dt), a, T(z['x0'], dt))
+        dx, da = torch.autograd.grad(f, (x, a), T(z['cot'], dt))
+        for got, key in ((f, 'f'), (dx, 'dx'), (da, 'dalpha')):
+            assert torch.allclose(got, T(z[key], dt), rtol=2e-6, atol=2e-6), key
+
+
 @pytest.mark.parametrize('path', sorted(glob.glob(os.path.join(GOLD, 'ref_laplacian_*.npz'))))
 def test_laplacian_f_and_grads(path):
     z = np.load(path)
