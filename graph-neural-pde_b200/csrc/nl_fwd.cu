@@ -39,7 +39,10 @@ int nl_fill_args(NlArgs& a, const gb_graph* g, int row_lo, int row_hi, const flo
   a.dv = d / 4; a.adim = heads * dk; a.dk = dk; a.q = q; a.ldq = ldq; a.wk = wk; a.ldwk = ldwk;
   a.counter = static_cast<int32_t*>(workspace);
   a.long_list = g->long_rows;
-  a.long_threshold = g->long_threshold > 0 ? (g->long_threshold > kNlLongRow ? g->long_threshold : kNlLongRow) : 0x7fffffff;
+  // rows above this are worked by a whole CTA.  Few listed rows (small graphs: 9 on the ogbn-arxiv shape, the longest
+  // 1367 edges = 171 batches on ONE warp, a third of the launch) -> all of them; many (C4 / C5) -> only the real hubs
+  const int cta_rows = g->n_long_rows <= 4 * sm_count() ? g->long_threshold : kNlLongRow;
+  a.long_threshold = g->long_threshold > 0 ? (g->long_threshold > cta_rows ? g->long_threshold : cta_rows) : 0x7fffffff;
   SpmmArgs& sp = a.sp;
   sp.src = x; sp.lds = ldx; sp.alpha_train = alpha_train; sp.alpha_sigmoid = alpha_sigmoid; sp.n = g->n; sp.dv = d / 4;
   const bool source = x0 != nullptr && beta_train != nullptr;

@@ -48,6 +48,33 @@ _FUSE_MIN = 1 << 14        # below this many elements the launch overhead of eit
 _FUSE_STAGES = True        # stage combinations in the epilogue of the function's kernel (tests switch it off to compare)
 
 
+def _stage_combine_raw(yi, ks, cs):
+    import ctypes as C
+    from . import _lib
+    lib = _lib.load()
+    out = torch.empty_like(yi)
+    kp = (C.c_void_p * len(ks))(*[k.data_ptr() for k in ks])
+    cp = (C.c_float * len(ks))(*[float(c) for c in cs])
+    _lib.check(lib.gb_stage_combine(yi.data_ptr(), kp, cp, len(ks), yi.numel(), out.data_ptr(), _lib.stream()),
+               'gb_stage_combine')
+    return out
+
+
+class _StageCombineFn(torch.autograd.Function):
+    """the one-pass combination under autograd (plain `odeint` differentiated through the solver, e.g. adjoint=False
+    training and CGNN): d/dyi = g, d/dk_j = c_j g"""
+
+    @staticmethod
+    def forward(ctx, cs, yi, *ks):
+        ctx.cs = cs
+        return _stage_combine_raw(yi, ks, cs)
+
+    @staticmethod
+    def backward(ctx, g):
+        need = ctx.needs_input_grad
+        return (None, g if need[1] else None) + tuple((g * c) if need[2 + j] else None for j, c in enumerate(ctx.cs))
+
+
 def _combine_one(yi, terms):
     """yi + sum_j c_j * k_j: ONE pass (csrc/stage.cu) for fp32 CUDA tensors, else torchdiffeq's axpy chain"""
     terms = [(k, c) for k, c in terms if c != 0]
@@ -55,15 +82,10 @@ def _combine_one(yi, terms):
         return yi
     if (yi.is_cuda and yi.dtype == torch.float32 and yi.numel() >= _FUSE_MIN and len(terms) <= 7 and yi.is_contiguous()
             and all(k.shape == yi.shape and k.dtype == yi.dtype and k.is_contiguous() for k, _ in terms)):
-        import ctypes as C
-        from . import _lib
-        lib = _lib.load()
-        out = torch.empty_like(yi)
-        ks = (C.c_void_p * len(terms))(*[k.data_ptr() for k, _ in terms])
-        cs = (C.c_float * len(terms))(*[float(c) for _, c in terms])
-        _lib.check(lib.gb_stage_combine(yi.data_ptr(), ks, cs, len(terms), yi.numel(), out.data_ptr(), _lib.stream()),
-                   'gb_stage_combine')
-        return out
+        ks, cs = [k for k, _ in terms], tuple(float(c) for _, c in terms)
+        if torch.is_grad_enabled() and (yi.requires_grad or any(k.requires_grad for k in ks)):
+            return _StageCombineFn.apply(cs, yi, *ks)
+        return _stage_combine_raw(yi, ks, cs)
     acc = yi
     for k, c in terms:
         acc = torch.add(acc, k, alpha=c)

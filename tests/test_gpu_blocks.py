@@ -43,8 +43,9 @@ def t64(a):
 
 @pytest.mark.parametrize('adjoint', [False, True])
 @pytest.mark.parametrize('method', ['rk4', 'euler'])
-def test_constant_block_laplacian_rk4(adjoint, method):
-    n, e, d, T = 400, 3000, 16, 3.0
+@pytest.mark.parametrize('n,e', [(400, 3000), (3000, 20000)])    # 3000 x 16 elements: the one-pass stage combination
+def test_constant_block_laplacian_rk4(adjoint, method, n, e):      # (integrators._FUSE_MIN) is on the autograd path
+    d, T = 16, 3.0
     opt = dict(OPT, adjoint=adjoint, method=method, adjoint_method=method)
     block, data, ei = build(opt, n, e, T)
     block.train()

@@ -182,7 +182,7 @@ def test_unsupported_options_raise():
     import grand_b200
     x = torch.randn(5, 8, device='cuda')
     ei = torch.tensor([[0, 1, 2], [1, 2, 0]], device='cuda')
-    for key, val in (('mix_features', True), ('square_plus', True)):
+    for key, val in (('mix_features', True),):                # square_plus: supported since round 2 (test_gpu_variants.py)
         func = grand_b200.ODEFuncTransformerAtt(8, 8, dict(BASE_OPT, **{key: val}), torch.device('cuda')).cuda()
         func.edge_index, func.x0 = ei, x
         with pytest.raises(NotImplementedError):

@@ -409,3 +409,38 @@ def test_dopri5_agrees_with_scipy_rk45_on_a_linear_system():
     with torch.no_grad():
         got = P.odeint(func, y0, torch.tensor([0.0, 2.0]), method='dopri5', rtol=1e-9, atol=1e-11)[1, 0].numpy()
     assert np.allclose(got, ref, rtol=1e-7, atol=1e-9)
+
+
+def test_one_pass_stage_combination_is_differentiable(emulated_abi, monkeypatch):
+    """above integrators._FUSE_MIN the stage combination is one kernel: under autograd it must stay on the graph
+    (plain odeint differentiated through the solver: adjoint=False training, CGNN)"""
+    from grand_b200 import integrators
+    calls = []
+
+    def raw(yi, ks, cs):
+        calls.append(len(ks))
+        out = yi.clone()
+        for k, c in zip(ks, cs):
+            out = out + c * k
+        return out.detach()
+
+    monkeypatch.setattr(integrators, '_stage_combine_raw', raw)
+    monkeypatch.setattr(integrators, '_FUSE_MIN', 1)
+    real_is_cuda = torch.Tensor.is_cuda
+    monkeypatch.setattr(torch.Tensor, 'is_cuda', property(lambda self: True))
+    try:
+        a = torch.tensor(0.7, requires_grad=True)
+        y0 = torch.randn(6, 3, requires_grad=True)
+        z = integrators.odeint(lambda t, y: -a * y, y0, torch.tensor([0., 1.]), method='rk4', options=dict(step_size=0.5))[1]
+        gy, ga = torch.autograd.grad(z.sum(), (y0, a))
+    finally:
+        monkeypatch.setattr(torch.Tensor, 'is_cuda', real_is_cuda)
+    assert calls                                                   # the one-pass form was taken
+    y0d, ad = y0.detach().double().requires_grad_(True), torch.tensor(0.7, dtype=torch.float64, requires_grad=True)
+    acc = y0d
+    for _ in range(2):                                             # two rk4 steps of y' = -a y by hand
+        h = 0.5
+        k1 = -ad * acc; k2 = -ad * (acc + h / 2 * k1); k3 = -ad * (acc + h / 2 * k2); k4 = -ad * (acc + h * k3)
+        acc = acc + h / 6 * (k1 + 2 * k2 + 2 * k3 + k4)
+    ry, ra = torch.autograd.grad(acc.sum(), (y0d, ad))
+    assert torch.allclose(gy.double(), ry, rtol=1e-5) and torch.allclose(ga.double(), ra, rtol=1e-5)
