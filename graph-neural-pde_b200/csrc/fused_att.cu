@@ -702,7 +702,9 @@ int nl_cols_pass(const gb_graph* g, int32_t row_lo, int32_t row_hi, const float*
   sp.alpha_sigmoid = alpha_sigmoid; sp.x0 = (dparams && beta_train) ? x0 : nullptr; sp.ldx0 = ldx0;
   sp.x = dparams ? x : nullptr; sp.ldx = ldx; sp.out = dx; sp.ldo = lddx; sp.accumulate = 0;
   sp.partials = partials + kMidFloats; sp.partial_base = 0; sp.long_list = g->long_cols;
-  if (part) { sp.part_lo = row_lo; sp.part_hi = row_hi; }
+  // (0, 0) means "own every column" to row_epilogue: a rank WITHOUT rows (row_lo == row_hi, possibly both 0 under a
+  // compact halo) must own none - an empty range that can never test as (0, 0)
+  if (part) { sp.part_lo = row_lo; sp.part_hi = row_hi > row_lo ? row_hi : -1; }
   const char* why = "";
   if (!fused_supported(q, ldq, q, ldq, heads, dk, &why)) {
     set_error("gb_nl_adjoint: column pass does not support this shape (%s)", why);

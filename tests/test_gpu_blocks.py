@@ -81,8 +81,9 @@ def test_constant_block_laplacian_rk4(adjoint, method, n, e):      # (integrator
 
 
 @pytest.mark.parametrize('adjoint', [False, True])
-def test_attention_block_transformer_function(adjoint):
-    n, e, d, T = 300, 2000, 16, 2.0
+@pytest.mark.parametrize('n,e', [(300, 2000), (2000, 14000)])    # 2000 x 16: above integrators._FUSE_MIN
+def test_attention_block_transformer_function(adjoint, n, e):
+    d, T = 16, 2.0
     opt = dict(OPT, block='attention', function='transformer', adjoint=adjoint)
     block, data, ei = build(opt, n, e, T, seed=2)
     block.train()

@@ -156,3 +156,35 @@ def test_block_api_world_of_one_matches_unpartitioned():
     for base, other in ((results[0], results[1]), (results[2], results[3])):
         for a, b, name in zip(base, other, ('z', 'dx', 'dWq', 'dWk', 'dalpha', 'dbeta')):
             assert_close(b, a, 2e-5, name)
+
+
+def test_an_empty_row_range_owns_no_column():
+    """the column pass takes its ownership range from (row_lo, row_hi), and (0, 0) used to read as "own every column"
+    (subtract g_j, accumulate dalpha / dbeta for every row) - what a compact-halo rank without rows would pass.
+    Column pass of the same prepared row pass with range (0, n) and with (0, 0): the results differ by exactly the
+    self term, dx_(0,0) - dx_(0,n) = alpha g."""
+    import types
+    import grand_b200
+    from grand_b200 import partition as P
+    from grand_b200.ops import _nl_workspace
+    n, d, heads, adim = 640, 32, 4, 32
+    func = make_func(d, heads, adim)
+    L = func.multihead_att_layer
+    ei = dev(rand_graph(n, 6 * n, 5))
+    part = P.RowPartition(n, 1, 0)
+    assert part.n_pad == n
+    plan = grand_b200.GraphPlan(ei, n)
+    gen = torch.Generator(device='cuda').manual_seed(4)
+    x, g, x0 = (torch.randn(n, d, device='cuda', generator=gen) for _ in range(3))
+    _, q = P.nl_local_forward(part, plan, x, x, L.Q.weight.detach(), L.Q.bias.detach(), L.K.weight.detach(),
+                              func.alpha_train.detach(), func.beta_train.detach(), x0, heads, True)
+    h = P.nl_local_vjp_rows(part, plan, x, q, L.Q.weight.detach(), L.K.weight.detach(), func.alpha_train.detach(),
+                            func.beta_train.detach(), x0, heads, True, g, True)
+    lib, ws = grand_b200._lib.load(), _nl_workspace(x.device)
+    P._nl_adjoint_phase(lib, h, 2, ws)                                       # GB_NL_PHASE_COLS, owner of every column
+    dx_all, dparams_all = h.dx.clone(), h.grads[-2:].clone()
+    h.part = types.SimpleNamespace(lo=0, hi=0, slab=part.slab, n_pad=n)
+    P._nl_adjoint_phase(lib, h, 2, ws)                                       # same edges, owner of none
+    alpha = torch.sigmoid(func.alpha_train.detach())
+    assert_close(h.dx - dx_all, alpha * g, 1e-6, 'self term')
+    assert float((h.grads[-2:] - dparams_all).abs().max()) > 0               # <g, x0> and the -g_j x_j part are the owner's
