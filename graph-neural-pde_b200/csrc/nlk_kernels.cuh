@@ -282,7 +282,7 @@ struct NlkWarp {
       f4_scale(ax, inv_h);
       if (lane < a.dv) {
         float s1 = 0.f, s2 = 0.f;
-        row_epilogue<4, false>(a.sp, row, 4 * lane, Vec<4>{ax}, alpha, beta, s1, s2);
+        row_epilogue<4, false, !ADJ>(a.sp, row, 4 * lane, Vec<4>{ax}, alpha, beta, s1, s2);
       }
     }
     if constexpr (ADJ) {
