@@ -21,9 +21,12 @@ fp32 CUDA tensors instead of torchdiffeq's chain of axpy kernels, and the revers
 signs ride on the stage coefficients instead of negating [N,d] tensors.  A function may expose
 `eval_vjp(t, y, cot, params)` (fused f + VJP); the adjoint driver uses it when present.
 """
+import ctypes as C
 import math
 
 import torch
+
+from . import _lib
 
 _FIXED = ('euler', 'midpoint', 'rk4')
 _ADAPTIVE = ('dopri5', 'adaptive_heun')
@@ -48,15 +51,18 @@ _FUSE_MIN = 1 << 14        # below this many elements the launch overhead of eit
 _FUSE_STAGES = True        # stage combinations in the epilogue of the function's kernel (tests switch it off to compare)
 
 
+_KPTR = [None] + [C.c_void_p * n for n in range(1, 8)]       # ctypes array types, built once
+_CVAL = [None] + [C.c_float * n for n in range(1, 8)]
+
+
 def _stage_combine_raw(yi, ks, cs):
-    import ctypes as C
-    from . import _lib
-    lib = _lib.load()
+    # launch-bound solves (adaptive adjoint on small graphs) call this ~600 times per step: keep the host side lean
+    n = len(ks)
     out = torch.empty_like(yi)
-    kp = (C.c_void_p * len(ks))(*[k.data_ptr() for k in ks])
-    cp = (C.c_float * len(ks))(*[float(c) for c in cs])
-    _lib.check(lib.gb_stage_combine(yi.data_ptr(), kp, cp, len(ks), yi.numel(), out.data_ptr(), _lib.stream()),
-               'gb_stage_combine')
+    rc = _lib.load().gb_stage_combine(yi.data_ptr(), _KPTR[n](*[k.data_ptr() for k in ks]), _CVAL[n](*cs), n,
+                                      yi.numel(), out.data_ptr(), _lib.stream())
+    if rc:
+        _lib.check(rc, 'gb_stage_combine')
     return out
 
 
@@ -129,8 +135,27 @@ def _rms(x):
     return x.pow(2).mean().sqrt()
 
 
-def _mixed_norm(state):
-    """max over the components of their RMS (torchdiffeq's mixed norm) - ONE device read for all of them"""
+def _segment_rms(v, lengths):
+    """RMS of each consecutive segment of the flat tensor v (lengths: int64 tensor on v's device) - the packed
+    parameter integrals of the adjoint are judged per parameter tensor, exactly like the unpacked components"""
+    sq = v.detach().reshape(-1).pow(2)
+    return torch.segment_reduce(sq, 'mean', lengths=lengths).sqrt()
+
+
+def _mixed_norm(state, segments=None):
+    """max over the components of their RMS (torchdiffeq's mixed norm) - ONE device read for all of them.
+    `segments` = {component index: lengths tensor}: that component is a concatenation whose pieces each count as a
+    component of their own."""
+    if segments:
+        vals = []
+        for i, s in enumerate(state):
+            if s.numel() == 0:
+                continue
+            if i in segments:
+                vals.extend(_segment_rms(s, segments[i]).unbind(0))
+            else:
+                vals.append(_rms(s.detach()))
+        return float(torch.stack(vals).max())
     vals = [_rms(s.detach()) for s in state if s.numel() > 0]
     if len(vals) == 1 or len({(v.device, v.dtype) for v in vals}) > 1:
         return max(float(v) for v in vals)
@@ -159,6 +184,7 @@ class _Problem:
         # values are never formed, only the end-of-step combination (`passive`), or not even that (`dead`: the
         # caller drops the component).  Same end-of-step numbers as forming everything, fewer tiny kernels.
         self.passive, self.dead = (), ()
+        self.segments = None             # adaptive solvers: see _mixed_norm
 
     def tensor_time(self, s):
         return _time_tensor(self.sign * s, self.dtype, self.device)
@@ -260,12 +286,12 @@ def _solve_fixed(prob, method, step_size, on_step=None):
 
 def _initial_step(prob, t0, y0, order, rtol, atol, f0):
     scale = tuple(atol + y.abs() * rtol for y in y0)
-    d0 = _mixed_norm(tuple(y / s for y, s in zip(y0, scale)))
-    d1 = _mixed_norm(tuple(f / s for f, s in zip(f0, scale)))
+    d0 = _mixed_norm(tuple(y / s for y, s in zip(y0, scale)), prob.segments)
+    d1 = _mixed_norm(tuple(f / s for f, s in zip(f0, scale)), prob.segments)
     h0 = 1e-6 if (d0 < 1e-5 or d1 < 1e-5) else 0.01 * d0 / d1
     y1 = _combine(y0, h0, [f0], [1.0])
     f1 = prob.f(t0 + h0, y1)
-    d2 = _mixed_norm(tuple((a - b) / s for a, b, s in zip(f1, f0, scale))) / h0
+    d2 = _mixed_norm(tuple((a - b) / s for a, b, s in zip(f1, f0, scale)), prob.segments) / h0
     if d1 <= 1e-15 and d2 <= 1e-15:
         h1 = max(1e-6, h0 * 1e-3)
     else:
@@ -312,7 +338,7 @@ def _solve_adaptive(prob, method, rtol, atol, max_num_steps=2 ** 31 - 1, on_step
             y1 = _combine(y, dt, ks, tab['c_sol'])
             err = _combine(tuple(torch.zeros_like(v) for v in y), dt, ks, tab['c_err'])
             tol = tuple(atol + rtol * torch.max(a.abs(), b.abs()) for a, b in zip(y, y1))
-            ratio = _mixed_norm(tuple(e / s for e, s in zip(err, tol)))
+            ratio = _mixed_norm(tuple(e / s for e, s in zip(err, tol)), prob.segments)
             if ratio <= 1:
                 # torchdiffeq's _runge_kutta_step returns f1 = k[..., -1] for EVERY tableau (exact for the FSAL
                 # Dormand-Prince pair; for adaptive_heun it is f(t1, y + dt k1), no extra evaluation)
@@ -353,7 +379,7 @@ def odeint(func, y0, t, **kwargs):
 
 
 def _odeint_impl(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, event_fn=None, _comp_signs=None,
-                 _on_step=None, _max_attempts=None, _passive=(), _dead=()):
+                 _on_step=None, _max_attempts=None, _passive=(), _dead=(), _segments=None):
     if event_fn is not None:
         raise NotImplementedError('event handling is not part of the reference call sites')
     method = method or 'dopri5'
@@ -367,6 +393,7 @@ def _odeint_impl(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None
         if method not in _FIXED:
             raise ValueError('_passive / _dead components are only supported by the fixed-grid solvers')
         prob.passive, prob.dead = tuple(_passive), tuple(_dead)
+    prob.segments = _segments
     if method in _FIXED:
         sols = _solve_fixed(prob, method, options.get('step_size'), on_step=_on_step)
     elif method in _ADAPTIVE:
@@ -426,7 +453,7 @@ def _adjoint_fixed_phased(func, params, state, t_hi, t_lo, method, step_size):
     return list(state)
 
 
-_PACK_PARAMS = True      # fixed-grid adjoint: one flat buffer for all parameter integrals (see _OdeintAdjoint.backward)
+_PACK_PARAMS = True      # adjoint: one flat buffer for all parameter integrals (see _OdeintAdjoint.backward)
 
 
 class _OdeintAdjoint(torch.autograd.Function):
@@ -455,9 +482,15 @@ class _OdeintAdjoint(torch.autograd.Function):
         # Fixed grid: the parameter integrals ride in ONE flat buffer (the VJPs of an evaluation are packed with one
         # cat), are only combined at the end of a step (nothing reads their stage values) and the time integral is
         # dropped altogether - the reference pays ~10 axpy kernels per parameter tensor per step for the same numbers.
-        packed = fixed and _PACK_PARAMS and len(params) > 0 and \
+        # Adaptive solves pack as well (a dopri5 step forms 8 combinations of every component: 12 parameter tensors
+        # of the transformer function = ~650 launch-sized kernels per attempted step, 4 components = ~80); their error
+        # norm still judges every parameter tensor on its own (`_segments`), as torchdiffeq's mixed norm does.
+        packed = _PACK_PARAMS and len(params) > 0 and all(p.numel() > 0 for p in params) and \
             all(p.dtype == ys.dtype and p.device == ys.device for p in params)
         sizes = [p.numel() for p in params]
+        segments = None
+        if packed and not fixed:
+            segments = {3: torch.tensor(sizes, dtype=torch.int64, device=ys.device)}
         zero_t = torch.zeros((), dtype=ys.dtype, device=ys.device)
         zero_piece = {}
 
@@ -481,7 +514,7 @@ class _OdeintAdjoint(torch.autograd.Function):
                 if res is not None:
                     f, vy, vps = res
                     if packed:
-                        return (zero_t, f, vy, pack(vps))
+                        return (zero_t, f, vy, pack(vps))              # df/dt == 0: the time integral stays zero
                     vp = [g if g is not None else torch.zeros_like(p) for g, p in zip(vps, params)]
                     return (torch.zeros_like(tt), f, vy, *vp)
             with torch.enable_grad():
@@ -491,7 +524,8 @@ class _OdeintAdjoint(torch.autograd.Function):
                 grads = torch.autograd.grad(f, (tt_, y_) + tuple(params), cot, allow_unused=True)
             vy = grads[1] if grads[1] is not None else torch.zeros_like(y)
             if packed:
-                return (zero_t, f.detach(), vy, pack(grads[2:]))
+                vt = zero_t if (fixed or grads[0] is None) else grads[0]
+                return (vt, f.detach(), vy, pack(grads[2:]))
             vt = grads[0] if grads[0] is not None else torch.zeros_like(tt)
             vp = [g if g is not None else torch.zeros_like(p) for g, p in zip(grads[2:], params)]
             return (vt, f.detach(), vy, *vp)
@@ -517,8 +551,8 @@ class _OdeintAdjoint(torch.autograd.Function):
                     continue
                 sol = odeint(aug_dynamics, tuple(state), [times[i], times[i - 1]], rtol=cfg['adjoint_rtol'],
                              atol=cfg['adjoint_atol'], method=cfg['adjoint_method'], options=cfg['adjoint_options'],
-                             _comp_signs=comp_signs if fixed else None, _passive=(3,) if packed else (),
-                             _dead=(0,) if packed else ())
+                             _comp_signs=comp_signs if fixed else None, _passive=(3,) if (packed and fixed) else (),
+                             _dead=(0,) if (packed and fixed) else (), _segments=segments)
                 state = [s[1] for s in sol]
                 state[1] = ys[i - 1]
                 state[2] = state[2] + grad_ys[i - 1]
