@@ -948,8 +948,10 @@ def main():
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--workload', default='c4', choices=['c1', 'c2', 'c3', 'c4', 'c5'])
-    ap.add_argument('--cuda-graph', action='store_true',
-                    help='replay the whole pass as one CUDA graph (for the launch-bound shapes c1-c3; 1 GPU)')
+    ap.add_argument('--cuda-graph', dest='cuda_graph', action='store_true', default=None,
+                    help='replay the whole pass as one CUDA graph (1 GPU).  Default: on for the launch-bound fixed-step '
+                         'presets c1 and c3, off otherwise (an adaptive solve decides on the host after every step)')
+    ap.add_argument('--eager', dest='cuda_graph', action='store_false', help='no CUDA-graph replay')
     ap.add_argument('--no-cpu-baseline', dest='cpu_baseline', action='store_false')
     ap.add_argument('--no-gpu-reference', dest='gpu_reference', action='store_false',
                     help='skip the torch-CUDA-ops comparator (N = 1 only)')
@@ -983,6 +985,10 @@ def main():
     METHOD = args.method or preset['method']
     T_END = args.t_end if args.t_end is not None else preset['t_end']
     TOL_SCALE = args.tol_scale if args.tol_scale is not None else (1.0 if METHOD in ('rk4', 'euler', 'midpoint') else 1e3)
+    if args.cuda_graph is None:
+        args.cuda_graph = (args.workload in ('c1', 'c3') and METHOD in ('rk4', 'euler', 'midpoint') and args.gpus == 1
+                           and int(os.environ.get('WORLD_SIZE', '1')) == 1 and not args.microbench
+                           and args.impl == 'ours')
     if int(os.environ.get('WORLD_SIZE', '1')) > 1 and args.function is None and args.workload in ('c1', 'c2', 'c3'):
         pass                                           # the small shapes stay on one GPU; a partitioned run is by request
     if args.watchdog > 0:

@@ -489,8 +489,12 @@ class _OdeintAdjoint(torch.autograd.Function):
             all(p.dtype == ys.dtype and p.device == ys.device for p in params)
         sizes = [p.numel() for p in params]
         segments = None
+        # the ODE functions that evaluate their own VJP (eval_vjp) are autonomous: the time integral is identically
+        # zero, never the maximum of the mixed norm, and is not returned - an adaptive packed solve leaves it out
+        no_t = packed and not fixed and fused_vjp is not None
+        off = 0 if no_t else 1                                     # index of y in the augmented state
         if packed and not fixed:
-            segments = {3: torch.tensor(sizes, dtype=torch.int64, device=ys.device)}
+            segments = {off + 2: torch.tensor(sizes, dtype=torch.int64, device=ys.device)}
         zero_t = torch.zeros((), dtype=ys.dtype, device=ys.device)
         zero_piece = {}
 
@@ -505,7 +509,7 @@ class _OdeintAdjoint(torch.autograd.Function):
             return torch.cat(parts)
 
         def aug_dynamics(tt, state):
-            y, a_y = state[1], state[2]
+            y, a_y = state[off], state[off + 1]
             cot = a_y if fixed else -a_y
             if fused_vjp is not None:
                 # the function evaluates f and cot^T df/d(y, params) in one fused pass (same numbers as
@@ -513,6 +517,8 @@ class _OdeintAdjoint(torch.autograd.Function):
                 res = fused_vjp(tt, y, cot, params)
                 if res is not None:
                     f, vy, vps = res
+                    if no_t:
+                        return (f, vy, pack(vps))
                     if packed:
                         return (zero_t, f, vy, pack(vps))              # df/dt == 0: the time integral stays zero
                     vp = [g if g is not None else torch.zeros_like(p) for g, p in zip(vps, params)]
@@ -523,6 +529,8 @@ class _OdeintAdjoint(torch.autograd.Function):
                 f = func(tt_, y_)
                 grads = torch.autograd.grad(f, (tt_, y_) + tuple(params), cot, allow_unused=True)
             vy = grads[1] if grads[1] is not None else torch.zeros_like(y)
+            if no_t:
+                return (f.detach(), vy, pack(grads[2:]))
             if packed:
                 vt = zero_t if (fixed or grads[0] is None) else grads[0]
                 return (vt, f.detach(), vy, pack(grads[2:]))
@@ -534,6 +542,8 @@ class _OdeintAdjoint(torch.autograd.Function):
             if packed:
                 state = [zero_t, ys[-1], grad_ys[-1], torch.zeros(sum(sizes), dtype=ys.dtype, device=ys.device)]
                 comp_signs = (-1.0, 1.0, -1.0, -1.0)
+                if no_t:
+                    state = state[1:]
             else:
                 state = [torch.zeros((), dtype=ys.dtype, device=ys.device), ys[-1], grad_ys[-1]] + \
                         [torch.zeros_like(p) for p in params]
@@ -554,8 +564,10 @@ class _OdeintAdjoint(torch.autograd.Function):
                              _comp_signs=comp_signs if fixed else None, _passive=(3,) if (packed and fixed) else (),
                              _dead=(0,) if (packed and fixed) else (), _segments=segments)
                 state = [s[1] for s in sol]
-                state[1] = ys[i - 1]
-                state[2] = state[2] + grad_ys[i - 1]
+                state[off] = ys[i - 1]
+                state[off + 1] = state[off + 1] + grad_ys[i - 1]
+            if no_t:
+                state = [zero_t] + state
             if packed:
                 state = state[:3] + [v.reshape(p.shape) for v, p in zip(state[3].split(sizes), params)]
         return (None, None, None, None, state[2]) + tuple(state[3:])

@@ -349,3 +349,40 @@ def test_mixed_block(variants):
 @pytest.mark.parametrize('function', ['laplacian', 'transformer', 'GAT'])
 def test_hard_attention_block(variants, function, capsys):
     zz.test_hard_attention_block_samples_edges_while_training(function, capsys)
+
+
+def test_adaptive_adjoint_of_the_transformer_block_packs_the_parameter_integrals(host, monkeypatch):
+    """dopri5 forward and adjoint (BASELINE config 2) on a function that evaluates its own VJP: the parameter integrals
+    ride in one flat component, the identically-zero time integral is left out, and the error norm still judges every
+    parameter tensor separately - so the packed solve takes the same steps and returns the same numbers as the
+    component-per-parameter solve torchdiffeq would run"""
+    from grand_b200 import integrators
+    n, e, d, T = 90, 600, 16, 1.5
+    opt = dict(OPT, block='attention', function='transformer', adjoint=True, method='dopri5', adjoint_method='dopri5',
+               tol_scale=100.0, tol_scale_adjoint=100.0)
+    out = {}
+    for pack in (True, False):
+        monkeypatch.setattr(integrators, '_PACK_PARAMS', pack)
+        block, data, ei = _block(opt, n, e, T, seed=6)
+        block.train()
+        func = block.odefunc
+        g = torch.Generator().manual_seed(5)
+        L = func.multihead_att_layer
+        with torch.no_grad():
+            for lin in (L.Q, L.K):
+                lin.weight.copy_(torch.randn(lin.weight.shape, generator=g) / 4.0)
+                lin.bias.copy_(0.1 * torch.randn(lin.bias.shape, generator=g))
+            func.alpha_train.fill_(0.2)
+            func.beta_train.fill_(0.3)
+        x = torch.randn(n, d, generator=g).requires_grad_(True)
+        gout = torch.randn(n, d, generator=g)
+        block.set_x0(x)
+        z = block(x, data)
+        nfe_fwd = func.nfe
+        params = [x, func.alpha_train, func.beta_train, L.Q.weight, L.Q.bias, L.K.weight, L.K.bias]
+        grads = torch.autograd.grad(z, params, gout)
+        out[pack] = (nfe_fwd, func.nfe, z.detach(), grads)
+    assert out[True][:2] == out[False][:2] and out[True][1] > out[True][0] > 0       # same number of evaluations
+    assert torch.equal(out[True][2], out[False][2])
+    for a, b in zip(out[True][3], out[False][3]):
+        assert torch.equal(a, b)
