@@ -570,7 +570,7 @@ def run_partitioned(args, cfg, device, rank, world):
     d = cfg['d']
     part = grand_b200.RowPartition(n, world, rank)
     halo_kind = args.halo
-    halo = {'dense': grand_b200.Halo, 'compact': grand_b200.CompactHalo, 'push': grand_b200.PushHalo}.get(
+    halo = {'dense': grand_b200.Halo, 'compact': grand_b200.CompactHalo, 'push': grand_b200.PushHalo, 'copy': grand_b200.CopyHalo}.get(
         halo_kind, grand_b200.SparseHalo)(part)
     # the SAME global state and cotangent as the 1-GPU run (seed 99), sliced to this rank's slab: the loss checksum of
     # the JSON line is comparable across N
@@ -581,7 +581,7 @@ def run_partitioned(args, cfg, device, rank, world):
     block = build_block(cfg, device)
     block.set_partition(part, halo)
     referenced = None
-    if halo_kind not in ('dense', 'push'):
+    if halo_kind not in ('dense', 'push', 'copy'):
         train_pass(block, data, x_dev, g_dev)           # builds the per-peer index lists (SparseHalo.prepare)
         frac = torch.tensor([halo.referenced_fraction], device=device)
         dist.all_reduce(frac, op=dist.ReduceOp.MAX)
@@ -713,7 +713,9 @@ def run_partitioned(args, cfg, device, rank, world):
                                         'compact': ' (all_to_all_v of the referenced rows only; local graph relabelled to '
                                                    '[own slab | referenced rows])',
                                         'push': ' (all-gather = one broadcast-store kernel into symmetric memory + barrier; '
-                                                'reduce-scatter = barrier + one kernel pulling the peers\' shares)'}.get(
+                                                'reduce-scatter = barrier + one kernel pulling the peers\' shares)',
+                                        'copy': ' (all-gather = local copy + barrier + P-1 copy-engine pulls from the peers\' '
+                                                'symmetric matrices, no SMs; reduce-scatter as push)'}.get(
                                             halo_kind, ' (all-gather / reduce-scatter of whole slabs)'),
                    'rows_of_the_local_problem_rank0': getattr(halo, 'view', part).n_pad,
                    'remote_rows_referenced_max_over_ranks': referenced},
@@ -957,7 +959,7 @@ def main():
                     help='skip the torch-CUDA-ops comparator (N = 1 only)')
     ap.add_argument('--function', default=None, choices=['transformer', 'laplacian'],
                     help='transformer = GRAND-nl (BASELINE.json headline); laplacian = GRAND-l sweep of config 5')
-    ap.add_argument('--halo', default=os.environ.get('GRANDB200_HALO', 'dense'), choices=['dense', 'sparse', 'compact', 'push', 'auto'],
+    ap.add_argument('--halo', default=os.environ.get('GRANDB200_HALO', 'dense'), choices=['dense', 'sparse', 'compact', 'push', 'copy', 'auto'],
                     help='N > 1: exchange whole slabs (dense), only the rows the peers reference (sparse: R-MAT slabs '
                          'reference ~25 %% of the others at 8 ranks), sparse exchange + the rank\'s graph relabelled to '
                          '[own slab | referenced rows] so all per-rank work is O(N/P + halo) (compact), or dense / sparse '

@@ -498,6 +498,69 @@ class PushHalo(Halo):
         return PendingScatter(full, None, lambda: out)
 
 
+class CopyHalo(PushHalo):
+    """PushHalo whose all-gather moves the bytes with the COPY ENGINES instead of a kernel: every rank writes its slab
+    into its own symmetric matrix (one local copy), a symmetric-memory barrier, then P - 1 peer-to-peer copies
+    (cudaMemcpyAsync from the peers' matrices over NVLink, one stream per peer so the engines run side by side) pull
+    the other slabs.  No SM is involved apart from the barrier's few threads, so a gather prefetched on a side stream
+    (GRANDB200_OVERLAP=1) does not take SMs or issue slots from the kernels it overlaps - what limited the overlapped
+    NCCL / push exchanges at 8 GPUs (DESIGN.md "(e)").  Buffer reuse: a rank overwrites its slab in ring entry b three
+    gathers later, after passing two more barriers, which every peer reaches only after its pulls from b were
+    complete in stream order.  The reduce-scatter is PushHalo's pull kernel."""
+
+    def _symmetric(self, rows, width, dtype, device):
+        import warnings
+        import torch.distributed._symmetric_memory as symm
+        group = self.group if self.group is not None else self.dist.group.WORLD
+        try:
+            with warnings.catch_warnings():
+                warnings.simplefilter('ignore')
+                if not symm.is_symm_mem_enabled_for_group(group.group_name):
+                    symm.enable_symm_mem_for_group(group.group_name)
+        except (AttributeError, RuntimeError):
+            pass
+        t = symm.empty(rows, width, dtype=dtype, device=device)
+        handle = symm.rendezvous(t, group)
+        views = [t if p == self.part.rank else handle.get_buffer(p, (rows, width), dtype)
+                 for p in range(self.part.world)]
+        self.__dict__.setdefault('_views', {})[id(t)] = views
+        return t, [int(p) for p in handle.buffer_ptrs], handle.barrier
+
+    def _peer_streams(self, device):
+        st = self.__dict__.get('_pstreams')
+        if st is None:
+            st = self._pstreams = [torch.cuda.Stream(device=device) for _ in range(max(1, self.part.world - 1))]
+        return st
+
+    @_nvtx('halo.all_gather')
+    def all_gather_rows(self, slab, keep=False):
+        slab = slab.contiguous()
+        if slab.dim() != 2 or slab.dtype != torch.float32:
+            raise TypeError('CopyHalo exchanges fp32 [S, d] slabs')
+        part = self.part
+        full, _ptrs, barrier = self._next(slab.shape[1], slab.dtype, slab.device)
+        views = self._views[id(full)]
+        s = part.slab
+        full[part.rank * s:(part.rank + 1) * s].copy_(slab)
+        barrier()                                                          # every rank's own slab is in its matrix
+        cur = torch.cuda.current_stream(slab.device)
+        streams = self._peer_streams(slab.device)
+        i = 0
+        for p in range(part.world):
+            if p == part.rank:
+                continue
+            st = streams[i % len(streams)]
+            i += 1
+            st.wait_stream(cur)
+            with torch.cuda.stream(st):
+                full[p * s:(p + 1) * s].copy_(views[p][p * s:(p + 1) * s], non_blocking=True)
+        for st in streams[:i]:
+            cur.wait_stream(st)
+        self.bytes_in += (part.world - 1) * slab.numel() * slab.element_size()
+        self.n_gathers += 1
+        return full.clone() if (keep or torch.is_grad_enabled()) else full
+
+
 class _StreamPending:
     """work queued on a side stream; wait() makes the current stream wait for it (no host block)"""
 

@@ -108,6 +108,7 @@ def main():
             kinds = [('dense', grand_b200.Halo), ('sparse', grand_b200.SparseHalo), ('compact', grand_b200.CompactHalo)]
             if not args.emulate:                                   # symmetric memory needs real GPUs
                 kinds.append(('push', grand_b200.PushHalo))
+                kinds.append(('copy', grand_b200.CopyHalo))
             for kind, cls in kinds:
                 for overlap in (('0', '1') if adjoint else ('0',)):
                     os.environ['GRANDB200_OVERLAP'] = overlap
