@@ -17,6 +17,8 @@ One exchange per evaluation, none inside the kernels:
 `RowPartition` and `Halo` are plain torch / torch.distributed and run on any backend (the world_size-2
 gloo tests exercise them on CPU); the compute entry points below call the CUDA library and need a GPU.
 """
+import os
+
 import torch
 
 from . import _lib
@@ -500,9 +502,9 @@ class PushHalo(Halo):
 
 class CopyHalo(PushHalo):
     """PushHalo whose all-gather moves the bytes with the COPY ENGINES instead of a kernel: every rank writes its slab
-    into its own symmetric matrix (one local copy), a symmetric-memory barrier, then P - 1 peer-to-peer copies
-    (cudaMemcpyAsync from the peers' matrices over NVLink, one stream per peer so the engines run side by side) pull
-    the other slabs.  No SM is involved apart from the barrier's few threads, so a gather prefetched on a side stream
+    into its own symmetric matrix and, with P - 1 peer-to-peer copies (cudaMemcpyAsync over NVLink, one stream per
+    peer so the engines run side by side), into its row range of every peer's matrix; then a symmetric-memory barrier
+    (GRANDB200_COPY_HALO=pull: barrier first, then every rank reads the peers' slabs instead).  No SM is involved apart from the barrier's few threads, so a gather prefetched on a side stream
     (GRANDB200_OVERLAP=1) does not take SMs or issue slots from the kernels it overlaps - what limited the overlapped
     NCCL / push exchanges at 8 GPUs (DESIGN.md "(e)").  Buffer reuse: a rank overwrites its slab in ring entry b three
     gathers later, after passing two more barriers, which every peer reaches only after its pulls from b were
@@ -541,10 +543,13 @@ class CopyHalo(PushHalo):
         full, _ptrs, barrier = self._next(slab.shape[1], slab.dtype, slab.device)
         views = self._views[id(full)]
         s = part.slab
-        full[part.rank * s:(part.rank + 1) * s].copy_(slab)
-        barrier()                                                          # every rank's own slab is in its matrix
+        mine = slice(part.rank * s, (part.rank + 1) * s)
         cur = torch.cuda.current_stream(slab.device)
         streams = self._peer_streams(slab.device)
+        pull = os.environ.get('GRANDB200_COPY_HALO', 'push') == 'pull'
+        full[mine].copy_(slab)
+        if pull:
+            barrier()                                                      # every rank's own slab is in its matrix
         i = 0
         for p in range(part.world):
             if p == part.rank:
@@ -553,9 +558,14 @@ class CopyHalo(PushHalo):
             i += 1
             st.wait_stream(cur)
             with torch.cuda.stream(st):
-                full[p * s:(p + 1) * s].copy_(views[p][p * s:(p + 1) * s], non_blocking=True)
+                if pull:                                                   # remote reads: measured 2.3x slower at P = 8
+                    full[p * s:(p + 1) * s].copy_(views[p][p * s:(p + 1) * s], non_blocking=True)
+                else:                                                      # posted writes into the peer's matrix
+                    views[p][mine].copy_(slab, non_blocking=True)
         for st in streams[:i]:
             cur.wait_stream(st)
+        if not pull:
+            barrier()                                                      # all writes landed before any rank reads
         self.bytes_in += (part.world - 1) * slab.numel() * slab.element_size()
         self.n_gathers += 1
         return full.clone() if (keep or torch.is_grad_enabled()) else full
