@@ -714,8 +714,8 @@ def run_partitioned(args, cfg, device, rank, world):
                                                    '[own slab | referenced rows])',
                                         'push': ' (all-gather = one broadcast-store kernel into symmetric memory + barrier; '
                                                 'reduce-scatter = barrier + one kernel pulling the peers\' shares)',
-                                        'copy': ' (all-gather = local copy + barrier + P-1 copy-engine pulls from the peers\' '
-                                                'symmetric matrices, no SMs; reduce-scatter as push)'}.get(
+                                        'copy': ' (all-gather = P-1 copy-engine copies into the peers\' symmetric matrices + '
+                                                'barrier, no SMs; reduce-scatter as push)'}.get(
                                             halo_kind, ' (all-gather / reduce-scatter of whole slabs)'),
                    'rows_of_the_local_problem_rank0': getattr(halo, 'view', part).n_pad,
                    'remote_rows_referenced_max_over_ranks': referenced},
