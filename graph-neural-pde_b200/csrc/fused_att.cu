@@ -759,7 +759,7 @@ int gb_nl_adjoint_phase(const gb_graph* g, int32_t row_lo, int32_t row_hi, const
   if (int rc = nl_fill_args(a, g, row_lo, row_hi, x, ldx, q, ldq, wk, ldwk, heads, dk, d, x0, ldx0, alpha_train,
                             alpha_sigmoid, beta_train, out, ldo, nullptr, workspace, "gb_nl_adjoint"))
     return rc;
-  GB_REQUIRE(gout && ds && dabar_scratch && abar && dq && dk_out && dx && partials, "gb_nl_adjoint: null pointer");
+  GB_REQUIRE(gout && (g->e == 0 || (ds && dabar_scratch && abar)) && dq && dk_out && dx && partials, "gb_nl_adjoint: null pointer");
   GB_REQUIRE(g->colptr && (g->e == 0 || (g->rowidx && g->tperm)), "gb_nl_adjoint: graph without CSC arrays");
   GB_REQUIRE(ldg >= d && lddx >= d && vec_width(gout, ldg, d) == 4 && vec_width(dx, lddx, d) == 4,
              "gb_nl_adjoint: gout / dx rows must be 16-byte aligned");

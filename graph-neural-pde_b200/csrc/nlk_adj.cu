@@ -32,7 +32,7 @@ int gb_nlk_adjoint_phase(const gb_graph* g, int32_t row_lo, int32_t row_hi, cons
   if (int rc = nlk_fill_args(a, g, row_lo, row_hi, x, ldx, q, ldq, k, ldk, heads, dk, d, x0, ldx0, alpha_train,
                              alpha_sigmoid, beta_train, out, ldo, nullptr, workspace, "gb_nlk_adjoint_phase"))
     return rc;
-  GB_REQUIRE(gout && ds && dabar_scratch && abar && dq && dk_out && dx && partials, "gb_nlk_adjoint_phase: null pointer");
+  GB_REQUIRE(gout && (g->e == 0 || (ds && dabar_scratch && abar)) && dq && dk_out && dx && partials, "gb_nlk_adjoint_phase: null pointer");
   GB_REQUIRE(g->colptr && (g->e == 0 || (g->rowidx && g->tperm)), "gb_nlk_adjoint_phase: graph without CSC arrays");
   GB_REQUIRE(ldg >= d && lddx >= d && vec_width(gout, ldg, d) == 4 && vec_width(dx, lddx, d) == 4,
              "gb_nlk_adjoint_phase: gout / dx rows must be 16-byte aligned");

@@ -341,7 +341,8 @@ int gb_nl_fwd(const gb_graph* g, int32_t row_lo, int32_t row_hi, const float* x,
               const float* beta_train, float* out, int32_t ldo, const gb_stage* stage,
               void* workspace, void* stream);
 /* Evaluation + VJP in one row pass and one column pass, given gout = dL/df (rows [row_lo,row_hi)):
- *   rows    : [out = f when out != NULL], dq [rows, A], ds [E,H], abar [E]   (dabar_scratch [E] is caller scratch)
+ *   rows    : [out = f when out != NULL], dq [rows, A], ds [E,H], abar [E]   (dabar_scratch [E] is caller scratch;
+ *             the three per-edge buffers may be NULL when the graph has no edges: f = -alpha x + beta x0, dq = dk = 0)
  *   columns : dx[j,:] = alpha (sum_{e: col_e = j} abar_e gout[row_e,:] - [j owned] gout[j,:])   for ALL columns j
  *             dk[j,:] = sum_e ds[e,:] q[row_e,:] / sqrt(dk)                                      for ALL columns j
  *             dparams = {dalpha_train, dbeta_train} (this rank's share when partitioned)

@@ -160,6 +160,41 @@ def test_hub_segments_long_path_both_norms():
             assert_close(g, r, G_RTOL, name, floor=bias_scale if name in ('gbq', 'gbk') else 0.0)
 
 
+@pytest.mark.parametrize('impl', ['3', '2', '1'])
+@pytest.mark.parametrize('e', [0, 40])
+def test_isolated_nodes_and_empty_graph_through_the_row_kernels(impl, e, monkeypatch):
+    """rows without any edge (no self loops: the function is also called on raw edge lists, test/test_*.py) and
+    columns nobody points to; e = 0: f = -alpha x + beta x0 and every attention gradient is zero"""
+    import grand_b200
+    monkeypatch.setenv('GRANDB200_NL_IMPL', impl)
+    n, d, heads, adim = 97, 32, 4, 32
+    rng = np.random.default_rng(e)
+    ei = np.stack([rng.integers(0, n // 3, e), rng.integers(n // 2, n, e)]).astype(np.int64)   # two thirds of the rows empty
+    x, x0, gout = (rng.standard_normal((n, d)).astype(np.float32) for _ in range(3))
+    wq, wk = (rng.standard_normal((adim, d)).astype(np.float32) / np.sqrt(d) for _ in range(2))
+    bq, bk = (0.1 * rng.standard_normal(adim).astype(np.float32) for _ in range(2))
+    opt = dict(BASE_OPT, heads=heads, attention_dim=adim, hidden_dim=d)
+    func = grand_b200.ODEFuncTransformerAtt(d, d, opt, torch.device('cuda')).cuda()
+    set_layer(func.multihead_att_layer, dict(wq=wq, bq=bq, wk=wk, bk=bk))
+    with torch.no_grad():
+        func.alpha_train.fill_(0.3)
+        func.beta_train.fill_(0.1)
+    func.edge_index, func.x0 = dev(ei), dev(x0)
+    xg = dev(x).requires_grad_(True)
+    out = func(0.0, xg)
+    L = func.multihead_att_layer
+    grads = torch.autograd.grad(out, [xg, L.Q.weight, L.Q.bias, L.K.weight, L.K.bias, func.alpha_train, func.beta_train],
+                                dev(gout))
+    ref, rg = oracle_transformer(ei, x, x0, gout, wq, bq, wk, bk, heads, 0.3, 0.1, 0)
+    assert_close(out, ref, F_RTOL, 'f')
+    scale = max(float(r.abs().max()) for r in rg[1:5]) if e else 1.0
+    for g, r, name in zip(grads, rg, ('gx', 'gwq', 'gbq', 'gwk', 'gbk', 'galpha', 'gbeta')):
+        assert_close(g, r, G_RTOL, name, floor=scale if name in ('gwq', 'gbq', 'gwk', 'gbk') else 0.0)
+    f2, dx2, p2 = func.eval_vjp(0.0, dev(x), dev(gout), [L.Q.weight, func.alpha_train])      # the fused adjoint evaluation
+    assert_close(f2, ref, F_RTOL, 'f (eval_vjp)')
+    assert_close(dx2, rg[0], G_RTOL, 'dx (eval_vjp)')
+
+
 def test_head_mean_identity_through_kernels():
     """test/test_transformer_attention.py:118-143: mean_h(A_h x) == (mean_h A_h) x"""
     import grand_b200
