@@ -70,7 +70,10 @@ extern "C" {
 
 int gb_nl_supported(int32_t heads, int32_t dk, int32_t d) {
   const bool h_ok = heads == 1 || heads == 2 || heads == 4 || heads == 8;
-  return h_ok && dk > 0 && dk % 4 == 0 && d > 0 && d % 4 == 0 && d <= 128 && heads * dk <= 256;
+  // attention_dim <= 128: the limit of the column pass of the VJP (one float4 of dk per lane); wider layers take the
+  // composite kernels for the forward evaluation too, so that a function never evaluates on one route and fails on the
+  // other when it is differentiated
+  return h_ok && dk > 0 && dk % 4 == 0 && d > 0 && d % 4 == 0 && d <= 128 && heads * dk <= 128;
 }
 
 size_t gb_nl_workspace_bytes(void) { return 256; }

@@ -63,6 +63,13 @@ class SpGraphTransAttentionLayer(nn.Module):
             self.h, self.attention_dim)
         self.d_k = self.attention_dim // self.h
         self.beltrami_kernel = bool(opt.get('beltrami', False)) and opt.get('attention_type') == 'exp_kernel'
+        # one warp holds a q / k row as 32 lanes x 4 floats in every score kernel (the beltrami kernel product works on
+        # per-head vectors of twice the width); the reference's tuned configurations use 8 .. 128 (best_params.py)
+        width = self.attention_dim * (2 if self.beltrami_kernel else 1)
+        if width > 128:
+            raise NotImplementedError(f"opt['attention_dim'] = {self.attention_dim}" +
+                                      (' with beltrami + exp_kernel' if self.beltrami_kernel else '') +
+                                      ': the score kernels hold at most 128 floats of q / k per node')
         if self.beltrami_kernel:
             fd = opt['hidden_dim'] - opt['pos_enc_hidden_dim']
             for name in ('output_var_x', 'lengthscale_x', 'output_var_p', 'lengthscale_p'):

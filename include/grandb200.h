@@ -333,7 +333,7 @@ int gb_stage_combine_multi(const float* y, const float* const* k_host, const flo
  * Rows [row_lo, row_hi) are evaluated (1-D row partition; pass 0, g->n on one GPU).  Matrices indexed by the
  * row (q, x0, out, gout, dq) are addressed with the GLOBAL row id; x is addressed by global column id.
  * workspace: gb_nl_workspace_bytes() bytes of device memory (scheduler counter). */
-int gb_nl_supported(int32_t heads, int32_t dk, int32_t d);   /* heads in {1,2,4,8}, dk % 4 == 0, d % 4 == 0, d <= 128 */
+int gb_nl_supported(int32_t heads, int32_t dk, int32_t d);   /* heads in {1,2,4,8}, dk % 4 == 0, d % 4 == 0, d <= 128, heads * dk <= 128 */
 size_t gb_nl_workspace_bytes(void);
 int gb_nl_fwd(const gb_graph* g, int32_t row_lo, int32_t row_hi, const float* x, int32_t ldx,
               const float* q, int32_t ldq, const float* wk, int32_t ldwk, int32_t heads, int32_t dk, int32_t d,

@@ -392,7 +392,7 @@ class Emulator:
     nl_enabled = False                            # tests flip this to route evaluations to gb_nl_fwd / gb_nl_adjoint
 
     def gb_nl_supported(self, heads, dk, d):
-        return int(self.nl_enabled and heads in (1, 2, 4, 8) and dk % 4 == 0 and d % 4 == 0 and d <= 128)
+        return int(self.nl_enabled and heads in (1, 2, 4, 8) and dk % 4 == 0 and d % 4 == 0 and d <= 128 and heads * dk <= 128)
 
     def gb_spmm_fwd_part(self, g, lo, hi, vals, x, ldx, x0, ldx0, alpha_train, alpha_sigmoid, beta_train, d, out, ldo,
                          stage, stream):

@@ -106,7 +106,8 @@ def oracle_transformer(ei, x, x0, gout, wq, bq, wk, bk, heads, alpha, beta, norm
 
 @pytest.mark.parametrize('n,e,d,heads,adim', [(60, 400, 8, 2, 8), (2000, 12000, 64, 4, 64), (1500, 9000, 128, 4, 64),
                                                (900, 6000, 96, 4, 64), (500, 3000, 80, 8, 128), (400, 2500, 16, 4, 8),
-                                               (300, 2000, 6, 2, 6), (700, 4000, 162, 2, 32)])
+                                               (300, 2000, 6, 2, 6), (700, 4000, 162, 2, 32),
+                                               (60, 400, 16, 8, 8), (60, 400, 4, 4, 128)])
 @pytest.mark.parametrize('norm_idx', [0, 1])
 def test_scaled_dot_forward_and_all_gradients(n, e, d, heads, adim, norm_idx):
     import grand_b200
@@ -222,6 +223,8 @@ def test_unsupported_options_raise():
         func.edge_index, func.x0 = ei, x
         with pytest.raises(NotImplementedError):
             func(0.0, x)
+    with pytest.raises(NotImplementedError, match='attention_dim'):           # wider than a warp's 32 x 4 floats
+        grand_b200.ODEFuncTransformerAtt(128, 128, dict(BASE_OPT, heads=8, attention_dim=256, hidden_dim=128), torch.device('cuda'))
 
 
 @pytest.mark.parametrize('d,heads,adim', [(64, 4, 64), (128, 4, 64), (96, 4, 64), (80, 8, 128), (32, 1, 16)])
