@@ -383,6 +383,6 @@ def test_adaptive_adjoint_of_the_transformer_block_packs_the_parameter_integrals
         grads = torch.autograd.grad(z, params, gout)
         out[pack] = (nfe_fwd, func.nfe, z.detach(), grads)
     assert out[True][:2] == out[False][:2] and out[True][1] > out[True][0] > 0       # same number of evaluations
-    assert torch.equal(out[True][2], out[False][2])
+    assert_close(out[True][2], out[False][2], 1e-6, 'z(T)')
     for a, b in zip(out[True][3], out[False][3]):
-        assert torch.equal(a, b)
+        assert_close(a, b, 1e-5, 'gradient', floor=1e-6)

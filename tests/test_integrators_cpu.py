@@ -446,10 +446,12 @@ def test_one_pass_stage_combination_is_differentiable(emulated_abi, monkeypatch)
     assert torch.allclose(gy.double(), ry, rtol=1e-5) and torch.allclose(ga.double(), ra, rtol=1e-5)
 
 
-def test_adaptive_adjoint_with_packed_parameter_integrals_is_the_unpacked_solve(monkeypatch):
+@pytest.mark.parametrize('method', ['dopri5', 'adaptive_heun'])
+def test_adaptive_adjoint_with_packed_parameter_integrals_is_the_unpacked_solve(monkeypatch, method):
     """the adaptive adjoint carries all parameter integrals in one flat component (4 components instead of 3 + one per
     parameter tensor: ~8x fewer launch-sized kernels per attempted dopri5 step); the error norm still takes the RMS
-    of every parameter tensor on its own (torchdiffeq's mixed norm), so step sequence, NFE and gradients are unchanged"""
+    of every parameter tensor on its own (torchdiffeq's mixed norm), so step sequence, NFE and gradients are unchanged
+    (up to the rounding of a segmented mean in the step-size controller)"""
     from grand_b200 import integrators
 
     class Func(torch.nn.Module):
@@ -471,12 +473,12 @@ def test_adaptive_adjoint_with_packed_parameter_integrals_is_the_unpacked_solve(
         torch.manual_seed(0)
         f = Func()
         y0 = torch.randn(7, 5, dtype=torch.float64, requires_grad=True)
-        z = integrators.odeint_adjoint(f, y0, torch.tensor([0., 2.]), method='dopri5', rtol=1e-6, atol=1e-8,
+        z = integrators.odeint_adjoint(f, y0, torch.tensor([0., 2.]), method=method, rtol=1e-6, atol=1e-8,
                                        adjoint_params=tuple(f.parameters()))[1]
         f.nfe = 0
         grads = torch.autograd.grad(z.square().sum(), [y0] + list(f.parameters()), allow_unused=True)
         out[pack] = (f.nfe, grads)
     assert out[True][0] == out[False][0] > 0
-    for a, b in zip(out[True][1], out[False][1]):
-        assert (a is None and b is None) or torch.equal(a, b)
+    for a, b in zip(out[True][1], out[False][1]):            # the per-tensor RMS comes from a segmented sum: the step
+        assert torch.allclose(a, b, rtol=1e-9, atol=1e-13)   # controller sees the same ratio up to its last bits
     assert float(out[True][1][4].abs().max()) == 0.0          # the parameter the dynamics never read
