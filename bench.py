@@ -959,7 +959,7 @@ def main():
                     help='skip the torch-CUDA-ops comparator (N = 1 only)')
     ap.add_argument('--function', default=None, choices=['transformer', 'laplacian'],
                     help='transformer = GRAND-nl (BASELINE.json headline); laplacian = GRAND-l sweep of config 5')
-    ap.add_argument('--halo', default=os.environ.get('GRANDB200_HALO', 'dense'), choices=['dense', 'sparse', 'compact', 'push', 'copy', 'auto'],
+    ap.add_argument('--halo', default=os.environ.get('GRANDB200_HALO'), choices=['dense', 'sparse', 'compact', 'push', 'copy', 'auto'],
                     help='N > 1: exchange whole slabs (dense), only the rows the peers reference (sparse: R-MAT slabs '
                          'reference ~25 %% of the others at 8 ranks), sparse exchange + the rank\'s graph relabelled to '
                          '[own slab | referenced rows] so all per-rank work is O(N/P + halo) (compact), or dense / sparse '
@@ -987,6 +987,11 @@ def main():
     METHOD = args.method or preset['method']
     T_END = args.t_end if args.t_end is not None else preset['t_end']
     TOL_SCALE = args.tol_scale if args.tol_scale is not None else (1.0 if METHOD in ('rk4', 'euler', 'midpoint') else 1e3)
+    if args.halo is None:
+        # R-MAT slabs reference ~21 % of the remote rows at 8 ranks: the compact halo (exchange + per-rank problem over
+        # [own slab | referenced rows]) is 2.3x - 2.8x the dense exchange there (profiles/r02z_c5_*_n8_compact.json);
+        # the c4 shape references 97 %: whole slabs
+        args.halo = 'compact' if args.workload == 'c5' else 'dense'
     if args.cuda_graph is None:
         args.cuda_graph = (args.workload in ('c1', 'c3') and METHOD in ('rk4', 'euler', 'midpoint') and args.gpus == 1
                            and int(os.environ.get('WORLD_SIZE', '1')) == 1 and not args.microbench
