@@ -570,7 +570,8 @@ def run_partitioned(args, cfg, device, rank, world):
     d = cfg['d']
     part = grand_b200.RowPartition(n, world, rank)
     halo_kind = args.halo
-    halo = {'dense': grand_b200.Halo, 'compact': grand_b200.CompactHalo, 'push': grand_b200.PushHalo, 'copy': grand_b200.CopyHalo}.get(
+    halo = {'dense': grand_b200.Halo, 'compact': grand_b200.CompactHalo, 'push': grand_b200.PushHalo, 'copy': grand_b200.CopyHalo,
+            'compact_push': grand_b200.CompactPushHalo}.get(
         halo_kind, grand_b200.SparseHalo)(part)
     # the SAME global state and cotangent as the 1-GPU run (seed 99), sliced to this rank's slab: the loss checksum of
     # the JSON line is comparable across N
@@ -714,6 +715,8 @@ def run_partitioned(args, cfg, device, rank, world):
                                                    '[own slab | referenced rows])',
                                         'push': ' (all-gather = one broadcast-store kernel into symmetric memory + barrier; '
                                                 'reduce-scatter = barrier + one kernel pulling the peers\' shares)',
+                                        'compact_push': ' (compact halo; both exchanges are one gb_rows_push kernel per rank '
+                                                        'storing the requested rows straight into the peers\' symmetric matrices + a barrier)',
                                         'copy': ' (all-gather = P-1 copy-engine copies into the peers\' symmetric matrices + '
                                                 'barrier, no SMs; reduce-scatter as push)'}.get(
                                             halo_kind, ' (all-gather / reduce-scatter of whole slabs)'),
@@ -959,7 +962,7 @@ def main():
                     help='skip the torch-CUDA-ops comparator (N = 1 only)')
     ap.add_argument('--function', default=None, choices=['transformer', 'laplacian'],
                     help='transformer = GRAND-nl (BASELINE.json headline); laplacian = GRAND-l sweep of config 5')
-    ap.add_argument('--halo', default=os.environ.get('GRANDB200_HALO'), choices=['dense', 'sparse', 'compact', 'push', 'copy', 'auto'],
+    ap.add_argument('--halo', default=os.environ.get('GRANDB200_HALO'), choices=['dense', 'sparse', 'compact', 'compact_push', 'push', 'copy', 'auto'],
                     help='N > 1: exchange whole slabs (dense), only the rows the peers reference (sparse: R-MAT slabs '
                          'reference ~25 %% of the others at 8 ranks), sparse exchange + the rank\'s graph relabelled to '
                          '[own slab | referenced rows] so all per-rank work is O(N/P + halo) (compact), or dense / sparse '

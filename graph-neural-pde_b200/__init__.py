@@ -24,7 +24,7 @@ from .model_configurations import set_block, set_function
 from . import integrators
 from . import partition
 from .graphed import GraphedPass
-from .partition import RowPartition, Halo, LoopbackHalo, SparseHalo, CompactHalo, PushHalo, CopyHalo
+from .partition import RowPartition, Halo, LoopbackHalo, SparseHalo, CompactHalo, PushHalo, CopyHalo, CompactPushHalo
 from .integrators import odeint, odeint_adjoint
 from .early_stop_solver import EarlyStopInt
 from .base_classes import BaseGNN
@@ -35,4 +35,4 @@ from . import CGNN, graph_rewiring, ops
 __all__ = ['GraphPlan', 'get_plan', 'MaxNFEException', 'get_rw_adj', 'gcn_norm_fill_val',
            'add_remaining_self_loops', 'Meter', 'ODEFunc', 'ODEblock', 'GraphData', 'LaplacianODEFunc',
            'ODEFuncTransformerAtt', 'SpGraphTransAttentionLayer', 'ODEFuncAtt', 'SpGraphAttentionLayer', 'ConstantODEblock', 'AttODEblock', 'MixedODEblock', 'HardAttODEblock',
-           'set_block', 'set_function', 'partition', 'GraphedPass', 'RowPartition', 'Halo', 'LoopbackHalo', 'SparseHalo', 'CompactHalo', 'PushHalo', 'CopyHalo', 'odeint', 'odeint_adjoint', 'integrators', 'EarlyStopInt', 'BaseGNN', 'GNN', 'GNNEarly']
+           'set_block', 'set_function', 'partition', 'GraphedPass', 'RowPartition', 'Halo', 'LoopbackHalo', 'SparseHalo', 'CompactHalo', 'PushHalo', 'CopyHalo', 'CompactPushHalo', 'odeint', 'odeint_adjoint', 'integrators', 'EarlyStopInt', 'BaseGNN', 'GNN', 'GNNEarly']

@@ -103,6 +103,7 @@ SIGNATURES = {
     'gb_edge_score_bwd': (C.c_int, [_G, _P, _P, _I32, _P, _I32, _I32, _I32, _I32, _P, _P, _P, _I32, _P, _I32, _P, _P, _P]),
     'gb_gat_softmax_fwd': (C.c_int, [_G, _I32, _P, _P, _I32, _I32, C.c_float, _P, _P, _P, _P]),
     'gb_segment_softmax_fwd': (C.c_int, [_P, _P, _I32, _I32, _P, _P, _P, _P, _I32, _I32, _P]),
+    'gb_rows_push': (C.c_int, [_P, _I32, _P, _I32, C.POINTER(C.c_int64), C.POINTER(C.c_void_p), _I32, _I32, _P]),
     'gb_decode_eval_max_classes': (C.c_int, []),
     'gb_decode_eval': (C.c_int, [_P, _I32, _I32, _I32, _P, _I32, _P, _I32, _P, _P, _P, _P, _P, _P, _I32, _P, _P]),
 }

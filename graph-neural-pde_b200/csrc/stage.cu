@@ -147,3 +147,63 @@ extern "C" int gb_stage_combine_multi(const float* y, const float* const* k_host
   }
   return check_launch("stage_combine_multi");
 }
+
+// ---- gb_rows_push: rows of a local matrix, optionally picked by an index list, stored into up to 8 destination
+// matrices in consecutive segments - the sending half of a sparse halo exchange as ONE kernel over NVLink peer
+// memory (no packing buffer, no collective): segment s = rows [seg_start[s], seg_start[s + 1]) of the request list
+// goes to dst[s], row after row.  Posted 128-bit stores: the kernel runs at the speed of the local gather while the
+// writes drain over the links.
+namespace gb {
+struct RowsPushArgs {
+  const float* src;
+  int64_t ld;
+  const int64_t* idx;        // [total] local row of every request, or null: request r is row r
+  int64_t seg_start[9];
+  float* dst[8];
+  int64_t dst_ld;
+  int32_t nseg, dv;          // dv = row width in 128-bit chunks
+};
+
+__global__ void __launch_bounds__(256) rows_push_kernel(const RowsPushArgs a) {
+  const int64_t total = a.seg_start[a.nseg] * a.dv;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / a.dv;
+    const int c = (int)(i - r * a.dv);
+    int s = 0;
+#pragma unroll
+    for (int j = 1; j < 8; ++j) s += (j < a.nseg && r >= a.seg_start[j]) ? 1 : 0;
+    const int64_t row = a.idx ? __ldg(a.idx + r) : r;
+    const float4 v = ld_stream4(a.src + row * a.ld + 4 * c);
+    *reinterpret_cast<float4*>(a.dst[s] + (r - a.seg_start[s]) * a.dst_ld + 4 * c) = v;
+  }
+}
+}  // namespace gb
+
+extern "C" int gb_rows_push(const float* src, int32_t ld, const int64_t* idx, int32_t nseg, const int64_t* seg_start_host,
+                            float* const* dst_host, int32_t dst_ld, int32_t d, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  GB_REQUIRE(src && seg_start_host && dst_host && nseg >= 1 && nseg <= 8 && d > 0 && d % 4 == 0 && ld >= d && dst_ld >= d,
+             "gb_rows_push: bad arguments (1 <= nseg <= 8, d % 4 == 0)");
+  GB_REQUIRE(ld % 4 == 0 && dst_ld % 4 == 0 && reinterpret_cast<uintptr_t>(src) % 16 == 0,
+             "gb_rows_push: rows must be 16-byte aligned");
+  RowsPushArgs a{};
+  a.src = src; a.ld = ld; a.idx = idx; a.nseg = nseg; a.dst_ld = dst_ld; a.dv = d / 4;
+  for (int s = 0; s <= nseg; ++s) {
+    a.seg_start[s] = seg_start_host[s];
+    GB_REQUIRE(s == 0 ? seg_start_host[0] == 0 : seg_start_host[s] >= seg_start_host[s - 1], "gb_rows_push: segment starts must ascend from 0");
+  }
+  for (int s = 0; s < nseg; ++s) {
+    const bool empty = seg_start_host[s + 1] == seg_start_host[s];
+    GB_REQUIRE(empty || (dst_host[s] != nullptr && reinterpret_cast<uintptr_t>(dst_host[s]) % 16 == 0),
+               "gb_rows_push: null / unaligned destination %d", s);
+    a.dst[s] = dst_host[s];
+  }
+  const int64_t work = a.seg_start[nseg] * a.dv;
+  if (work == 0) return GB_OK;
+  int64_t blocks = (work + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  LaunchScope ls(K_STAGE_AXPY, stream);
+  rows_push_kernel<<<(unsigned)blocks, 256, 0, stream>>>(a);
+  return check_launch("rows_push");
+}

@@ -501,6 +501,155 @@ class PushHalo(Halo):
         return PendingScatter(full, None, lambda: out)
 
 
+class CompactPushHalo(CompactHalo):
+    """CompactHalo whose two exchanges are PUSHES over NVLink peer memory instead of NCCL all_to_all_v calls
+    (293 GB/s into a rank at 8 GPUs on R-MAT 24: more than half of a GRAND-l step).
+
+    gather   the local state matrices [S + R, d] live in symmetric memory.  ONE kernel per rank (gb_rows_push) picks the
+             rows each peer asked for out of the rank's slab and stores them straight into the peer's tail, at the
+             offset where that peer expects this rank's block (no packing buffer, no collective); a symmetric-memory
+             barrier orders every rank's reads after every rank's writes.
+    scatter  the tail of a rank's share (its contributions to rows the peers own, already in peer order) is pushed
+             block by block into the owners' symmetric staging matrices (the same kernel without an index list);
+             barrier; the owner adds the blocks to its own rows peer after peer in rank order (unique indices per
+             peer: deterministic), exactly as CompactHalo does with what all_to_all_v delivered.
+    Ring of RING buffers per kind and width, reused as in PushHalo (a rank writes a peer's buffer b again only after
+    passing two more barriers, which that peer reaches after its reads of b were queued)."""
+
+    RING = 3
+
+    def __init__(self, part, group=None):
+        super().__init__(part, group)
+        self._sym = {}
+
+    def _exchange_lists(self, remote, owner, dev):
+        super()._exchange_lists(remote, owner, dev)
+        part, dist = self.part, self.dist
+        # need[q][r] = rows rank q needs from rank r, on every rank: where my block starts inside each peer's buffers
+        mine = torch.tensor(self.recv_splits, dtype=torch.int64, device=dev)
+        need = [torch.empty_like(mine) for _ in range(part.world)]
+        dist.all_gather(need, mine, group=self.group)
+        need = torch.stack(need).cpu()                                      # [q, r]
+        me = part.rank
+        self._tail_off = [int(need[q, :me].sum()) for q in range(part.world)]       # my block inside q's tail
+        self._stage_off = [int(need[:me, q].sum()) for q in range(part.world)]      # my block inside q's staging rows
+        sizes = torch.tensor([part.slab + int(need[me].sum()), int(need[:, me].sum())], dtype=torch.int64, device=dev)
+        dist.all_reduce(sizes, op=dist.ReduceOp.MAX, group=self.group)
+        self._rows_local, self._rows_stage = max(1, int(sizes[0])), max(1, int(sizes[1]))
+        self._sym.clear()
+
+    def _symmetric(self, kind, width, dtype, device):
+        import warnings
+        import torch.distributed._symmetric_memory as symm
+        key = (kind, int(width), dtype, str(device))
+        ring = self._sym.get(key)
+        if ring is None:
+            group = self.group if self.group is not None else self.dist.group.WORLD
+            try:
+                with warnings.catch_warnings():
+                    warnings.simplefilter('ignore')
+                    if not symm.is_symm_mem_enabled_for_group(group.group_name):
+                        symm.enable_symm_mem_for_group(group.group_name)
+            except (AttributeError, RuntimeError):
+                pass
+            rows = self._rows_local if kind == 'local' else self._rows_stage
+            entries = []
+            for _ in range(self.RING):
+                t = symm.empty(rows, width, dtype=dtype, device=device)
+                handle = symm.rendezvous(t, group)
+                entries.append((t, [int(p) for p in handle.buffer_ptrs], handle.barrier))
+            ring = self._sym[key] = [entries, 0]
+        entry = ring[0][ring[1] % self.RING]
+        ring[1] += 1
+        return entry
+
+    def _push(self, src, idx, counts, ptrs, row_off, width):
+        """rows of `src` (picked by idx, or consecutive) -> peer q's matrix at row row_off[q], q in rank order"""
+        import ctypes as C
+        part = self.part
+        peers = [q for q in range(part.world) if q != part.rank and counts[q] > 0]
+        if not peers:
+            return
+        # the request list is ordered by peer; the kernel takes at most 8 segments per launch
+        starts = [0]
+        for q in range(part.world):
+            starts.append(starts[-1] + counts[q])
+        lib = _lib.load()
+        for i in range(0, len(peers), 8):
+            grp = peers[i:i + 8]
+            base = starts[grp[0]]
+            seg = [starts[q] - base for q in grp] + [starts[grp[-1] + 1] - base]
+            # peers of one launch must be consecutive in the list: split where a skipped (empty / own) block intervenes
+            ok = all(starts[grp[j] + 1] == starts[grp[j + 1]] for j in range(len(grp) - 1))
+            if not ok:
+                for q in grp:
+                    self._push_one(lib, src, idx, starts[q], counts[q], ptrs[q] + 4 * row_off[q] * width, width)
+                continue
+            dst = (C.c_void_p * len(grp))(*[ptrs[q] + 4 * row_off[q] * width for q in grp])
+            segs = (C.c_int64 * len(seg))(*seg)
+            idx_ptr = None if idx is None else idx.data_ptr() + 8 * base
+            src_ptr = src.data_ptr() if idx is not None else src.data_ptr() + 4 * base * width
+            _lib.check(lib.gb_rows_push(src_ptr, width, idx_ptr, len(grp), segs, dst, width, width, _lib.stream()),
+                       'gb_rows_push')
+
+    def _push_one(self, lib, src, idx, start, cnt, dst_ptr, width):
+        import ctypes as C
+        dst = (C.c_void_p * 1)(dst_ptr)
+        segs = (C.c_int64 * 2)(0, cnt)
+        idx_ptr = None if idx is None else idx.data_ptr() + 8 * start
+        src_ptr = src.data_ptr() if idx is not None else src.data_ptr() + 4 * start * width
+        _lib.check(lib.gb_rows_push(src_ptr, width, idx_ptr, 1, segs, dst, width, width, _lib.stream()), 'gb_rows_push')
+
+    @_nvtx('halo.all_gather')
+    def all_gather_rows(self, slab, keep=False):
+        self._check()
+        slab = slab.contiguous()
+        if slab.dim() != 2 or slab.dtype != torch.float32 or slab.shape[1] % 4:
+            raise TypeError('CompactPushHalo exchanges fp32 [S, d] slabs with d % 4 == 0')
+        part, s, width = self.part, self.part.slab, slab.shape[1]
+        buf, ptrs, barrier = self._symmetric('local', width, slab.dtype, slab.device)
+        buf[:s] = slab
+        self._push(slab, self.send_idx, self.send_splits, ptrs, [s + o for o in self._tail_off], width)
+        barrier()                                                          # all writes landed before any rank reads
+        self.bytes_in += sum(self.recv_splits) * width * slab.element_size()
+        self.n_gathers += 1
+        local = buf[:self.view.n_pad]
+        return local.clone() if (keep or torch.is_grad_enabled()) else local
+
+    def all_gather_rows_async(self, slab):
+        side = self.__dict__.get('_side')
+        if side is None:
+            side = self._side = torch.cuda.Stream(device=slab.device)
+        main = torch.cuda.current_stream(slab.device)
+        side.wait_stream(main)
+        slab_c = slab.contiguous()
+        with torch.cuda.stream(side):
+            local = self.all_gather_rows(slab_c)
+        slab_c.record_stream(side)
+        local.record_stream(side)
+        self.n_prefetched = getattr(self, 'n_prefetched', 0) + 1
+        return _StreamPending(slab, local, side)
+
+    @_nvtx('halo.reduce_scatter')
+    def reduce_scatter_rows(self, full):
+        self._check()
+        full = full.contiguous()
+        part, s, width = self.part, self.part.slab, full.shape[1]
+        if full.dtype != torch.float32 or width % 4:
+            raise TypeError('CompactPushHalo exchanges fp32 rows with d % 4 == 0')
+        stage, ptrs, barrier = self._symmetric('stage', width, full.dtype, full.device)
+        tail = full[s:]                                                    # contributions to the peers' rows, peer order
+        self._push(tail, None, self.recv_splits, ptrs, self._stage_off, width)
+        barrier()
+        self.bytes_in += sum(self.send_splits) * width * full.element_size()
+        self.n_scatters += 1
+        return self._finish_scatter(full, stage)
+
+    def reduce_scatter_rows_async(self, full):
+        out = self.reduce_scatter_rows(full)
+        return PendingScatter(full, None, lambda: out)
+
+
 class CopyHalo(PushHalo):
     """PushHalo whose all-gather moves the bytes with the COPY ENGINES instead of a kernel: every rank writes its slab
     into its own symmetric matrix and, with P - 1 peer-to-peer copies (cudaMemcpyAsync over NVLink, one stream per

@@ -324,6 +324,14 @@ int gb_stage_combine(const float* y, const float* const* k_host, const float* c_
 int gb_stage_combine_multi(const float* y, const float* const* k_host, const float* c_host, int32_t nk, int64_t count,
                            float* const* outs_host, int32_t n_out, void* stream);
 
+/* Sending half of a sparse halo exchange as one kernel over peer memory (NO COUNTERPART IN THE REFERENCE, which has no
+ * multi-GPU graph path): request r (row idx[r] of src, or row r when idx is NULL) of segment s =
+ * [seg_start_host[s], seg_start_host[s + 1]) is stored to row r - seg_start_host[s] of dst_host[s] (a peer's matrix:
+ * symmetric memory / CUDA IPC pointer).  nseg <= 8; idx is a DEVICE array, seg_start_host [nseg + 1] and dst_host
+ * [nseg] are HOST arrays; d % 4 == 0, 16-byte aligned rows.  The caller orders the peers' reads after the writes. */
+int gb_rows_push(const float* src, int32_t ld, const int64_t* idx, int32_t nseg, const int64_t* seg_start_host,
+                 float* const* dst_host, int32_t dst_ld, int32_t d, void* stream);
+
 /* ---- single-gather GRAND-nl evaluation and VJP (csrc/nl_kernels.cuh; scaled_dot, attention_norm_idx 0) ----
  * One row gather per edge: scores are formed as <Wk_h^T q_ih / sqrt(dk), x_j> (the per-(row, head) constant
  * <q_ih, bk_h> cancels in the row softmax), the softmax is online, so neither k = x Wk^T + bk nor the

@@ -109,6 +109,7 @@ def main():
             if not args.emulate:                                   # symmetric memory needs real GPUs
                 kinds.append(('push', grand_b200.PushHalo))
                 kinds.append(('copy', grand_b200.CopyHalo))
+                kinds.append(('cpush', grand_b200.CompactPushHalo))
             for kind, cls in kinds:
                 for overlap in (('0', '1') if adjoint else ('0',)):
                     os.environ['GRANDB200_OVERLAP'] = overlap
