@@ -125,16 +125,60 @@ class LaplacianODEFunc(ODEFunc):
         return f.view_as(x), finish
 
     def eval_vjp(self, t, x, cot, params):
-        """f(t, x) and cot^T df/d(x, params) without an autograd graph - offered on a row-partitioned graph with
-        fixed edge weights (the two local kernels + the two exchanges, same numbers as forward() + autograd.grad);
-        None elsewhere: the solver then differentiates forward()."""
-        if self.partition is None or self.opt['block'] != 'constant':
+        """f(t, x) and cot^T df/d(x, params) without an autograd graph (same numbers as forward() + autograd.grad):
+        on one GPU whenever the edge values carry no gradient, on a row-partitioned graph with fixed edge weights
+        (the two local kernels + the two exchanges); None elsewhere: the solver then differentiates forward()."""
+        if self.partition is None:
+            return self._eval_vjp_single(x, cot, params)
+        if self.opt['block'] != 'constant':
             return None
         if self._as_2d(x).shape[0] != self.partition[0].slab:
             return None
         f, finish = self.eval_vjp_phased(t, x, cot, params)
         vy, vps = finish()
         return f, vy, vps
+
+    def _eval_vjp_single(self, x, cot, params):
+        """un-partitioned graph: gb_spmm_fwd + gb_spmm_bwd called directly - the two kernels DiffusionFn's forward and
+        backward launch, without building and walking an autograd graph per adjoint evaluation.  Offered when the edge
+        values carry no gradient (constant block; attention / mixed blocks under no_grad or with detached attention):
+        their VJP (SDDMM) belongs to the autograd route."""
+        from . import _lib
+        x2 = self._as_2d(x)
+        plan = self._plan(x2.shape[0])
+        src = self.attention_weights if self.opt['block'] != 'constant' else self.edge_weight
+        if src is None or src.requires_grad or x2.dtype != torch.float32 or not x2.is_cuda:
+            return None
+        self._check_nfe()
+        lib = _lib.load()
+        vals = self._edge_values(plan).detach()
+        x2 = x2.detach().contiguous()
+        g = self._as_2d(cot).detach().contiguous()
+        n, d = x2.shape
+        source = bool(self.opt['add_source']) and self.x0 is not None
+        x0 = self._as_2d(self.x0).detach().contiguous() if source else None
+        sig = int(not self.opt['no_alpha_sigmoid'])
+        alpha, beta = self.alpha_train.detach(), self.beta_train.detach()
+        f = torch.empty_like(x2)
+        _lib.check(lib.gb_spmm_fwd(plan.c, vals.data_ptr(), x2.data_ptr(), d, _lib.ptr(x0), d, alpha.data_ptr(), sig,
+                                   beta.data_ptr() if source else None, d, f.data_ptr(), d, None, _lib.stream()),
+                   'gb_spmm_fwd')
+        dx = torch.empty_like(x2)
+        partials = torch.empty(int(lib.gb_spmm_bwd_partials(plan.c, d)), dtype=torch.float32, device=x2.device)
+        dparams = torch.empty(2, dtype=torch.float32, device=x2.device)
+        _lib.check(lib.gb_spmm_bwd(plan.c, vals.data_ptr(), g.data_ptr(), d, x2.data_ptr(), d, _lib.ptr(x0), d,
+                                   alpha.data_ptr(), sig, d, dx.data_ptr(), d, 0, partials.data_ptr(),
+                                   dparams.data_ptr(), _lib.stream()), 'gb_spmm_bwd')
+        named = ((self.alpha_train, dparams[0].reshape(self.alpha_train.shape)),
+                 (self.beta_train, dparams[1].reshape(self.beta_train.shape) if source else None))
+        out = []
+        for p_ in params:
+            gp = None
+            for q_, gq in named:
+                if p_ is q_:
+                    gp = gq
+            out.append(gp)
+        return f.view_as(x), dx.view_as(x), out
 
     def forward(self, t, x):  # the t param is needed by the ODE solver.
         self._check_nfe()
