@@ -19,6 +19,9 @@ SOURCES = [
     ('r02h_ncu_full_nl2_c4.csv', 'c4', {r'nl2_rows_kernel<.*?, 0, ': 'nl_fwd@single-gather', r'nl2_rows_kernel<.*?, 1, ': 'nl_adj_rows@single-gather'}),
     ('r02j_ncu_full_nlk_c4.csv', 'c4', {r'nlk_rows_kernel<\d+, 0, ': 'nl_fwd', r'nlk_rows_kernel<\d+, 1, ': 'nl_adj_rows'}),
     ('r02r_ncu_full_spmm2_c4.csv', 'c4', {r'spmm2_kernel<\d+, 0, ': 'spmm_fwd', r'spmm2_kernel<\d+, 1, ': 'spmm_bwd'}),
+    # end of round 2: the three kernels of a C4 step in their final form (forward launches include the fused stage store)
+    ('r02zz_ncu_full_c4.csv', 'c4', {r'nlk_rows_kernel<\d+, 0, ': 'nl_fwd', r'nlk_rows_kernel<\d+, 1, ': 'nl_adj_rows',
+                                     r'att_col_bwd_kernel': 'fused_att_bwd_col'}),
 ]
 
 
