@@ -200,7 +200,7 @@ int gb_spmm_bwd_static(const gb_graph* g, const float* vals, const float* gout, 
  * accumulators, persistent warp-specialised CTAs.  Taken by gb_linear_fwd / gb_linear_bwd_x when the reduction
  * length is a multiple of 32 and <= 128, the output width a multiple of 16 and <= 128, rows 16-byte aligned
  * (every GRAND-nl configuration of BASELINE.json).  gb_linear_fwd also takes it for ANY reduction length >= 32 when
- * n >= 128 and the output qualifies (the encoder m1 / mx / mp of src/GNN.py:30-38, e.g. [N, 1433] x [1433, 64]):
+ * n >= 12288 and the output qualifies (the encoder m1 / mx / mp of src/GNN.py:30-38, e.g. [N, 1433] x [1433, 64]):
  * slices of 128 input columns accumulate into `out`, a ragged last slice is zero-filled, rows that are not 16-byte
  * aligned are loaded element-wise.  Other shapes run the CUDA-core SGEMM.  Returns 1 / 0 (the un-sliced form). */
 int gb_linear_tc_eligible(const float* a, int32_t lda, const float* w, int32_t ldw, const float* out, int32_t ldo,

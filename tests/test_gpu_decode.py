@@ -124,8 +124,8 @@ def test_decode_eval_full_size_properties():
 # ---- encoder / decoder layers -----------------------------------------------------------------------------------
 # (rows, F, nout): Cora encoder (ragged K, unaligned rows), Pubmed, ogbn-products, ogbn-arxiv, decoder (CUDA-core tiles),
 # few rows (tiles path), K of exactly one slice
-LINEAR = [(2708, 1433, 64), (2708, 1433, 80), (19717, 500, 64), (50000, 100, 128), (40000, 128, 64), (2708, 64, 7),
-          (100, 300, 64), (1000, 256, 16), (513, 33, 32)]
+LINEAR = [(2708, 1433, 64), (13000, 1433, 80), (19717, 500, 64), (50000, 100, 128), (40000, 128, 64), (2708, 64, 7),
+          (100, 300, 64), (1000, 256, 16), (12500, 33, 32)]
 
 
 @pytest.mark.parametrize('rows,k,nout', LINEAR)
@@ -148,14 +148,16 @@ def test_linear_layer_forward_and_backward(rows, k, nout, bias):
     assert torch.equal(y, y2)                                 # deterministic
 
 
-def test_linear_layer_takes_the_sliced_tensor_core_path_for_the_cora_encoder():
-    """[2708, 1433] x [1433, 64]: 12 launches of the tcgen05 kernel (K slices of 128), not the CUDA-core tiles"""
+def test_linear_layer_takes_the_sliced_tensor_core_path_for_wide_reductions_on_large_graphs():
+    """[20000, 1433] x [1433, 64]: 12 launches of the tcgen05 kernel (K slices of 128); the Cora-sized encoder
+    (2708 rows: 22 row tiles, launch-bound per slice) stays on the CUDA-core tiles - one launch"""
     from grand_b200 import _lib, ops
     lin = ops.Linear(1433, 64).cuda()
-    x = torch.randn(2708, 1433, device='cuda')
-    before = _lib.launch_count()
-    lin(x)
-    assert _lib.launch_count() - before == 12
+    for rows, launches in ((20000, 12), (2708, 1)):
+        x = torch.randn(rows, 1433, device='cuda')
+        before = _lib.launch_count()
+        lin(x)
+        assert _lib.launch_count() - before == launches
 
 
 def test_linear_layer_on_the_batched_fork_layout_and_empty_input():
