@@ -11,9 +11,8 @@
 //
 // Roofline: HBM - the state is read once (4 d bytes per node), labels 8 bytes, masks 3 bytes; the [C, d] decoder
 // weights (<= 48 KB) live in shared memory.  Per node 2 C d flops on the CUDA cores (C = classes <= 64):
-// lane = node, C accumulators in registers, the weights arrive by shared-memory broadcast (one LDS.128 per four
-// FFMA2-able products), the state row from a per-warp shared-memory tile staged with coalesced 128-bit loads
-// (row stride 4 d + 16 bytes: conflict-free 128-bit reads down a column of the tile).
+// lane = two nodes, 2 C accumulators in registers, the weights arrive by shared-memory broadcast (one LDS.128 per
+// eight products), the state rows straight from global memory (L1 keeps the 128-byte lines a lane walks through).
 // Integer atomics only (counts): the result does not depend on the order of arrival.
 #include "common.cuh"
 
@@ -45,15 +44,19 @@ __device__ __forceinline__ bool dec_better(float v, float best) {
 // F.relu keeps NaN (fmaxf would not)
 __device__ __forceinline__ float dec_relu(float v) { return v < 0.f ? 0.f : v; }
 
-template <int CP>
+// lane = kNpt nodes (rows base + lane, base + 32 + lane): CP x kNpt accumulators in registers; every weight float4 fetched
+// from shared memory (one broadcast LDS.128) feeds 4 kNpt FFMAs; the state rows come straight from global memory -
+// 16 bytes per lane per step, whole 128-byte lines over 8 steps (L1), one load per 4 CP kNpt FFMAs - so shared memory holds
+// only the weights and the resident warps are limited by registers alone.
+constexpr int kNpt = 2;
+
+template <int CP, bool VEC>
 __global__ void __launch_bounds__(kDecThreads) decode_eval_kernel(const DecodeArgs a) {
   extern __shared__ __align__(16) float dec_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int d4 = a.dpad >> 2;
-  const int zs = a.dpad + 4;                                  // tile row stride in floats
   float* w_s = dec_smem;                                      // [CP][dpad], zero padded
   float* b_s = w_s + CP * a.dpad;                             // [CP]
-  float* tile = b_s + CP + (size_t)warp * 32 * zs;            // [32][zs] per warp
   __shared__ int cnt_s[6];
   if (threadIdx.x < 6) cnt_s[threadIdx.x] = 0;
   for (int i = threadIdx.x; i < CP * a.dpad; i += kDecThreads) {
@@ -63,68 +66,73 @@ __global__ void __launch_bounds__(kDecThreads) decode_eval_kernel(const DecodeAr
   for (int c = threadIdx.x; c < CP; c += kDecThreads) b_s[c] = (c < a.classes && a.b2) ? __ldg(a.b2 + c) : 0.f;
   __syncthreads();
 
-  const bool vec = (a.d % 4 == 0) && (a.ldz % 4 == 0) && (reinterpret_cast<uintptr_t>(a.z) % 16 == 0);
-  const int ntiles = (a.n + 31) / 32;
+  const int ntiles = (a.n + 32 * kNpt - 1) / (32 * kNpt);
   int correct[3] = {0, 0, 0}, total[3] = {0, 0, 0};
   for (int t = blockIdx.x * kDecWarps + warp; t < ntiles; t += gridDim.x * kDecWarps) {
-    const int row0 = t * 32;
-    const int nrows = min(32, a.n - row0);
-    // ---- stage relu(z[row0 .. row0+32, :d]) -------------------------------------------------------------
-    if (vec) {
-      for (int i = lane; i < nrows * d4; i += 32) {
-        const int r = i / d4, c = i % d4;
-        float4 v = ld_stream4(a.z + (int64_t)(row0 + r) * a.ldz + 4 * c);
-        v.x = dec_relu(v.x); v.y = dec_relu(v.y); v.z = dec_relu(v.z); v.w = dec_relu(v.w);
-        *reinterpret_cast<float4*>(tile + r * zs + 4 * c) = v;
-      }
-    } else {
-      for (int i = lane; i < nrows * a.dpad; i += 32) {
-        const int r = i / a.dpad, k = i % a.dpad;
-        const float v = k < a.d ? __ldg(a.z + (int64_t)(row0 + r) * a.ldz + k) : 0.f;
-        tile[r * zs + k] = dec_relu(v);
-      }
+    int row[kNpt];
+    bool live[kNpt];
+    const float* zr[kNpt];
+#pragma unroll
+    for (int p = 0; p < kNpt; ++p) {
+      row[p] = t * 32 * kNpt + 32 * p + lane;
+      live[p] = row[p] < a.n;
+      zr[p] = a.z + (int64_t)(live[p] ? row[p] : 0) * a.ldz;
     }
-    __syncwarp();
-    // ---- lane = node: logits ----------------------------------------------------------------------------
-    const int row = row0 + lane;
-    const bool live = lane < nrows;
-    float acc[CP];
+    float acc[kNpt][CP];
 #pragma unroll
-    for (int c = 0; c < CP; ++c) acc[c] = b_s[c];
-    if (live) {
-      const float4* zr = reinterpret_cast<const float4*>(tile + lane * zs);
-      for (int k4 = 0; k4 < d4; ++k4) {
-        const float4 zv = zr[k4];
+    for (int p = 0; p < kNpt; ++p)
 #pragma unroll
-        for (int c = 0; c < CP; ++c) {
-          const float4 w = *reinterpret_cast<const float4*>(w_s + c * a.dpad + 4 * k4);      // broadcast
-          acc[c] = fmaf(zv.x, w.x, acc[c]);
-          acc[c] = fmaf(zv.y, w.y, acc[c]);
-          acc[c] = fmaf(zv.z, w.z, acc[c]);
-          acc[c] = fmaf(zv.w, w.w, acc[c]);
+      for (int c = 0; c < CP; ++c) acc[p][c] = b_s[c];
+#pragma unroll 2
+    for (int k4 = 0; k4 < d4; ++k4) {
+      float4 zv[kNpt];
+#pragma unroll
+      for (int p = 0; p < kNpt; ++p) {
+        if (VEC) {
+          zv[p] = __ldg(reinterpret_cast<const float4*>(zr[p]) + k4);
+        } else {                                              // ragged width / unaligned rows
+          const int k = 4 * k4;
+          zv[p].x = k < a.d ? __ldg(zr[p] + k) : 0.f;
+          zv[p].y = k + 1 < a.d ? __ldg(zr[p] + k + 1) : 0.f;
+          zv[p].z = k + 2 < a.d ? __ldg(zr[p] + k + 2) : 0.f;
+          zv[p].w = k + 3 < a.d ? __ldg(zr[p] + k + 3) : 0.f;
+        }
+        zv[p].x = dec_relu(zv[p].x); zv[p].y = dec_relu(zv[p].y); zv[p].z = dec_relu(zv[p].z); zv[p].w = dec_relu(zv[p].w);
+      }
+#pragma unroll
+      for (int c = 0; c < CP; ++c) {
+        const float4 w = *reinterpret_cast<const float4*>(w_s + c * a.dpad + 4 * k4);        // broadcast
+#pragma unroll
+        for (int p = 0; p < kNpt; ++p) {
+          acc[p][c] = fmaf(zv[p].x, w.x, acc[p][c]);
+          acc[p][c] = fmaf(zv[p].y, w.y, acc[p][c]);
+          acc[p][c] = fmaf(zv[p].z, w.z, acc[p][c]);
+          acc[p][c] = fmaf(zv[p].w, w.w, acc[p][c]);
         }
       }
     }
-    __syncwarp();                                             // the tile is free for the next iteration
-    int best = 0;
-    float bv = acc[0];
 #pragma unroll
-    for (int c = 1; c < CP; ++c)
-      if (c < a.classes && dec_better(acc[c], bv)) { bv = acc[c]; best = c; }
-    if (live) {
-      if (a.logits) {
+    for (int p = 0; p < kNpt; ++p) {
+      int best = 0;
+      float bv = acc[p][0];
 #pragma unroll
-        for (int c = 0; c < CP; ++c)
-          if (c < a.classes) a.logits[(int64_t)row * a.ldl + c] = acc[c];
-      }
-      if (a.pred) a.pred[row] = best;
-      if (a.y) {
-        const bool hit = a.y[row] == (int64_t)best;
+      for (int c = 1; c < CP; ++c)
+        if (c < a.classes && dec_better(acc[p][c], bv)) { bv = acc[p][c]; best = c; }
+      if (live[p]) {
+        if (a.logits) {
 #pragma unroll
-        for (int m = 0; m < 3; ++m) {
-          if (a.mask[m] && a.mask[m][row]) {
-            ++total[m];
-            correct[m] += hit ? 1 : 0;
+          for (int c = 0; c < CP; ++c)
+            if (c < a.classes) a.logits[(int64_t)row[p] * a.ldl + c] = acc[p][c];
+        }
+        if (a.pred) a.pred[row[p]] = best;
+        if (a.y) {
+          const bool hit = a.y[row[p]] == (int64_t)best;
+#pragma unroll
+          for (int m = 0; m < 3; ++m) {
+            if (a.mask[m] && a.mask[m][row[p]]) {
+              ++total[m];
+              correct[m] += hit ? 1 : 0;
+            }
           }
         }
       }
@@ -147,23 +155,23 @@ __global__ void __launch_bounds__(kDecThreads) decode_eval_kernel(const DecodeAr
 
 template <int CP>
 static int decode_launch(const DecodeArgs& a, cudaStream_t stream) {
-  const size_t smem = ((size_t)CP * a.dpad + CP + (size_t)kDecWarps * 32 * (a.dpad + 4)) * sizeof(float);
+  const size_t smem = ((size_t)CP * a.dpad + CP) * sizeof(float);
   if (smem > 226 * 1024) {
     set_error("gb_decode_eval: %d classes x %d features need %zu bytes of shared memory (limit 226 KB)", a.classes, a.d, smem);
     return GB_ERR_UNSUPPORTED;
   }
+  const bool vec = (a.d % 4 == 0) && (a.ldz % 4 == 0) && (reinterpret_cast<uintptr_t>(a.z) % 16 == 0);
   static bool configured = false;
   if (!configured) {
-    GB_CUDA(cudaFuncSetAttribute(decode_eval_kernel<CP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));   // + 24 B static
+    GB_CUDA(cudaFuncSetAttribute(decode_eval_kernel<CP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));   // + 24 B static
+    GB_CUDA(cudaFuncSetAttribute(decode_eval_kernel<CP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
     configured = true;
   }
-  const int ntiles = (a.n + 31) / 32;
-  int per_sm = (int)((size_t)(220 * 1024) / (smem + 1024));
-  if (per_sm > 8) per_sm = 8;
-  if (per_sm < 1) per_sm = 1;
-  const int blocks = max(1, min((ntiles + kDecWarps - 1) / kDecWarps, sm_count() * per_sm));
+  const int ntiles = (a.n + 32 * kNpt - 1) / (32 * kNpt);
+  const int blocks = max(1, min((ntiles + kDecWarps - 1) / kDecWarps, sm_count() * 8));
   LaunchScope ls(K_DECODE_EVAL, stream);
-  decode_eval_kernel<CP><<<blocks, kDecThreads, smem, stream>>>(a);
+  if (vec) decode_eval_kernel<CP, true><<<blocks, kDecThreads, smem, stream>>>(a);
+  else decode_eval_kernel<CP, false><<<blocks, kDecThreads, smem, stream>>>(a);
   return check_launch("decode_eval_kernel");
 }
 
